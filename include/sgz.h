@@ -1,0 +1,217 @@
+/*
+ * sgz.h — C ABI of the B200-native Signalizer analysis hot path.
+ *
+ * This is the drop-in boundary for the Spectrum transform pipeline of
+ * jthorborg/signalizer (reference paths are relative to the reference
+ * checkout, `Source/...`).  The reference exposes the path as the C++
+ * template pair TransformConstant<T> / TransformPair<T>; there is no C ABI
+ * upstream, so every entry point below names the C++ member it replaces.
+ *
+ * All entry points are batched over the `n_streams` stereo pairs of a handle
+ * (the reference loops `parallel_for(numChannels / 2, ...)` over at most 8
+ * pairs, SpectrumDSP.cpp:83-102).  A handle owns all device memory; the caller
+ * owns host buffers (and device buffers it passes with SGZ_MEM_DEVICE).  A
+ * handle is externally synchronised like the reference's `streamState` mutex
+ * (SpectrumDSP.cpp:67, SpectrumRendering.cpp:594): one caller at a time.
+ *
+ * Nothing here has a CPU fallback: without a CUDA device every compute entry
+ * point returns SGZ_ECUDA.
+ */
+#ifndef SGZ_H
+#define SGZ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SGZ_ABI_VERSION 1
+
+/* ---- status codes -------------------------------------------------------
+ * The reference signals "skip this frame" with `return false`
+ * (TransformDSP.inl:45-46, :241-242), silently returns on degenerate sizes
+ * (:519-520) and throws on invariants (:1301, :613-616).  Nothing is thrown
+ * across this ABI. */
+enum {
+    SGZ_OK           = 0,
+    SGZ_SKIPPED      = 1,  /* prepareTransform() == false */
+    SGZ_EINVAL       = -1,
+    SGZ_ECUDA        = -2,
+    SGZ_ENOMEM       = -3,
+    SGZ_EUNSUPPORTED = -4,
+    SGZ_ESTATE       = -5  /* call order violated (TransformPair.h:123-124) */
+};
+
+/* SpectrumChannels, Source/Common/CommonSignalizer.h:495-539 (same values). */
+enum {
+    SGZ_CH_LEFT = 0, SGZ_CH_RIGHT = 1, SGZ_CH_MERGE = 2, SGZ_CH_SIDE = 3,
+    SGZ_CH_PHASE = 4, SGZ_CH_SEPARATE = 5, SGZ_CH_MIDSIDE = 6, SGZ_CH_COMPLEX = 7
+};
+/* SpectrumContent::BinInterpolation, Source/Spectrum/SpectrumParameters.h:53-58 */
+enum { SGZ_BIN_NONE = 0, SGZ_BIN_LINEAR = 1, SGZ_BIN_LANCZOS = 2 };
+/* SpectrumContent::DisplayMode, SpectrumParameters.h:60-64 */
+enum { SGZ_DISPLAY_LINEGRAPH = 0, SGZ_DISPLAY_COLOURSPECTRUM = 1 };
+/* SpectrumContent::TransformAlgorithm, SpectrumParameters.h:66-69 */
+enum { SGZ_ALGO_FFT = 0, SGZ_ALGO_RSNT = 1 };
+/* SpectrumContent::ViewScaling, SpectrumParameters.h:71-75 */
+enum { SGZ_VIEW_LINEAR = 0, SGZ_VIEW_LOGARITHMIC = 1 };
+/* SpectrumContent::LineGraphs, SpectrumParameters.h:48-51 */
+enum { SGZ_LINE_MAIN = 0, SGZ_LINE_SECOND = 1, SGZ_LINE_END = 2 };
+
+/* cpl::dsp::WindowTypes (cpl is absent from the reference checkout; the set
+ * below is the cosine-sum family the restatement defines). */
+enum {
+    SGZ_WIN_RECTANGULAR = 0, SGZ_WIN_HANN = 1, SGZ_WIN_HAMMING = 2,
+    SGZ_WIN_BLACKMAN = 3, SGZ_WIN_BLACKMAN_HARRIS = 4, SGZ_WIN_NUTTALL = 5,
+    SGZ_WIN_FLATTOP = 6, SGZ_WIN_END = 7
+};
+/* cpl::dsp::Windows::Shape */
+enum { SGZ_WINSHAPE_SYMMETRIC = 0, SGZ_WINSHAPE_PERIODIC = 1 };
+
+/* where a caller-provided buffer lives */
+enum { SGZ_MEM_HOST = 0, SGZ_MEM_DEVICE = 1 };
+/* audio layouts: PLANAR is the reference's `float** buffer`, pair i =
+ * channels 2i, 2i+1 (SpectrumDSP.cpp:98) flattened to [stream][2][sample];
+ * INTERLEAVED is [stream][sample][2]. */
+enum { SGZ_LAYOUT_PLANAR = 0, SGZ_LAYOUT_INTERLEAVED = 1 };
+
+/* Everything TransformConstant<T> holds that the hot path reads
+ * (Source/Spectrum/TransformConstant.h:188-239) plus the inputs of the
+ * functions that derive its tables (setStorage :81-92, remapFrequencies
+ * :125-180, generateSlopeMap :109-118, regenerateWindowKernel :104-107,
+ * remapResonator :120-123; driven from Spectrum.cpp:365-394,489,571-595). */
+typedef struct sgz_spectrum_config {
+    uint32_t abi_version;        /* SGZ_ABI_VERSION */
+    float    sample_rate;        /* Constant::sampleRate (float, Spectrum.cpp:430-431) */
+    uint32_t window_size;        /* effectiveWindowSize; transformSize = max(32, nextPow2(window)) */
+    uint32_t axis_points;        /* elements == display points == filters */
+    int32_t  algo;               /* SGZ_ALGO_* */
+    int32_t  configuration;      /* SGZ_CH_* */
+    int32_t  bin_polation;       /* SGZ_BIN_* */
+    int32_t  display_mode;       /* SGZ_DISPLAY_* */
+    int32_t  view_scaling;       /* SGZ_VIEW_* */
+    double   view_left;          /* viewRect.left  (0..1) */
+    double   view_right;         /* viewRect.right (0..1) */
+    double   min_freq;           /* state.minLogFreq, 10 Hz (Spectrum.cpp:83) */
+    double   slope_a;            /* PowerFunction{a,b}: slope = b * f^a */
+    double   slope_b;
+    double   low_dbs;            /* Constant::lowDBs */
+    double   high_dbs;           /* Constant::highDBs */
+    double   clip_db;            /* Constant::clipDB, kMinDbs = -384 */
+    float    pole[2];            /* Constant::filter[k].pole, k = LineMain, LineSecond */
+    int32_t  window_type;        /* SGZ_WIN_* */
+    int32_t  window_shape;       /* SGZ_WINSHAPE_* */
+    uint32_t sample_buffer_size; /* Constant::sampleBufferSize ("blob"), default 200 */
+    int32_t  free_q;             /* remapResonator(shouldHaveFreeQ, ...) */
+} sgz_spectrum_config;
+
+typedef struct sgz_spectrum_info {
+    uint32_t transform_size;     /* N */
+    uint32_t window_size;        /* W */
+    uint32_t axis_points;        /* P */
+    uint32_t n_streams;
+    uint32_t state_channels;     /* getStateConfigurationChannels(): 1 or 2 */
+    uint32_t break_point;        /* first display point handled by max-of-bins */
+    float    window_kernel_scale;
+    float    inv_size;           /* windowKernelScale / (W * 0.5) */
+    float    freq_to_bin;
+    uint32_t resonator_vectors;  /* windowCoefficients(window).second */
+    int32_t  device;
+    int32_t  fused_available;    /* 1 if sgz_spectrum_process_frames has a fused kernel for this config */
+} sgz_spectrum_info;
+
+typedef struct sgz_spectrum sgz_spectrum;
+
+/* Fills `cfg` with the defaults of SURVEY.md §8(d) (Separate, FFT, Lanczos,
+ * log view, -120..0 dB, poles {0.95, 0.99}). */
+void sgz_spectrum_default_config(sgz_spectrum_config* cfg);
+
+/* Replaces: `TransformConstant<T>` construction + `handleFlagUpdates`
+ * (Spectrum.cpp:351-616) + `pairs.resize(channels / 2)`
+ * (SpectrumDSP.cpp:225).  Builds every table on the host and uploads it. */
+int  sgz_spectrum_create(const sgz_spectrum_config* cfg, uint32_t n_streams, int device,
+                         sgz_spectrum** out);
+void sgz_spectrum_destroy(sgz_spectrum* h);
+int  sgz_spectrum_get_info(const sgz_spectrum* h, sgz_spectrum_info* out);
+const char* sgz_last_error(void);
+
+/* All work of a handle is enqueued on one CUDA stream (default: a stream the
+ * handle creates).  `cuda_stream` is a cudaStream_t. */
+int  sgz_spectrum_set_cuda_stream(sgz_spectrum* h, void* cuda_stream);
+int  sgz_spectrum_synchronize(sgz_spectrum* h);
+
+/* Host copies of the derived tables (bit-exact parity targets).
+ * windowKernel[N] (TransformConstant.h:220), mappedFrequencies[P] (:215),
+ * slopeMap[P] (:232). */
+int  sgz_spectrum_get_window_kernel(const sgz_spectrum* h, float* out, size_t n);
+int  sgz_spectrum_get_mapped_frequencies(const sgz_spectrum* h, float* out, size_t n);
+int  sgz_spectrum_get_slope_map(const sgz_spectrum* h, float* out, size_t n);
+/* Per display point: mode[x] (0 = interpolate, 1 = max-of-bins), and the
+ * integer bin ranges the loops of TransformDSP.inl:568-639 visit:
+ * first[x] / count[x] = bins scanned (max) or nearest/floor index
+ * (interpolate), fallback[x] = the `maxLBin = bin` initial value. */
+int  sgz_spectrum_get_bin_map(const sgz_spectrum* h, int32_t* mode, int32_t* first,
+                              int32_t* count, int32_t* fallback, size_t n);
+
+/* ---- staged pipeline: TransformPair.h:123-157 ---------------------------
+ * `audio` holds, per stream, `n_samples` samples per channel of history,
+ * oldest first; the last window_size samples are used
+ * (TransformDSP.inl:49).  stream_stride is in floats between streams.
+ * Replaces `bool prepareTransform(const Constant&, const AudioPair&)`
+ * (TransformDSP.inl:39-231).  Returns SGZ_SKIPPED when n_samples <
+ * window_size. */
+int  sgz_spectrum_prepare(sgz_spectrum* h, const float* audio, int mem, int layout,
+                          uint64_t n_samples, uint64_t stream_stride);
+/* Replaces the preliminary-audio overload (TransformDSP.inl:234-484): the
+ * timeline is `history` (n_history samples/channel) followed by `prelim`
+ * (n_prelim samples/channel, newest). */
+int  sgz_spectrum_prepare_preliminary(sgz_spectrum* h, const float* history, uint64_t n_history,
+                                      uint64_t history_stride, const float* prelim,
+                                      uint64_t n_prelim, uint64_t prelim_stride, int mem,
+                                      int layout);
+/* Replaces `void doTransform(const Constant&)` (TransformDSP.inl:487-502). */
+int  sgz_spectrum_transform(sgz_spectrum* h);
+/* Replaces `template<ISA> void mapToLinearSpace(const Constant&)`
+ * (TransformDSP.inl:506-1135). */
+int  sgz_spectrum_map(sgz_spectrum* h);
+/* Replaces `void postProcessStdTransform(const Constant&)`
+ * (TransformDSP.inl:1438-1441 -> mapAndTransformDFTFilters :1299-1435). */
+int  sgz_spectrum_postprocess(sgz_spectrum* h);
+
+/* Replaces `getRawFFT` (TransformPair.h:164-167): [stream][N] complex. */
+int  sgz_spectrum_get_raw_fft(sgz_spectrum* h, float* out, int mem);
+/* Replaces `getTransformResult` (TransformDSP.inl:1444-1447):
+ * [stream][P * state_channels * 2] floats. */
+int  sgz_spectrum_get_transform_result(sgz_spectrum* h, float* out, int mem);
+/* Replaces `lineGraphs[graph].getResults(size)` (TransformPair.h:72-76):
+ * [stream][P] UComplexFilter<float> = 2 floats each
+ * (CommonSignalizer.h:541-591). */
+int  sgz_spectrum_get_results(sgz_spectrum* h, int graph, float* out, int mem);
+/* The peak-hold states behind the results (TransformPair.h:92). */
+int  sgz_spectrum_get_states(sgz_spectrum* h, int graph, float* out, int mem);
+int  sgz_spectrum_set_states(sgz_spectrum* h, int graph, const float* in, int mem);
+/* Replaces `clearLineGraphStates` / `clearAudioState` (TransformPair.h:169-184). */
+int  sgz_spectrum_clear_line_graph_states(sgz_spectrum* h);
+int  sgz_spectrum_clear_audio_state(sgz_spectrum* h);
+
+/* ---- fused batched path --------------------------------------------------
+ * One call = for every stream, `n_frames` successive frames: frame f uses
+ * samples [f*hop, f*hop + window_size) of the stream and runs
+ * prepareTransform -> doTransform -> mapToLinearSpace ->
+ * postProcessStdTransform (the body of the loop at
+ * SpectrumRendering.cpp:622-634, and of `addAudioFrame`,
+ * TransformDSP.inl:1139-1148, at every `sampleBufferSize` boundary of
+ * audioEntryPoint :1172-1204 when hop == sample_buffer_size).
+ * `results`: [stream][frame][graph(2)][P][2] floats.  Peak-hold state is
+ * carried frame to frame and call to call.  n_samples must be >=
+ * (n_frames-1)*hop + window_size. */
+int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout,
+                                 uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
+                                 uint32_t n_frames, float* results, int results_mem);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGZ_H */

@@ -1,0 +1,204 @@
+"""ctypes binding of the CPU oracle (oracle/libsgz_oracle*.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs.  Never import this from signalizer_b200/.
+PARITY UNPINNED — see oracle/sgz_oracle.hpp."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from signalizer_b200 import _abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_libs = {}
+
+
+def build(force: bool = False) -> None:
+    need = force or not all(os.path.exists(os.path.join(_HERE, n)) for n in ("libsgz_oracle.so", "libsgz_oracle_fast.so"))
+    if need:
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+
+
+def _cpu_has_avx2() -> bool:
+    try:
+        with open("/proc/cpuinfo") as f:
+            txt = f.read()
+        return " avx2" in txt and " fma" in txt
+    except OSError:
+        return False
+
+
+def load(fast: bool = False):
+    name = "libsgz_oracle_fast.so" if fast and _cpu_has_avx2() else "libsgz_oracle.so"
+    if name in _libs:
+        return _libs[name]
+    path = os.path.join(_HERE, name)
+    if not os.path.exists(path):
+        build()
+    lib = C.CDLL(path)
+    vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+    fp, dp, ip = C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_int32)
+    lib.sgzo_create.restype = vp
+    lib.sgzo_create.argtypes = [C.POINTER(_abi.SpectrumConfig), u32, i32]
+    lib.sgzo_destroy.argtypes = [vp]
+    lib.sgzo_get_info.argtypes = [vp, C.POINTER(_abi.SpectrumInfo)]
+    for n in ("sgzo_get_window_kernel", "sgzo_get_mapped_frequencies", "sgzo_get_slope_map",
+              "sgzo_get_raw_fft", "sgzo_get_transform_result"):
+        getattr(lib, n).argtypes = [vp, dp]
+    lib.sgzo_get_bin_map.argtypes = [vp, ip, ip, ip, ip]
+    lib.sgzo_prepare.argtypes = [vp, fp, i32, u64, u64, u64]
+    lib.sgzo_prepare_preliminary.argtypes = [vp, fp, u64, u64, u64, fp, u64, u64, i32]
+    for n in ("sgzo_transform", "sgzo_map", "sgzo_postprocess", "sgzo_clear_line_graph_states", "sgzo_clear_audio_state"):
+        getattr(lib, n).argtypes = [vp]
+    lib.sgzo_get_results.argtypes = [vp, i32, fp]
+    lib.sgzo_get_states.argtypes = [vp, i32, fp]
+    lib.sgzo_set_states.argtypes = [vp, i32, fp]
+    lib.sgzo_process_frames.argtypes = [vp, fp, i32, u64, u64, u32, u32, fp, i32, u32, u32]
+    lib.sgzo_resonate.argtypes = [vp, fp, i32, u64, u64]
+    lib.sgzo_audio_entry_point.argtypes = [vp, fp, u64, u64, fp, u64, u64, i32, fp, u32, C.POINTER(u32)]
+    lib.sgzo_hardware_concurrency.restype = C.c_uint
+    _libs[name] = lib
+    return lib
+
+
+def _f32(a):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a, a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class OracleSpectrum:
+    """`n_streams` TransformPair objects sharing one TransformConstant (float32 like the
+    reference, Spectrum.h:71; `double=True` instantiates the same restatement in float64)."""
+
+    def __init__(self, cfg: _abi.SpectrumConfig, n_streams: int = 1, double: bool = False, fast: bool = False):
+        self.lib = load(fast)
+        self.cfg = _abi.copy_config(cfg)
+        self.n_streams = n_streams
+        self.h = self.lib.sgzo_create(C.byref(self.cfg), n_streams, int(double))
+        if not self.h:
+            raise ValueError("sgzo_create rejected the configuration")
+        self.info = _abi.SpectrumInfo()
+        self.lib.sgzo_get_info(self.h, C.byref(self.info))
+        self.N = self.info.transform_size
+        self.P = self.info.axis_points
+        self.channels = self.info.state_channels
+
+    def close(self):
+        if self.h:
+            self.lib.sgzo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dbl(self, fn, n):
+        out = np.empty(n, dtype=np.float64)
+        fn(self.h, out.ctypes.data_as(C.POINTER(C.c_double)))
+        return out
+
+    def window_kernel(self):
+        return self._dbl(self.lib.sgzo_get_window_kernel, self.N)
+
+    def mapped_frequencies(self):
+        return self._dbl(self.lib.sgzo_get_mapped_frequencies, self.P)
+
+    def slope_map(self):
+        return self._dbl(self.lib.sgzo_get_slope_map, self.P)
+
+    def bin_map(self):
+        arrs = [np.empty(self.P, dtype=np.int32) for _ in range(4)]
+        self.lib.sgzo_get_bin_map(self.h, *[a.ctypes.data_as(C.POINTER(C.c_int32)) for a in arrs])
+        return arrs
+
+    @staticmethod
+    def _layout(audio):
+        # [S, n, 2] interleaved or [S, 2, n] planar is ambiguous by shape alone; callers pass layout
+        raise NotImplementedError
+
+    def prepare(self, audio, layout=_abi.LAYOUT_INTERLEAVED, split=None):
+        a, p = _f32(audio)
+        n = a.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else a.shape[2]
+        stride = a[0].size
+        return self.lib.sgzo_prepare(self.h, p, layout, n, stride, n if split is None else split)
+
+    def prepare_preliminary(self, history, prelim, layout=_abi.LAYOUT_INTERLEAVED, split=None):
+        h, hp = _f32(history)
+        q, qp = _f32(prelim)
+        nh = h.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else h.shape[2]
+        nq = q.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else q.shape[2]
+        return self.lib.sgzo_prepare_preliminary(self.h, hp, nh, h[0].size, nh if split is None else split, qp, nq, q[0].size, layout)
+
+    def transform(self):
+        self.lib.sgzo_transform(self.h)
+
+    def map(self):
+        self.lib.sgzo_map(self.h)
+
+    def postprocess(self):
+        self.lib.sgzo_postprocess(self.h)
+
+    def raw_fft(self):
+        out = self._dbl(self.lib.sgzo_get_raw_fft, self.n_streams * self.N * 2)
+        return out.reshape(self.n_streams, self.N, 2)
+
+    def transform_result(self):
+        n = self.P * self.channels * 2
+        return self._dbl(self.lib.sgzo_get_transform_result, self.n_streams * n).reshape(self.n_streams, n)
+
+    def results(self, graph=0):
+        out = np.empty((self.n_streams, self.P, 2), dtype=np.float32)
+        self.lib.sgzo_get_results(self.h, graph, out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
+
+    def states(self, graph=0):
+        out = np.empty((self.n_streams, self.P, 2), dtype=np.float32)
+        self.lib.sgzo_get_states(self.h, graph, out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
+
+    def set_states(self, graph, states):
+        a, p = _f32(states)
+        assert a.shape == (self.n_streams, self.P, 2)
+        self.lib.sgzo_set_states(self.h, graph, p)
+
+    def clear_line_graph_states(self):
+        self.lib.sgzo_clear_line_graph_states(self.h)
+
+    def clear_audio_state(self):
+        self.lib.sgzo_clear_audio_state(self.h)
+
+    def process_frames(self, audio, hop, n_frames, layout=_abi.LAYOUT_INTERLEAVED, threads=1,
+                       want_results=True, first_stream=0, num_streams=None):
+        a, p = _f32(audio)
+        n = a.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else a.shape[2]
+        ns = self.n_streams - first_stream if num_streams is None else num_streams
+        out = np.zeros((self.n_streams, n_frames, 2, self.P, 2), dtype=np.float32) if want_results else None
+        op = out.ctypes.data_as(C.POINTER(C.c_float)) if want_results else None
+        rc = self.lib.sgzo_process_frames(self.h, p, layout, n, a[0].size, hop, n_frames, op, threads, first_stream, ns)
+        if rc != 0:
+            raise ValueError(f"sgzo_process_frames rc={rc}")
+        return out
+
+    def resonate(self, audio, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        n = a.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else a.shape[2]
+        return self.lib.sgzo_resonate(self.h, p, layout, n, a[0].size)
+
+    def audio_entry_point(self, history, block, layout=_abi.LAYOUT_INTERLEAVED, max_frames=64):
+        h, hp = _f32(history)
+        b, bp = _f32(block)
+        nh = h.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else h.shape[2]
+        nb = b.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else b.shape[2]
+        out = np.zeros((self.n_streams, max_frames, self.P, 2), dtype=np.float32)
+        nf = C.c_uint32(0)
+        self.lib.sgzo_audio_entry_point(self.h, hp, nh, h[0].size, bp, nb, b[0].size, layout,
+                                        out.ctypes.data_as(C.POINTER(C.c_float)), max_frames, C.byref(nf))
+        return out[:, :nf.value]
+
+
+def hardware_concurrency() -> int:
+    return int(load().sgzo_hardware_concurrency())

@@ -1,0 +1,416 @@
+// sgz_oracle_capi.cpp — C entry points over the CPU oracle (sgz_oracle.hpp) for ctypes.
+//
+// TEST INFRASTRUCTURE ONLY (see the header of sgz_oracle.hpp): used by tests/,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+// PARITY UNPINNED (no reference tests or golden vectors exist; cpl is absent).
+//
+// The handle mirrors the product's batched C ABI (include/sgz.h) so one test
+// harness drives both: `n_streams` TransformPair objects sharing one
+// TransformConstant, as in SpectrumDSP.cpp:83-102.
+#include "sgz_oracle.hpp"
+#include "../include/sgz.h"
+
+#include <atomic>
+#include <memory>
+#include <thread>
+
+using namespace sgzo;
+
+namespace
+{
+	struct IOracle
+	{
+		virtual ~IOracle() = default;
+		virtual void info(sgz_spectrum_info* out) = 0;
+		virtual void window(double* out) = 0;
+		virtual void freqs(double* out) = 0;
+		virtual void slopes(double* out) = 0;
+		virtual void binMap(int32_t* mode, int32_t* first, int32_t* count, int32_t* fallback) = 0;
+		virtual int prepare(const float* audio, int layout, uint64_t n, uint64_t stride, uint64_t split) = 0;
+		virtual int preparePrelim(const float* hist, uint64_t nh, uint64_t hstride, uint64_t split, const float* prelim, uint64_t np, uint64_t pstride, int layout) = 0;
+		virtual void transform() = 0;
+		virtual void map() = 0;
+		virtual void post() = 0;
+		virtual void rawFFT(double* out) = 0;
+		virtual void transformResult(double* out) = 0;
+		virtual void results(int graph, float* out) = 0;
+		virtual void states(int graph, float* out) = 0;
+		virtual void setStates(int graph, const float* in) = 0;
+		virtual void clearLineGraphs() = 0;
+		virtual void clearAudio() = 0;
+		virtual int frames(const float* audio, int layout, uint64_t n, uint64_t stride, uint32_t hop, uint32_t nFrames, float* results, int threads, uint32_t firstStream, uint32_t numStreams) = 0;
+		virtual int resonate(const float* audio, int layout, uint64_t n, uint64_t stride) = 0;
+		virtual int audioEntry(const float* hist, uint64_t nh, uint64_t hstride, const float* block, uint64_t nb, uint64_t bstride, int layout, float* frames, uint32_t maxFrames, uint32_t* numFrames) = 0;
+	};
+
+	// de-interleave helper: returns planar pointers for stream s
+	struct StreamAudio
+	{
+		std::vector<float> storage;
+		const float* ch[2];
+	};
+
+	static void fetch(const float* audio, int layout, uint64_t n, uint64_t stride, std::size_t s, StreamAudio& out)
+	{
+		const float* base = audio + s * stride;
+		if (layout == SGZ_LAYOUT_PLANAR)
+		{
+			out.ch[0] = base; out.ch[1] = base + n;
+		}
+		else
+		{
+			out.storage.resize(2 * n);
+			for (uint64_t i = 0; i < n; ++i) { out.storage[i] = base[2 * i]; out.storage[n + i] = base[2 * i + 1]; }
+			out.ch[0] = out.storage.data(); out.ch[1] = out.storage.data() + n;
+		}
+	}
+
+	template<typename T>
+	struct Oracle : IOracle
+	{
+		TransformConstant<T> constant;
+		std::vector<TransformPair<T>> pairs;
+		sgz_spectrum_config cfg;
+
+		Oracle(const sgz_spectrum_config& c, uint32_t nStreams) : pairs(nStreams), cfg(c)
+		{
+			// order of derivation: Spectrum.cpp:365-394 (scalars), :412-431 (configuration, sample
+			// rate), :489 setStorage, :571-576 remapFrequencies, :578-581 slope map, :583-588
+			// window kernel, :590-595 resonator
+			constant.sampleBufferSize = c.sample_buffer_size;
+			constant.algo = static_cast<TransformAlgorithm>(c.algo);
+			constant.binPolation = static_cast<BinInterpolation>(c.bin_polation);
+			constant.displayMode = static_cast<DisplayMode>(c.display_mode);
+			constant.lowDBs = c.low_dbs; constant.clipDB = c.clip_db; constant.highDBs = c.high_dbs;
+			constant.filter[0].pole = static_cast<T>(c.pole[0]);
+			constant.filter[1].pole = static_cast<T>(c.pole[1]);
+			constant.configuration = static_cast<SpectrumChannels>(c.configuration);
+			constant.sampleRate = static_cast<T>(c.sample_rate);
+			std::size_t ts;
+			constant.setStorage(c.axis_points, c.window_size, ts);
+			constant.remapFrequencies(c.view_left, c.view_right, static_cast<ViewScaling>(c.view_scaling), c.min_freq);
+			constant.generateSlopeMap(c.slope_a, c.slope_b);
+			constant.regenerateWindowKernel(static_cast<WindowTypes>(c.window_type), static_cast<WindowShape>(c.window_shape));
+			constant.remapResonator(c.free_q != 0, dsp::windowCoefficientCount(static_cast<WindowTypes>(c.window_type)));
+			for (auto& p : pairs)
+				for (auto& g : p.lineGraphs) g.resize(c.axis_points);
+		}
+
+		void info(sgz_spectrum_info* out) override
+		{
+			std::memset(out, 0, sizeof(*out));
+			out->transform_size = (uint32_t)constant.transformSize;
+			out->window_size = (uint32_t)constant.windowSize;
+			out->axis_points = (uint32_t)constant.axisPoints;
+			out->n_streams = (uint32_t)pairs.size();
+			out->state_channels = (uint32_t)constant.getStateConfigurationChannels();
+			out->window_kernel_scale = (float)constant.windowKernelScale;
+			out->inv_size = (float)static_cast<T>(constant.windowKernelScale / (constant.windowSize * 0.5));
+			const auto topFrequency = constant.sampleRate / 2;
+			out->freq_to_bin = (float)static_cast<T>((constant.transformSize >> 1) / topFrequency);
+			out->resonator_vectors = (uint32_t)constant.resonator.numVectors;
+			out->device = -1;
+			std::vector<int32_t> mode(constant.axisPoints), a(constant.axisPoints), b(constant.axisPoints), c(constant.axisPoints);
+			binMap(mode.data(), a.data(), b.data(), c.data());
+			uint32_t bp = (uint32_t)constant.axisPoints;
+			for (std::size_t x = 0; x < constant.axisPoints; ++x) if (mode[x] == 1) { bp = (uint32_t)x; break; }
+			out->break_point = bp;
+		}
+		void window(double* out) override { for (std::size_t i = 0; i < constant.transformSize; ++i) out[i] = i < constant.windowSize ? (double)constant.windowKernel[i] : 0.0; }
+		void freqs(double* out) override { for (std::size_t i = 0; i < constant.axisPoints; ++i) out[i] = constant.mappedFrequencies[i]; }
+		void slopes(double* out) override { for (std::size_t i = 0; i < constant.axisPoints; ++i) out[i] = constant.slopeMap[i]; }
+
+		// The integer skeleton of the loops at TransformDSP.inl:562-639 (mono), :875-984
+		// (Separate/MidSide), :666-850 (Phase), :995-1096 (Complex): which display points
+		// interpolate, which take max-of-bins, and over which bins.
+		void binMap(int32_t* mode, int32_t* first, int32_t* count, int32_t* fallback) override
+		{
+			typedef std::ptrdiff_t ssz;
+			const int N = (int)constant.transformSize;
+			const int P = (int)constant.axisPoints;
+			const std::size_t numBins = N >> 1;
+			const auto topFrequency = constant.sampleRate / 2;
+			const auto freqToBin = static_cast<T>(numBins / topFrequency);
+			const auto& mf = constant.mappedFrequencies;
+			const bool isComplex = constant.configuration == SpectrumChannels::Complex;
+			const bool isPhase = constant.configuration == SpectrumChannels::Phase;
+			const double fftBandwidth = isComplex ? 1.0 / (numBins * 2) : 1.0 / numBins;
+			auto interp = [&](int x)
+			{
+				mode[x] = 0; count[x] = 0; fallback[x] = 0;
+				if (constant.binPolation == BinInterpolation::None)
+				{
+					std::size_t hi = isComplex ? (std::size_t)N : (isPhase ? numBins - 1 : numBins);
+					first[x] = (int32_t)Math::confineTo<std::size_t>((std::size_t)(mf[x] * freqToBin + 0.5), 0, hi);
+				}
+				else
+					first[x] = (int32_t)std::floor(mf[x] * freqToBin);
+			};
+			auto maxOf = [&](int x, ssz& oldBin)
+			{
+				ssz bin = static_cast<ssz>(static_cast<std::size_t>(mf[x] * freqToBin));
+				ssz diff = bin - oldBin;
+				ssz counter = diff ? 1 : 0;
+				mode[x] = 1; first[x] = (int32_t)(oldBin + counter);
+				int32_t c = 0;
+				do { c++; diff--; } while (diff > 0);
+				count[x] = c;
+				fallback[x] = isPhase ? 0 : (int32_t)bin;
+				oldBin = bin;
+			};
+			int x = 0;
+			ssz oldBin = 0;
+			if (!isComplex)
+			{
+				for (x = 0; x < P - 1; ++x)
+				{
+					double bwForLine = (mf[x + 1] - mf[x]) / topFrequency;
+					if (bwForLine > fftBandwidth) break;
+					interp(x);
+				}
+				if (x < P) oldBin = static_cast<ssz>(mf[x] * freqToBin);
+				for (; x < P; ++x) maxOf(x, oldBin);
+			}
+			else
+			{
+				while (x < P)
+				{
+					for (; x < P; ++x)
+					{
+						if (x != P - 1)
+						{
+							double bwForLine = (mf[x + 1] - mf[x]) / topFrequency;
+							if (bwForLine > fftBandwidth) break;
+						}
+						interp(x);
+					}
+					if (x != P) oldBin = static_cast<ssz>(mf[x] * freqToBin);
+					for (; x < P; ++x)
+					{
+						if (x != P - 1)
+						{
+							double bwForLine = (mf[x + 1] - mf[x]) / topFrequency;
+							if (bwForLine < fftBandwidth) break;
+						}
+						maxOf(x, oldBin);
+					}
+				}
+			}
+		}
+
+		static AudioPair makeViews(const float* l, const float* r, uint64_t n, uint64_t split)
+		{
+			AudioPair v;
+			if (split > n) split = n;
+			// segment 0 = oldest `split` samples, segment 1 = the rest (a wrapped ring)
+			v[0].seg[0] = l; v[0].len[0] = split; v[0].seg[1] = l + split; v[0].len[1] = n - split;
+			v[1].seg[0] = r; v[1].len[0] = split; v[1].seg[1] = r + split; v[1].len[1] = n - split;
+			return v;
+		}
+
+		int prepare(const float* audio, int layout, uint64_t n, uint64_t stride, uint64_t split) override
+		{
+			int rc = SGZ_OK;
+			StreamAudio sa;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				fetch(audio, layout, n, stride, s, sa);
+				if (!pairs[s].prepareTransform(constant, makeViews(sa.ch[0], sa.ch[1], n, split))) rc = SGZ_SKIPPED;
+			}
+			return rc;
+		}
+		int preparePrelim(const float* hist, uint64_t nh, uint64_t hstride, uint64_t split, const float* prelim, uint64_t np, uint64_t pstride, int layout) override
+		{
+			int rc = SGZ_OK;
+			StreamAudio sh, sp;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				fetch(hist, layout, nh, hstride, s, sh);
+				fetch(prelim, layout, np, pstride, s, sp);
+				if (!pairs[s].prepareTransform(constant, makeViews(sh.ch[0], sh.ch[1], nh, split), { sp.ch[0], sp.ch[1] }, np)) rc = SGZ_SKIPPED;
+			}
+			return rc;
+		}
+		void transform() override { for (auto& p : pairs) p.doTransform(constant); }
+		void map() override { for (auto& p : pairs) p.mapToLinearSpace(constant); }
+		void post() override { for (auto& p : pairs) p.postProcessStdTransform(constant); }
+		void rawFFT(double* out) override
+		{
+			const std::size_t N = constant.transformSize;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				auto* z = pairs[s].getRawFFT(constant);
+				for (std::size_t i = 0; i < N; ++i) { out[2 * (s * N + i)] = z[i].real(); out[2 * (s * N + i) + 1] = z[i].imag(); }
+			}
+		}
+		void transformResult(double* out) override
+		{
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				std::size_t n;
+				const T* r = pairs[s].getTransformResult(constant, &n);
+				for (std::size_t i = 0; i < n; ++i) out[s * n + i] = r[i];
+			}
+		}
+		void results(int graph, float* out) override
+		{
+			const std::size_t P = constant.axisPoints;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				const auto& r = pairs[s].lineGraphs[graph].getResults(P);
+				for (std::size_t i = 0; i < P; ++i) { out[2 * (s * P + i)] = r[i].a; out[2 * (s * P + i) + 1] = r[i].b; }
+			}
+		}
+		void states(int graph, float* out) override
+		{
+			const std::size_t P = constant.axisPoints;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				auto& g = pairs[s].lineGraphs[graph]; g.resize(P);
+				for (std::size_t i = 0; i < P; ++i) { out[2 * (s * P + i)] = g.states[i].a; out[2 * (s * P + i) + 1] = g.states[i].b; }
+			}
+		}
+		void setStates(int graph, const float* in) override
+		{
+			const std::size_t P = constant.axisPoints;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				auto& g = pairs[s].lineGraphs[graph]; g.resize(P);
+				for (std::size_t i = 0; i < P; ++i) { g.states[i].a = in[2 * (s * P + i)]; g.states[i].b = in[2 * (s * P + i) + 1]; }
+			}
+		}
+		void clearLineGraphs() override { for (auto& p : pairs) p.clearLineGraphStates(); }
+		void clearAudio() override { for (auto& p : pairs) p.clearAudioState(); }
+
+		// The body of the loop at SpectrumRendering.cpp:622-634 per frame and stream; the thread
+		// pool over streams stands in for cpl::jobs::parallel_for (SpectrumDSP.cpp:83).
+		int frames(const float* audio, int layout, uint64_t n, uint64_t stride, uint32_t hop, uint32_t nFrames, float* results, int threads, uint32_t firstStream, uint32_t numStreams) override
+		{
+			const std::size_t W = constant.windowSize, P = constant.axisPoints;
+			if (nFrames && n < (uint64_t)(nFrames - 1) * hop + W) return SGZ_EINVAL;
+			if ((uint64_t)firstStream + numStreams > pairs.size()) return SGZ_EINVAL;
+			std::atomic<std::size_t> next{ firstStream };
+			const std::size_t end = (std::size_t)firstStream + numStreams;
+			auto worker = [&]()
+			{
+				StreamAudio sa;
+				for (;;)
+				{
+					const std::size_t s = next.fetch_add(1);
+					if (s >= end) break;
+					fetch(audio, layout, n, stride, s, sa);
+					for (uint32_t f = 0; f < nFrames; ++f)
+					{
+						const uint64_t off = (uint64_t)f * hop;
+						auto views = makeViews(sa.ch[0] + off, sa.ch[1] + off, W, W);
+						auto& p = pairs[s];
+						if (!p.prepareTransform(constant, views)) continue;
+						p.doTransform(constant);
+						p.mapToLinearSpace(constant);
+						p.postProcessStdTransform(constant);
+						if (results)
+						{
+							for (int g = 0; g < 2; ++g)
+							{
+								const auto& r = p.lineGraphs[g].getResults(P);
+								float* o = results + (((s * nFrames + f) * 2 + g) * P) * 2;
+								for (std::size_t i = 0; i < P; ++i) { o[2 * i] = r[i].a; o[2 * i + 1] = r[i].b; }
+							}
+						}
+					}
+				}
+			};
+			if (threads <= 1) worker();
+			else
+			{
+				std::vector<std::thread> pool;
+				for (int t = 0; t < threads; ++t) pool.emplace_back(worker);
+				for (auto& t : pool) t.join();
+			}
+			return SGZ_OK;
+		}
+
+		int resonate(const float* audio, int layout, uint64_t n, uint64_t stride) override
+		{
+			StreamAudio sa;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				fetch(audio, layout, n, stride, s, sa);
+				pairs[s].resonatingDispatch(constant, { sa.ch[0], sa.ch[1] }, n);
+			}
+			return SGZ_OK;
+		}
+
+		// audioEntryPoint over one callback block (TransformDSP.inl:1165-1211); copies the
+		// emitted sfbuf frames of every stream to frames[stream][frame][P][2].
+		int audioEntry(const float* hist, uint64_t nh, uint64_t hstride, const float* block, uint64_t nb, uint64_t bstride, int layout, float* frames, uint32_t maxFrames, uint32_t* numFrames) override
+		{
+			StreamAudio sh, sb;
+			const std::size_t P = constant.axisPoints;
+			uint32_t emitted = 0;
+			const auto authorityCounter = pairs.empty() ? 0 : pairs[0].processedSamplesSinceLastFrame; // SpectrumDSP.cpp:81
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				fetch(block, layout, nb, bstride, s, sb);
+				AudioPair views;
+				if (constant.algo == TransformAlgorithm::FFT)
+				{
+					fetch(hist, layout, nh, hstride, s, sh);
+					views = makeViews(sh.ch[0], sh.ch[1], nh, nh);
+				}
+				pairs[s].processedSamplesSinceLastFrame = authorityCounter; // SpectrumDSP.cpp:93
+				pairs[s].audioEntryPoint(constant, &views, { sb.ch[0], sb.ch[1] }, nb);
+				emitted = (uint32_t)pairs[s].sfbuf.size();
+				for (uint32_t f = 0; f < emitted && f < maxFrames; ++f)
+				{
+					float* o = frames + ((s * maxFrames + f) * P) * 2;
+					for (std::size_t i = 0; i < P; ++i) { o[2 * i] = pairs[s].sfbuf[f][i].a; o[2 * i + 1] = pairs[s].sfbuf[f][i].b; }
+				}
+				pairs[s].sfbuf.clear();
+			}
+			*numFrames = emitted;
+			return SGZ_OK;
+		}
+	};
+}
+
+extern "C"
+{
+	void* sgzo_create(const sgz_spectrum_config* cfg, uint32_t n_streams, int use_double)
+	{
+		if (!cfg || cfg->abi_version != SGZ_ABI_VERSION || cfg->axis_points < 2 || cfg->window_size < 1) return nullptr;
+		if (use_double) return static_cast<IOracle*>(new Oracle<double>(*cfg, n_streams));
+		return static_cast<IOracle*>(new Oracle<float>(*cfg, n_streams));
+	}
+	void sgzo_destroy(void* h) { delete static_cast<IOracle*>(h); }
+	void sgzo_get_info(void* h, sgz_spectrum_info* out) { static_cast<IOracle*>(h)->info(out); }
+	void sgzo_get_window_kernel(void* h, double* out) { static_cast<IOracle*>(h)->window(out); }
+	void sgzo_get_mapped_frequencies(void* h, double* out) { static_cast<IOracle*>(h)->freqs(out); }
+	void sgzo_get_slope_map(void* h, double* out) { static_cast<IOracle*>(h)->slopes(out); }
+	void sgzo_get_bin_map(void* h, int32_t* mode, int32_t* first, int32_t* count, int32_t* fallback) { static_cast<IOracle*>(h)->binMap(mode, first, count, fallback); }
+	int sgzo_prepare(void* h, const float* audio, int layout, uint64_t n, uint64_t stride, uint64_t split) { return static_cast<IOracle*>(h)->prepare(audio, layout, n, stride, split); }
+	int sgzo_prepare_preliminary(void* h, const float* hist, uint64_t nh, uint64_t hstride, uint64_t split, const float* prelim, uint64_t np, uint64_t pstride, int layout)
+	{
+		return static_cast<IOracle*>(h)->preparePrelim(hist, nh, hstride, split, prelim, np, pstride, layout);
+	}
+	void sgzo_transform(void* h) { static_cast<IOracle*>(h)->transform(); }
+	void sgzo_map(void* h) { static_cast<IOracle*>(h)->map(); }
+	void sgzo_postprocess(void* h) { static_cast<IOracle*>(h)->post(); }
+	void sgzo_get_raw_fft(void* h, double* out) { static_cast<IOracle*>(h)->rawFFT(out); }
+	void sgzo_get_transform_result(void* h, double* out) { static_cast<IOracle*>(h)->transformResult(out); }
+	void sgzo_get_results(void* h, int graph, float* out) { static_cast<IOracle*>(h)->results(graph, out); }
+	void sgzo_get_states(void* h, int graph, float* out) { static_cast<IOracle*>(h)->states(graph, out); }
+	void sgzo_set_states(void* h, int graph, const float* in) { static_cast<IOracle*>(h)->setStates(graph, in); }
+	void sgzo_clear_line_graph_states(void* h) { static_cast<IOracle*>(h)->clearLineGraphs(); }
+	void sgzo_clear_audio_state(void* h) { static_cast<IOracle*>(h)->clearAudio(); }
+	int sgzo_process_frames(void* h, const float* audio, int layout, uint64_t n, uint64_t stride, uint32_t hop, uint32_t n_frames, float* results, int threads, uint32_t first_stream, uint32_t num_streams)
+	{
+		return static_cast<IOracle*>(h)->frames(audio, layout, n, stride, hop, n_frames, results, threads, first_stream, num_streams);
+	}
+	int sgzo_resonate(void* h, const float* audio, int layout, uint64_t n, uint64_t stride) { return static_cast<IOracle*>(h)->resonate(audio, layout, n, stride); }
+	int sgzo_audio_entry_point(void* h, const float* hist, uint64_t nh, uint64_t hstride, const float* block, uint64_t nb, uint64_t bstride, int layout, float* frames, uint32_t max_frames, uint32_t* num_frames)
+	{
+		return static_cast<IOracle*>(h)->audioEntry(hist, nh, hstride, block, nb, bstride, layout, frames, max_frames, num_frames);
+	}
+	unsigned sgzo_hardware_concurrency(void) { return std::thread::hardware_concurrency(); }
+}

@@ -1,0 +1,111 @@
+"""ctypes mirror of include/sgz.h (enums, PODs).  Keep in lock-step with the header."""
+import ctypes as C
+
+ABI_VERSION = 1
+
+# status codes
+OK, SKIPPED, EINVAL, ECUDA, ENOMEM, EUNSUPPORTED, ESTATE = 0, 1, -1, -2, -3, -4, -5
+
+# SpectrumChannels — Source/Common/CommonSignalizer.h:495-539
+CH_LEFT, CH_RIGHT, CH_MERGE, CH_SIDE, CH_PHASE, CH_SEPARATE, CH_MIDSIDE, CH_COMPLEX = range(8)
+CHANNEL_NAMES = ["Left", "Right", "Merge", "Side", "Phase", "Separate", "MidSide", "Complex"]
+# SpectrumParameters.h:48-75
+BIN_NONE, BIN_LINEAR, BIN_LANCZOS = range(3)
+DISPLAY_LINEGRAPH, DISPLAY_COLOURSPECTRUM = range(2)
+ALGO_FFT, ALGO_RSNT = range(2)
+VIEW_LINEAR, VIEW_LOGARITHMIC = range(2)
+LINE_MAIN, LINE_SECOND, LINE_END = range(3)
+(WIN_RECTANGULAR, WIN_HANN, WIN_HAMMING, WIN_BLACKMAN, WIN_BLACKMAN_HARRIS, WIN_NUTTALL,
+ WIN_FLATTOP, WIN_END) = range(8)
+WINSHAPE_SYMMETRIC, WINSHAPE_PERIODIC = range(2)
+MEM_HOST, MEM_DEVICE = range(2)
+LAYOUT_PLANAR, LAYOUT_INTERLEAVED = range(2)
+
+
+class SpectrumConfig(C.Structure):
+    """sgz_spectrum_config — the fields of TransformConstant<T> the path reads
+    (Source/Spectrum/TransformConstant.h:188-239) and the inputs of its table builders."""
+    _fields_ = [
+        ("abi_version", C.c_uint32),
+        ("sample_rate", C.c_float),
+        ("window_size", C.c_uint32),
+        ("axis_points", C.c_uint32),
+        ("algo", C.c_int32),
+        ("configuration", C.c_int32),
+        ("bin_polation", C.c_int32),
+        ("display_mode", C.c_int32),
+        ("view_scaling", C.c_int32),
+        ("view_left", C.c_double),
+        ("view_right", C.c_double),
+        ("min_freq", C.c_double),
+        ("slope_a", C.c_double),
+        ("slope_b", C.c_double),
+        ("low_dbs", C.c_double),
+        ("high_dbs", C.c_double),
+        ("clip_db", C.c_double),
+        ("pole", C.c_float * 2),
+        ("window_type", C.c_int32),
+        ("window_shape", C.c_int32),
+        ("sample_buffer_size", C.c_uint32),
+        ("free_q", C.c_int32),
+    ]
+
+
+class SpectrumInfo(C.Structure):
+    _fields_ = [
+        ("transform_size", C.c_uint32),
+        ("window_size", C.c_uint32),
+        ("axis_points", C.c_uint32),
+        ("n_streams", C.c_uint32),
+        ("state_channels", C.c_uint32),
+        ("break_point", C.c_uint32),
+        ("window_kernel_scale", C.c_float),
+        ("inv_size", C.c_float),
+        ("freq_to_bin", C.c_float),
+        ("resonator_vectors", C.c_uint32),
+        ("device", C.c_int32),
+        ("fused_available", C.c_int32),
+    ]
+
+
+def default_config(**overrides) -> SpectrumConfig:
+    """Defaults of SURVEY.md §8(d): Separate, FFT, Lanczos, log view 10 Hz..fs/2, slope a=0 b=1,
+    -120..0 dB, clip -384 dB (SpectrumParameters.h:78), poles {0.95, 0.99}."""
+    cfg = SpectrumConfig()
+    cfg.abi_version = ABI_VERSION
+    cfg.sample_rate = 48000.0
+    cfg.window_size = 8192
+    cfg.axis_points = 1024
+    cfg.algo = ALGO_FFT
+    cfg.configuration = CH_SEPARATE
+    cfg.bin_polation = BIN_LANCZOS
+    cfg.display_mode = DISPLAY_LINEGRAPH
+    cfg.view_scaling = VIEW_LOGARITHMIC
+    cfg.view_left, cfg.view_right = 0.0, 1.0
+    cfg.min_freq = 10.0
+    cfg.slope_a, cfg.slope_b = 0.0, 1.0
+    cfg.low_dbs, cfg.high_dbs, cfg.clip_db = -120.0, 0.0, -384.0
+    cfg.pole[0], cfg.pole[1] = 0.95, 0.99
+    cfg.window_type = WIN_BLACKMAN_HARRIS
+    cfg.window_shape = WINSHAPE_PERIODIC
+    cfg.sample_buffer_size = 200
+    cfg.free_q = 0
+    for k, v in overrides.items():
+        if k == "pole":
+            cfg.pole[0], cfg.pole[1] = v
+        else:
+            if not hasattr(cfg, k):
+                raise AttributeError(k)
+            setattr(cfg, k, v)
+    return cfg
+
+
+def copy_config(cfg: SpectrumConfig, **overrides) -> SpectrumConfig:
+    out = SpectrumConfig()
+    C.memmove(C.byref(out), C.byref(cfg), C.sizeof(SpectrumConfig))
+    for k, v in overrides.items():
+        if k == "pole":
+            out.pole[0], out.pole[1] = v
+        else:
+            setattr(out, k, v)
+    return out

@@ -1,0 +1,161 @@
+"""The C++ oracle against an independently written float64 numpy model and analytic
+known-answer tests (the reference has no tests of its own)."""
+import numpy as np
+import pytest
+
+from oracle import model_f64
+from oracle.binding import OracleSpectrum
+from signalizer_b200 import _abi, signals
+from tolerances import assert_linear_close, assert_log_close
+
+CONFIGS = [
+    dict(window_size=4096, window_type=_abi.WIN_HANN),            # BASELINE config 1
+    dict(window_size=8192, window_type=_abi.WIN_BLACKMAN_HARRIS),  # BASELINE config 3
+    dict(window_size=1000, window_type=_abi.WIN_HAMMING, axis_points=300),  # zero-padded, odd sizes
+    dict(window_size=512, window_type=_abi.WIN_RECTANGULAR, axis_points=64, view_scaling=_abi.VIEW_LINEAR),
+]
+
+
+@pytest.mark.parametrize("over", CONFIGS)
+def test_tables_match_model_bit_exact(over):
+    cfg = _abi.default_config(**over)
+    o = OracleSpectrum(cfg, 1)
+    assert o.N == model_f64.transform_size(cfg.window_size)
+    w, scale = model_f64.window(cfg)
+    np.testing.assert_array_equal(o.window_kernel()[:cfg.window_size].astype(np.float32), w)
+    assert np.all(o.window_kernel()[cfg.window_size:] == 0)
+    assert np.float32(o.info.window_kernel_scale) == scale
+    mf = model_f64.mapped_frequencies(cfg)
+    np.testing.assert_array_equal(o.mapped_frequencies().astype(np.float32), mf)
+    np.testing.assert_array_equal(o.slope_map().astype(np.float32), model_f64.slope_map(cfg, mf))
+    for bp in (_abi.BIN_NONE, _abi.BIN_LINEAR, _abi.BIN_LANCZOS):
+        c2 = _abi.copy_config(cfg, bin_polation=bp)
+        got = OracleSpectrum(c2, 1).bin_map()
+        want = model_f64.bin_map(c2)
+        for g, w_, name in zip(got, want, ("mode", "first", "count", "fallback")):
+            np.testing.assert_array_equal(g, w_, err_msg=name)
+
+
+def test_break_points_of_survey():
+    # N=8192 -> x=571, N=4096 -> x=662 at 48 kHz, P=1024, log 10 Hz..24 kHz
+    assert OracleSpectrum(_abi.default_config(window_size=8192), 1).info.break_point == 571
+    assert OracleSpectrum(_abi.default_config(window_size=4096), 1).info.break_point == 662
+
+
+@pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_RIGHT, _abi.CH_MERGE, _abi.CH_SIDE, _abi.CH_SEPARATE, _abi.CH_MIDSIDE])
+@pytest.mark.parametrize("bp", [_abi.BIN_NONE, _abi.BIN_LINEAR, _abi.BIN_LANCZOS])
+@pytest.mark.parametrize("size", [(4096, _abi.WIN_HANN), (8192, _abi.WIN_BLACKMAN_HARRIS), (700, _abi.WIN_BLACKMAN)])
+def test_oracle_matches_float64_model(conf, bp, size):
+    cfg = _abi.default_config(window_size=size[0], window_type=size[1], configuration=conf, bin_polation=bp)
+    n_streams = 3
+    audio = signals.batch(n_streams, cfg.window_size + 37)  # more history than the window
+    o = OracleSpectrum(cfg, n_streams)
+    assert o.prepare(audio) == _abi.OK
+    o.transform(); o.map(); o.postprocess()
+    ch = o.channels
+    tr = o.transform_result().reshape(n_streams, ch, cfg.axis_points, 2)
+    got_mag = np.hypot(tr[..., 0], tr[..., 1])
+    res = [o.results(0), o.results(1)]
+    for s in range(n_streams):
+        states = np.zeros((2, ch, cfg.axis_points))
+        mags, want = model_f64.frame(cfg, audio[s], states)
+        assert_linear_close(got_mag[s], mags, what=f"stream {s} magnitudes")
+        # first frame from zero state: state == magnitude, so the linear bound maps to the log scale
+        mask = mags > 0
+        for k in range(2):
+            got = np.stack([res[k][s, :, c] for c in range(ch)])
+            assert_log_close(got[mask], want[k][mask], lin=mags[mask], peak=mags.max(), what=f"stream {s} graph {k}")
+
+
+def test_bin_centred_sine_reads_its_amplitude():
+    # analytic KAT: amplitude A at an exact bin -> normalised magnitude A (TransformDSP.inl:537-540)
+    for W, wt in ((4096, _abi.WIN_HANN), (8192, _abi.WIN_BLACKMAN_HARRIS), (2048, _abi.WIN_RECTANGULAR)):
+        cfg = _abi.default_config(window_size=W, window_type=wt, bin_polation=_abi.BIN_NONE)
+        n = np.arange(W)
+        k1, k2 = W // 8, W // 5
+        x = np.zeros((1, W, 2), np.float32)
+        x[0, :, 0] = 0.5 * np.sin(2 * np.pi * k1 * n / W)
+        x[0, :, 1] = 0.25 * np.cos(2 * np.pi * k2 * n / W)
+        o = OracleSpectrum(cfg, 1)
+        o.prepare(x); o.transform(); o.map(); o.postprocess()
+        tr = o.transform_result().reshape(2, cfg.axis_points, 2)
+        assert abs(tr[0, :, 0].max() - 0.5) < 1e-5
+        assert abs(tr[1, :, 0].max() - 0.25) < 1e-5
+        # 0.5 = -6.02 dB on a -120..0 dB scale -> 1 - 6.0206/120
+        r = o.results(0)[0]
+        assert abs(r[:, 0].max() - (1 - 6.0206 / 120)) < 1e-4
+        assert abs(r[:, 1].max() - (1 - 12.0412 / 120)) < 1e-4
+
+
+def test_silence_gives_clip_db_and_impulse_is_flat():
+    cfg = _abi.default_config(window_size=4096, window_type=_abi.WIN_HANN, bin_polation=_abi.BIN_NONE)
+    o = OracleSpectrum(cfg, 1)
+    x = np.zeros((1, 4096, 2), np.float32)
+    o.prepare(x); o.transform(); o.map(); o.postprocess()
+    assert np.all(o.results(0) == np.float32(cfg.clip_db))
+    # impulse at sample j: |X[k]| = w[j] for every k -> flat at w[j] * invSize
+    j = 1000
+    x[0, j, 0] = 1.0
+    o.prepare(x); o.transform(); o.map()
+    tr = o.transform_result().reshape(2, cfg.axis_points, 2)
+    w = o.window_kernel()[j]
+    # bin 0 (halved) is below 10 Hz; N/2 and N/2-1 are halved (reference quirk, TransformDSP.inl:863-864)
+    flat = tr[0, :-8, 0]
+    np.testing.assert_allclose(flat, w * o.info.inv_size, rtol=2e-5)
+
+
+def test_peak_hold_decay_and_state_roundtrip():
+    cfg = _abi.default_config(window_size=1024, axis_points=128, pole=(0.5, 0.9))
+    o = OracleSpectrum(cfg, 2)
+    a = signals.batch(2, 1024)
+    o.prepare(a); o.transform(); o.map(); o.postprocess()
+    s0 = o.states(0).copy(); s1 = o.states(1).copy()
+    assert np.all(s0 >= 0)
+    z = np.zeros_like(a)
+    o.prepare(z); o.transform(); o.map(); o.postprocess()
+    np.testing.assert_allclose(o.states(0), s0 * np.float32(0.5), rtol=1e-6)
+    np.testing.assert_allclose(o.states(1), s1 * np.float32(0.9), rtol=1e-6)
+    o.set_states(0, s0)
+    np.testing.assert_array_equal(o.states(0), s0)
+    o.clear_line_graph_states()
+    assert np.all(o.states(0) == 0) and np.all(o.results(1) == 0)
+
+
+def test_prepare_skips_short_history_and_ring_split_is_transparent():
+    cfg = _abi.default_config(window_size=2048)
+    o = OracleSpectrum(cfg, 1)
+    assert o.prepare(signals.batch(1, 2047)) == _abi.SKIPPED  # TransformDSP.inl:45-46
+    a = signals.batch(1, 3000, first_stream=2)
+    o.prepare(a); o.transform(); ref = o.raw_fft().copy()
+    for split in (0, 1, 952, 953, 1500, 2999, 3000):
+        o.prepare(a, split=split); o.transform()
+        np.testing.assert_array_equal(o.raw_fft(), ref)
+
+
+def test_fft_against_numpy():
+    rng = np.random.default_rng(7)
+    for W in (32, 64, 128, 2048, 8192, 16384):
+        cfg = _abi.default_config(window_size=W, window_type=_abi.WIN_RECTANGULAR, configuration=_abi.CH_COMPLEX)
+        o = OracleSpectrum(cfg, 1)
+        x = rng.standard_normal((1, W, 2)).astype(np.float32)
+        o.prepare(x); o.transform()
+        z = o.raw_fft()[0]
+        want = np.fft.fft(x[0, :, 0].astype(np.float64) + 1j * x[0, :, 1].astype(np.float64))
+        got = z[:, 0] + 1j * z[:, 1]
+        assert np.max(np.abs(got - want)) < 3e-7 * np.sqrt(W) * np.log2(W) * 4
+
+
+def test_double_oracle_agrees_with_float_oracle():
+    cfg = _abi.default_config(window_size=4096, window_type=_abi.WIN_HANN)
+    a = signals.batch(2, 4096)
+    of, od = OracleSpectrum(cfg, 2), OracleSpectrum(cfg, 2, double=True)
+    for o in (of, od):
+        o.prepare(a); o.transform(); o.map(); o.postprocess()
+    f = of.transform_result().reshape(2, 2, -1, 2)[..., 0]
+    d = od.transform_result().reshape(2, 2, -1, 2)[..., 0]
+    # channel 1 only: channel 2 is interpolated at `N - pos`, which the float32 build rounds to
+    # 2^-10 bins at N = 4096..8192 (TransformDSP.inl:912) and the double build does not; that
+    # reference quirk moves Lanczos weights by ~3e-4 and is replayed by model_f64 instead.
+    assert_linear_close(np.abs(f[:, 0]), np.abs(d[:, 0]), frame_axes=(1,), what="float vs double oracle")
+    bp = of.info.break_point
+    assert_linear_close(np.abs(f[:, 1, bp:]), np.abs(d[:, 1, bp:]), frame_axes=(1,), what="float vs double oracle, max-of-bins part")
