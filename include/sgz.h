@@ -70,6 +70,10 @@ enum {
 /* cpl::dsp::Windows::Shape */
 enum { SGZ_WINSHAPE_SYMMETRIC = 0, SGZ_WINSHAPE_PERIODIC = 1 };
 
+/* `device` value for sgz_spectrum_create that builds the host-side tables only (for inspecting the
+ * derived constants without a GPU).  Every compute entry point of such a handle returns SGZ_ECUDA. */
+#define SGZ_DEVICE_NONE (-1)
+
 /* where a caller-provided buffer lives */
 enum { SGZ_MEM_HOST = 0, SGZ_MEM_DEVICE = 1 };
 /* audio layouts: PLANAR is the reference's `float** buffer`, pair i =

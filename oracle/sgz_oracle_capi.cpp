@@ -168,8 +168,13 @@ namespace
 					if (bwForLine > fftBandwidth) break;
 					interp(x);
 				}
+				const bool neverBroke = x == P - 1;
 				if (x < P) oldBin = static_cast<ssz>(mf[x] * freqToBin);
 				for (; x < P; ++x) maxOf(x, oldBin);
+				// Phase + Linear/Lanczos: bandWidthBreakingPoint stays at axisPoints when the loop
+				// never breaks, so the magnitude pass (:709, :759) also interpolates the last point
+				// and the max-of-bins loop does not run (:808-813)
+				if (isPhase && neverBroke && constant.binPolation != BinInterpolation::None) interp(P - 1);
 			}
 			else
 			{

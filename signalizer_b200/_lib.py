@@ -1,0 +1,86 @@
+"""Loader for the CUDA shared library (signalizer_b200/libsgz_cuda.so).
+
+The product path has no CPU fallback: if the library is missing this raises, and every compute
+entry point returns SGZ_ECUDA (raised as SgzError) when no CUDA device is present."""
+import ctypes as C
+import os
+import subprocess
+
+from . import _abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsgz_cuda.so")
+_lib = None
+
+# every symbol include/sgz.h declares
+EXPORTS = [
+    "sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_create", "sgz_spectrum_destroy",
+    "sgz_spectrum_get_info", "sgz_spectrum_set_cuda_stream", "sgz_spectrum_synchronize",
+    "sgz_spectrum_get_window_kernel", "sgz_spectrum_get_mapped_frequencies", "sgz_spectrum_get_slope_map",
+    "sgz_spectrum_get_bin_map", "sgz_spectrum_prepare", "sgz_spectrum_prepare_preliminary",
+    "sgz_spectrum_transform", "sgz_spectrum_map", "sgz_spectrum_postprocess", "sgz_spectrum_get_raw_fft",
+    "sgz_spectrum_get_transform_result", "sgz_spectrum_get_results", "sgz_spectrum_get_states",
+    "sgz_spectrum_set_states", "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state",
+    "sgz_spectrum_process_frames",
+]
+
+
+class SgzError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"sgz error {code}: {msg}")
+        self.code = code
+
+
+def build(force: bool = False) -> str:
+    """Compile the library for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    csrc = os.path.join(_HERE, "csrc")
+    cmd = ["make", "-C", csrc, "-s"] + (["-B"] if force else [])
+    subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, u32, u64, i32, sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
+    fp, ip = C.c_void_p, C.POINTER(C.c_int32)  # float buffers are passed as raw addresses (host or device)
+    lib.sgz_last_error.restype = C.c_char_p
+    lib.sgz_spectrum_default_config.argtypes = [C.POINTER(_abi.SpectrumConfig)]
+    lib.sgz_spectrum_default_config.restype = None
+    lib.sgz_spectrum_create.argtypes = [C.POINTER(_abi.SpectrumConfig), u32, i32, C.POINTER(vp)]
+    lib.sgz_spectrum_destroy.argtypes = [vp]
+    lib.sgz_spectrum_destroy.restype = None
+    lib.sgz_spectrum_get_info.argtypes = [vp, C.POINTER(_abi.SpectrumInfo)]
+    lib.sgz_spectrum_set_cuda_stream.argtypes = [vp, vp]
+    lib.sgz_spectrum_synchronize.argtypes = [vp]
+    for n in ("sgz_spectrum_get_window_kernel", "sgz_spectrum_get_mapped_frequencies", "sgz_spectrum_get_slope_map"):
+        getattr(lib, n).argtypes = [vp, fp, sz]
+    lib.sgz_spectrum_get_bin_map.argtypes = [vp, ip, ip, ip, ip, sz]
+    lib.sgz_spectrum_prepare.argtypes = [vp, fp, i32, i32, u64, u64]
+    lib.sgz_spectrum_prepare_preliminary.argtypes = [vp, fp, u64, u64, fp, u64, u64, i32, i32]
+    for n in ("sgz_spectrum_transform", "sgz_spectrum_map", "sgz_spectrum_postprocess",
+              "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state"):
+        getattr(lib, n).argtypes = [vp]
+    lib.sgz_spectrum_get_raw_fft.argtypes = [vp, fp, i32]
+    lib.sgz_spectrum_get_transform_result.argtypes = [vp, fp, i32]
+    lib.sgz_spectrum_get_results.argtypes = [vp, i32, fp, i32]
+    lib.sgz_spectrum_get_states.argtypes = [vp, i32, fp, i32]
+    lib.sgz_spectrum_set_states.argtypes = [vp, i32, fp, i32]
+    lib.sgz_spectrum_process_frames.argtypes = [vp, fp, i32, i32, u64, u64, u32, u32, fp, i32]
+    for n in EXPORTS:
+        f = getattr(lib, n)  # raises AttributeError if the symbol is not exported
+        if n not in ("sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_destroy"):
+            f.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def check(rc: int, allow=(0,)):
+    if rc not in allow:
+        raise SgzError(rc, load().sgz_last_error().decode(errors="replace"))
+    return rc

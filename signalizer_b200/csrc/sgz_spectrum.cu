@@ -1,0 +1,1382 @@
+// sgz_spectrum.cu — sm_100a kernels and the C ABI (include/sgz.h) of the Spectrum transform path.
+//
+// Reference path (relative to the reference checkout):
+//   Source/Spectrum/TransformDSP.inl   prepareTransform :39-484, doTransform :487-502,
+//                                      mapToLinearSpace :506-1135, mapAndTransformDFTFilters :1299-1435
+//   Source/Spectrum/TransformConstant.h, TransformPair.h
+//
+// Two implementations of the same arithmetic live here:
+//   * the staged kernels (k_prepare, k_fft_*, k_map, k_post) mirror the reference's four calls one to
+//     one, for every SpectrumChannels x BinInterpolation combination and every power-of-two size,
+//     keeping the intermediate buffers (audioMemory / workingMemory of TransformPair.h:238-243) in HBM;
+//   * k_fused runs a whole frame (all four calls) per CTA without touching HBM in between, for the
+//     mono and Separate/MidSide configurations at N = 4096 / 8192, looping over the frames of one
+//     stream so the peak-hold state stays on chip.
+// There is no CPU fallback anywhere in this file.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/sgz.h"
+#include "sgz_device.cuh"
+#include "sgz_tables.hpp"
+
+namespace sgz
+{
+	// ------------------------------------------------------------------------------------------
+	// error plumbing
+	// ------------------------------------------------------------------------------------------
+	static thread_local std::string g_lastError;
+
+	static int fail(int code, const char* fmt, ...)
+	{
+		char buf[512];
+		va_list ap;
+		va_start(ap, fmt);
+		vsnprintf(buf, sizeof(buf), fmt, ap);
+		va_end(ap);
+		g_lastError = buf;
+		return code;
+	}
+
+#define SGZ_CUDA(expr)                                                                                      \
+	do {                                                                                                    \
+		cudaError_t e__ = (expr);                                                                           \
+		if (e__ != cudaSuccess)                                                                             \
+			return fail(SGZ_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+	} while (0)
+
+	// ------------------------------------------------------------------------------------------
+	// device-side view of the tables (all pointers are device memory owned by the handle)
+	// ------------------------------------------------------------------------------------------
+	struct DeviceTables
+	{
+		const float* window;     // [N]
+		const float* slope;      // [P]
+		const int4* binmap;      // [P] {mode, first, count, fallback}
+		const float* posL;       // [P]
+		const float* posR;       // [P]
+		const int* baseL;        // [P]
+		const int* baseR;        // [P]
+		const float* wL;         // [P][10]
+		const float* wR;         // [P][10]
+		const int* phaseNormPos; // [P]
+		const float2* twN;       // [N/2] W_N^k (generic FFT)
+		const float2* tw1;       // [16][T]  W_M^(u k1)          (fused FFT)
+		const float2* tw2;       // [16][R3] W_(16 R3)^(n3 k2)
+		const float2* tw3;       // [M]      W_N^k
+		int phaseNormFinal;
+		uint32_t N, W, P, M, linLimit;
+		uint32_t workStride; // float2 entries of workingMemory per stream
+		int conf, binpol;
+		float invSize, deltaYRecip, minFracRecip, lowerClip;
+		float pole0, pole1, phasePole0, phasePole1;
+	};
+
+	__device__ __forceinline__ bool isMonoConf(int conf) { return conf <= SGZ_CH_SIDE; }
+
+	// channel matrix of prepareTransform (TransformDSP.inl:59-217), multiplication order as written
+	__device__ __forceinline__ float2 channelMatrix(int conf, float l, float r, float w)
+	{
+		switch (conf)
+		{
+		case SGZ_CH_LEFT: return make_float2(l * w, 0.f);
+		case SGZ_CH_RIGHT: return make_float2(r * w, 0.f);
+		case SGZ_CH_MERGE: return make_float2((l + r) * w * 0.5f, 0.f);
+		case SGZ_CH_SIDE: return make_float2((l - r) * w * 0.5f, 0.f);
+		case SGZ_CH_MIDSIDE: return make_float2((l + r) * w * 0.5f, (l - r) * w * 0.5f);
+		default: return make_float2(l * w, r * w);
+		}
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// staged kernel 1: prepareTransform
+	// ------------------------------------------------------------------------------------------
+	struct PrepareArgs
+	{
+		const float* hist; uint64_t nHist; uint64_t histStride;     // history, per stream
+		const float* prelim; uint64_t nPrelim; uint64_t prelimStride; // preliminary audio (may be null)
+		int layout;
+		uint32_t histSkip;   // index of the first history sample used
+		uint32_t histCount;  // number of window taps filled from history
+		uint32_t prelimCount; // number of taps filled from preliminary audio ("stop")
+	};
+
+	__device__ __forceinline__ void fetchLR(const float* base, int layout, uint64_t n, uint64_t i, float& l, float& r)
+	{
+		if (layout == SGZ_LAYOUT_INTERLEAVED) { const float2 v = reinterpret_cast<const float2*>(base)[i]; l = v.x; r = v.y; }
+		else { l = base[i]; r = base[n + i]; }
+	}
+
+	__global__ void k_prepare(DeviceTables t, PrepareArgs a, float2* __restrict__ csf)
+	{
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		const uint32_t s = blockIdx.y;
+		if (i > t.N) return;
+		float2 out = make_float2(0.f, 0.f);
+		if (i < a.histCount)
+		{
+			float l, r;
+			fetchLR(a.hist + s * a.histStride, a.layout, a.nHist, uint64_t(a.histSkip) + i, l, r);
+			out = channelMatrix(t.conf, l, r, t.window[i]);
+		}
+		else if (i < a.histCount + a.prelimCount)
+		{
+			float l, r;
+			fetchLR(a.prelim + s * a.prelimStride, a.layout, a.nPrelim, uint64_t(i - a.histCount), l, r);
+			out = channelMatrix(t.conf, l, r, t.window[i]);
+		}
+		csf[uint64_t(s) * (t.N + 1) + i] = out; // zero-pad, including the extra element N
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// staged kernel 2: doTransform — generic power-of-two forward FFT, natural order, in place
+	// ------------------------------------------------------------------------------------------
+	// N <= 16384: one CTA per stream, radix-2 DIT in shared memory
+	__global__ void __launch_bounds__(256) k_fft_smem(DeviceTables t, float2* __restrict__ csf)
+	{
+		extern __shared__ float2 sm[];
+		const uint32_t N = t.N;
+		float2* x = csf + uint64_t(blockIdx.x) * (N + 1);
+		const int bits = 31 - __clz(N);
+		for (uint32_t i = threadIdx.x; i < N; i += blockDim.x)
+			sm[__brev(i) >> (32 - bits)] = x[i];
+		__syncthreads();
+		for (uint32_t half = 1; half < N; half <<= 1)
+		{
+			const uint32_t step = (N >> 1) / half; // twiddle stride: W_(2 half)^j = W_N^(j step)
+			for (uint32_t b = threadIdx.x; b < (N >> 1); b += blockDim.x)
+			{
+				const uint32_t j = b & (half - 1);
+				const uint32_t i0 = ((b - j) << 1) + j;
+				const float2 w = t.twN[j * step];
+				const float2 u = sm[i0];
+				const float2 v = cmul(sm[i0 + half], w);
+				sm[i0] = cadd(u, v);
+				sm[i0 + half] = csub(u, v);
+			}
+			__syncthreads();
+		}
+		for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) x[i] = sm[i];
+	}
+
+	// N > 16384: Stockham radix-2 passes through HBM (ping-pong with the work buffer)
+	__global__ void k_fft_global_pass(const float2* __restrict__ tw, const float2* __restrict__ src, float2* __restrict__ dst,
+		uint32_t N, uint32_t n, uint32_t s, uint64_t srcStride, uint64_t dstStride)
+	{
+		// one thread per butterfly: p in [0, n/2), q in [0, s): b = p * s + q
+		const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+		if (b >= (N >> 1)) return;
+		const float2* x = src + uint64_t(blockIdx.y) * srcStride;
+		float2* y = dst + uint64_t(blockIdx.y) * dstStride;
+		const uint32_t q = b % s, p = b / s;
+		const uint32_t n1 = n >> 1;
+		const float2 w = tw[p * s]; // W_n^p = W_N^(p s)
+		const float2 u = x[q + s * p], v = x[q + s * (p + n1)];
+		y[q + s * (2 * p)] = cadd(u, v);
+		y[q + s * (2 * p + 1)] = cmul(csub(u, v), w);
+	}
+
+	__global__ void k_copy_strided(const float2* __restrict__ src, float2* __restrict__ dst, uint32_t N, uint64_t srcStride, uint64_t dstStride)
+	{
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i < N) dst[uint64_t(blockIdx.y) * dstStride + i] = src[uint64_t(blockIdx.y) * srcStride + i];
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// staged kernel 3: mapToLinearSpace (FFT branch), one CTA per stream, csf modified in place like
+	// the reference does.
+	// ------------------------------------------------------------------------------------------
+	__device__ __forceinline__ float2 tapOr0(const float2* csf, int i, int N) { return (i >= 0 && i <= N) ? csf[i] : make_float2(0.f, 0.f); }
+
+	__device__ __forceinline__ float2 linearAt(const float2* csf, float pos, int N)
+	{
+		const float fl = floorf(pos);
+		const int i = int(fl);
+		const float frac = pos - fl;
+		const float2 a = tapOr0(csf, i, N), b = tapOr0(csf, i + 1, N);
+		return make_float2(a.x * (1.f - frac) + b.x * frac, a.y * (1.f - frac) + b.y * frac);
+	}
+
+	__device__ __forceinline__ float2 lanczosAt(const float2* csf, int base, const float* w, int N)
+	{
+		float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+		for (int k = 0; k < kLanczosTaps; ++k)
+		{
+			const float2 v = tapOr0(csf, base + k, N);
+			acc.x += v.x * w[k]; acc.y += v.y * w[k];
+		}
+		return acc;
+	}
+
+	// Phase configuration: value of csf[i] as the reference's magnitude pass sees it when `np` low
+	// indices (and their mirrors) have been replaced by their magnitude (TransformDSP.inl:715-720)
+	__device__ __forceinline__ float2 phaseView(const float2* csf, int i, int N, int np)
+	{
+		if (i < 0 || i > N) return make_float2(0.f, 0.f);
+		const float2 v = csf[i];
+		return (i < np || i > N - np) ? make_float2(cabs(v), 0.f) : v;
+	}
+
+	__global__ void __launch_bounds__(256) k_map(DeviceTables t, float2* __restrict__ csfAll, float2* __restrict__ workAll)
+	{
+		const int N = int(t.N), M = int(t.M), P = int(t.P);
+		float2* csf = csfAll + uint64_t(blockIdx.x) * (N + 1);
+		const int conf = t.conf;
+		const bool mono = isMonoConf(conf);
+		const bool phase = conf == SGZ_CH_PHASE;
+		const bool cplx = conf == SGZ_CH_COMPLEX;
+		const int chans = mono || cplx ? 1 : 2;
+		float2* work = workAll + uint64_t(blockIdx.x) * t.workStride;
+
+		// ---- phase A: in-place normalisation ----
+		if (mono)
+		{
+			// :553-560  csf[0] *= .5; csf[N/2] *= .5; csf[i] = |csf[i]| for i < numBins
+			for (int i = threadIdx.x; i < M; i += blockDim.x)
+			{
+				float2 v = csf[i];
+				if (i == 0) { v.x *= 0.5f; v.y *= 0.5f; }
+				csf[i] = make_float2(cabs(v), 0.f);
+			}
+			if (threadIdx.x == 0) { float2 v = csf[M]; csf[M] = make_float2(v.x * 0.5f, v.y * 0.5f); }
+		}
+		else if (cplx)
+		{
+			// :993-1002
+			for (int i = threadIdx.x; i < N; i += blockDim.x)
+			{
+				float2 v = csf[i];
+				if (i == 0) csf[0] = make_float2(v.x * 0.5f, v.y * 0.5f);
+				else csf[i] = make_float2(cabs(v), 0.f);
+			}
+		}
+		else
+		{
+			// two-for-one split (cpl::dsp::separateTransformsIPL) + :861-869 / :649-652
+			for (int k = threadIdx.x; k < M; k += blockDim.x)
+			{
+				if (k == 0)
+				{
+					const float2 z0 = csf[0], zm = csf[M];
+					csf[N] = make_float2(z0.y * 0.5f, 0.f);
+					csf[0] = make_float2(z0.x * 0.5f, 0.f);
+					const float2 h = make_float2(zm.x * 0.5f, zm.y * 0.5f);
+					csf[M] = phase ? h : make_float2(cabs(h), 0.f);
+					continue;
+				}
+				const float2 zk = csf[k], zn = csf[N - k];
+				float2 A = make_float2((zk.x + zn.x) * 0.5f, (zk.y - zn.y) * 0.5f);
+				const float2 D = make_float2((zk.x - zn.x) * 0.5f, (zk.y + zn.y) * 0.5f);
+				const float2 B = make_float2(D.y, -D.x);
+				if (k == M - 1) { A.x *= 0.5f; A.y *= 0.5f; }
+				if (phase) { csf[k] = A; csf[N - k] = B; }
+				else { csf[k] = make_float2(cabs(A), 0.f); csf[N - k] = make_float2(cabs(B), 0.f); }
+			}
+		}
+		__syncthreads();
+
+		// ---- phase B: display points ----
+		const float invSize = t.invSize;
+		for (int x = threadIdx.x; x < P; x += blockDim.x)
+		{
+			const int4 bm = t.binmap[x];
+			if (phase)
+			{
+				float mid, cancelOut;
+				if (bm.x == 0)
+				{
+					float2 iL, iR, mL, mR;
+					if (t.binpol == SGZ_BIN_NONE)
+					{
+						iL = csf[bm.y]; iR = csf[N - bm.y]; mL = iL; mR = iR;
+					}
+					else if (t.binpol == SGZ_BIN_LINEAR)
+					{
+						iL = linearAt(csf, t.posL[x], N); iR = linearAt(csf, t.posR[x], N);
+						const int np = t.phaseNormPos[x];
+						{
+							const float pos = t.posL[x]; const float fl = floorf(pos); const int i = int(fl); const float fr = pos - fl;
+							const float2 a = phaseView(csf, i, N, np), b = phaseView(csf, i + 1, N, np);
+							mL = make_float2(a.x * (1.f - fr) + b.x * fr, a.y * (1.f - fr) + b.y * fr);
+						}
+						{
+							const float pos = t.posR[x]; const float fl = floorf(pos); const int i = int(fl); const float fr = pos - fl;
+							const float2 a = phaseView(csf, i, N, np), b = phaseView(csf, i + 1, N, np);
+							mR = make_float2(a.x * (1.f - fr) + b.x * fr, a.y * (1.f - fr) + b.y * fr);
+						}
+					}
+					else
+					{
+						const float* wl = t.wL + x * kLanczosTaps; const float* wr = t.wR + x * kLanczosTaps;
+						iL = lanczosAt(csf, t.baseL[x], wl, N); iR = lanczosAt(csf, t.baseR[x], wr, N);
+						const int np = t.phaseNormPos[x];
+						mL = make_float2(0.f, 0.f); mR = make_float2(0.f, 0.f);
+#pragma unroll
+						for (int k = 0; k < kLanczosTaps; ++k)
+						{
+							const float2 a = phaseView(csf, t.baseL[x] + k, N, np), b = phaseView(csf, t.baseR[x] + k, N, np);
+							mL.x += a.x * wl[k]; mL.y += a.y * wl[k];
+							mR.x += b.x * wr[k]; mR.y += b.y * wr[k];
+						}
+					}
+					const float cancellation = invSize * cabs(cadd(iL, iR));
+					const float midRaw = invSize * (cabs(iL) + cabs(iR));
+					cancelOut = 1.f - (midRaw > 0.f ? cancellation / midRaw : 0.f);
+					mid = invSize * (cabs(mL) + cabs(mR));
+				}
+				else
+				{
+					const int np = t.phaseNormFinal;
+					int maxBin = 0; float maxValue = 0.f;
+					for (int c = 0; c < bm.z; ++c)
+					{
+						const int off = bm.y + c;
+						const float m = fmaxf(cnorm(phaseView(csf, off, N, np)), cnorm(phaseView(csf, N - off, N, np)));
+						if (m > maxValue) { maxValue = m; maxBin = off; }
+					}
+					const float2 l = phaseView(csf, maxBin, N, np), r = phaseView(csf, N - maxBin, N, np);
+					const float interference = invSize * cabs(cadd(l, r));
+					mid = invSize * (cabs(l) + cabs(r));
+					cancelOut = 1.f - (mid > 0.f ? interference / mid : 0.f);
+				}
+				work[x] = make_float2(mid, cancelOut); // wsp[2x], wsp[2x+1]
+				continue;
+			}
+
+			float2 vL, vR = make_float2(0.f, 0.f);
+			if (bm.x == 0)
+			{
+				if (t.binpol == SGZ_BIN_NONE) { vL = csf[bm.y]; if (chans == 2) vR = csf[N - bm.y]; }
+				else if (t.binpol == SGZ_BIN_LINEAR) { vL = linearAt(csf, t.posL[x], N); if (chans == 2) vR = linearAt(csf, t.posR[x], N); }
+				else
+				{
+					vL = lanczosAt(csf, t.baseL[x], t.wL + x * kLanczosTaps, N);
+					if (chans == 2) vR = lanczosAt(csf, t.baseR[x], t.wR + x * kLanczosTaps, N);
+				}
+			}
+			else
+			{
+				int maxL = bm.w, maxR = bm.w; float bestL = 0.f, bestR = 0.f;
+				for (int c = 0; c < bm.z; ++c)
+				{
+					const int off = bm.y + c;
+					const float mL = cnorm(csf[off]);
+					if (mL > bestL) { bestL = mL; maxL = off; }
+					if (chans == 2)
+					{
+						const float mR = cnorm(csf[N - off]);
+						if (mR > bestR) { bestR = mR; maxR = N - off; }
+					}
+				}
+				vL = csf[maxL];
+				if (chans == 2) vR = csf[maxR];
+			}
+			work[x] = make_float2(invSize * vL.x, invSize * vL.y);
+			if (chans == 2) work[P + x] = make_float2(invSize * vR.x, invSize * vR.y);
+		}
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// staged kernel 4: mapAndTransformDFTFilters (TransformDSP.inl:1299-1435)
+	// states / results: [stream][graph][P] float2
+	// ------------------------------------------------------------------------------------------
+	__device__ __forceinline__ float logScale(float slope, float st, float minFracRecip, float dy, float clip)
+	{
+		const float d = slope * st * minFracRecip;
+		return d > 0.f ? logf(d) * dy : clip;
+	}
+
+	__global__ void k_post(DeviceTables t, const float2* __restrict__ workAll, float2* __restrict__ states, float2* __restrict__ results)
+	{
+		const int x = blockIdx.x * blockDim.x + threadIdx.x;
+		const int s = blockIdx.y;
+		const int P = int(t.P);
+		if (x >= P) return;
+		const int conf = t.conf;
+		const bool mono = isMonoConf(conf);
+		const float2* work = workAll + uint64_t(s) * t.workStride;
+		const float slope = t.slope[x];
+		const float poles[2] = { t.pole0, t.pole1 };
+		const float phasePoles[2] = { t.phasePole0, t.phasePole1 };
+		if (mono || conf == SGZ_CH_COMPLEX)
+		{
+			const float2 v = work[x];
+			const float mag = sqrtf(v.x * v.x + v.y * v.y);
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+			{
+				float2* st = states + (uint64_t(s) * 2 + k) * P + x;
+				float2 sv = *st;
+				sv.x *= poles[k];
+				if (mag > sv.x) sv.x = mag;
+				*st = sv;
+				results[(uint64_t(s) * 2 + k) * P + x] = make_float2(logScale(slope, sv.x, t.minFracRecip, t.deltaYRecip, t.lowerClip), 0.f);
+			}
+		}
+		else if (conf == SGZ_CH_PHASE)
+		{
+			const float2 v = work[x];
+			const float mag = v.x * 0.5f;
+			float ph = v.y;
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+			{
+				float2* st = states + (uint64_t(s) * 2 + k) * P + x;
+				float2 sv = *st;
+				sv.x *= poles[k];
+				if (mag > sv.x) sv.x = mag;
+				ph *= mag; // inside the k loop, as the reference (:1417)
+				sv.y = ph + phasePoles[k] * (sv.y - ph);
+				*st = sv;
+				results[(uint64_t(s) * 2 + k) * P + x] = make_float2(
+					logScale(slope, sv.x, t.minFracRecip, t.deltaYRecip, t.lowerClip),
+					logScale(slope, sv.y, t.minFracRecip, t.deltaYRecip, t.lowerClip));
+			}
+		}
+		else
+		{
+			const float2 l = work[x], r = work[P + x];
+			const float lmag = sqrtf(l.x * l.x + l.y * l.y), rmag = sqrtf(r.x * r.x + r.y * r.y);
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+			{
+				float2* st = states + (uint64_t(s) * 2 + k) * P + x;
+				float2 sv = *st;
+				sv.x *= poles[k]; sv.y *= poles[k];
+				if (lmag > sv.x) sv.x = lmag;
+				if (rmag > sv.y) sv.y = rmag;
+				*st = sv;
+				results[(uint64_t(s) * 2 + k) * P + x] = make_float2(
+					logScale(slope, sv.x, t.minFracRecip, t.deltaYRecip, t.lowerClip),
+					logScale(slope, sv.y, t.minFracRecip, t.deltaYRecip, t.lowerClip));
+			}
+		}
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// fused kernel: prepare -> FFT -> map -> post for every frame of one stream, one CTA per stream.
+	//
+	// FFT plan for N = 2 M, M = 16 * 16 * R3 (R3 = 16: N = 8192, R3 = 8: N = 4096), T = 16 R3 threads:
+	// the complex input x[n] = (L w, R w)[n] is split into even and odd samples; thread u carries one
+	// element of each (E, O) through three register-resident radix-16/16/R3 passes of two M-point
+	// FFTs that share every twiddle; the exchanges between passes go through shared memory as float4
+	// (E.re, E.im, O.re, O.im) with an XOR swizzle that keeps all three access patterns conflict free
+	// and lets pass 2 run in place.  The last radix-2 (Z[k] = E[k] + W^k O[k], Z[k+M] = E[k] - W^k O[k])
+	// is fused with the two-for-one split, which needs Z[k] and Z[N-k] = E[M-k] - W^(M-k) O[M-k].
+	// (index algebra checked by tools/fft_plan_prototype.py)
+	// ------------------------------------------------------------------------------------------
+	struct FusedArgs
+	{
+		const float* audio; uint64_t nSamples; uint64_t streamStride; int layout;
+		uint32_t hop, nFrames;
+		float2* states;  // [S][2][P]
+		float2* results; // [S][F][2][P]
+	};
+
+	template<int R3> struct FusedGeom
+	{
+		static constexpr int T = 16 * R3;
+		static constexpr int M = 16 * T;
+		static constexpr int N = 2 * M;
+		static constexpr int G = 16 / R3;
+		static constexpr size_t xbufBytes = size_t(M) * 16;          // float4[M]; csfmag[N+1] aliases its upper half (+4 B)
+		static constexpr size_t stateOffset = xbufBytes + 16;
+		static size_t smemBytes(uint32_t P) { return stateOffset + size_t(P) * 16; }
+	};
+
+	template<int R3>
+	__device__ __forceinline__ int physAddr(int k1, int j, int n3)
+	{
+		return k1 * (16 * R3) + j * R3 + (n3 ^ (k1 & 7));
+	}
+
+	template<int R3, bool STEREO, int BINPOL>
+	__global__ void __launch_bounds__(16 * R3, (R3 == 16 ? 2 : 4))
+	k_fused(DeviceTables t, FusedArgs a)
+	{
+		typedef FusedGeom<R3> Gm;
+		constexpr int T = Gm::T, M = Gm::M, N = Gm::N;
+		extern __shared__ __align__(16) unsigned char smemRaw[];
+		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
+		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
+		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
+		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
+
+		const int u = threadIdx.x;
+		const int stream = blockIdx.x;
+		const int P = int(t.P);
+		const int W = int(t.W);
+		const int conf = t.conf;
+		const int linLimit = int(t.linLimit);
+
+		// peak-hold state of this stream lives in shared memory for the whole frame loop
+		for (int i = u; i < 2 * P; i += T) st[i] = a.states[uint64_t(stream) * 2 * P + i];
+
+		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
+		const bool interleaved = a.layout == SGZ_LAYOUT_INTERLEAVED;
+		const bool vec4 = interleaved && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0);
+
+		for (uint32_t f = 0; f < a.nFrames; ++f)
+		{
+			const uint64_t start = uint64_t(f) * a.hop;
+			float2 ve[16], vo[16];
+
+			// ---- pass 1: load (window + channel matrix), DFT16 over n1, twiddle W_M^(u k1) ----
+#pragma unroll
+			for (int n1 = 0; n1 < 16; ++n1)
+			{
+				const int p = n1 * T + u;       // sample-pair index: samples 2p, 2p+1
+				const int n = 2 * p;
+				float l0 = 0.f, r0 = 0.f, l1 = 0.f, r1 = 0.f;
+				if (n + 1 < W)
+				{
+					if (vec4)
+					{
+						const float4 v = ldg_stream_f4(reinterpret_cast<const float4*>(sbase + 2 * start) + p);
+						l0 = v.x; r0 = v.y; l1 = v.z; r1 = v.w;
+					}
+					else
+					{
+						fetchLR(sbase, a.layout, a.nSamples, start + n, l0, r0);
+						fetchLR(sbase, a.layout, a.nSamples, start + n + 1, l1, r1);
+					}
+				}
+				else if (n < W)
+					fetchLR(sbase, a.layout, a.nSamples, start + n, l0, r0);
+				const float2 w = reinterpret_cast<const float2*>(t.window)[p];
+				ve[n1] = channelMatrix(conf, l0, r0, w.x);
+				vo[n1] = channelMatrix(conf, l1, r1, w.y);
+			}
+			dft16(ve); dft16(vo);
+#pragma unroll
+			for (int k1 = 0; k1 < 16; ++k1)
+			{
+				float2 e = ve[perm16(k1)], o = vo[perm16(k1)];
+				if (k1 > 0)
+				{
+					const float2 w = __ldg(t.tw1 + k1 * T + u);
+					e = cmul(e, w); o = cmul(o, w);
+				}
+				xbuf[k1 * T + (u ^ (k1 & 7))] = make_float4(e.x, e.y, o.x, o.y); // physAddr(k1, n2, n3), u = n2 R3 + n3
+			}
+			__syncthreads();
+
+			// ---- pass 2 (in place): DFT16 over n2, twiddle W_(16 R3)^(n3 k2) ----
+			{
+				const int k1 = u / R3, n3 = u % R3;
+#pragma unroll
+				for (int n2 = 0; n2 < 16; ++n2)
+				{
+					const float4 v = xbuf[physAddr<R3>(k1, n2, n3)];
+					ve[n2] = make_float2(v.x, v.y); vo[n2] = make_float2(v.z, v.w);
+				}
+				dft16(ve); dft16(vo);
+#pragma unroll
+				for (int k2 = 0; k2 < 16; ++k2)
+				{
+					float2 e = ve[perm16(k2)], o = vo[perm16(k2)];
+					if (k2 > 0)
+					{
+						const float2 w = __ldg(t.tw2 + k2 * R3 + n3);
+						e = cmul(e, w); o = cmul(o, w);
+					}
+					xbuf[physAddr<R3>(k1, k2, n3)] = make_float4(e.x, e.y, o.x, o.y);
+				}
+			}
+			__syncthreads();
+
+			// ---- pass 3: DFT_R3 over n3; thread owns bins k = u + T g + 256 k3 ----
+#pragma unroll
+			for (int g = 0; g < Gm::G; ++g)
+			{
+				const int q = u + T * g;
+				const int k1 = q & 15, k2 = q >> 4;
+#pragma unroll
+				for (int n3 = 0; n3 < R3; ++n3)
+				{
+					const float4 v = xbuf[physAddr<R3>(k1, k2, n3)];
+					ve[g * R3 + n3] = make_float2(v.x, v.y); vo[g * R3 + n3] = make_float2(v.z, v.w);
+				}
+			}
+			if constexpr (R3 == 16) { dft16(ve); dft16(vo); }
+			else { dft8<0>(ve); dft8<8>(ve); dft8<0>(vo); dft8<8>(vo); }
+
+			// ---- last radix-2: Zp[k] = E + W_N^k O (= Z[k]), Zm[k] = E - W_N^k O (= Z[k + M]) ----
+			// ve[] <- Zp, vo[] <- Zm, indexed by slot = g R3 + perm(k3)
+#pragma unroll
+			for (int g = 0; g < Gm::G; ++g)
+			{
+#pragma unroll
+				for (int k3 = 0; k3 < R3; ++k3)
+				{
+					const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
+					const int k = u + T * g + 256 * k3;
+					const float2 wo = cmul(vo[slot], __ldg(t.tw3 + k));
+					const float2 e = ve[slot];
+					ve[slot] = cadd(e, wo); vo[slot] = csub(e, wo);
+				}
+			}
+			__syncthreads(); // every pass-3 read of xbuf is done before zm / csfmag overwrite it
+
+			if constexpr (STEREO)
+			{
+#pragma unroll
+				for (int g = 0; g < Gm::G; ++g)
+#pragma unroll
+					for (int k3 = 0; k3 < R3; ++k3)
+					{
+						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
+						zm[u + T * g + 256 * k3] = vo[slot];
+					}
+				__syncthreads();
+				// two-for-one split + |.| (or |.|^2 beyond linLimit) into the reference's csf layout:
+				// channel 1 bin j at csfmag[j], channel 2 bin j at csfmag[N - j]
+#pragma unroll
+				for (int g = 0; g < Gm::G; ++g)
+#pragma unroll
+					for (int k3 = 0; k3 < R3; ++k3)
+					{
+						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
+						const int j = u + T * g + 256 * k3;
+						const float2 zj = ve[slot];
+						if (j == 0)
+						{
+							// :861-864: csf[N] = Im Z[0] / 2, csf[0] = Re Z[0] / 2, csf[N/2] *= .5 (packed Nyquists)
+							const float2 ny = vo[slot]; // Z[M] = Zm[0]
+							const float h = 0.5f * cabs(ny);
+							csfmag[0] = linLimit > 0 ? zj.x * 0.5f : (zj.x * 0.5f) * (zj.x * 0.5f);
+							csfmag[N] = linLimit > 0 ? zj.y * 0.5f : (zj.y * 0.5f) * (zj.y * 0.5f);
+							csfmag[M] = (M < linLimit) ? h : h * h;
+							continue;
+						}
+						const float2 zn = zm[M - j]; // Z[N - j]
+						float ax = (zj.x + zn.x) * 0.5f, ay = (zj.y - zn.y) * 0.5f;
+						const float dx = (zj.x - zn.x) * 0.5f, dy = (zj.y + zn.y) * 0.5f;
+						if (j == M - 1) { ax *= 0.5f; ay *= 0.5f; } // csf[(N >> 1) - 1] *= 0.5, channel 1 only
+						float a2 = ax * ax + ay * ay, b2 = dx * dx + dy * dy;
+						if (j < linLimit) { a2 = sqrtf(a2); b2 = sqrtf(b2); }
+						csfmag[j] = a2;
+						csfmag[N - j] = b2;
+					}
+			}
+			else
+			{
+				// mono: csf[i] = |Z[i]| for i < M (csf[0] halved), csf[M] = Z[M] / 2 (kept as |.|)
+#pragma unroll
+				for (int g = 0; g < Gm::G; ++g)
+#pragma unroll
+					for (int k3 = 0; k3 < R3; ++k3)
+					{
+						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
+						const int j = u + T * g + 256 * k3;
+						float2 zj = ve[slot];
+						if (j == 0)
+						{
+							zj.x *= 0.5f; zj.y *= 0.5f;
+							const float2 ny = vo[slot];
+							const float h2 = 0.25f * cnorm(ny);
+							csfmag[M] = (M < linLimit) ? sqrtf(h2) : h2;
+						}
+						const float m2 = cnorm(zj);
+						csfmag[j] = (j < linLimit) ? sqrtf(m2) : m2;
+					}
+			}
+			__syncthreads();
+
+			// ---- display-point mapping + log scale + peak hold ----
+			float2* resOut = a.results + ((uint64_t(stream) * a.nFrames + f) * 2) * P;
+			for (int x = u; x < P; x += T)
+			{
+				const int4 bm = t.binmap[x];
+				float vL, vR = 0.f;
+				if (bm.x == 0)
+				{
+					if constexpr (BINPOL == SGZ_BIN_NONE)
+					{
+						vL = csfmag[bm.y];
+						if constexpr (STEREO) vR = csfmag[N - bm.y];
+					}
+					else if constexpr (BINPOL == SGZ_BIN_LINEAR)
+					{
+						{
+							const float pos = t.posL[x]; const float fl = floorf(pos); const int i = int(fl); const float fr = pos - fl;
+							const float va = (i >= 0 && i <= N) ? csfmag[i] : 0.f, vb = (i + 1 >= 0 && i + 1 <= N) ? csfmag[i + 1] : 0.f;
+							vL = va * (1.f - fr) + vb * fr;
+						}
+						if constexpr (STEREO)
+						{
+							const float pos = t.posR[x]; const float fl = floorf(pos); const int i = int(fl); const float fr = pos - fl;
+							const float va = (i >= 0 && i <= N) ? csfmag[i] : 0.f, vb = (i + 1 >= 0 && i + 1 <= N) ? csfmag[i + 1] : 0.f;
+							vR = va * (1.f - fr) + vb * fr;
+						}
+					}
+					else
+					{
+						const int bl = t.baseL[x];
+						const float* wl = t.wL + x * kLanczosTaps;
+						vL = 0.f;
+#pragma unroll
+						for (int k = 0; k < kLanczosTaps; ++k)
+						{
+							const int i = bl + k;
+							if (i >= 0 && i <= N) vL += csfmag[i] * wl[k];
+						}
+						if constexpr (STEREO)
+						{
+							const int br = t.baseR[x];
+							const float* wr = t.wR + x * kLanczosTaps;
+#pragma unroll
+							for (int k = 0; k < kLanczosTaps; ++k)
+							{
+								const int i = br + k;
+								if (i >= 0 && i <= N) vR += csfmag[i] * wr[k];
+							}
+						}
+					}
+				}
+				else
+				{
+					// max-of-bins (:944-984): entries beyond linLimit are already squared
+					int maxL = bm.w, maxR = bm.w; float bestL = 0.f, bestR = 0.f;
+					for (int c = 0; c < bm.z; ++c)
+					{
+						const int off = bm.y + c;
+						const float v = csfmag[off];
+						const float mL = (off < linLimit) ? v * v : v;
+						if (mL > bestL) { bestL = mL; maxL = off; }
+						if constexpr (STEREO)
+						{
+							const float vr = csfmag[N - off];
+							const float mR = (off < linLimit) ? vr * vr : vr;
+							if (mR > bestR) { bestR = mR; maxR = N - off; }
+						}
+					}
+					{
+						const float v = csfmag[maxL];
+						vL = (maxL < linLimit || maxL > N - linLimit) ? v : sqrtf(v);
+					}
+					if constexpr (STEREO)
+					{
+						const float v = csfmag[maxR];
+						vR = (maxR < linLimit || maxR > N - linLimit) ? v : sqrtf(v);
+					}
+				}
+				const float lmag = fabsf(t.invSize * vL);
+				const float rmag = fabsf(t.invSize * vR);
+				const float slope = t.slope[x];
+				const float poles[2] = { t.pole0, t.pole1 };
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+				{
+					float2 sv = st[k * P + x];
+					sv.x *= poles[k];
+					if (lmag > sv.x) sv.x = lmag;
+					float2 res;
+					res.x = logScale(slope, sv.x, t.minFracRecip, t.deltaYRecip, t.lowerClip);
+					if constexpr (STEREO)
+					{
+						sv.y *= poles[k];
+						if (rmag > sv.y) sv.y = rmag;
+						res.y = logScale(slope, sv.y, t.minFracRecip, t.deltaYRecip, t.lowerClip);
+					}
+					else res.y = 0.f;
+					st[k * P + x] = sv;
+					stg_stream_f2(resOut + k * P + x, res);
+				}
+			}
+			__syncthreads(); // csfmag / zm are overwritten by the next frame's pass 1
+		}
+
+		for (int i = u; i < 2 * P; i += T) a.states[uint64_t(stream) * 2 * P + i] = st[i];
+	}
+} // namespace sgz
+
+// ----------------------------------------------------------------------------------------------
+// handle
+// ----------------------------------------------------------------------------------------------
+using namespace sgz;
+
+struct sgz_spectrum
+{
+	sgz_spectrum_config cfg{};
+	Tables tab;
+	DeviceTables dev{};
+	uint32_t nStreams{ 0 };
+	int device{ 0 };
+	cudaStream_t stream{ nullptr };
+	bool ownStream{ false };
+	std::vector<void*> allocations;
+	// per-stream buffers
+	float2* dCsf{ nullptr };     // [S][N+1]  audioMemory
+	float2* dWork{ nullptr };    // [S][max(N, 2P)] workingMemory (FFT scratch / transform result)
+	float2* dStates{ nullptr };  // [S][2][P]
+	float2* dResults{ nullptr }; // [S][2][P]
+	// staging for host-resident callers
+	float* dAudioStage{ nullptr }; size_t audioStageBytes{ 0 };
+	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
+	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
+	int fusedR3{ 0 };
+	size_t fusedSmem{ 0 };
+};
+
+namespace
+{
+	struct DeviceGuard
+	{
+		int prev{ -1 };
+		bool ok{ true };
+		explicit DeviceGuard(int dev)
+		{
+			if (dev < 0) { ok = false; return; }
+			if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+			if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+		}
+		~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+	};
+
+	template<typename T>
+	int upload(sgz_spectrum* h, const std::vector<T>& src, const T** dst)
+	{
+		void* p = nullptr;
+		const size_t bytes = std::max<size_t>(src.size(), 1) * sizeof(T);
+		SGZ_CUDA(cudaMalloc(&p, bytes));
+		h->allocations.push_back(p);
+		if (!src.empty()) SGZ_CUDA(cudaMemcpy(p, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+		*dst = static_cast<const T*>(p);
+		return SGZ_OK;
+	}
+
+	template<typename T>
+	int allocZero(sgz_spectrum* h, size_t count, T** dst)
+	{
+		void* p = nullptr;
+		SGZ_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+		h->allocations.push_back(p);
+		SGZ_CUDA(cudaMemset(p, 0, std::max<size_t>(count, 1) * sizeof(T)));
+		*dst = static_cast<T*>(p);
+		return SGZ_OK;
+	}
+
+	std::vector<float2> twiddleTable(size_t count, double denom, const std::vector<uint64_t>& exponents)
+	{
+		std::vector<float2> out(count);
+		const double twoPi = 6.283185307179586476925286766559;
+		for (size_t i = 0; i < count; ++i)
+		{
+			const double a = -twoPi * double(exponents[i] % uint64_t(denom)) / denom;
+			out[i] = make_float2(float(std::cos(a)), float(std::sin(a)));
+		}
+		return out;
+	}
+
+	int ensureStage(sgz_spectrum* h, float** buf, size_t* have, size_t need)
+	{
+		if (*have >= need) return SGZ_OK;
+		if (*buf) { cudaFree(*buf); *buf = nullptr; *have = 0; }
+		SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(buf), need));
+		*have = need;
+		return SGZ_OK;
+	}
+
+	template<int R3, bool STEREO>
+	int launchFusedBinpol(sgz_spectrum* h, const FusedArgs& a)
+	{
+		const size_t smem = FusedGeom<R3>::smemBytes(h->tab.P);
+		const dim3 grid(h->nStreams), block(16 * R3);
+#define SGZ_LAUNCH(BP)                                                                                              \
+		{                                                                                                           \
+			auto kern = k_fused<R3, STEREO, BP>;                                                                    \
+			SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));           \
+			kern<<<grid, block, smem, h->stream>>>(h->dev, a);                                                      \
+		}
+		switch (h->cfg.bin_polation)
+		{
+		case SGZ_BIN_NONE: SGZ_LAUNCH(SGZ_BIN_NONE); break;
+		case SGZ_BIN_LINEAR: SGZ_LAUNCH(SGZ_BIN_LINEAR); break;
+		default: SGZ_LAUNCH(SGZ_BIN_LANCZOS); break;
+		}
+#undef SGZ_LAUNCH
+		SGZ_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
+	int launchFused(sgz_spectrum* h, const FusedArgs& a)
+	{
+		const bool stereo = h->tab.stateChannels == 2;
+		if (h->fusedR3 == 16) return stereo ? launchFusedBinpol<16, true>(h, a) : launchFusedBinpol<16, false>(h, a);
+		if (h->fusedR3 == 8) return stereo ? launchFusedBinpol<8, true>(h, a) : launchFusedBinpol<8, false>(h, a);
+		return fail(SGZ_EUNSUPPORTED, "no fused kernel for this configuration");
+	}
+
+	size_t audioFloatsPerStream(uint64_t nSamples) { return size_t(nSamples) * 2; }
+
+	// copies caller audio to the device if needed; returns the device pointer to use
+	int stageAudio(sgz_spectrum* h, const float* audio, int mem, uint64_t nSamples, uint64_t streamStride, const float** dptr, float** slot, size_t* slotBytes)
+	{
+		if (mem == SGZ_MEM_DEVICE) { *dptr = audio; return SGZ_OK; }
+		const size_t floats = size_t(streamStride) * (h->nStreams - 1) + audioFloatsPerStream(nSamples);
+		const int rc = ensureStage(h, slot, slotBytes, floats * sizeof(float));
+		if (rc != SGZ_OK) return rc;
+		SGZ_CUDA(cudaMemcpyAsync(*slot, audio, floats * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+		*dptr = *slot;
+		return SGZ_OK;
+	}
+
+	int copyOut(sgz_spectrum* h, void* dst, const void* src, size_t bytes, int mem)
+	{
+		SGZ_CUDA(cudaMemcpyAsync(dst, src, bytes, mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+}
+
+#define SGZ_GUARD(h)                                                                                        \
+	DeviceGuard g__((h)->device);                                                                           \
+	if (!g__.ok) return fail(SGZ_ECUDA, (h)->device < 0 ? "tables-only handle (SGZ_DEVICE_NONE): no compute, and there is no CPU fallback" : "cudaSetDevice failed")
+
+// ----------------------------------------------------------------------------------------------
+// C ABI
+// ----------------------------------------------------------------------------------------------
+extern "C"
+{
+	const char* sgz_last_error(void) { return g_lastError.c_str(); }
+
+	void sgz_spectrum_default_config(sgz_spectrum_config* cfg)
+	{
+		if (!cfg) return;
+		std::memset(cfg, 0, sizeof(*cfg));
+		cfg->abi_version = SGZ_ABI_VERSION;
+		cfg->sample_rate = 48000.f;
+		cfg->window_size = 8192;
+		cfg->axis_points = 1024;
+		cfg->algo = SGZ_ALGO_FFT;
+		cfg->configuration = SGZ_CH_SEPARATE;
+		cfg->bin_polation = SGZ_BIN_LANCZOS;
+		cfg->display_mode = SGZ_DISPLAY_LINEGRAPH;
+		cfg->view_scaling = SGZ_VIEW_LOGARITHMIC;
+		cfg->view_left = 0.0; cfg->view_right = 1.0;
+		cfg->min_freq = 10.0;
+		cfg->slope_a = 0.0; cfg->slope_b = 1.0;
+		cfg->low_dbs = -120.0; cfg->high_dbs = 0.0; cfg->clip_db = -384.0;
+		cfg->pole[0] = 0.95f; cfg->pole[1] = 0.99f;
+		cfg->window_type = SGZ_WIN_BLACKMAN_HARRIS;
+		cfg->window_shape = SGZ_WINSHAPE_PERIODIC;
+		cfg->sample_buffer_size = 200;
+		cfg->free_q = 0;
+	}
+
+	void sgz_spectrum_destroy(sgz_spectrum* h)
+	{
+		if (!h) return;
+		if (h->device != SGZ_DEVICE_NONE)
+		{
+			DeviceGuard g(h->device);
+			if (h->stream) cudaStreamSynchronize(h->stream);
+			for (void* p : h->allocations) cudaFree(p);
+			if (h->dAudioStage) cudaFree(h->dAudioStage);
+			if (h->dResultStage) cudaFree(h->dResultStage);
+			if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
+		}
+		delete h;
+	}
+
+	int sgz_spectrum_create(const sgz_spectrum_config* cfg, uint32_t n_streams, int device, sgz_spectrum** out)
+	{
+		if (!cfg || !out || n_streams == 0) return fail(SGZ_EINVAL, "null argument or zero streams");
+		*out = nullptr;
+		if (device == SGZ_DEVICE_NONE)
+		{
+			// tables-only handle: the derived constants can be inspected, nothing can be computed
+			sgz_spectrum* h = new (std::nothrow) sgz_spectrum();
+			if (!h) return fail(SGZ_ENOMEM, "out of host memory");
+			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
+			const int rc = buildTables(*cfg, h->tab);
+			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
+			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 4096) ? (h->tab.N == 8192 ? 16 : 8) : 0;
+			*out = h;
+			return SGZ_OK;
+		}
+		int count = 0;
+		if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return fail(SGZ_ECUDA, "no CUDA device (this library has no CPU fallback)");
+		if (device < 0 || device >= count) return fail(SGZ_EINVAL, "device %d out of range (%d devices)", device, count);
+
+		sgz_spectrum* h = new (std::nothrow) sgz_spectrum();
+		if (!h) return fail(SGZ_ENOMEM, "out of host memory");
+		h->cfg = *cfg; h->nStreams = n_streams; h->device = device;
+		int rc = buildTables(*cfg, h->tab);
+		if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
+
+		DeviceGuard guard(device);
+		if (!guard.ok) { delete h; return fail(SGZ_ECUDA, "cudaSetDevice(%d) failed", device); }
+		auto bail = [&](int code) { sgz_spectrum_destroy(h); return code; };
+		if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(fail(SGZ_ECUDA, "cudaStreamCreate failed"));
+		h->ownStream = true;
+
+		const Tables& t = h->tab;
+		DeviceTables& d = h->dev;
+		d.N = t.N; d.W = t.W; d.P = t.P; d.M = t.numBins; d.linLimit = t.linLimit;
+		d.conf = cfg->configuration; d.binpol = cfg->bin_polation;
+		d.invSize = t.invSize; d.deltaYRecip = t.deltaYRecip; d.minFracRecip = t.minFracRecip; d.lowerClip = t.lowerClip;
+		d.pole0 = t.pole[0]; d.pole1 = t.pole[1]; d.phasePole0 = t.phasePole[0]; d.phasePole1 = t.phasePole[1];
+		d.phaseNormFinal = t.phaseNormFinal;
+		d.workStride = uint32_t(std::max<size_t>(t.N, size_t(2) * t.P));
+
+		std::vector<int4> binmap(t.P);
+		for (uint32_t x = 0; x < t.P; ++x) binmap[x] = make_int4(t.mode[x], t.first[x], t.count[x], t.fallback[x]);
+#define SGZ_TRY(expr) do { rc = (expr); if (rc != SGZ_OK) return bail(rc); } while (0)
+		SGZ_TRY(upload(h, t.window, &d.window));
+		SGZ_TRY(upload(h, t.slope, &d.slope));
+		SGZ_TRY(upload(h, binmap, &d.binmap));
+		SGZ_TRY(upload(h, t.posL, &d.posL));
+		SGZ_TRY(upload(h, t.posR, &d.posR));
+		SGZ_TRY(upload(h, t.baseL, &d.baseL));
+		SGZ_TRY(upload(h, t.baseR, &d.baseR));
+		SGZ_TRY(upload(h, t.wL, &d.wL));
+		SGZ_TRY(upload(h, t.wR, &d.wR));
+		SGZ_TRY(upload(h, t.phaseNormPos, &d.phaseNormPos));
+		{
+			std::vector<uint64_t> e(t.N / 2);
+			for (size_t k = 0; k < e.size(); ++k) e[k] = k;
+			SGZ_TRY(upload(h, twiddleTable(e.size(), double(t.N), e), &d.twN));
+		}
+		h->fusedR3 = 0;
+		if (t.fusedOk && t.P <= 4096)
+		{
+			const int R3 = t.N == 8192 ? 16 : 8;
+			const int T = 16 * R3, M = 16 * T;
+			std::vector<uint64_t> e1(size_t(16) * T), e2(size_t(16) * R3), e3(M);
+			for (int k1 = 0; k1 < 16; ++k1) for (int u = 0; u < T; ++u) e1[size_t(k1) * T + u] = uint64_t(u) * k1;
+			for (int k2 = 0; k2 < 16; ++k2) for (int n3 = 0; n3 < R3; ++n3) e2[size_t(k2) * R3 + n3] = uint64_t(n3) * k2;
+			for (int k = 0; k < M; ++k) e3[k] = k;
+			SGZ_TRY(upload(h, twiddleTable(e1.size(), double(M), e1), &d.tw1));
+			SGZ_TRY(upload(h, twiddleTable(e2.size(), double(16 * R3), e2), &d.tw2));
+			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(2 * M), e3), &d.tw3));
+			h->fusedR3 = R3;
+			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
+		}
+		const size_t workPerStream = std::max<size_t>(t.N, size_t(2) * t.P);
+		SGZ_TRY(allocZero(h, size_t(n_streams) * (t.N + 1), &h->dCsf));
+		SGZ_TRY(allocZero(h, size_t(n_streams) * workPerStream, &h->dWork));
+		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dStates));
+		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dResults));
+#undef SGZ_TRY
+		*out = h;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_get_info(const sgz_spectrum* h, sgz_spectrum_info* out)
+	{
+		if (!h || !out) return fail(SGZ_EINVAL, "null argument");
+		std::memset(out, 0, sizeof(*out));
+		out->transform_size = h->tab.N; out->window_size = h->tab.W; out->axis_points = h->tab.P;
+		out->n_streams = h->nStreams; out->state_channels = h->tab.stateChannels;
+		out->break_point = h->tab.P;
+		for (uint32_t x = 0; x < h->tab.P; ++x) if (h->tab.mode[x] == 1) { out->break_point = x; break; }
+		out->window_kernel_scale = h->tab.windowKernelScale; out->inv_size = h->tab.invSize; out->freq_to_bin = h->tab.freqToBin;
+		out->resonator_vectors = h->tab.resonatorVectors; out->device = h->device; out->fused_available = h->fusedR3 != 0;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_set_cuda_stream(sgz_spectrum* h, void* cuda_stream)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		SGZ_GUARD(h);
+		if (h->stream) cudaStreamSynchronize(h->stream);
+		if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
+		h->stream = static_cast<cudaStream_t>(cuda_stream);
+		h->ownStream = false;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_synchronize(sgz_spectrum* h)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		SGZ_GUARD(h);
+		SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_get_window_kernel(const sgz_spectrum* h, float* out, size_t n)
+	{
+		if (!h || !out || n != h->tab.N) return fail(SGZ_EINVAL, "window kernel has %u entries", h ? h->tab.N : 0);
+		std::memcpy(out, h->tab.window.data(), n * sizeof(float));
+		return SGZ_OK;
+	}
+	int sgz_spectrum_get_mapped_frequencies(const sgz_spectrum* h, float* out, size_t n)
+	{
+		if (!h || !out || n != h->tab.P) return fail(SGZ_EINVAL, "mapped frequencies have %u entries", h ? h->tab.P : 0);
+		std::memcpy(out, h->tab.mappedFreq.data(), n * sizeof(float));
+		return SGZ_OK;
+	}
+	int sgz_spectrum_get_slope_map(const sgz_spectrum* h, float* out, size_t n)
+	{
+		if (!h || !out || n != h->tab.P) return fail(SGZ_EINVAL, "slope map has %u entries", h ? h->tab.P : 0);
+		std::memcpy(out, h->tab.slope.data(), n * sizeof(float));
+		return SGZ_OK;
+	}
+	int sgz_spectrum_get_bin_map(const sgz_spectrum* h, int32_t* mode, int32_t* first, int32_t* count, int32_t* fallback, size_t n)
+	{
+		if (!h || !mode || !first || !count || !fallback || n != h->tab.P) return fail(SGZ_EINVAL, "bin map has %u entries", h ? h->tab.P : 0);
+		std::memcpy(mode, h->tab.mode.data(), n * sizeof(int32_t));
+		std::memcpy(first, h->tab.first.data(), n * sizeof(int32_t));
+		std::memcpy(count, h->tab.count.data(), n * sizeof(int32_t));
+		std::memcpy(fallback, h->tab.fallback.data(), n * sizeof(int32_t));
+		return SGZ_OK;
+	}
+
+	static int prepareCommon(sgz_spectrum* h, const float* hist, uint64_t nHist, uint64_t histStride, const float* prelim, uint64_t nPrelim,
+		uint64_t prelimStride, int mem, int layout, bool withPrelim)
+	{
+		if (!h || !hist) return fail(SGZ_EINVAL, "null argument");
+		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "prepareTransform is the FFT algorithm's entry (TransformDSP.inl:51-53)");
+		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
+		const uint32_t W = h->tab.W;
+		if (nHist < W) { h->stage = 0; return SGZ_SKIPPED; } // TransformDSP.inl:45-46
+		if (histStride < 2 * nHist && h->nStreams > 1) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		SGZ_GUARD(h);
+		PrepareArgs a{};
+		a.layout = layout;
+		int rc = stageAudio(h, hist, mem, nHist, histStride, &a.hist, &h->dAudioStage, &h->audioStageBytes);
+		if (rc != SGZ_OK) return rc;
+		a.nHist = nHist; a.histStride = histStride;
+		if (!withPrelim)
+		{
+			a.histSkip = uint32_t(nHist - W); a.histCount = W; a.prelimCount = 0;
+		}
+		else
+		{
+			// TransformDSP.inl:245-257: stop = min(numSamples, W); offset = stop + extraDiscarded;
+			// sizeToStopAt = W - offset.  Left/Right skip `offset` history samples; every other
+			// configuration advances only an unused iterator and so starts at history sample 0.
+			if (!prelim) return fail(SGZ_EINVAL, "null preliminary audio");
+			const uint64_t extra = nHist - W;
+			const uint64_t stop = std::min<uint64_t>(nPrelim, W);
+			const uint64_t offset = stop + extra;
+			if (offset > W) return fail(SGZ_EUNSUPPORTED, "history larger than the window together with preliminary audio overruns the reference's buffer (TransformDSP.inl:256-257)");
+			const bool lr = h->cfg.configuration == SGZ_CH_LEFT || h->cfg.configuration == SGZ_CH_RIGHT;
+			a.histSkip = lr ? uint32_t(offset) : 0u;
+			a.histCount = uint32_t(W - offset);
+			a.prelimCount = uint32_t(stop);
+			if (mem == SGZ_MEM_DEVICE) a.prelim = prelim;
+			else
+			{
+				const size_t floats = size_t(prelimStride) * (h->nStreams - 1) + audioFloatsPerStream(nPrelim);
+				rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, floats * sizeof(float));
+				if (rc != SGZ_OK) return rc;
+				SGZ_CUDA(cudaMemcpyAsync(h->dResultStage, prelim, floats * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+				a.prelim = h->dResultStage;
+			}
+			a.nPrelim = nPrelim; a.prelimStride = prelimStride;
+		}
+		const dim3 block(256), grid((h->tab.N + 1 + 255) / 256, h->nStreams);
+		k_prepare<<<grid, block, 0, h->stream>>>(h->dev, a, h->dCsf);
+		SGZ_CUDA(cudaGetLastError());
+		h->stage = 1;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_prepare(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride)
+	{
+		return prepareCommon(h, audio, n_samples, stream_stride, nullptr, 0, 0, mem, layout, false);
+	}
+
+	int sgz_spectrum_prepare_preliminary(sgz_spectrum* h, const float* history, uint64_t n_history, uint64_t history_stride, const float* prelim,
+		uint64_t n_prelim, uint64_t prelim_stride, int mem, int layout)
+	{
+		return prepareCommon(h, history, n_history, history_stride, prelim, n_prelim, prelim_stride, mem, layout, true);
+	}
+
+	int sgz_spectrum_transform(sgz_spectrum* h)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (h->cfg.algo != SGZ_ALGO_FFT) return SGZ_OK; // doTransform is a no-op for RSNT (:489-501)
+		if (h->stage < 1) return fail(SGZ_ESTATE, "call prepareTransform() first (TransformPair.h:123-124)");
+		SGZ_GUARD(h);
+		const uint32_t N = h->tab.N;
+		if (N <= 16384)
+		{
+			const size_t smem = size_t(N) * sizeof(float2);
+			SGZ_CUDA(cudaFuncSetAttribute(k_fft_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+			k_fft_smem<<<h->nStreams, 256, smem, h->stream>>>(h->dev, h->dCsf);
+		}
+		else
+		{
+			const uint64_t csfStride = N + 1, workStride = std::max<size_t>(N, size_t(2) * h->tab.P);
+			const float2* src = h->dCsf; float2* dst = h->dWork;
+			uint64_t sStride = csfStride, dStride = workStride;
+			const dim3 block(256), grid((N / 2 + 255) / 256, h->nStreams);
+			for (uint32_t n = N, s = 1; n > 1; n >>= 1, s <<= 1)
+			{
+				k_fft_global_pass<<<grid, block, 0, h->stream>>>(h->dev.twN, src, dst, N, n, s, sStride, dStride);
+				const float2* nsrc = dst; dst = const_cast<float2*>(src); src = nsrc;
+				std::swap(sStride, dStride);
+			}
+			if (src != h->dCsf)
+			{
+				const dim3 g2((N + 255) / 256, h->nStreams);
+				k_copy_strided<<<g2, block, 0, h->stream>>>(src, h->dCsf, N, sStride, csfStride);
+			}
+		}
+		SGZ_CUDA(cudaGetLastError());
+		h->stage = 2;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_map(sgz_spectrum* h)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "resonator snapshot: use sgz_resonator_* (not built yet)");
+		if (h->stage < 2) return fail(SGZ_ESTATE, "call doTransform() first (TransformPair.h:123-124)");
+		if (h->tab.N < 3 || h->tab.sampleRate < 1) return SGZ_OK; // :519-520
+		SGZ_GUARD(h);
+		k_map<<<h->nStreams, 256, 0, h->stream>>>(h->dev, h->dCsf, h->dWork);
+		SGZ_CUDA(cudaGetLastError());
+		h->stage = 3;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_postprocess(sgz_spectrum* h)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (h->stage < 3) return fail(SGZ_ESTATE, "call mapToLinearSpace() first");
+		SGZ_GUARD(h);
+		const dim3 block(128), grid((h->tab.P + 127) / 128, h->nStreams);
+		k_post<<<grid, block, 0, h->stream>>>(h->dev, h->dWork, h->dStates, h->dResults);
+		SGZ_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_get_raw_fft(sgz_spectrum* h, float* out, int mem)
+	{
+		if (!h || !out) return fail(SGZ_EINVAL, "null argument");
+		SGZ_GUARD(h);
+		const uint32_t N = h->tab.N;
+		SGZ_CUDA(cudaMemcpy2DAsync(out, size_t(N) * sizeof(float2), h->dCsf, size_t(N + 1) * sizeof(float2), size_t(N) * sizeof(float2), h->nStreams,
+			mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_get_transform_result(sgz_spectrum* h, float* out, int mem)
+	{
+		if (!h || !out) return fail(SGZ_EINVAL, "null argument");
+		SGZ_GUARD(h);
+		const size_t want = size_t(h->tab.P) * h->tab.stateChannels;     // getTransformResult size / 2
+		const size_t workStride = std::max<size_t>(h->tab.N, size_t(2) * h->tab.P);
+		SGZ_CUDA(cudaMemcpy2DAsync(out, want * sizeof(float2), h->dWork, workStride * sizeof(float2), want * sizeof(float2), h->nStreams,
+			mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+
+	static int graphCopy(sgz_spectrum* h, int graph, float* out, const float* in, float2* base, int mem)
+	{
+		if (!h || (!out && !in)) return fail(SGZ_EINVAL, "null argument");
+		if (graph < 0 || graph >= SGZ_LINE_END) return fail(SGZ_EINVAL, "graph %d out of range", graph);
+		SGZ_GUARD(h);
+		const size_t P = h->tab.P;
+		const auto kind = out ? (mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost)
+		                      : (mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
+		if (out)
+			SGZ_CUDA(cudaMemcpy2DAsync(out, P * sizeof(float2), base + size_t(graph) * P, 2 * P * sizeof(float2), P * sizeof(float2), h->nStreams, kind, h->stream));
+		else
+			SGZ_CUDA(cudaMemcpy2DAsync(base + size_t(graph) * P, 2 * P * sizeof(float2), in, P * sizeof(float2), P * sizeof(float2), h->nStreams, kind, h->stream));
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_get_results(sgz_spectrum* h, int graph, float* out, int mem) { return graphCopy(h, graph, out, nullptr, h ? h->dResults : nullptr, mem); }
+	int sgz_spectrum_get_states(sgz_spectrum* h, int graph, float* out, int mem) { return graphCopy(h, graph, out, nullptr, h ? h->dStates : nullptr, mem); }
+	int sgz_spectrum_set_states(sgz_spectrum* h, int graph, const float* in, int mem) { return graphCopy(h, graph, nullptr, in, h ? h->dStates : nullptr, mem); }
+
+	int sgz_spectrum_clear_line_graph_states(sgz_spectrum* h)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		SGZ_GUARD(h);
+		const size_t bytes = size_t(h->nStreams) * 2 * h->tab.P * sizeof(float2);
+		SGZ_CUDA(cudaMemsetAsync(h->dStates, 0, bytes, h->stream));
+		SGZ_CUDA(cudaMemsetAsync(h->dResults, 0, bytes, h->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_clear_audio_state(sgz_spectrum* h)
+	{
+		int rc = sgz_spectrum_clear_line_graph_states(h);
+		if (rc != SGZ_OK) return rc;
+		SGZ_GUARD(h);
+		const size_t workStride = std::max<size_t>(h->tab.N, size_t(2) * h->tab.P);
+		SGZ_CUDA(cudaMemsetAsync(h->dCsf, 0, size_t(h->nStreams) * (h->tab.N + 1) * sizeof(float2), h->stream));
+		SGZ_CUDA(cudaMemsetAsync(h->dWork, 0, size_t(h->nStreams) * workStride * sizeof(float2), h->stream));
+		h->stage = 0;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
+		uint32_t n_frames, float* results, int results_mem)
+	{
+		if (!h || !audio || !results) return fail(SGZ_EINVAL, "null argument");
+		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "process_frames is the FFT path");
+		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
+		if (n_frames == 0) return SGZ_OK;
+		const uint32_t W = h->tab.W, P = h->tab.P;
+		if (n_samples < uint64_t(n_frames - 1) * hop + W) return fail(SGZ_EINVAL, "n_samples %llu < (n_frames-1)*hop + window_size", (unsigned long long)n_samples);
+		if (h->nStreams > 1 && stream_stride < 2 * n_samples) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		SGZ_GUARD(h);
+		const float* dAudio = nullptr;
+		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);
+		if (rc != SGZ_OK) return rc;
+		const size_t resFloats = size_t(h->nStreams) * n_frames * 2 * P * 2;
+		float* dRes = results;
+		if (results_mem == SGZ_MEM_HOST)
+		{
+			rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, resFloats * sizeof(float));
+			if (rc != SGZ_OK) return rc;
+			dRes = h->dResultStage;
+		}
+		if (h->fusedR3 != 0)
+		{
+			FusedArgs a{};
+			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
+			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(dRes);
+			rc = launchFused(h, a);
+			if (rc != SGZ_OK) return rc;
+			// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
+			SGZ_CUDA(cudaMemcpy2DAsync(h->dResults, size_t(2) * P * sizeof(float2), dRes + size_t(n_frames - 1) * 2 * P * 2,
+				size_t(n_frames) * 2 * P * sizeof(float2), size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+		}
+		else
+		{
+			// staged fallback ON THE GPU (every configuration / size): four kernels per frame
+			for (uint32_t f = 0; f < n_frames; ++f)
+			{
+				PrepareArgs a{};
+				a.layout = layout; a.hist = dAudio; a.nHist = n_samples; a.histStride = stream_stride;
+				a.histSkip = uint32_t(uint64_t(f) * hop); a.histCount = W; a.prelimCount = 0;
+				if (uint64_t(f) * hop > 0xFFFFFFFFull) return fail(SGZ_EUNSUPPORTED, "frame offset exceeds 32 bits");
+				const dim3 block(256), grid((h->tab.N + 1 + 255) / 256, h->nStreams);
+				k_prepare<<<grid, block, 0, h->stream>>>(h->dev, a, h->dCsf);
+				h->stage = 1;
+				if ((rc = sgz_spectrum_transform(h)) != SGZ_OK) return rc;
+				if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return rc;
+				if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return rc;
+				SGZ_CUDA(cudaMemcpy2DAsync(dRes + size_t(f) * 2 * P * 2, size_t(n_frames) * 2 * P * sizeof(float2), h->dResults, size_t(2) * P * sizeof(float2),
+					size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+			}
+		}
+		SGZ_CUDA(cudaGetLastError());
+		if (results_mem == SGZ_MEM_HOST)
+		{
+			SGZ_CUDA(cudaMemcpyAsync(results, dRes, resFloats * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+			SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		}
+		return SGZ_OK;
+	}
+}

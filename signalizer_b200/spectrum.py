@@ -1,0 +1,180 @@
+"""Host-side mirror of the reference's per-stream Spectrum interface, batched over streams.
+
+`TransformPairBatch` exposes the members of `Signalizer::TransformPair<float>`
+(Source/Spectrum/TransformPair.h:99-184) with the same names, call order
+(prepare_transform -> do_transform -> map_to_linear_space -> post_process_std_transform,
+TransformPair.h:123-124) and error behaviour (prepare_transform returns False to skip a frame,
+TransformDSP.inl:45-46), over `n_streams` stereo pairs that share one `TransformConstant`
+(SpectrumDSP.cpp:83-102).  All arithmetic runs in libsgz_cuda.so on the GPU; buffers may be numpy
+arrays (host, copied inside the call) or torch CUDA tensors (used in place)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from ._lib import check, load
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _buf(x, dtype=np.float32, writable=False):
+    """-> (keepalive, address, mem)"""
+    if _is_torch(x):
+        import torch
+        assert x.dtype == torch.float32 and x.is_contiguous(), "float32 contiguous tensor required"
+        return x, x.data_ptr(), (_abi.MEM_DEVICE if x.is_cuda else _abi.MEM_HOST)
+    a = np.ascontiguousarray(x, dtype=dtype)
+    if writable:
+        assert a is x or np.shares_memory(a, x), "output array must be contiguous float32"
+    return a, a.ctypes.data, _abi.MEM_HOST
+
+
+class TransformConstant:
+    """The read-only per-view constants (Source/Spectrum/TransformConstant.h:47-241), derived on
+    the host by the library exactly when the reference's handleFlagUpdates would
+    (Spectrum.cpp:351-616)."""
+
+    def __init__(self, cfg: _abi.SpectrumConfig):
+        self.cfg = _abi.copy_config(cfg)
+
+
+class TransformPairBatch:
+    def __init__(self, constant, n_streams: int = 1, device: int = 0):
+        cfg = constant.cfg if isinstance(constant, TransformConstant) else constant
+        self.lib = load()
+        self.cfg = _abi.copy_config(cfg)
+        self.n_streams = int(n_streams)
+        self._h = C.c_void_p()
+        check(self.lib.sgz_spectrum_create(C.byref(self.cfg), self.n_streams, int(device), C.byref(self._h)))
+        self.info = _abi.SpectrumInfo()
+        check(self.lib.sgz_spectrum_get_info(self._h, C.byref(self.info)))
+        self.N = self.info.transform_size
+        self.P = self.info.axis_points
+        self.W = self.info.window_size
+        self.channels = self.info.state_channels
+        self.device = device  # -1 (SGZ_DEVICE_NONE) = tables-only handle, cannot compute
+
+    # -- lifetime -------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self.lib.sgz_spectrum_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_cuda_stream(self, stream_ptr: int):
+        check(self.lib.sgz_spectrum_set_cuda_stream(self._h, C.c_void_p(stream_ptr)))
+
+    def synchronize(self):
+        check(self.lib.sgz_spectrum_synchronize(self._h))
+
+    # -- tables ---------------------------------------------------------------------------
+    def _table(self, fn, n):
+        out = np.empty(n, dtype=np.float32)
+        check(fn(self._h, out.ctypes.data, n))
+        return out
+
+    def window_kernel(self):
+        return self._table(self.lib.sgz_spectrum_get_window_kernel, self.N)
+
+    def mapped_frequencies(self):
+        return self._table(self.lib.sgz_spectrum_get_mapped_frequencies, self.P)
+
+    def slope_map(self):
+        return self._table(self.lib.sgz_spectrum_get_slope_map, self.P)
+
+    def bin_map(self):
+        arrs = [np.empty(self.P, dtype=np.int32) for _ in range(4)]
+        check(self.lib.sgz_spectrum_get_bin_map(self._h, *[a.ctypes.data_as(C.POINTER(C.c_int32)) for a in arrs], self.P))
+        return arrs
+
+    # -- staged pipeline ------------------------------------------------------------------
+    @staticmethod
+    def _geometry(audio, layout):
+        shape = tuple(audio.shape)
+        assert len(shape) == 3, "audio must be [streams, samples, 2] (interleaved) or [streams, 2, samples] (planar)"
+        n = shape[1] if layout == _abi.LAYOUT_INTERLEAVED else shape[2]
+        return shape[0], n, shape[1] * shape[2]
+
+    def prepare_transform(self, audio, layout=_abi.LAYOUT_INTERLEAVED, preliminary=None) -> bool:
+        """bool prepareTransform(const Constant&, const AudioPair&[, preliminaryAudio, numSamples])
+        (TransformDSP.inl:39-231, :234-484).  False = skip this frame."""
+        keep, ptr, mem = _buf(audio)
+        s, n, stride = self._geometry(keep, layout)
+        assert s == self.n_streams
+        if preliminary is None:
+            rc = self.lib.sgz_spectrum_prepare(self._h, ptr, mem, layout, n, stride)
+        else:
+            keep2, ptr2, mem2 = _buf(preliminary)
+            assert mem2 == mem, "history and preliminary audio must live in the same memory space"
+            s2, n2, stride2 = self._geometry(keep2, layout)
+            assert s2 == self.n_streams
+            rc = self.lib.sgz_spectrum_prepare_preliminary(self._h, ptr, n, stride, ptr2, n2, stride2, mem, layout)
+        check(rc, allow=(_abi.OK, _abi.SKIPPED))
+        return rc == _abi.OK
+
+    def do_transform(self):
+        check(self.lib.sgz_spectrum_transform(self._h))
+
+    def map_to_linear_space(self):
+        check(self.lib.sgz_spectrum_map(self._h))
+
+    def post_process_std_transform(self):
+        check(self.lib.sgz_spectrum_postprocess(self._h))
+
+    def get_raw_fft(self):
+        out = np.empty((self.n_streams, self.N, 2), dtype=np.float32)
+        check(self.lib.sgz_spectrum_get_raw_fft(self._h, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
+    def get_transform_result(self):
+        out = np.empty((self.n_streams, self.P * self.channels * 2), dtype=np.float32)
+        check(self.lib.sgz_spectrum_get_transform_result(self._h, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
+    def get_results(self, graph=_abi.LINE_MAIN):
+        out = np.empty((self.n_streams, self.P, 2), dtype=np.float32)
+        check(self.lib.sgz_spectrum_get_results(self._h, graph, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
+    def get_states(self, graph=_abi.LINE_MAIN):
+        out = np.empty((self.n_streams, self.P, 2), dtype=np.float32)
+        check(self.lib.sgz_spectrum_get_states(self._h, graph, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
+    def set_states(self, graph, states):
+        keep, ptr, mem = _buf(states)
+        assert tuple(keep.shape) == (self.n_streams, self.P, 2)
+        check(self.lib.sgz_spectrum_set_states(self._h, graph, ptr, mem))
+
+    def clear_line_graph_states(self):
+        check(self.lib.sgz_spectrum_clear_line_graph_states(self._h))
+
+    def clear_audio_state(self):
+        check(self.lib.sgz_spectrum_clear_audio_state(self._h))
+
+    # -- fused batched path ---------------------------------------------------------------
+    def process_frames(self, audio, hop: int, n_frames: int, layout=_abi.LAYOUT_INTERLEAVED, out=None):
+        """For every stream, `n_frames` frames at `hop`: the loop body of
+        SpectrumRendering.cpp:622-634 / addAudioFrame (TransformDSP.inl:1139-1148).
+        Returns results [streams, frames, 2 graphs, P, 2]."""
+        keep, ptr, mem = _buf(audio)
+        s, n, stride = self._geometry(keep, layout)
+        assert s == self.n_streams
+        shape = (self.n_streams, n_frames, 2, self.P, 2)
+        if out is None:
+            if mem == _abi.MEM_DEVICE:
+                import torch
+                out = torch.empty(shape, dtype=torch.float32, device=keep.device)
+            else:
+                out = np.empty(shape, dtype=np.float32)
+        okeep, optr, omem = _buf(out, writable=True)
+        assert tuple(okeep.shape) == shape
+        check(self.lib.sgz_spectrum_process_frames(self._h, ptr, mem, layout, n, stride, hop, n_frames, optr, omem))
+        return out

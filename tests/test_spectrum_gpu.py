@@ -1,0 +1,269 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on seeded inputs.
+Run on the B200 box: python -m pytest tests -m gpu"""
+import numpy as np
+import pytest
+
+from oracle.binding import OracleSpectrum
+from signalizer_b200 import _abi, _lib, signals
+from signalizer_b200.spectrum import TransformPairBatch
+from tolerances import FLOOR, REL, assert_linear_close, assert_log_close
+
+pytestmark = pytest.mark.gpu
+
+ALL_CONFS = list(range(8))
+INTERPS = [_abi.BIN_NONE, _abi.BIN_LINEAR, _abi.BIN_LANCZOS]
+
+
+def complex_close(got, want, what, rel=REL, floor=FLOOR):
+    """[..., 2] (re, im) arrays; distance in the complex plane, per-stream peak."""
+    g = got[..., 0].astype(np.float64) + 1j * got[..., 1].astype(np.float64)
+    w = want[..., 0].astype(np.float64) + 1j * want[..., 1].astype(np.float64)
+    peak = np.abs(w).reshape(w.shape[0], -1).max(axis=1).reshape((-1,) + (1,) * (w.ndim - 1))
+    bound = rel * np.abs(w) + floor * peak
+    err = np.abs(g - w)
+    bad = err > bound
+    if np.any(bad):
+        i = np.unravel_index(np.argmax(err - bound), err.shape)
+        raise AssertionError(f"{what}: {bad.sum()} of {bad.size} outside tolerance; worst at {i}: got {g[i]} want {w[i]} err {err[i]:.3e} bound {bound[i]:.3e}")
+
+
+def run_staged(obj, audio, oracle=False):
+    if oracle:
+        assert obj.prepare(audio) == _abi.OK
+        obj.transform(); raw = obj.raw_fft().copy(); obj.map(); tr = obj.transform_result().copy(); obj.postprocess()
+        return raw, tr, [obj.results(0), obj.results(1)], [obj.states(0), obj.states(1)]
+    assert obj.prepare_transform(audio)
+    obj.do_transform(); raw = obj.get_raw_fft(); obj.map_to_linear_space(); tr = obj.get_transform_result(); obj.post_process_std_transform()
+    return raw, tr, [obj.get_results(0), obj.get_results(1)], [obj.get_states(0), obj.get_states(1)]
+
+
+SIZES = [(4096, _abi.WIN_HANN, 1024), (8192, _abi.WIN_BLACKMAN_HARRIS, 1024), (700, _abi.WIN_BLACKMAN, 300),
+         (20, _abi.WIN_HANN, 40), (20000, _abi.WIN_NUTTALL, 512)]
+
+
+@pytest.mark.parametrize("size", SIZES)
+@pytest.mark.parametrize("conf", ALL_CONFS)
+@pytest.mark.parametrize("bp", INTERPS)
+def test_staged_pipeline_matches_oracle(size, conf, bp):
+    W, wt, P = size
+    cfg = _abi.default_config(window_size=W, window_type=wt, axis_points=P, configuration=conf, bin_polation=bp)
+    S = 3
+    audio = signals.batch(S, W + 11)
+    o = OracleSpectrum(cfg, S)
+    g = TransformPairBatch(cfg, S)
+    phase = conf == _abi.CH_PHASE
+    for rep in range(2):  # second pass exercises the peak-hold carry
+        raw_o, tr_o, res_o, st_o = run_staged(o, audio if rep == 0 else audio * np.float32(0.25), oracle=True)
+        raw_g, tr_g, res_g, st_g = run_staged(g, audio if rep == 0 else audio * np.float32(0.25))
+        # raw FFT: error relative to the spectrum's largest bin (float32 FFT error model)
+        complex_close(raw_g, raw_o, f"raw FFT rep {rep}", rel=2e-6, floor=2e-6)
+        ch = o.channels
+        tg = tr_g.reshape(S, ch, P, 2); to = tr_o.reshape(S, ch, P, 2)
+        if not phase:
+            used = 1 if conf in (_abi.CH_LEFT, _abi.CH_RIGHT, _abi.CH_MERGE, _abi.CH_SIDE, _abi.CH_COMPLEX) else 2
+            complex_close(tg[:, :used], to[:, :used], f"transform result rep {rep}")
+            lin = np.hypot(to[:, :used, :, 0], to[:, :used, :, 1])
+        else:
+            # wsp[2x] = magnitude sum, wsp[2x+1] = 1 - cancellation ratio
+            mag_g, mag_o = tg.reshape(S, 2 * P, 2)[:, :P, 0], to.reshape(S, 2 * P, 2)[:, :P, 0]
+            assert_linear_close(mag_g, mag_o, frame_axes=(1,), what="phase magnitudes")
+            can_g, can_o = tg.reshape(S, 2 * P, 2)[:, :P, 1], to.reshape(S, 2 * P, 2)[:, :P, 1]
+            strong = mag_o > 1e-3 * mag_o.max(axis=1, keepdims=True)
+            strong[:, -1] = False  # never-broke edge: the reference leaves the last cancellation stale
+            assert np.all(np.abs(can_g[strong] - can_o[strong]) < 2e-3)
+            lin = None
+        for k in range(2):
+            if not phase:
+                assert_linear_close(st_g[k][..., :used], st_o[k][..., :used], frame_axes=(1, 2), what=f"states {k} rep {rep}")
+                st_lin = st_o[k][..., :used].astype(np.float64)
+                mask = st_lin > 0
+                peak = st_lin.max()
+                assert_log_close(res_g[k][..., :used][mask], res_o[k][..., :used][mask], lin=st_lin[mask], peak=peak, what=f"results {k} rep {rep}")
+                zero = ~mask
+                assert np.all(res_g[k][..., :used][zero] == res_o[k][..., :used][zero])
+            else:
+                assert_linear_close(st_g[k][..., 0], st_o[k][..., 0], frame_axes=(1,), what=f"phase states {k}")
+
+
+def frames_case(cfg, S, F, hop, layout=_abi.LAYOUT_INTERLEAVED, first_stream=0, scale=1.0):
+    n = signals.frames_length(cfg.window_size, hop, F)
+    audio = signals.batch(S, n, first_stream=first_stream) * np.float32(scale)
+    if layout == _abi.LAYOUT_PLANAR:
+        audio = np.ascontiguousarray(audio.transpose(0, 2, 1))
+    return audio
+
+
+def compare_frames(got, want, cfg, what):
+    """results [S, F, 2, P, 2] on the display scale: recover the linear peak-held state
+    v = low * exp(y / dy) from the oracle to scale the tolerance per (stream, frame)."""
+    dy = 1.0 / np.log(10.0 ** (cfg.high_dbs / 20.0) / 10.0 ** (cfg.low_dbs / 20.0))
+    low = 10.0 ** (cfg.low_dbs / 20.0)
+    want64 = want.astype(np.float64)
+    clipped = want == np.float32(cfg.clip_db)
+    lin = np.where(clipped, 0.0, low * np.exp(np.where(clipped, 0.0, want64) / dy))
+    S, F = want.shape[:2]
+    for s in range(S):
+        for f in range(F):
+            w = want[s, f]; g = got[s, f]; l = lin[s, f]
+            m = ~clipped[s, f]
+            assert np.all(g[~m] == w[~m]) or np.all(l[~m] == 0), f"{what}: clip mismatch stream {s} frame {f}"
+            if m.any():
+                assert_log_close(g[m], w[m], lin=l[m], peak=l.max(), dy=dy, what=f"{what} stream {s} frame {f}")
+
+
+FUSED_SIZES = [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (6000, _abi.WIN_HAMMING), (3000, _abi.WIN_BLACKMAN)]
+
+
+@pytest.mark.parametrize("size", FUSED_SIZES)
+@pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_RIGHT, _abi.CH_MERGE, _abi.CH_SIDE, _abi.CH_SEPARATE, _abi.CH_MIDSIDE])
+@pytest.mark.parametrize("bp", INTERPS)
+def test_fused_frames_match_oracle(size, conf, bp):
+    cfg = _abi.default_config(window_size=size[0], window_type=size[1], configuration=conf, bin_polation=bp)
+    S, F, hop = 5, 6, size[0] // 4
+    g = TransformPairBatch(cfg, S)
+    assert g.info.fused_available == 1
+    audio = frames_case(cfg, S, F, hop)
+    o = OracleSpectrum(cfg, S)
+    want = o.process_frames(audio, hop, F)
+    got = g.process_frames(audio, hop, F)
+    used = 2 if conf in (_abi.CH_SEPARATE, _abi.CH_MIDSIDE) else 1
+    compare_frames(got[..., :used], want[..., :used], cfg, "fused")
+    if used == 1:
+        assert np.all(got[..., 1] == 0)  # results[i].phase = 0 (TransformDSP.inl:1347)
+    # states carried out of the call and the handle's last results
+    for k in range(2):
+        assert_linear_close(g.get_states(k)[..., :used], o.states(k)[..., :used], frame_axes=(1, 2), what=f"final states {k}")
+        np.testing.assert_array_equal(g.get_results(k), got[:, -1, k])
+
+
+@pytest.mark.parametrize("layout", [_abi.LAYOUT_INTERLEAVED, _abi.LAYOUT_PLANAR])
+@pytest.mark.parametrize("hop", [2048, 1023, 1])
+def test_fused_layouts_and_unaligned_hops(layout, hop):
+    cfg = _abi.default_config()
+    S, F = 3, 4
+    audio = frames_case(cfg, S, F, hop, layout=layout)
+    got = TransformPairBatch(cfg, S).process_frames(audio, hop, F, layout=layout)
+    want = OracleSpectrum(cfg, S).process_frames(audio, hop, F, layout=layout)
+    compare_frames(got, want, cfg, f"layout {layout} hop {hop}")
+
+
+def test_fused_equals_staged_and_call_splitting_is_exact():
+    """process_frames(F) == F x the four staged calls (same device arithmetic up to FFT
+    algorithm), and splitting one call into two is bit-exact (state carried across calls)."""
+    cfg = _abi.default_config()
+    S, F, hop = 4, 5, 2048
+    audio = frames_case(cfg, S, F, hop)
+    a = TransformPairBatch(cfg, S)
+    whole = a.process_frames(audio, hop, F)
+    b = TransformPairBatch(cfg, S)
+    part1 = b.process_frames(audio[:, :cfg.window_size + 2 * hop], hop, 3)
+    part2 = b.process_frames(audio[:, 3 * hop:], hop, 2)
+    np.testing.assert_array_equal(np.concatenate([part1, part2], axis=1), whole)
+    c = TransformPairBatch(cfg, S)
+    staged = np.empty_like(whole)
+    for f in range(F):
+        assert c.prepare_transform(audio[:, f * hop: f * hop + cfg.window_size])
+        c.do_transform(); c.map_to_linear_space(); c.post_process_std_transform()
+        staged[:, f, 0] = c.get_results(0); staged[:, f, 1] = c.get_results(1)
+    compare_frames(whole, staged, cfg, "fused vs staged")
+
+
+def test_device_resident_buffers_and_stream():
+    import torch
+    cfg = _abi.default_config()
+    S, F, hop = 8, 3, 2048
+    audio = frames_case(cfg, S, F, hop)
+    host = TransformPairBatch(cfg, S).process_frames(audio, hop, F)
+    g = TransformPairBatch(cfg, S)
+    g.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+    d_audio = torch.from_numpy(audio).cuda()
+    d_out = g.process_frames(d_audio, hop, F)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(d_out.cpu().numpy(), host)
+
+
+def test_staged_fallback_for_unfused_configs_in_process_frames():
+    for conf in (_abi.CH_PHASE, _abi.CH_COMPLEX):
+        cfg = _abi.default_config(window_size=2048, configuration=conf, axis_points=256)
+        S, F, hop = 2, 3, 512
+        g = TransformPairBatch(cfg, S)
+        assert g.info.fused_available == 0
+        audio = frames_case(cfg, S, F, hop)
+        got = g.process_frames(audio, hop, F)
+        want = OracleSpectrum(cfg, S).process_frames(audio, hop, F)
+        compare_frames(got[..., :1], want[..., :1], cfg, f"staged frames conf {conf}")
+
+
+def test_preliminary_audio_overload():
+    # TransformDSP.inl:234-484 incl. its iterator quirk
+    for conf in (_abi.CH_LEFT, _abi.CH_RIGHT, _abi.CH_MERGE, _abi.CH_SEPARATE, _abi.CH_MIDSIDE):
+        cfg = _abi.default_config(window_size=2048, configuration=conf)
+        S = 2
+        hist = signals.batch(S, 2048)
+        for n_prelim in (1, 200, 2048, 3000):
+            prelim = signals.batch(S, n_prelim, first_stream=7)
+            o = OracleSpectrum(cfg, S); g = TransformPairBatch(cfg, S)
+            assert o.prepare_preliminary(hist, prelim) == _abi.OK
+            assert g.prepare_transform(hist, preliminary=prelim)
+            o.transform(); g.do_transform()
+            complex_close(g.get_raw_fft(), o.raw_fft(), f"prelim conf {conf} n {n_prelim}", rel=2e-6, floor=2e-6)
+
+
+def test_error_behaviour():
+    cfg = _abi.default_config(window_size=4096)
+    g = TransformPairBatch(cfg, 2)
+    assert g.prepare_transform(signals.batch(2, 4095)) is False      # skip frame, TransformDSP.inl:45-46
+    with pytest.raises(_lib.SgzError) as e:
+        g.do_transform()                                               # call order, TransformPair.h:123-124
+    assert e.value.code == _abi.ESTATE
+    with pytest.raises(_lib.SgzError) as e:
+        g.process_frames(signals.batch(2, 5000), 1024, 3)              # not enough samples
+    assert e.value.code == _abi.EINVAL
+    out = g.process_frames(signals.batch(2, 4096), 1024, 0)
+    assert out.shape == (2, 0, 2, 1024, 2)
+    g.clear_audio_state()
+    assert np.all(g.get_states(0) == 0) and np.all(g.get_results(1) == 0)
+
+
+def test_known_answers_on_gpu():
+    # bin-centred sines read their amplitude; silence reads clipDB; scaling the input by 2 shifts
+    # the display value by ln 2 / ln(high/low)
+    cfg = _abi.default_config(bin_polation=_abi.BIN_NONE)
+    W = 8192
+    n = np.arange(W)
+    x = np.zeros((3, W, 2), np.float32)
+    x[0, :, 0] = 0.5 * np.sin(2 * np.pi * 1024 * n / W); x[0, :, 1] = 0.25 * np.cos(2 * np.pi * 1638 * n / W)
+    x[2] = 2 * x[0]
+    g = TransformPairBatch(cfg, 3)
+    r = g.process_frames(x, W, 1)[:, 0, 0]
+    assert abs(r[0, :, 0].max() - (1 - 6.0206 / 120)) < 1e-4
+    assert abs(r[0, :, 1].max() - (1 - 12.0412 / 120)) < 1e-4
+    assert np.all(r[1] == np.float32(-384.0))
+    strong = r[0] > 0.5
+    assert np.allclose((r[2] - r[0])[strong], np.log(2.0) / np.log(1e6), atol=2e-5)
+
+
+def test_full_size_c3_properties():
+    """BASELINE config 3 at full width (1024 stereo streams, N = 8192): batch independence (a
+    stream's result does not depend on its batch), idempotence of peak hold on a repeated frame,
+    and oracle parity on a sample of streams."""
+    import torch
+    cfg = _abi.default_config()
+    S, F, hop = 1024, 4, 2048
+    audio = frames_case(cfg, S, F, hop)
+    g = TransformPairBatch(cfg, S)
+    d_audio = torch.from_numpy(audio).cuda()
+    got = g.process_frames(d_audio, hop, F).cpu().numpy()
+    assert np.isfinite(got).all()
+    pick = [0, 1, 2, 511, 700, 1023]
+    sub = np.ascontiguousarray(audio[pick])
+    again = TransformPairBatch(cfg, len(pick)).process_frames(sub, hop, F)
+    np.testing.assert_array_equal(again, got[pick])
+    want = OracleSpectrum(cfg, len(pick)).process_frames(sub, hop, F, threads=4)
+    compare_frames(again, want, cfg, "C3 sample")
+    # idempotence: re-running the last frame only decays then re-peaks -> identical display values
+    h = TransformPairBatch(cfg, len(pick))
+    last = np.ascontiguousarray(sub[:, -cfg.window_size:])
+    first = h.process_frames(last, hop, 1)
+    second = h.process_frames(last, hop, 1)
+    np.testing.assert_array_equal(first, second)
