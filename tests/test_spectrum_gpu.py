@@ -253,7 +253,9 @@ def test_full_size_c3_properties():
     audio = frames_case(cfg, S, F, hop)
     g = TransformPairBatch(cfg, S)
     d_audio = torch.from_numpy(audio).cuda()
-    got = g.process_frames(d_audio, hop, F).cpu().numpy()
+    d_got = g.process_frames(d_audio, hop, F)
+    g.synchronize()  # device-buffer calls are asynchronous on the handle's stream
+    got = d_got.cpu().numpy()
     assert np.isfinite(got).all()
     pick = [0, 1, 2, 511, 700, 1023]
     sub = np.ascontiguousarray(audio[pick])
