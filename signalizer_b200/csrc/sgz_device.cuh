@@ -87,6 +87,14 @@ namespace sgz
 		asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
 		return r;
 	}
+	// table loads through the read-only path that the compiler may not hoist out of the frame loop
+	// (hoisting 16 window + 46 twiddle values per thread would blow the 128-register budget)
+	__device__ __forceinline__ float2 ldg_f2(const float2* p)
+	{
+		float2 r;
+		asm volatile("ld.global.nc.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
+		return r;
+	}
 	__device__ __forceinline__ void stg_stream_f2(float2* p, float2 v)
 	{
 		asm volatile("st.global.cs.v2.f32 [%0], {%1, %2};" :: "l"(p), "f"(v.x), "f"(v.y) : "memory");

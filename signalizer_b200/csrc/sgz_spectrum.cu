@@ -76,6 +76,7 @@ namespace sgz
 		uint32_t workStride; // float2 entries of workingMemory per stream
 		int conf, binpol;
 		float invSize, deltaYRecip, minFracRecip, lowerClip;
+		float deltaYLn2; // deltaYRecip * ln 2, for the log2-based display scale of the fused kernel
 		float pole0, pole1, phasePole0, phasePole1;
 	};
 
@@ -315,7 +316,7 @@ namespace sgz
 					}
 					else
 					{
-						const float* wl = t.wL + x * kLanczosTaps; const float* wr = t.wR + x * kLanczosTaps;
+						const float* wl = t.wL + x * kLanczosStride; const float* wr = t.wR + x * kLanczosStride;
 						iL = lanczosAt(csf, t.baseL[x], wl, N); iR = lanczosAt(csf, t.baseR[x], wr, N);
 						const int np = t.phaseNormPos[x];
 						mL = make_float2(0.f, 0.f); mR = make_float2(0.f, 0.f);
@@ -358,8 +359,8 @@ namespace sgz
 				else if (t.binpol == SGZ_BIN_LINEAR) { vL = linearAt(csf, t.posL[x], N); if (chans == 2) vR = linearAt(csf, t.posR[x], N); }
 				else
 				{
-					vL = lanczosAt(csf, t.baseL[x], t.wL + x * kLanczosTaps, N);
-					if (chans == 2) vR = lanczosAt(csf, t.baseR[x], t.wR + x * kLanczosTaps, N);
+					vL = lanczosAt(csf, t.baseL[x], t.wL + x * kLanczosStride, N);
+					if (chans == 2) vR = lanczosAt(csf, t.baseR[x], t.wR + x * kLanczosStride, N);
 				}
 			}
 			else
@@ -461,342 +462,8 @@ namespace sgz
 		}
 	}
 
-	// ------------------------------------------------------------------------------------------
-	// fused kernel: prepare -> FFT -> map -> post for every frame of one stream, one CTA per stream.
-	//
-	// FFT plan for N = 2 M, M = 16 * 16 * R3 (R3 = 16: N = 8192, R3 = 8: N = 4096), T = 16 R3 threads:
-	// the complex input x[n] = (L w, R w)[n] is split into even and odd samples; thread u carries one
-	// element of each (E, O) through three register-resident radix-16/16/R3 passes of two M-point
-	// FFTs that share every twiddle; the exchanges between passes go through shared memory as float4
-	// (E.re, E.im, O.re, O.im) with an XOR swizzle that keeps all three access patterns conflict free
-	// and lets pass 2 run in place.  The last radix-2 (Z[k] = E[k] + W^k O[k], Z[k+M] = E[k] - W^k O[k])
-	// is fused with the two-for-one split, which needs Z[k] and Z[N-k] = E[M-k] - W^(M-k) O[M-k].
-	// (index algebra checked by tools/fft_plan_prototype.py)
-	// ------------------------------------------------------------------------------------------
-	struct FusedArgs
-	{
-		const float* audio; uint64_t nSamples; uint64_t streamStride; int layout;
-		uint32_t hop, nFrames;
-		float2* states;  // [S][2][P]
-		float2* results; // [S][F][2][P]
-	};
+#include "sgz_fused.cuh"
 
-	template<int R3> struct FusedGeom
-	{
-		static constexpr int T = 16 * R3;
-		static constexpr int M = 16 * T;
-		static constexpr int N = 2 * M;
-		static constexpr int G = 16 / R3;
-		static constexpr size_t xbufBytes = size_t(M) * 16;          // float4[M]; csfmag[N+1] aliases its upper half (+4 B)
-		static constexpr size_t stateOffset = xbufBytes + 16;
-		static size_t smemBytes(uint32_t P) { return stateOffset + size_t(P) * 16; }
-	};
-
-	template<int R3>
-	__device__ __forceinline__ int physAddr(int k1, int j, int n3)
-	{
-		return k1 * (16 * R3) + j * R3 + (n3 ^ (k1 & 7));
-	}
-
-	template<int R3, bool STEREO, int BINPOL>
-	__global__ void __launch_bounds__(16 * R3, (R3 == 16 ? 2 : 4))
-	k_fused(DeviceTables t, FusedArgs a)
-	{
-		typedef FusedGeom<R3> Gm;
-		constexpr int T = Gm::T, M = Gm::M, N = Gm::N;
-		extern __shared__ __align__(16) unsigned char smemRaw[];
-		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
-		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
-		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
-		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
-
-		const int u = threadIdx.x;
-		const int stream = blockIdx.x;
-		const int P = int(t.P);
-		const int W = int(t.W);
-		const int conf = t.conf;
-		const int linLimit = int(t.linLimit);
-
-		// peak-hold state of this stream lives in shared memory for the whole frame loop
-		for (int i = u; i < 2 * P; i += T) st[i] = a.states[uint64_t(stream) * 2 * P + i];
-
-		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
-		const bool interleaved = a.layout == SGZ_LAYOUT_INTERLEAVED;
-		const bool vec4 = interleaved && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0);
-
-		for (uint32_t f = 0; f < a.nFrames; ++f)
-		{
-			const uint64_t start = uint64_t(f) * a.hop;
-			float2 ve[16], vo[16];
-
-			// ---- pass 1: load (window + channel matrix), DFT16 over n1, twiddle W_M^(u k1) ----
-#pragma unroll
-			for (int n1 = 0; n1 < 16; ++n1)
-			{
-				const int p = n1 * T + u;       // sample-pair index: samples 2p, 2p+1
-				const int n = 2 * p;
-				float l0 = 0.f, r0 = 0.f, l1 = 0.f, r1 = 0.f;
-				if (n + 1 < W)
-				{
-					if (vec4)
-					{
-						const float4 v = ldg_stream_f4(reinterpret_cast<const float4*>(sbase + 2 * start) + p);
-						l0 = v.x; r0 = v.y; l1 = v.z; r1 = v.w;
-					}
-					else
-					{
-						fetchLR(sbase, a.layout, a.nSamples, start + n, l0, r0);
-						fetchLR(sbase, a.layout, a.nSamples, start + n + 1, l1, r1);
-					}
-				}
-				else if (n < W)
-					fetchLR(sbase, a.layout, a.nSamples, start + n, l0, r0);
-				const float2 w = reinterpret_cast<const float2*>(t.window)[p];
-				ve[n1] = channelMatrix(conf, l0, r0, w.x);
-				vo[n1] = channelMatrix(conf, l1, r1, w.y);
-			}
-			dft16(ve); dft16(vo);
-#pragma unroll
-			for (int k1 = 0; k1 < 16; ++k1)
-			{
-				float2 e = ve[perm16(k1)], o = vo[perm16(k1)];
-				if (k1 > 0)
-				{
-					const float2 w = __ldg(t.tw1 + k1 * T + u);
-					e = cmul(e, w); o = cmul(o, w);
-				}
-				xbuf[k1 * T + (u ^ (k1 & 7))] = make_float4(e.x, e.y, o.x, o.y); // physAddr(k1, n2, n3), u = n2 R3 + n3
-			}
-			__syncthreads();
-
-			// ---- pass 2 (in place): DFT16 over n2, twiddle W_(16 R3)^(n3 k2) ----
-			{
-				const int k1 = u / R3, n3 = u % R3;
-#pragma unroll
-				for (int n2 = 0; n2 < 16; ++n2)
-				{
-					const float4 v = xbuf[physAddr<R3>(k1, n2, n3)];
-					ve[n2] = make_float2(v.x, v.y); vo[n2] = make_float2(v.z, v.w);
-				}
-				dft16(ve); dft16(vo);
-#pragma unroll
-				for (int k2 = 0; k2 < 16; ++k2)
-				{
-					float2 e = ve[perm16(k2)], o = vo[perm16(k2)];
-					if (k2 > 0)
-					{
-						const float2 w = __ldg(t.tw2 + k2 * R3 + n3);
-						e = cmul(e, w); o = cmul(o, w);
-					}
-					xbuf[physAddr<R3>(k1, k2, n3)] = make_float4(e.x, e.y, o.x, o.y);
-				}
-			}
-			__syncthreads();
-
-			// ---- pass 3: DFT_R3 over n3; thread owns bins k = u + T g + 256 k3 ----
-#pragma unroll
-			for (int g = 0; g < Gm::G; ++g)
-			{
-				const int q = u + T * g;
-				const int k1 = q & 15, k2 = q >> 4;
-#pragma unroll
-				for (int n3 = 0; n3 < R3; ++n3)
-				{
-					const float4 v = xbuf[physAddr<R3>(k1, k2, n3)];
-					ve[g * R3 + n3] = make_float2(v.x, v.y); vo[g * R3 + n3] = make_float2(v.z, v.w);
-				}
-			}
-			if constexpr (R3 == 16) { dft16(ve); dft16(vo); }
-			else { dft8<0>(ve); dft8<8>(ve); dft8<0>(vo); dft8<8>(vo); }
-
-			// ---- last radix-2: Zp[k] = E + W_N^k O (= Z[k]), Zm[k] = E - W_N^k O (= Z[k + M]) ----
-			// ve[] <- Zp, vo[] <- Zm, indexed by slot = g R3 + perm(k3)
-#pragma unroll
-			for (int g = 0; g < Gm::G; ++g)
-			{
-#pragma unroll
-				for (int k3 = 0; k3 < R3; ++k3)
-				{
-					const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
-					const int k = u + T * g + 256 * k3;
-					const float2 wo = cmul(vo[slot], __ldg(t.tw3 + k));
-					const float2 e = ve[slot];
-					ve[slot] = cadd(e, wo); vo[slot] = csub(e, wo);
-				}
-			}
-			__syncthreads(); // every pass-3 read of xbuf is done before zm / csfmag overwrite it
-
-			if constexpr (STEREO)
-			{
-#pragma unroll
-				for (int g = 0; g < Gm::G; ++g)
-#pragma unroll
-					for (int k3 = 0; k3 < R3; ++k3)
-					{
-						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
-						zm[u + T * g + 256 * k3] = vo[slot];
-					}
-				__syncthreads();
-				// two-for-one split + |.| (or |.|^2 beyond linLimit) into the reference's csf layout:
-				// channel 1 bin j at csfmag[j], channel 2 bin j at csfmag[N - j]
-#pragma unroll
-				for (int g = 0; g < Gm::G; ++g)
-#pragma unroll
-					for (int k3 = 0; k3 < R3; ++k3)
-					{
-						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
-						const int j = u + T * g + 256 * k3;
-						const float2 zj = ve[slot];
-						if (j == 0)
-						{
-							// :861-864: csf[N] = Im Z[0] / 2, csf[0] = Re Z[0] / 2, csf[N/2] *= .5 (packed Nyquists)
-							const float2 ny = vo[slot]; // Z[M] = Zm[0]
-							const float h = 0.5f * cabs(ny);
-							csfmag[0] = linLimit > 0 ? zj.x * 0.5f : (zj.x * 0.5f) * (zj.x * 0.5f);
-							csfmag[N] = linLimit > 0 ? zj.y * 0.5f : (zj.y * 0.5f) * (zj.y * 0.5f);
-							csfmag[M] = (M < linLimit) ? h : h * h;
-							continue;
-						}
-						const float2 zn = zm[M - j]; // Z[N - j]
-						float ax = (zj.x + zn.x) * 0.5f, ay = (zj.y - zn.y) * 0.5f;
-						const float dx = (zj.x - zn.x) * 0.5f, dy = (zj.y + zn.y) * 0.5f;
-						if (j == M - 1) { ax *= 0.5f; ay *= 0.5f; } // csf[(N >> 1) - 1] *= 0.5, channel 1 only
-						float a2 = ax * ax + ay * ay, b2 = dx * dx + dy * dy;
-						if (j < linLimit) { a2 = sqrtf(a2); b2 = sqrtf(b2); }
-						csfmag[j] = a2;
-						csfmag[N - j] = b2;
-					}
-			}
-			else
-			{
-				// mono: csf[i] = |Z[i]| for i < M (csf[0] halved), csf[M] = Z[M] / 2 (kept as |.|)
-#pragma unroll
-				for (int g = 0; g < Gm::G; ++g)
-#pragma unroll
-					for (int k3 = 0; k3 < R3; ++k3)
-					{
-						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
-						const int j = u + T * g + 256 * k3;
-						float2 zj = ve[slot];
-						if (j == 0)
-						{
-							zj.x *= 0.5f; zj.y *= 0.5f;
-							const float2 ny = vo[slot];
-							const float h2 = 0.25f * cnorm(ny);
-							csfmag[M] = (M < linLimit) ? sqrtf(h2) : h2;
-						}
-						const float m2 = cnorm(zj);
-						csfmag[j] = (j < linLimit) ? sqrtf(m2) : m2;
-					}
-			}
-			__syncthreads();
-
-			// ---- display-point mapping + log scale + peak hold ----
-			float2* resOut = a.results + ((uint64_t(stream) * a.nFrames + f) * 2) * P;
-			for (int x = u; x < P; x += T)
-			{
-				const int4 bm = t.binmap[x];
-				float vL, vR = 0.f;
-				if (bm.x == 0)
-				{
-					if constexpr (BINPOL == SGZ_BIN_NONE)
-					{
-						vL = csfmag[bm.y];
-						if constexpr (STEREO) vR = csfmag[N - bm.y];
-					}
-					else if constexpr (BINPOL == SGZ_BIN_LINEAR)
-					{
-						{
-							const float pos = t.posL[x]; const float fl = floorf(pos); const int i = int(fl); const float fr = pos - fl;
-							const float va = (i >= 0 && i <= N) ? csfmag[i] : 0.f, vb = (i + 1 >= 0 && i + 1 <= N) ? csfmag[i + 1] : 0.f;
-							vL = va * (1.f - fr) + vb * fr;
-						}
-						if constexpr (STEREO)
-						{
-							const float pos = t.posR[x]; const float fl = floorf(pos); const int i = int(fl); const float fr = pos - fl;
-							const float va = (i >= 0 && i <= N) ? csfmag[i] : 0.f, vb = (i + 1 >= 0 && i + 1 <= N) ? csfmag[i + 1] : 0.f;
-							vR = va * (1.f - fr) + vb * fr;
-						}
-					}
-					else
-					{
-						const int bl = t.baseL[x];
-						const float* wl = t.wL + x * kLanczosTaps;
-						vL = 0.f;
-#pragma unroll
-						for (int k = 0; k < kLanczosTaps; ++k)
-						{
-							const int i = bl + k;
-							if (i >= 0 && i <= N) vL += csfmag[i] * wl[k];
-						}
-						if constexpr (STEREO)
-						{
-							const int br = t.baseR[x];
-							const float* wr = t.wR + x * kLanczosTaps;
-#pragma unroll
-							for (int k = 0; k < kLanczosTaps; ++k)
-							{
-								const int i = br + k;
-								if (i >= 0 && i <= N) vR += csfmag[i] * wr[k];
-							}
-						}
-					}
-				}
-				else
-				{
-					// max-of-bins (:944-984): entries beyond linLimit are already squared
-					int maxL = bm.w, maxR = bm.w; float bestL = 0.f, bestR = 0.f;
-					for (int c = 0; c < bm.z; ++c)
-					{
-						const int off = bm.y + c;
-						const float v = csfmag[off];
-						const float mL = (off < linLimit) ? v * v : v;
-						if (mL > bestL) { bestL = mL; maxL = off; }
-						if constexpr (STEREO)
-						{
-							const float vr = csfmag[N - off];
-							const float mR = (off < linLimit) ? vr * vr : vr;
-							if (mR > bestR) { bestR = mR; maxR = N - off; }
-						}
-					}
-					{
-						const float v = csfmag[maxL];
-						vL = (maxL < linLimit || maxL > N - linLimit) ? v : sqrtf(v);
-					}
-					if constexpr (STEREO)
-					{
-						const float v = csfmag[maxR];
-						vR = (maxR < linLimit || maxR > N - linLimit) ? v : sqrtf(v);
-					}
-				}
-				const float lmag = fabsf(t.invSize * vL);
-				const float rmag = fabsf(t.invSize * vR);
-				const float slope = t.slope[x];
-				const float poles[2] = { t.pole0, t.pole1 };
-#pragma unroll
-				for (int k = 0; k < 2; ++k)
-				{
-					float2 sv = st[k * P + x];
-					sv.x *= poles[k];
-					if (lmag > sv.x) sv.x = lmag;
-					float2 res;
-					res.x = logScale(slope, sv.x, t.minFracRecip, t.deltaYRecip, t.lowerClip);
-					if constexpr (STEREO)
-					{
-						sv.y *= poles[k];
-						if (rmag > sv.y) sv.y = rmag;
-						res.y = logScale(slope, sv.y, t.minFracRecip, t.deltaYRecip, t.lowerClip);
-					}
-					else res.y = 0.f;
-					st[k * P + x] = sv;
-					stg_stream_f2(resOut + k * P + x, res);
-				}
-			}
-			__syncthreads(); // csfmag / zm are overwritten by the next frame's pass 1
-		}
-
-		for (int i = u; i < 2 * P; i += T) a.states[uint64_t(stream) * 2 * P + i] = st[i];
-	}
 } // namespace sgz
 
 // ----------------------------------------------------------------------------------------------
@@ -824,6 +491,7 @@ struct sgz_spectrum
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
 	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
 	int fusedR3{ 0 };
+	bool fusedAttrSet{ false };
 	size_t fusedSmem{ 0 };
 };
 
@@ -886,15 +554,19 @@ namespace
 		return SGZ_OK;
 	}
 
-	template<int R3, bool STEREO>
+	template<int R3, bool STEREO, int MATRIX>
 	int launchFusedBinpol(sgz_spectrum* h, const FusedArgs& a)
 	{
 		const size_t smem = FusedGeom<R3>::smemBytes(h->tab.P);
 		const dim3 grid(h->nStreams), block(16 * R3);
 #define SGZ_LAUNCH(BP)                                                                                              \
 		{                                                                                                           \
-			auto kern = k_fused<R3, STEREO, BP>;                                                                    \
-			SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));           \
+			auto kern = k_fused<R3, STEREO, BP, MATRIX>;                                                            \
+			if (!h->fusedAttrSet)                                                                                   \
+			{                                                                                                       \
+				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
+				h->fusedAttrSet = true;                                                                             \
+			}                                                                                                       \
 			kern<<<grid, block, smem, h->stream>>>(h->dev, a);                                                      \
 		}
 		switch (h->cfg.bin_polation)
@@ -911,8 +583,17 @@ namespace
 	int launchFused(sgz_spectrum* h, const FusedArgs& a)
 	{
 		const bool stereo = h->tab.stateChannels == 2;
-		if (h->fusedR3 == 16) return stereo ? launchFusedBinpol<16, true>(h, a) : launchFusedBinpol<16, false>(h, a);
-		if (h->fusedR3 == 8) return stereo ? launchFusedBinpol<8, true>(h, a) : launchFusedBinpol<8, false>(h, a);
+		const bool passthru = h->cfg.configuration == SGZ_CH_SEPARATE;
+		if (h->fusedR3 == 16)
+		{
+			if (passthru) return launchFusedBinpol<16, true, 0>(h, a);
+			return stereo ? launchFusedBinpol<16, true, 1>(h, a) : launchFusedBinpol<16, false, 1>(h, a);
+		}
+		if (h->fusedR3 == 8)
+		{
+			if (passthru) return launchFusedBinpol<8, true, 0>(h, a);
+			return stereo ? launchFusedBinpol<8, true, 1>(h, a) : launchFusedBinpol<8, false, 1>(h, a);
+		}
 		return fail(SGZ_EUNSUPPORTED, "no fused kernel for this configuration");
 	}
 
@@ -1024,6 +705,7 @@ extern "C"
 		DeviceTables& d = h->dev;
 		d.N = t.N; d.W = t.W; d.P = t.P; d.M = t.numBins; d.linLimit = t.linLimit;
 		d.conf = cfg->configuration; d.binpol = cfg->bin_polation;
+		d.deltaYLn2 = float(double(t.deltaYRecip) * 0.69314718055994530942);
 		d.invSize = t.invSize; d.deltaYRecip = t.deltaYRecip; d.minFracRecip = t.minFracRecip; d.lowerClip = t.lowerClip;
 		d.pole0 = t.pole[0]; d.pole1 = t.pole[1]; d.phasePole0 = t.phasePole[0]; d.phasePole1 = t.phasePole[1];
 		d.phaseNormFinal = t.phaseNormFinal;
@@ -1141,6 +823,8 @@ extern "C"
 		const uint32_t W = h->tab.W;
 		if (nHist < W) { h->stage = 0; return SGZ_SKIPPED; } // TransformDSP.inl:45-46
 		if (histStride < 2 * nHist && h->nStreams > 1) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		if (layout == SGZ_LAYOUT_INTERLEAVED && ((histStride & 1) || (reinterpret_cast<uintptr_t>(hist) & 7) || (withPrelim && ((prelimStride & 1) || (reinterpret_cast<uintptr_t>(prelim) & 7)))))
+			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
 		SGZ_GUARD(h);
 		PrepareArgs a{};
 		a.layout = layout;
@@ -1329,6 +1013,8 @@ extern "C"
 		const uint32_t W = h->tab.W, P = h->tab.P;
 		if (n_samples < uint64_t(n_frames - 1) * hop + W) return fail(SGZ_EINVAL, "n_samples %llu < (n_frames-1)*hop + window_size", (unsigned long long)n_samples);
 		if (h->nStreams > 1 && stream_stride < 2 * n_samples) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stream_stride & 1) || (reinterpret_cast<uintptr_t>(audio) & 7)))
+			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
 		SGZ_GUARD(h);
 		const float* dAudio = nullptr;
 		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);

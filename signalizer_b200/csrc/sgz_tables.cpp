@@ -154,7 +154,7 @@ namespace sgz
 		// ---- bin map: integer skeleton of the mapping loops ----
 		t.mode.assign(P, 0); t.first.assign(P, 0); t.count.assign(P, 0); t.fallback.assign(P, 0);
 		t.posL.assign(P, 0); t.posR.assign(P, 0); t.baseL.assign(P, 0); t.baseR.assign(P, 0);
-		t.wL.assign(std::size_t(P) * kLanczosTaps, 0); t.wR.assign(std::size_t(P) * kLanczosTaps, 0);
+		t.wL.assign(std::size_t(P) * kLanczosStride, 0); t.wR.assign(std::size_t(P) * kLanczosStride, 0);
 		t.phaseNormPos.assign(P, 0); t.phaseNormFinal = 0;
 		const bool cplx = cfg.configuration == SGZ_CH_COMPLEX;
 		const bool phase = cfg.configuration == SGZ_CH_PHASE;
@@ -236,8 +236,8 @@ namespace sgz
 			t.baseL[x] = static_cast<int32_t>(bl); t.baseR[x] = static_cast<int32_t>(br);
 			for (int k = 0; k < kLanczosTaps; ++k)
 			{
-				t.wL[std::size_t(x) * kLanczosTaps + k] = static_cast<float>(lanczosKernel(double(pl) - double(bl + k), kLanczosSize));
-				t.wR[std::size_t(x) * kLanczosTaps + k] = static_cast<float>(lanczosKernel(double(pr) - double(br + k), kLanczosSize));
+				t.wL[std::size_t(x) * kLanczosStride + k] = static_cast<float>(lanczosKernel(double(pl) - double(bl + k), kLanczosSize));
+				t.wR[std::size_t(x) * kLanczosStride + k] = static_cast<float>(lanczosKernel(double(pr) - double(br + k), kLanczosSize));
 			}
 		}
 

@@ -17,6 +17,7 @@ namespace sgz
 {
 	constexpr int kLanczosSize = 5;               // lanczosFilterSize, TransformDSP.inl:514
 	constexpr int kLanczosTaps = 2 * kLanczosSize; // floor(x)-a+1 .. floor(x)+a
+	constexpr int kLanczosStride = 12;             // weights per point in the tables (10 taps + 2 zeros, float4 aligned)
 
 	struct Tables
 	{
@@ -41,7 +42,7 @@ namespace sgz
 		std::vector<int32_t> fallback;    // max: initial maxBin
 		std::vector<float> posL, posR;    // fractional csf positions: f*freqToBin and N - that (float32)
 		std::vector<int32_t> baseL, baseR; // Lanczos: first tap index floor(pos) - a + 1
-		std::vector<float> wL, wR;        // Lanczos weights [P][kLanczosTaps]
+		std::vector<float> wL, wR;        // Lanczos weights [P][kLanczosStride]
 		// Phase configuration: number of low csf indices already replaced by their magnitude when
 		// the magnitude pass evaluates point x (TransformDSP.inl:709-727, :759-776), and after it
 		std::vector<int32_t> phaseNormPos; // [P]
