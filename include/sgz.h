@@ -215,6 +215,28 @@ int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, i
                                  uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
                                  uint32_t n_frames, float* results, int results_mem);
 
+/* ---- allocation-free forward FFT ------------------------------------------
+ * No counterpart in the reference.  For callers that cannot allocate device
+ * memory at call time (real-time audio / render callbacks, hosts that forbid
+ * cudaMalloc after start-up, processes whose device pool is already spent):
+ * the unnormalised forward DFT of `batch` complex sequences of `n` points
+ * (n a power of two >= 2), natural order, X[k] = sum x[j] exp(-2 pi i j k / n),
+ * like sgz_spectrum_transform but without a handle.  d_in and d_out are
+ * DEVICE buffers of batch * n interleaved (re, im) floats, distinct, owned by
+ * the caller.  The call never invokes cudaMalloc/cudaFree or any allocating
+ * routine: its working buffer is a fixed 8 MiB array inside the library
+ * (resident on every GPU that loads the library, until the process exits), so
+ * n * batch must not exceed SGZ_NOALLOC_MAX_POINTS (SGZ_EINVAL otherwise).
+ * The first call on each device looks up that array's address (with that
+ * device current); make it before starting any stream capture.  All calls
+ * share the one working buffer: calls that overlap on the GPU (different
+ * streams, or different host threads) race with each other; issue them on one
+ * stream or order them yourself.  Work is enqueued on `cuda_stream`
+ * (a cudaStream_t, NULL = default stream) and is asynchronous. */
+#define SGZ_NOALLOC_MAX_POINTS (1u << 20)
+int  sgz_fft_forward_noalloc(const float* d_in, float* d_out, uint32_t n, uint32_t batch,
+                             void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

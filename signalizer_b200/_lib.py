@@ -21,7 +21,7 @@ EXPORTS = [
     "sgz_spectrum_transform", "sgz_spectrum_map", "sgz_spectrum_postprocess", "sgz_spectrum_get_raw_fft",
     "sgz_spectrum_get_transform_result", "sgz_spectrum_get_results", "sgz_spectrum_get_states",
     "sgz_spectrum_set_states", "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state",
-    "sgz_spectrum_process_frames",
+    "sgz_spectrum_process_frames", "sgz_fft_forward_noalloc",
 ]
 
 
@@ -72,6 +72,7 @@ def load():
     lib.sgz_spectrum_get_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_set_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_process_frames.argtypes = [vp, fp, i32, i32, u64, u64, u32, u32, fp, i32]
+    lib.sgz_fft_forward_noalloc.argtypes = [fp, fp, u32, u32, vp]
     for n in EXPORTS:
         f = getattr(lib, n)  # raises AttributeError if the symbol is not exported
         if n not in ("sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_destroy"):

@@ -34,7 +34,8 @@ namespace sgz
 	// ------------------------------------------------------------------------------------------
 	static thread_local std::string g_lastError;
 
-	static int fail(int code, const char* fmt, ...)
+	// records the message behind sgz_last_error(); shared with the other .cu files of the library
+	int fail(int code, const char* fmt, ...)
 	{
 		char buf[512];
 		va_list ap;

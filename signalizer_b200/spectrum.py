@@ -178,3 +178,17 @@ class TransformPairBatch:
         assert tuple(okeep.shape) == shape
         check(self.lib.sgz_spectrum_process_frames(self._h, ptr, mem, layout, n, stride, hop, n_frames, optr, omem))
         return out
+
+
+def fft_forward_noalloc(d_in, d_out, n: int, batch: int, cuda_stream: int = 0) -> None:
+    """Forward FFT of `batch` complex sequences of `n` points on DEVICE tensors, for callers that may
+    not allocate GPU memory when they call (real-time callbacks, hosts that forbid cudaMalloc after
+    start-up): wraps sgz_fft_forward_noalloc, which owns a fixed 8 MiB working buffer inside the
+    library instead of allocating one.  `d_in` / `d_out` are distinct float32 CUDA tensors holding
+    batch * n interleaved (re, im) pairs; n * batch <= 2**20.  Asynchronous on `cuda_stream`;
+    calls that overlap on the GPU share (and corrupt) the one working buffer."""
+    lib = load()
+    for t in (d_in, d_out):
+        assert _is_torch(t) and t.is_cuda and t.is_contiguous(), "device float32 tensors required"
+        assert t.numel() >= 2 * n * batch
+    check(lib.sgz_fft_forward_noalloc(C.c_void_p(d_in.data_ptr()), C.c_void_p(d_out.data_ptr()), n, batch, C.c_void_p(cuda_stream)))
