@@ -53,7 +53,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -199,12 +199,12 @@ def run_ours(args):
     # ---- device-resident throughput ("value") ----
     d_audio = torch.from_numpy(audio_np).to(dev)
     d_out = torch.empty((S, F, 2, P, 2), dtype=torch.float32, device=dev)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()   # nvidia-smi needs ~100 ms to start: launched before the warm-up, read after the timed region
     for _ in range(max(args.warmup, 3)):
         pairs.process_frames(d_audio, hop, F, out=d_out)
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     barrier()
     ev[0].record(stream)
@@ -263,7 +263,7 @@ def run_ours(args):
             from oracle import binding
             binding.build()
             cores = binding.hardware_concurrency() or os.cpu_count() or 1
-            cs, cf = max(2 * cores, 16), 16
+            cs, cf = min(max(16 * cores, 64), 1024), args.frames   # ~10-30 s of single-core work
             v, dt = cpu_sample(args, cores, cs, cf)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{cs} streams x {cf} frames of the same C3 workload in {dt:.2f} s, {cores} threads over streams",
@@ -276,7 +276,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--streams", type=int, default=1024)
