@@ -215,6 +215,20 @@ int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, i
                                  uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
                                  uint32_t n_frames, float* results, int results_mem);
 
+/* ---- resonator bank (algo = SGZ_ALGO_RSNT) ------------------------------
+ * Replaces `template<ISA> void resonatingDispatch(const Constant&,
+ * std::array<AFloat*, 2> buffer, size_t numSamples)` (TransformDSP.inl:1215-1295):
+ * advances every stream's complex one-pole bank (filters x window vectors x
+ * channels) over a block of `n_samples` samples.  `audio` as in
+ * sgz_spectrum_prepare.  The windowed snapshot (copyResonatorStateInto,
+ * TransformDSP.inl:1152-1161) is taken by sgz_spectrum_map, and
+ * sgz_spectrum_process_frames resonates `hop` samples per frame like
+ * audioEntryPoint (:1172-1204). */
+int  sgz_resonator_process(sgz_spectrum* h, const float* audio, int mem, int layout,
+                           uint64_t n_samples, uint64_t stream_stride);
+/* Raw resonator state (cresonator), [stream][channel][vector][filter] complex. */
+int  sgz_resonator_get_state(sgz_spectrum* h, float* out, int mem);
+
 /* ---- allocation-free forward FFT ------------------------------------------
  * No counterpart in the reference.  For callers that cannot allocate device
  * memory at call time (real-time audio / render callbacks, hosts that forbid

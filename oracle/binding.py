@@ -57,6 +57,7 @@ def load(fast: bool = False):
     lib.sgzo_set_states.argtypes = [vp, i32, fp]
     lib.sgzo_process_frames.argtypes = [vp, fp, i32, u64, u64, u32, u32, fp, i32, u32, u32]
     lib.sgzo_resonate.argtypes = [vp, fp, i32, u64, u64]
+    lib.sgzo_get_resonator_state.argtypes = [vp, dp]
     lib.sgzo_audio_entry_point.argtypes = [vp, fp, u64, u64, fp, u64, u64, i32, fp, u32, C.POINTER(u32)]
     lib.sgzo_hardware_concurrency.restype = C.c_uint
     _libs[name] = lib
@@ -187,6 +188,11 @@ class OracleSpectrum:
         a, p = _f32(audio)
         n = a.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else a.shape[2]
         return self.lib.sgzo_resonate(self.h, p, layout, n, a[0].size)
+
+    def resonator_state(self):
+        V = self.info.resonator_vectors
+        out = self._dbl(self.lib.sgzo_get_resonator_state, self.n_streams * self.channels * V * self.P * 2)
+        return out.reshape(self.n_streams, self.channels, V, self.P, 2)
 
     def audio_entry_point(self, history, block, layout=_abi.LAYOUT_INTERLEAVED, max_frames=64):
         h, hp = _f32(history)

@@ -40,6 +40,7 @@ namespace
 		virtual void clearAudio() = 0;
 		virtual int frames(const float* audio, int layout, uint64_t n, uint64_t stride, uint32_t hop, uint32_t nFrames, float* results, int threads, uint32_t firstStream, uint32_t numStreams) = 0;
 		virtual int resonate(const float* audio, int layout, uint64_t n, uint64_t stride) = 0;
+		virtual void resonatorState(double* out) = 0;
 		virtual int audioEntry(const float* hist, uint64_t nh, uint64_t hstride, const float* block, uint64_t nb, uint64_t bstride, int layout, float* frames, uint32_t maxFrames, uint32_t* numFrames) = 0;
 	};
 
@@ -291,8 +292,10 @@ namespace
 		// pool over streams stands in for cpl::jobs::parallel_for (SpectrumDSP.cpp:83).
 		int frames(const float* audio, int layout, uint64_t n, uint64_t stride, uint32_t hop, uint32_t nFrames, float* results, int threads, uint32_t firstStream, uint32_t numStreams) override
 		{
+			const bool rsnt = constant.algo == TransformAlgorithm::RSNT;
 			const std::size_t W = constant.windowSize, P = constant.axisPoints;
-			if (nFrames && n < (uint64_t)(nFrames - 1) * hop + W) return SGZ_EINVAL;
+			if (!rsnt && nFrames && n < (uint64_t)(nFrames - 1) * hop + W) return SGZ_EINVAL;
+			if (rsnt && n < (uint64_t)nFrames * hop) return SGZ_EINVAL;
 			if ((uint64_t)firstStream + numStreams > pairs.size()) return SGZ_EINVAL;
 			std::atomic<std::size_t> next{ firstStream };
 			const std::size_t end = (std::size_t)firstStream + numStreams;
@@ -307,10 +310,19 @@ namespace
 					for (uint32_t f = 0; f < nFrames; ++f)
 					{
 						const uint64_t off = (uint64_t)f * hop;
-						auto views = makeViews(sa.ch[0] + off, sa.ch[1] + off, W, W);
 						auto& p = pairs[s];
-						if (!p.prepareTransform(constant, views)) continue;
-						p.doTransform(constant);
+						if (rsnt)
+						{
+							// audioEntryPoint, RSNT branch (TransformDSP.inl:1178-1197): resonate one blob of
+							// `sampleBufferSize` (= hop) samples, then addAudioFrame
+							p.resonatingDispatch(constant, { sa.ch[0] + off, sa.ch[1] + off }, hop);
+						}
+						else
+						{
+							auto views = makeViews(sa.ch[0] + off, sa.ch[1] + off, W, W);
+							if (!p.prepareTransform(constant, views)) continue;
+							p.doTransform(constant);
+						}
 						p.mapToLinearSpace(constant);
 						p.postProcessStdTransform(constant);
 						if (results)
@@ -344,6 +356,22 @@ namespace
 				pairs[s].resonatingDispatch(constant, { sa.ch[0], sa.ch[1] }, n);
 			}
 			return SGZ_OK;
+		}
+
+		// raw resonator state [stream][channel][vector][filter] complex
+		void resonatorState(double* out) override
+		{
+			const std::size_t ch = constant.getStateConfigurationChannels(), V = constant.resonator.numVectors, P = constant.axisPoints;
+			for (std::size_t s = 0; s < pairs.size(); ++s)
+			{
+				auto& r = pairs[s].cresonator;
+				r.ensure(constant.resonator);
+				for (std::size_t k = 0; k < ch * V * P; ++k)
+				{
+					out[2 * (s * ch * V * P + k)] = r.real[k];
+					out[2 * (s * ch * V * P + k) + 1] = r.imag[k];
+				}
+			}
 		}
 
 		// audioEntryPoint over one callback block (TransformDSP.inl:1165-1211); copies the
@@ -412,6 +440,7 @@ extern "C"
 	{
 		return static_cast<IOracle*>(h)->frames(audio, layout, n, stride, hop, n_frames, results, threads, first_stream, num_streams);
 	}
+	void sgzo_get_resonator_state(void* h, double* out) { static_cast<IOracle*>(h)->resonatorState(out); }
 	int sgzo_resonate(void* h, const float* audio, int layout, uint64_t n, uint64_t stride) { return static_cast<IOracle*>(h)->resonate(audio, layout, n, stride); }
 	int sgzo_audio_entry_point(void* h, const float* hist, uint64_t nh, uint64_t hstride, const float* block, uint64_t nb, uint64_t bstride, int layout, float* frames, uint32_t max_frames, uint32_t* num_frames)
 	{

@@ -22,6 +22,7 @@ EXPORTS = [
     "sgz_spectrum_get_transform_result", "sgz_spectrum_get_results", "sgz_spectrum_get_states",
     "sgz_spectrum_set_states", "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state",
     "sgz_spectrum_process_frames", "sgz_fft_forward_noalloc",
+    "sgz_resonator_process", "sgz_resonator_get_state",
 ]
 
 
@@ -72,6 +73,8 @@ def load():
     lib.sgz_spectrum_get_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_set_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_process_frames.argtypes = [vp, fp, i32, i32, u64, u64, u32, u32, fp, i32]
+    lib.sgz_resonator_process.argtypes = [vp, fp, i32, i32, u64, u64]
+    lib.sgz_resonator_get_state.argtypes = [vp, fp, i32]
     lib.sgz_fft_forward_noalloc.argtypes = [fp, fp, u32, u32, vp]
     for n in EXPORTS:
         f = getattr(lib, n)  # raises AttributeError if the symbol is not exported

@@ -72,6 +72,10 @@ namespace sgz
 		const float2* tw1;       // [16][T]  W_M^(u k1)          (fused FFT)
 		const float2* tw2;       // [16][R3] W_(16 R3)^(n3 k2)
 		const float2* tw3;       // [M]      W_N^k
+		const float2* resCoeff;  // [V][P] pole per vector and filter
+		const float* resGain;    // [P]
+		const float* resTaps;    // [V]
+		uint32_t resVectors, resChannels;
 		int phaseNormFinal;
 		uint32_t N, W, P, M, linLimit;
 		uint32_t workStride; // float2 entries of workingMemory per stream
@@ -464,6 +468,7 @@ namespace sgz
 	}
 
 #include "sgz_fused.cuh"
+#include "sgz_resonator.cuh"
 
 } // namespace sgz
 
@@ -487,6 +492,8 @@ struct sgz_spectrum
 	float2* dWork{ nullptr };    // [S][max(N, 2P)] workingMemory (FFT scratch / transform result)
 	float2* dStates{ nullptr };  // [S][2][P]
 	float2* dResults{ nullptr }; // [S][2][P]
+	float2* dResState{ nullptr };   // [S][ch][V][P] resonator state (cresonator)
+	float2* dResPartial{ nullptr }; size_t resPartialBytes{ 0 }; // time-slice scratch of k_resonate
 	// staging for host-resident callers
 	float* dAudioStage{ nullptr }; size_t audioStageBytes{ 0 };
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
@@ -665,6 +672,7 @@ extern "C"
 			for (void* p : h->allocations) cudaFree(p);
 			if (h->dAudioStage) cudaFree(h->dAudioStage);
 			if (h->dResultStage) cudaFree(h->dResultStage);
+			if (h->dResPartial) cudaFree(h->dResPartial);
 			if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
 		}
 		delete h;
@@ -726,6 +734,14 @@ extern "C"
 		SGZ_TRY(upload(h, t.wR, &d.wR));
 		SGZ_TRY(upload(h, t.phaseNormPos, &d.phaseNormPos));
 		{
+			std::vector<float2> coeff(t.resCoeffReal.size());
+			for (size_t k = 0; k < coeff.size(); ++k) coeff[k] = make_float2(t.resCoeffReal[k], t.resCoeffImag[k]);
+			SGZ_TRY(upload(h, coeff, &d.resCoeff));
+			SGZ_TRY(upload(h, t.resGain, &d.resGain));
+			SGZ_TRY(upload(h, t.resWindowTaps, &d.resTaps));
+			d.resVectors = t.resonatorVectors; d.resChannels = t.stateChannels;
+		}
+		{
 			std::vector<uint64_t> e(t.N / 2);
 			for (size_t k = 0; k < e.size(); ++k) e[k] = k;
 			SGZ_TRY(upload(h, twiddleTable(e.size(), double(t.N), e), &d.twN));
@@ -750,6 +766,7 @@ extern "C"
 		SGZ_TRY(allocZero(h, size_t(n_streams) * workPerStream, &h->dWork));
 		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dStates));
 		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dResults));
+		if (cfg->algo == SGZ_ALGO_RSNT) SGZ_TRY(allocZero(h, size_t(n_streams) * t.stateChannels * t.resonatorVectors * t.P, &h->dResState));
 #undef SGZ_TRY
 		*out = h;
 		return SGZ_OK;
@@ -819,7 +836,7 @@ extern "C"
 		uint64_t prelimStride, int mem, int layout, bool withPrelim)
 	{
 		if (!h || !hist) return fail(SGZ_EINVAL, "null argument");
-		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "prepareTransform is the FFT algorithm's entry (TransformDSP.inl:51-53)");
+		if (h->cfg.algo != SGZ_ALGO_FFT) return nHist < h->tab.W ? SGZ_SKIPPED : SGZ_OK; // the switch at TransformDSP.inl:51-53 only has an FFT case
 		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
 		const uint32_t W = h->tab.W;
 		if (nHist < W) { h->stage = 0; return SGZ_SKIPPED; } // TransformDSP.inl:45-46
@@ -918,7 +935,16 @@ extern "C"
 	int sgz_spectrum_map(sgz_spectrum* h)
 	{
 		if (!h) return fail(SGZ_EINVAL, "null handle");
-		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "resonator snapshot: use sgz_resonator_* (not built yet)");
+		if (h->cfg.algo == SGZ_ALGO_RSNT)
+		{
+			// RSNT branch of mapToLinearSpace (TransformDSP.inl:1103-1133): windowed snapshot of the resonator state
+			SGZ_GUARD(h);
+			const dim3 block(256), grid((h->tab.P + 255) / 256, h->nStreams);
+			k_resonator_snapshot<<<grid, block, 0, h->stream>>>(h->dev, h->dResState, h->dWork);
+			SGZ_CUDA(cudaGetLastError());
+			h->stage = 3;
+			return SGZ_OK;
+		}
 		if (h->stage < 2) return fail(SGZ_ESTATE, "call doTransform() first (TransformPair.h:123-124)");
 		if (h->tab.N < 3 || h->tab.sampleRate < 1) return SGZ_OK; // :519-520
 		SGZ_GUARD(h);
@@ -1000,7 +1026,68 @@ extern "C"
 		const size_t workStride = std::max<size_t>(h->tab.N, size_t(2) * h->tab.P);
 		SGZ_CUDA(cudaMemsetAsync(h->dCsf, 0, size_t(h->nStreams) * (h->tab.N + 1) * sizeof(float2), h->stream));
 		SGZ_CUDA(cudaMemsetAsync(h->dWork, 0, size_t(h->nStreams) * workStride * sizeof(float2), h->stream));
+		if (h->dResState) // cresonator.resetState(), TransformPair.h:183
+			SGZ_CUDA(cudaMemsetAsync(h->dResState, 0, size_t(h->nStreams) * h->tab.stateChannels * h->tab.resonatorVectors * h->tab.P * sizeof(float2), h->stream));
 		h->stage = 0;
+		return SGZ_OK;
+	}
+
+	// launches resonatingDispatch over samples [first, first + count) of a device-resident buffer
+	static int resonateBlock(sgz_spectrum* h, const float* dAudio, int layout, uint64_t nSamples, uint64_t streamStride, uint64_t first, uint32_t count)
+	{
+		if (count == 0) return SGZ_OK; // TransformDSP.inl:1246-1247
+		const uint32_t total = h->tab.P * h->tab.resonatorVectors * h->tab.stateChannels;
+		const uint32_t blocksX = (total + 255) / 256;
+		// enough time slices for ~2 waves of CTAs over the SMs, each at least 256 samples long
+		int sms = 148;
+		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+		uint64_t want = (uint64_t(sms) * 8 + uint64_t(blocksX) * h->nStreams - 1) / (uint64_t(blocksX) * h->nStreams);
+		uint32_t chunks = uint32_t(std::max<uint64_t>(1, std::min<uint64_t>(want, count / 256)));
+		if (chunks > 65535) chunks = 65535;
+		ResArgs a{};
+		a.audio = dAudio; a.nSamples = nSamples; a.streamStride = streamStride; a.layout = layout;
+		a.first = first; a.count = count; a.chunks = chunks; a.chunkLen = (count + chunks - 1) / chunks;
+		a.chunks = (count + a.chunkLen - 1) / a.chunkLen;
+		if (a.chunks > 1)
+		{
+			const size_t need = size_t(h->nStreams) * a.chunks * total * sizeof(float2);
+			if (h->resPartialBytes < need)
+			{
+				if (h->dResPartial) { cudaFree(h->dResPartial); h->dResPartial = nullptr; h->resPartialBytes = 0; }
+				SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dResPartial), need));
+				h->resPartialBytes = need;
+			}
+		}
+		k_resonate<<<dim3(blocksX, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+		if (a.chunks > 1) k_resonate_combine<<<dim3(blocksX, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+		SGZ_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
+	int sgz_resonator_process(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride)
+	{
+		if (!h || !audio) return fail(SGZ_EINVAL, "null argument");
+		if (h->cfg.algo != SGZ_ALGO_RSNT) return fail(SGZ_EUNSUPPORTED, "handle was not created with algo = SGZ_ALGO_RSNT");
+		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
+		if (n_samples > 0xFFFFFFFFull) return fail(SGZ_EINVAL, "block too long");
+		if (h->nStreams > 1 && stream_stride < 2 * n_samples) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stream_stride & 1) || (reinterpret_cast<uintptr_t>(audio) & 7)))
+			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
+		SGZ_GUARD(h);
+		const float* dAudio = nullptr;
+		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);
+		if (rc != SGZ_OK) return rc;
+		return resonateBlock(h, dAudio, layout, n_samples, stream_stride, 0, uint32_t(n_samples));
+	}
+
+	int sgz_resonator_get_state(sgz_spectrum* h, float* out, int mem)
+	{
+		if (!h || !out) return fail(SGZ_EINVAL, "null argument");
+		if (!h->dResState) return fail(SGZ_EUNSUPPORTED, "handle was not created with algo = SGZ_ALGO_RSNT");
+		SGZ_GUARD(h);
+		const size_t bytes = size_t(h->nStreams) * h->tab.stateChannels * h->tab.resonatorVectors * h->tab.P * sizeof(float2);
+		SGZ_CUDA(cudaMemcpyAsync(out, h->dResState, bytes, mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
 		return SGZ_OK;
 	}
 
@@ -1008,11 +1095,12 @@ extern "C"
 		uint32_t n_frames, float* results, int results_mem)
 	{
 		if (!h || !audio || !results) return fail(SGZ_EINVAL, "null argument");
-		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "process_frames is the FFT path");
 		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
 		if (n_frames == 0) return SGZ_OK;
 		const uint32_t W = h->tab.W, P = h->tab.P;
-		if (n_samples < uint64_t(n_frames - 1) * hop + W) return fail(SGZ_EINVAL, "n_samples %llu < (n_frames-1)*hop + window_size", (unsigned long long)n_samples);
+		const bool rsnt = h->cfg.algo == SGZ_ALGO_RSNT;
+		if (rsnt && n_samples < uint64_t(n_frames) * hop) return fail(SGZ_EINVAL, "n_samples %llu < n_frames*hop", (unsigned long long)n_samples);
+		if (!rsnt && n_samples < uint64_t(n_frames - 1) * hop + W) return fail(SGZ_EINVAL, "n_samples %llu < (n_frames-1)*hop + window_size", (unsigned long long)n_samples);
 		if (h->nStreams > 1 && stream_stride < 2 * n_samples) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
 		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stream_stride & 1) || (reinterpret_cast<uintptr_t>(audio) & 7)))
 			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
@@ -1028,7 +1116,20 @@ extern "C"
 			if (rc != SGZ_OK) return rc;
 			dRes = h->dResultStage;
 		}
-		if (h->fusedR3 != 0)
+		if (rsnt)
+		{
+			// audioEntryPoint, RSNT (TransformDSP.inl:1172-1204): resonate one blob of `hop` samples, then
+			// addAudioFrame = snapshot + post-process
+			for (uint32_t f = 0; f < n_frames; ++f)
+			{
+				if ((rc = resonateBlock(h, dAudio, layout, n_samples, stream_stride, uint64_t(f) * hop, hop)) != SGZ_OK) return rc;
+				if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return rc;
+				if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return rc;
+				SGZ_CUDA(cudaMemcpy2DAsync(dRes + size_t(f) * 2 * P * 2, size_t(n_frames) * 2 * P * sizeof(float2), h->dResults, size_t(2) * P * sizeof(float2),
+					size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+			}
+		}
+		else if (h->fusedR3 != 0)
 		{
 			FusedArgs a{};
 			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;

@@ -159,6 +159,21 @@ class TransformPairBatch:
     def clear_audio_state(self):
         check(self.lib.sgz_spectrum_clear_audio_state(self._h))
 
+    # -- resonator bank (algo = RSNT) ------------------------------------------------------
+    def resonating_dispatch(self, audio, layout=_abi.LAYOUT_INTERLEAVED):
+        """template<ISA> void resonatingDispatch(const Constant&, array<AFloat*, 2> buffer, size_t n)
+        (TransformDSP.inl:1215-1295) for every stream."""
+        keep, ptr, mem = _buf(audio)
+        s, n, stride = self._geometry(keep, layout)
+        assert s == self.n_streams
+        check(self.lib.sgz_resonator_process(self._h, ptr, mem, layout, n, stride))
+
+    def get_resonator_state(self):
+        V = self.info.resonator_vectors
+        out = np.empty((self.n_streams, self.channels, V, self.P, 2), dtype=np.float32)
+        check(self.lib.sgz_resonator_get_state(self._h, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
     # -- fused batched path ---------------------------------------------------------------
     def process_frames(self, audio, hop: int, n_frames: int, layout=_abi.LAYOUT_INTERLEAVED, out=None):
         """For every stream, `n_frames` frames at `hop`: the loop body of

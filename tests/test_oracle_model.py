@@ -161,3 +161,27 @@ def test_double_oracle_agrees_with_float_oracle():
     for s in range(2):
         peak = np.abs(d[s]).max()
         assert np.all(np.abs(np.abs(f[s, 1, bp:]) - np.abs(d[s, 1, bp:])) <= 1e-4 * np.abs(d[s, 1, bp:]) + 1e-6 * peak)
+
+
+def test_resonator_oracle_known_answers():
+    """The restated resonator bank (cpl decision): a steady tone peaks at the
+    filter nearest its frequency, block splitting does not change the state, and silence decays it."""
+    cfg = _abi.default_config(algo=_abi.ALGO_RSNT, window_size=4096, window_type=_abi.WIN_HANN, configuration=_abi.CH_LEFT)
+    n = np.arange(24000)
+    x = np.zeros((1, 24000, 2), np.float32)
+    x[0, :, 0] = 0.5 * np.sin(2 * np.pi * 2000.0 * n / 48000.0)
+    o = OracleSpectrum(cfg, 1)
+    assert o.info.resonator_vectors == 3  # Hann: 2 cosine terms -> 3 frequency-domain taps
+    o.resonate(x); o.map()
+    mag = np.hypot(*np.moveaxis(o.transform_result().reshape(1024, 2), -1, 0))
+    f = o.mapped_frequencies()
+    assert abs(f[mag.argmax()] - 2000.0) < 2000.0 * 0.01
+    whole = o.resonator_state().copy()
+    o2 = OracleSpectrum(cfg, 1)
+    for a, b in ((0, 1), (1, 7000), (7000, 24000)):
+        o2.resonate(x[:, a:b])
+    np.testing.assert_array_equal(o2.resonator_state(), whole)
+    o.resonate(np.zeros((1, 48000, 2), np.float32))
+    assert np.abs(o.resonator_state()).max() < 1e-3 * np.abs(whole).max()
+    o.clear_audio_state()
+    assert np.all(o.resonator_state() == 0)

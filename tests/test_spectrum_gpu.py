@@ -269,3 +269,60 @@ def test_full_size_c3_properties():
     first = h.process_frames(last, hop, 1)
     second = h.process_frames(last, hop, 1)
     np.testing.assert_array_equal(first, second)
+
+
+# ---------------------------------------------------------------------------------------------
+# resonator bank (BASELINE config 2: RDFT mode, 1 stereo stream, 1024 log-spaced bins, 48 kHz)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_MERGE, _abi.CH_SIDE, _abi.CH_PHASE, _abi.CH_SEPARATE, _abi.CH_MIDSIDE])
+@pytest.mark.parametrize("win", [_abi.WIN_RECTANGULAR, _abi.WIN_HANN, _abi.WIN_BLACKMAN_HARRIS])
+@pytest.mark.parametrize("S", [1, 3])
+def test_resonator_matches_oracle(conf, win, S):
+    cfg = _abi.default_config(algo=_abi.ALGO_RSNT, window_size=4096, window_type=win, configuration=conf)
+    o = OracleSpectrum(cfg, S)
+    g = TransformPairBatch(cfg, S)
+    assert g.info.resonator_vectors == o.info.resonator_vectors
+    pos = 0
+    total = signals.batch(S, 60000)
+    for block in (100, 1, 5000, 333, 48000):  # short blocks run sequentially, long ones are time-sliced
+        chunk = np.ascontiguousarray(total[:, pos:pos + block]); pos += block
+        o.resonate(chunk); g.resonating_dispatch(chunk)
+        complex_close(g.get_resonator_state().reshape(S, -1, 2), o.resonator_state().reshape(S, -1, 2), f"state after {pos}", rel=1e-4, floor=2e-5)
+    o.map(); g.map_to_linear_space()
+    P, ch = cfg.axis_points, o.channels
+    to = o.transform_result().reshape(S, ch, P, 2); tg = g.get_transform_result().reshape(S, ch, P, 2)
+    if conf == _abi.CH_PHASE:
+        assert_linear_close(tg[:, 0, :, 0], to[:, 0, :, 0], frame_axes=(1,), floor=2e-5, what="phase mid")
+        strong = to[:, 0, :, 0] > 1e-2 * to[:, 0, :, 0].max(axis=1, keepdims=True)
+        assert np.all(np.abs(tg[:, 0, :, 1][strong] - to[:, 0, :, 1][strong]) < 2e-3)
+    else:
+        complex_close(tg, to, "snapshot", rel=1e-4, floor=2e-5)
+    o.postprocess(); g.post_process_std_transform()
+    for k in range(2):
+        so, sg = o.states(k), g.get_states(k)
+        used = 1 if ch == 1 or conf == _abi.CH_PHASE else 2
+        assert_linear_close(sg[..., :used], so[..., :used], frame_axes=(1, 2), floor=2e-5, what=f"peak-hold states {k}")
+
+
+def test_resonator_frames_match_oracle_c2():
+    # config 2 through the frame entry: `hop` samples of resonation per frame, then snapshot + post
+    cfg = _abi.default_config(algo=_abi.ALGO_RSNT, window_size=8192, window_type=_abi.WIN_HANN, display_mode=_abi.DISPLAY_COLOURSPECTRUM,
+                              sample_buffer_size=480)
+    S, F, hop = 1, 20, 480
+    audio = signals.batch(S, F * hop, first_stream=3)
+    want = OracleSpectrum(cfg, S).process_frames(audio, hop, F)
+    got = TransformPairBatch(cfg, S).process_frames(audio, hop, F)
+    dy = 1.0 / np.log(1e6); low = 1e-6
+    lin = np.where(want > -300, low * np.exp(want.astype(np.float64) / dy), 0.0)
+    for f in range(F):
+        m = want[0, f] > -300
+        assert_log_close(got[0, f][m], want[0, f][m], lin=lin[0, f][m], peak=lin[0, f].max(), floor=2e-5, what=f"rsnt frame {f}")
+
+
+def test_resonator_clear_state():
+    cfg = _abi.default_config(algo=_abi.ALGO_RSNT, window_size=2048, window_type=_abi.WIN_HANN)
+    g = TransformPairBatch(cfg, 2)
+    g.resonating_dispatch(signals.batch(2, 1000))
+    assert np.abs(g.get_resonator_state()).max() > 0
+    g.clear_audio_state()
+    assert np.all(g.get_resonator_state() == 0)
