@@ -229,6 +229,93 @@ int  sgz_resonator_process(sgz_spectrum* h, const float* audio, int mem, int lay
 /* Raw resonator state (cresonator), [stream][channel][vector][filter] complex. */
 int  sgz_resonator_get_state(sgz_spectrum* h, float* out, int mem);
 
+/* ==== secondary paths: Vectorscope and Oscilloscope =========================
+ * These views have no per-view constant object; a light context owns the
+ * device, the CUDA stream and staging buffers for host-resident callers. */
+typedef struct sgz_context sgz_context;
+int  sgz_context_create(int device, sgz_context** out);
+void sgz_context_destroy(sgz_context* ctx);
+int  sgz_context_set_cuda_stream(sgz_context* ctx, void* cuda_stream);
+int  sgz_context_synchronize(sgz_context* ctx);
+
+/* channel views of Source/Oscilloscope/SampleColourEvaluators.h:57-320 */
+enum { SGZ_OSC_LEFT = 0, SGZ_OSC_RIGHT = 1, SGZ_OSC_MID = 2, SGZ_OSC_SIDE = 3 };
+
+/* ---- Vectorscope ----------------------------------------------------------
+ * Replaces the per-sample vertex arithmetic of `VectorScope::drawPolarPlot`
+ * (Source/Vectorscope/VectorscopeRendering.cpp:500-746) and `drawRectPlot`
+ * (:444-497): polar = 135 degree rotation, atan fold, sincos, radius
+ * max(|L|, |R|); Lissajous = (R, L); then gain (:512-517) and the optional
+ * 0..1 -> -1..1 height transform (:286-300).  xyz: [stream][sample][3]. */
+typedef struct sgz_vscope_config {
+    uint32_t abi_version;
+    int32_t  polar;        /* state.isPolar */
+    int32_t  scale_polar;  /* state.scalePolar */
+    float    gain;         /* processor->envelopeGain * state.userGain */
+    uint32_t width;        /* histogram size (the GL viewport it stands in for) */
+    uint32_t height;
+} sgz_vscope_config;
+int  sgz_vscope_vertices(sgz_context* ctx, const sgz_vscope_config* cfg, const float* audio, int mem,
+                         int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+                         float* xyz, int out_mem);
+/* The GL_POINTS rasterisation of those vertices (VectorscopeRendering.cpp:547,
+ * the reference hands it to OpenGL) as a point-density histogram:
+ * hist[stream][row][col] += 1 at floor((c + 1) * size / 2); points outside
+ * [-1, 1) are clipped.  `hist` is overwritten.  [stream][height][width]. */
+int  sgz_vscope_histogram(sgz_context* ctx, const sgz_vscope_config* cfg, const float* audio, int mem,
+                          int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+                          uint32_t* hist, int out_mem);
+/* Replaces `VectorScope::Processor::audioProcessing` (Source/Vectorscope/
+ * Vectorscope.cpp:268-377): RMS envelope, slow/fast balance and phase
+ * correlation one-pole filters.  `filters` (HOST, [stream]) is read, advanced
+ * over the block and written back. */
+typedef struct sgz_vscope_filters { float envelope[2]; float balance[2][2]; float phase[2]; } sgz_vscope_filters;
+int  sgz_vscope_meters(sgz_context* ctx, const float* audio, int mem, int layout, uint32_t n_streams,
+                       uint64_t n_samples, uint64_t stream_stride, float envelope_coeff,
+                       float stereo_coeff, float second_stereo_filter_speed, sgz_vscope_filters* filters);
+
+/* ---- Oscilloscope ---------------------------------------------------------
+ * Replaces the Lanczos branch of `Oscilloscope::drawWavePlot`
+ * (Source/Oscilloscope/OscilloscopeRendering.cpp:790-891): windowed-sinc
+ * (a = 10, 21-tap sliding buffer) resampling of the newest samples to one
+ * vertex per output step.  `sample_pos` (HOST, [stream]) is `samplePos` after
+ * :826; the buffer's last sample is the newest.  out_xy: [stream][count][2],
+ * count = sgz_scope_resample_count(cfg). */
+typedef struct sgz_scope_resample_config {
+    uint32_t abi_version;
+    int32_t  channel;            /* SGZ_OSC_* */
+    double   samples_per_pixel;  /* 1 / pixelsPerSample (:824) */
+    double   left, right, inc;   /* unit-space range and step (:562-563, :822) */
+} sgz_scope_resample_config;
+uint64_t sgz_scope_resample_count(const sgz_scope_resample_config* cfg);
+int  sgz_scope_resample(sgz_context* ctx, const sgz_scope_resample_config* cfg, const double* sample_pos,
+                        const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+                        uint64_t stream_stride, float* out_xy, int out_mem);
+/* Replaces `ZeroCrossingProcessor::process` (mode 0) and
+ * `PeakHoldProcessor::process` (mode 1) driven by executeSamplingWindows
+ * (Source/Oscilloscope/StreamPreprocessing.h:284-347, OscilloscopeDSP.inl:
+ * 310-385): scans a block and appends trigger positions (steady-clock sample
+ * indices) per stream.  states / peaks / counts are HOST arrays; a stream that
+ * produces more than max_peaks keeps the first max_peaks and reports the full
+ * count. */
+typedef struct sgz_scope_trigger_state { double state; uint64_t cross_origin; int32_t is_peak_holding; int32_t reserved; } sgz_scope_trigger_state;
+int  sgz_scope_trigger(sgz_context* ctx, int mode, int channel, const float* audio, int mem, int layout,
+                       uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride, double threshold,
+                       double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* states,
+                       uint64_t* peaks, uint32_t* counts, uint32_t max_peaks);
+/* Replaces `calculateFundamentalPeriod` + `calculateTriggeringOffset`
+ * (Source/Oscilloscope/OscilloscopeDSP.inl:61-308, Spectral trigger mode):
+ * 8192-point float64 FFT of the newest samples, fundamental pick with
+ * harmonic rejection and quadratic bin offset, 8-deep median, then a Goertzel
+ * phase at the fractional bin -> sample offset.  state / result: HOST [stream]. */
+typedef struct sgz_scope_bin_record { uint64_t index; double value; double offset; } sgz_scope_bin_record;
+typedef struct sgz_scope_period_state { sgz_scope_bin_record median[8]; uint64_t median_pos; } sgz_scope_period_state;
+typedef struct sgz_scope_period_params { uint32_t abi_version; int32_t channel; double effective_window_size, sample_rate, threshold, hysteresis, phase_offset_degrees; } sgz_scope_period_params;
+typedef struct sgz_scope_period_result { sgz_scope_bin_record record; double fundamental, cycle_samples, phase, sample_offset; } sgz_scope_period_result;
+int  sgz_scope_period(sgz_context* ctx, const sgz_scope_period_params* params, const float* audio, int mem,
+                      int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+                      sgz_scope_period_state* states, sgz_scope_period_result* results);
+
 /* ---- allocation-free forward FFT ------------------------------------------
  * No counterpart in the reference.  For callers that cannot allocate device
  * memory at call time (real-time audio / render callbacks, hosts that forbid

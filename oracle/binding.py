@@ -208,3 +208,85 @@ class OracleSpectrum:
 
 def hardware_concurrency() -> int:
     return int(load().sgzo_hardware_concurrency())
+
+
+# ---- secondary paths (oracle/sgz_oracle_scope.hpp) -------------------------------------------------
+def _scope_lib():
+    lib = load()
+    if getattr(lib, "_scope_ready", False):
+        return lib
+    vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+    fp = C.POINTER(C.c_float)
+    vc = C.POINTER(_abi.VScopeConfig)
+    lib.sgzo_vscope_vertices.argtypes = [vc, fp, i32, u32, u64, u64, fp]
+    lib.sgzo_vscope_histogram.argtypes = [vc, fp, i32, u32, u64, u64, C.POINTER(C.c_uint32)]
+    lib.sgzo_vscope_meters.argtypes = [fp, i32, u32, u64, u64, C.c_float, C.c_float, C.c_float, C.POINTER(_abi.VScopeFilters)]
+    rc = C.POINTER(_abi.ScopeResampleConfig)
+    lib.sgzo_scope_resample_count.argtypes = [rc]
+    lib.sgzo_scope_resample_count.restype = C.c_uint64
+    lib.sgzo_scope_resample.argtypes = [rc, C.POINTER(C.c_double), fp, i32, u32, u64, u64, fp]
+    lib.sgzo_scope_trigger.argtypes = [i32, i32, fp, i32, u32, u64, u64, C.c_double, C.c_double, u64, C.POINTER(_abi.ScopeTriggerState),
+                                       C.POINTER(C.c_uint64), C.POINTER(u32), u32]
+    lib.sgzo_scope_period.argtypes = [C.POINTER(_abi.ScopePeriodParams), fp, i32, u32, u64, u64, C.POINTER(_abi.ScopePeriodState),
+                                      C.POINTER(_abi.ScopePeriodResult)]
+    lib._scope_ready = True
+    return lib
+
+
+def _geom(a, layout):
+    n = a.shape[1] if layout == _abi.LAYOUT_INTERLEAVED else a.shape[2]
+    return a.shape[0], n, a[0].size
+
+
+class OracleScope:
+    """CPU restatement of the Vectorscope / Oscilloscope arithmetic (test infrastructure only)."""
+
+    def __init__(self):
+        self.lib = _scope_lib()
+
+    def vscope_vertices(self, cfg, audio, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        out = np.empty((S, n, 3), dtype=np.float32)
+        self.lib.sgzo_vscope_vertices(C.byref(cfg), p, layout, S, n, stride, out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
+
+    def vscope_histogram(self, cfg, audio, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        out = np.empty((S, cfg.height, cfg.width), dtype=np.uint32)
+        self.lib.sgzo_vscope_histogram(C.byref(cfg), p, layout, S, n, stride, out.ctypes.data_as(C.POINTER(C.c_uint32)))
+        return out
+
+    def vscope_meters(self, audio, filters, envelope_coeff, stereo_coeff, second_speed, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        self.lib.sgzo_vscope_meters(p, layout, S, n, stride, envelope_coeff, stereo_coeff, second_speed, filters)
+        return filters
+
+    def scope_resample_count(self, cfg):
+        return int(self.lib.sgzo_scope_resample_count(C.byref(cfg)))
+
+    def scope_resample(self, cfg, sample_pos, audio, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        pos = np.ascontiguousarray(sample_pos, dtype=np.float64)
+        out = np.empty((S, self.scope_resample_count(cfg), 2), dtype=np.float32)
+        self.lib.sgzo_scope_resample(C.byref(cfg), pos.ctypes.data_as(C.POINTER(C.c_double)), p, layout, S, n, stride, out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
+
+    def scope_trigger(self, mode, channel, audio, states, threshold, hysteresis=0.0, steady_clock=0, max_peaks=4096, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        peaks = np.zeros((S, max_peaks), dtype=np.uint64)
+        counts = np.zeros(S, dtype=np.uint32)
+        self.lib.sgzo_scope_trigger(mode, channel, p, layout, S, n, stride, threshold, hysteresis, steady_clock, states,
+                                    peaks.ctypes.data_as(C.POINTER(C.c_uint64)), counts.ctypes.data_as(C.POINTER(C.c_uint32)), max_peaks)
+        return [peaks[s, :min(int(counts[s]), max_peaks)].copy() for s in range(S)], counts
+
+    def scope_period(self, params, audio, states, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        results = (_abi.ScopePeriodResult * S)()
+        self.lib.sgzo_scope_period(C.byref(params), p, layout, S, n, stride, states, results)
+        return results

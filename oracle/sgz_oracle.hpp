@@ -305,8 +305,8 @@ namespace sgzo
 				const double s0 = static_cast<double>(x[n]) + c * s1 - s2;
 				s2 = s1; s1 = s0;
 			}
-			// y = e^{i omega} s1 - s2 equals sum x[n] e^{-i omega (n - (N-1))}; rotate back
-			const std::complex<double> y = std::complex<double>(std::cos(omega), std::sin(omega)) * s1 - s2;
+			// y = s[N-1] - e^{-i omega} s[N-2] = sum x[n] e^{i omega (N-1-n)}; rotate back by (N-1) omega
+			const std::complex<double> y = s1 - std::complex<double>(std::cos(omega), -std::sin(omega)) * s2;
 			const double back = -omega * double(N - 1);
 			return y * std::complex<double>(std::cos(back), std::sin(back));
 		}

@@ -448,3 +448,121 @@ extern "C"
 	}
 	unsigned sgzo_hardware_concurrency(void) { return std::thread::hardware_concurrency(); }
 }
+
+// ---------------------------------------------------------------------------------------------
+// secondary paths (sgz_oracle_scope.hpp)
+// ---------------------------------------------------------------------------------------------
+#include "sgz_oracle_scope.hpp"
+
+namespace
+{
+	VScopeParams toParams(const sgz_vscope_config* c)
+	{
+		VScopeParams p;
+		p.polar = c->polar != 0; p.scalePolar = c->scale_polar != 0; p.gain = c->gain; p.width = c->width; p.height = c->height;
+		return p;
+	}
+	std::vector<float> channelOf(int channel, const StreamAudio& sa, uint64_t n)
+	{
+		std::vector<float> x(n);
+		for (uint64_t i = 0; i < n; ++i) x[i] = oscChannel(static_cast<OscChannels>(channel), sa.ch[0][i], sa.ch[1][i]);
+		return x;
+	}
+}
+
+extern "C"
+{
+	void sgzo_vscope_vertices(const sgz_vscope_config* cfg, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, float* xyz)
+	{
+		const VScopeParams p = toParams(cfg);
+		StreamAudio sa;
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			fetch(audio, layout, n, stride, s, sa);
+			for (uint64_t i = 0; i < n; ++i)
+			{
+				const Vertex v = vscopeVertex(p, sa.ch[0][i], sa.ch[1][i], i, n);
+				float* o = xyz + (uint64_t(s) * n + i) * 3;
+				o[0] = v.x; o[1] = v.y; o[2] = v.z;
+			}
+		}
+	}
+	void sgzo_vscope_histogram(const sgz_vscope_config* cfg, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, uint32_t* hist)
+	{
+		const VScopeParams p = toParams(cfg);
+		StreamAudio sa;
+		std::fill(hist, hist + uint64_t(S) * p.width * p.height, 0u);
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			fetch(audio, layout, n, stride, s, sa);
+			vscopeHistogram(p, sa.ch[0], sa.ch[1], n, hist + uint64_t(s) * p.width * p.height);
+		}
+	}
+	void sgzo_vscope_meters(const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, float envelopeCoeff, float stereoCoeff, float speed, sgz_vscope_filters* filters)
+	{
+		StreamAudio sa;
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			fetch(audio, layout, n, stride, s, sa);
+			VScopeFilters f;
+			std::memcpy(static_cast<void*>(&f), &filters[s], sizeof(f));
+			vscopeMeters(f, sa.ch[0], sa.ch[1], n, envelopeCoeff, stereoCoeff, speed);
+			std::memcpy(&filters[s], static_cast<const void*>(&f), sizeof(f));
+		}
+	}
+	uint64_t sgzo_scope_resample_count(const sgz_scope_resample_config* cfg)
+	{
+		ResampleParams p; p.left = cfg->left; p.right = cfg->right; p.inc = cfg->inc;
+		return resampleCount(p);
+	}
+	void sgzo_scope_resample(const sgz_scope_resample_config* cfg, const double* samplePos, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, float* out)
+	{
+		StreamAudio sa;
+		ResampleParams p; p.left = cfg->left; p.right = cfg->right; p.inc = cfg->inc; p.samplesPerPixel = cfg->samples_per_pixel;
+		const uint64_t count = resampleCount(p);
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			fetch(audio, layout, n, stride, s, sa);
+			const auto x = channelOf(cfg->channel, sa, n);
+			p.samplePos = samplePos[s];
+			lanczosResample(p, x.data(), (std::ptrdiff_t)n, out + uint64_t(s) * count * 2);
+		}
+	}
+	void sgzo_scope_trigger(int mode, int channel, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, double threshold, double hysteresis,
+		uint64_t steadyClock, sgz_scope_trigger_state* states, uint64_t* peaks, uint32_t* counts, uint32_t maxPeaks)
+	{
+		StreamAudio sa;
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			fetch(audio, layout, n, stride, s, sa);
+			const auto x = channelOf(channel, sa, n);
+			TriggerState st; st.state = states[s].state; st.isPeakHolding = states[s].is_peak_holding != 0; st.crossOrigin = states[s].cross_origin;
+			std::vector<uint64_t> found;
+			if (mode == 0) zeroCrossingTrigger(st, x.data(), n, threshold, steadyClock, found);
+			else peakHoldTrigger(st, x.data(), n, threshold, hysteresis, steadyClock, found);
+			states[s].state = st.state; states[s].is_peak_holding = st.isPeakHolding ? 1 : 0; states[s].cross_origin = st.crossOrigin;
+			counts[s] = (uint32_t)found.size();
+			for (uint32_t k = 0; k < found.size() && k < maxPeaks; ++k) peaks[uint64_t(s) * maxPeaks + k] = found[k];
+		}
+	}
+	void sgzo_scope_period(const sgz_scope_period_params* prm, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride,
+		sgz_scope_period_state* states, sgz_scope_period_result* results)
+	{
+		StreamAudio sa;
+		PeriodParams p; p.effectiveWindowSize = prm->effective_window_size; p.sampleRate = prm->sample_rate; p.threshold = prm->threshold;
+		p.hysteresis = prm->hysteresis; p.phaseOffsetDegrees = prm->phase_offset_degrees;
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			fetch(audio, layout, n, stride, s, sa);
+			const auto x = channelOf(prm->channel, sa, n);
+			PeriodState st;
+			for (int k = 0; k < 8; ++k) { st.median[k].index = states[s].median[k].index; st.median[k].value = states[s].median[k].value; st.median[k].offset = states[s].median[k].offset; }
+			st.medianPos = states[s].median_pos;
+			const PeriodResult r = spectralPeriod(st, p, x.data(), (std::ptrdiff_t)n);
+			for (int k = 0; k < 8; ++k) { states[s].median[k].index = st.median[k].index; states[s].median[k].value = st.median[k].value; states[s].median[k].offset = st.median[k].offset; }
+			states[s].median_pos = st.medianPos;
+			results[s].record.index = r.record.index; results[s].record.value = r.record.value; results[s].record.offset = r.record.offset;
+			results[s].fundamental = r.fundamental; results[s].cycle_samples = r.cycleSamples; results[s].phase = r.phase; results[s].sample_offset = r.sampleOffset;
+		}
+	}
+}

@@ -109,3 +109,51 @@ def copy_config(cfg: SpectrumConfig, **overrides) -> SpectrumConfig:
         else:
             setattr(out, k, v)
     return out
+
+
+# ---- secondary paths (include/sgz.h: Vectorscope / Oscilloscope) --------------------------------
+OSC_LEFT, OSC_RIGHT, OSC_MID, OSC_SIDE = range(4)
+
+
+class VScopeConfig(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("polar", C.c_int32), ("scale_polar", C.c_int32), ("gain", C.c_float),
+                ("width", C.c_uint32), ("height", C.c_uint32)]
+
+
+class VScopeFilters(C.Structure):
+    _fields_ = [("envelope", C.c_float * 2), ("balance", (C.c_float * 2) * 2), ("phase", C.c_float * 2)]
+
+
+class ScopeResampleConfig(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("channel", C.c_int32), ("samples_per_pixel", C.c_double),
+                ("left", C.c_double), ("right", C.c_double), ("inc", C.c_double)]
+
+
+class ScopeTriggerState(C.Structure):
+    _fields_ = [("state", C.c_double), ("cross_origin", C.c_uint64), ("is_peak_holding", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ScopeBinRecord(C.Structure):
+    _fields_ = [("index", C.c_uint64), ("value", C.c_double), ("offset", C.c_double)]
+
+
+class ScopePeriodState(C.Structure):
+    _fields_ = [("median", ScopeBinRecord * 8), ("median_pos", C.c_uint64)]
+
+
+class ScopePeriodParams(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("channel", C.c_int32), ("effective_window_size", C.c_double), ("sample_rate", C.c_double),
+                ("threshold", C.c_double), ("hysteresis", C.c_double), ("phase_offset_degrees", C.c_double)]
+
+
+class ScopePeriodResult(C.Structure):
+    _fields_ = [("record", ScopeBinRecord), ("fundamental", C.c_double), ("cycle_samples", C.c_double), ("phase", C.c_double),
+                ("sample_offset", C.c_double)]
+
+
+def vscope_config(polar=True, scale_polar=False, gain=1.0, width=512, height=512) -> VScopeConfig:
+    return VScopeConfig(ABI_VERSION, int(polar), int(scale_polar), gain, width, height)
+
+
+def resample_config(channel=OSC_LEFT, samples_per_pixel=1.0 / 16, left=0.0, right=1.0, inc=1.0 / 1024) -> ScopeResampleConfig:
+    return ScopeResampleConfig(ABI_VERSION, channel, samples_per_pixel, left, right, inc)

@@ -23,6 +23,9 @@ EXPORTS = [
     "sgz_spectrum_set_states", "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state",
     "sgz_spectrum_process_frames", "sgz_fft_forward_noalloc",
     "sgz_resonator_process", "sgz_resonator_get_state",
+    "sgz_context_create", "sgz_context_destroy", "sgz_context_set_cuda_stream", "sgz_context_synchronize",
+    "sgz_vscope_vertices", "sgz_vscope_histogram", "sgz_vscope_meters",
+    "sgz_scope_resample_count", "sgz_scope_resample", "sgz_scope_trigger", "sgz_scope_period",
 ]
 
 
@@ -73,12 +76,29 @@ def load():
     lib.sgz_spectrum_get_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_set_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_process_frames.argtypes = [vp, fp, i32, i32, u64, u64, u32, u32, fp, i32]
+    lib.sgz_context_create.argtypes = [i32, C.POINTER(vp)]
+    lib.sgz_context_destroy.argtypes = [vp]
+    lib.sgz_context_destroy.restype = None
+    lib.sgz_context_set_cuda_stream.argtypes = [vp, vp]
+    lib.sgz_context_synchronize.argtypes = [vp]
+    vc = C.POINTER(_abi.VScopeConfig)
+    lib.sgz_vscope_vertices.argtypes = [vp, vc, fp, i32, i32, u32, u64, u64, fp, i32]
+    lib.sgz_vscope_histogram.argtypes = [vp, vc, fp, i32, i32, u32, u64, u64, fp, i32]
+    lib.sgz_vscope_meters.argtypes = [vp, fp, i32, i32, u32, u64, u64, C.c_float, C.c_float, C.c_float, C.POINTER(_abi.VScopeFilters)]
+    rc_ = C.POINTER(_abi.ScopeResampleConfig)
+    lib.sgz_scope_resample_count.argtypes = [rc_]
+    lib.sgz_scope_resample_count.restype = C.c_uint64
+    lib.sgz_scope_resample.argtypes = [vp, rc_, C.POINTER(C.c_double), fp, i32, i32, u32, u64, u64, fp, i32]
+    lib.sgz_scope_trigger.argtypes = [vp, i32, i32, fp, i32, i32, u32, u64, u64, C.c_double, C.c_double, u64,
+                                      C.POINTER(_abi.ScopeTriggerState), C.POINTER(C.c_uint64), C.POINTER(u32), u32]
+    lib.sgz_scope_period.argtypes = [vp, C.POINTER(_abi.ScopePeriodParams), fp, i32, i32, u32, u64, u64,
+                                     C.POINTER(_abi.ScopePeriodState), C.POINTER(_abi.ScopePeriodResult)]
     lib.sgz_resonator_process.argtypes = [vp, fp, i32, i32, u64, u64]
     lib.sgz_resonator_get_state.argtypes = [vp, fp, i32]
     lib.sgz_fft_forward_noalloc.argtypes = [fp, fp, u32, u32, vp]
     for n in EXPORTS:
         f = getattr(lib, n)  # raises AttributeError if the symbol is not exported
-        if n not in ("sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_destroy"):
+        if n not in ("sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_destroy", "sgz_context_destroy", "sgz_scope_resample_count"):
             f.restype = C.c_int
     _lib = lib
     return lib

@@ -1,0 +1,820 @@
+// sgz_scope.cu — sm_100a kernels and C ABI of the secondary paths: Vectorscope (polar / Lissajous
+// vertices, point-density histogram, stereo meters) and Oscilloscope (Lanczos resampler, stream
+// triggers, spectral period search).  References are relative to the reference checkout.
+//
+// Bit-exactness: histogram counts and trigger positions must equal the CPU oracle's exactly, so the
+// float/double arithmetic that decides them is written with explicit round-to-nearest intrinsics
+// (__fmul_rn, __fadd_rn, ...) that the compiler may not contract into FMAs.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/sgz.h"
+#include "sgz_device.cuh"
+
+namespace sgz
+{
+	int fail(int code, const char* fmt, ...); // sgz_spectrum.cu
+}
+
+#define SGZS_CUDA(expr)                                                                                         \
+	do {                                                                                                        \
+		cudaError_t e__ = (expr);                                                                               \
+		if (e__ != cudaSuccess)                                                                                 \
+			return sgz::fail(SGZ_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+	} while (0)
+
+struct sgz_context
+{
+	int device{ 0 };
+	cudaStream_t stream{ nullptr };
+	bool ownStream{ false };
+	void* stage[4]{ nullptr, nullptr, nullptr, nullptr };
+	size_t stageBytes[4]{ 0, 0, 0, 0 };
+};
+
+namespace sgz
+{
+	struct CtxGuard
+	{
+		int prev{ -1 };
+		bool ok{ true };
+		explicit CtxGuard(int dev)
+		{
+			if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+			if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+		}
+		~CtxGuard() { if (prev >= 0) cudaSetDevice(prev); }
+	};
+
+	static int ensure(sgz_context* c, int slot, size_t need, void** out)
+	{
+		if (c->stageBytes[slot] < need)
+		{
+			if (c->stage[slot]) { cudaFree(c->stage[slot]); c->stage[slot] = nullptr; c->stageBytes[slot] = 0; }
+			SGZS_CUDA(cudaMalloc(&c->stage[slot], std::max<size_t>(need, 256)));
+			c->stageBytes[slot] = std::max<size_t>(need, 256);
+		}
+		*out = c->stage[slot];
+		return SGZ_OK;
+	}
+
+	static int validateAudio(const float* audio, int layout, uint32_t nStreams, uint64_t n, uint64_t stride)
+	{
+		if (!audio) return fail(SGZ_EINVAL, "null audio");
+		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
+		if (nStreams == 0) return fail(SGZ_EINVAL, "zero streams");
+		if (nStreams > 1 && stride < 2 * n) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stride & 1) || (reinterpret_cast<uintptr_t>(audio) & 7)))
+			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
+		return SGZ_OK;
+	}
+
+	static int stageIn(sgz_context* c, const float* audio, int mem, uint32_t nStreams, uint64_t n, uint64_t stride, const float** dptr)
+	{
+		if (mem == SGZ_MEM_DEVICE) { *dptr = audio; return SGZ_OK; }
+		const size_t floats = size_t(stride) * (nStreams - 1) + size_t(n) * 2;
+		void* p = nullptr;
+		const int rc = ensure(c, 0, floats * sizeof(float), &p);
+		if (rc != SGZ_OK) return rc;
+		SGZS_CUDA(cudaMemcpyAsync(p, audio, floats * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+		*dptr = static_cast<const float*>(p);
+		return SGZ_OK;
+	}
+
+	__device__ __forceinline__ void loadLR(const float* base, int layout, uint64_t n, uint64_t i, float& l, float& r)
+	{
+		if (layout == SGZ_LAYOUT_INTERLEAVED) { const float2 v = reinterpret_cast<const float2*>(base)[i]; l = v.x; r = v.y; }
+		else { l = base[i]; r = base[n + i]; }
+	}
+
+	__device__ __forceinline__ float oscChannel(int mode, float l, float r)
+	{
+		switch (mode)
+		{
+		case SGZ_OSC_LEFT: return l;
+		case SGZ_OSC_RIGHT: return r;
+		case SGZ_OSC_MID: return __fmul_rn(0.5f, __fadd_rn(l, r));
+		default: return __fmul_rn(0.5f, __fsub_rn(l, r));
+		}
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// Vectorscope
+	// ------------------------------------------------------------------------------------------
+	// (sin, cos)(atan(X / Y)) as (t, 1) / sqrt(1 + t^2), correctly rounded operation by operation
+	// (cpl::simd::atan / sincos are unknown SSE polynomials; DESIGN.md "cpl decisions")
+	__device__ __forceinline__ void sincosOfAtanRatio(float X, float Y, float& sx, float& cx)
+	{
+		const float aX = fabsf(X), aY = fabsf(Y);
+		if (aX == 0.0f && aY == 0.0f) { sx = 0.0f; cx = 1.0f; return; }
+		if (aY >= aX)
+		{
+			const float t = __fdiv_rn(X, Y);
+			const float h = __fsqrt_rn(__fadd_rn(1.0f, __fmul_rn(t, t)));
+			cx = __fdiv_rn(1.0f, h);
+			sx = __fdiv_rn(t, h);
+		}
+		else
+		{
+			const float u = __fdiv_rn(Y, X);
+			const float h = __fsqrt_rn(__fadd_rn(1.0f, __fmul_rn(u, u)));
+			cx = __fdiv_rn(fabsf(u), h);
+			const float m = __fdiv_rn(1.0f, h);
+			sx = (signbit(X) != signbit(Y)) ? -m : m;
+		}
+	}
+
+	__device__ __forceinline__ float3 vscopeVertex(const sgz_vscope_config& p, float left, float right, uint64_t i, uint64_t numSamples)
+	{
+		float3 v;
+		if (p.polar)
+		{
+			const float cosineRotation = -0.70710678118654752440f, sineRotation = 0.70710678118654752440f;
+			const float length = fmaxf(fabsf(left), fabsf(right));
+			const float vY = __fsub_rn(__fmul_rn(left, cosineRotation), __fmul_rn(right, sineRotation));
+			const float vX = __fadd_rn(__fmul_rn(left, sineRotation), __fmul_rn(right, cosineRotation));
+			float sx, cx;
+			if (left == 0.0f && right == 0.0f) { sx = 0.0f; cx = 1.0f; }
+			else sincosOfAtanRatio(vX, vY, sx, cx);
+			const float fadePerSample = __fdiv_rn(1.0f, float(numSamples));
+			v = make_float3(__fmul_rn(sx, length), __fmul_rn(cx, length), __fsub_rn(__fmul_rn(float(i), fadePerSample), 1.0f));
+		}
+		else
+		{
+			const long long denom = (long long)numSamples - 1;
+			const float sampleFade = __fdiv_rn(1.0f, float(denom < 1 ? 1 : int(denom)));
+			v = make_float3(right, left, __fsub_rn(__fmul_rn(float(i), sampleFade), 1.0f));
+		}
+		v.x = __fmul_rn(v.x, p.gain); v.y = __fmul_rn(v.y, p.gain);
+		if (p.polar && p.scale_polar) v.y = __fsub_rn(__fmul_rn(v.y, 2.0f), 1.0f);
+		return v;
+	}
+
+	__global__ void k_vscope_vertices(sgz_vscope_config p, const float* __restrict__ audio, int layout, uint64_t n, uint64_t stride, float* __restrict__ xyz)
+	{
+		const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+		const uint32_t s = blockIdx.y;
+		if (i >= n) return;
+		float l, r;
+		loadLR(audio + uint64_t(s) * stride, layout, n, i, l, r);
+		const float3 v = vscopeVertex(p, l, r, i, n);
+		float* o = xyz + (uint64_t(s) * n + i) * 3;
+		o[0] = v.x; o[1] = v.y; o[2] = v.z;
+	}
+
+	// one CTA column per stream slice; counts go straight to the L2-resident histogram with
+	// no-return reductions (RED.ADD), the natural fit for a 1 MiB-per-stream target
+	__global__ void k_vscope_histogram(sgz_vscope_config p, const float* __restrict__ audio, int layout, uint64_t n, uint64_t stride, uint32_t* __restrict__ hist)
+	{
+		const uint32_t s = blockIdx.y;
+		const float hw = __fmul_rn(0.5f, float(p.width)), hh = __fmul_rn(0.5f, float(p.height));
+		uint32_t* h = hist + uint64_t(s) * p.width * p.height;
+		for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += uint64_t(gridDim.x) * blockDim.x)
+		{
+			float l, r;
+			loadLR(audio + uint64_t(s) * stride, layout, n, i, l, r);
+			const float3 v = vscopeVertex(p, l, r, i, n);
+			const float fx = floorf(__fmul_rn(__fadd_rn(v.x, 1.0f), hw)), fy = floorf(__fmul_rn(__fadd_rn(v.y, 1.0f), hh));
+			if (!(fx >= 0.0f && fx < float(p.width) && fy >= 0.0f && fy < float(p.height))) continue;
+			atomicAdd(h + size_t(fy) * p.width + size_t(fx), 1u);
+		}
+	}
+
+	__device__ __forceinline__ float cosTwiceAtan(float y, float x)
+	{
+		if (x == 0.0f && y == 0.0f) return 0.0f;
+		if (fabsf(x) >= fabsf(y)) { const float t = __fdiv_rn(y, x); const float t2 = __fmul_rn(t, t); return __fdiv_rn(__fsub_rn(1.0f, t2), __fadd_rn(1.0f, t2)); }
+		const float u = __fdiv_rn(x, y); const float u2 = __fmul_rn(u, u); return __fdiv_rn(__fsub_rn(u2, 1.0f), __fadd_rn(u2, 1.0f));
+	}
+
+	// one warp per stream: lanes compute the per-sample inputs of 32 samples in parallel, lanes 0..7
+	// then each run one of the eight one-pole recurrences over them in order (bit-exact with the
+	// sequential reference; the filters are y <- x + p (y - x))
+	__global__ void k_vscope_meters(const float* __restrict__ audio, int layout, uint64_t n, uint64_t stride, uint32_t nStreams,
+		float envelopeCoeff, float pole0, float pole1, float* __restrict__ filters /* [S][8] */)
+	{
+		const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+		if (warp >= nStreams) return;
+		const float* base = audio + uint64_t(warp) * stride;
+		// filter slots: 0,1 envelope L/R; 2,3 balance slow L/R; 4,5 balance fast L/R; 6 phase slow; 7 phase fast
+		float y = lane < 8 ? filters[warp * 8 + lane] : 0.f;
+		const float pole = lane < 2 ? envelopeCoeff : ((lane == 2 || lane == 3 || lane == 6) ? pole0 : pole1);
+		const int src = lane < 6 ? (lane & 1) : 2; // which input the slot consumes: lSquared, rSquared, phase
+		const float mr = -0.70710678118654752440f, mi = 0.70710678118654752440f;
+		for (uint64_t n0 = 0; n0 < n; n0 += 32)
+		{
+			float l = 0.f, r = 0.f;
+			if (n0 + lane < n) loadLR(base, layout, n, n0 + lane, l, r);
+			const float lSq = __fmul_rn(l, l), rSq = __fmul_rn(r, r);
+			const float vX = __fsub_rn(__fmul_rn(l, mr), __fmul_rn(r, mi));
+			const float vY = __fadd_rn(__fmul_rn(r, mi), __fmul_rn(l, mr));
+			const float ph = cosTwiceAtan(vY, vX);
+			const int count = int(min(uint64_t(32), n - n0));
+			for (int j = 0; j < count; ++j)
+			{
+				const float a = __shfl_sync(0xffffffffu, lSq, j), b = __shfl_sync(0xffffffffu, rSq, j), c = __shfl_sync(0xffffffffu, ph, j);
+				const float x = src == 0 ? a : (src == 1 ? b : c);
+				y = __fadd_rn(x, __fmul_rn(pole, __fsub_rn(y, x)));
+			}
+		}
+		if (lane < 8) filters[warp * 8 + lane] = y;
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// Oscilloscope: Lanczos resampler (a = 10, 21-tap window)
+	// ------------------------------------------------------------------------------------------
+	struct ResampleArgs
+	{
+		const float* audio; int layout; uint64_t n; uint64_t stride; int channel;
+		const double* samplePos; // [S] device
+		double spp, left, inc; uint64_t count;
+		float* out;
+	};
+
+	__device__ __forceinline__ double sincD(double x)
+	{
+		if (x == 0.0) return 1.0;
+		const double px = 3.1415926535897932384626433832795 * x;
+		return sin(px) / px;
+	}
+
+	__global__ void k_scope_resample(ResampleArgs a)
+	{
+		const uint64_t m = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+		const uint32_t s = blockIdx.y;
+		if (m >= a.count) return;
+		constexpr int KernelSize = 10, KernelBufferSize = 21;
+		const double samplePos0 = a.samplePos[s];
+		const double fl0 = floor(samplePos0);
+		// closed form of the sequential loop at OscilloscopeRendering.cpp:863-886: after m steps
+		// currentSample = floor(samplePos0) + m spp, and the window has advanced k whole samples so
+		// that delta = currentSample - (samplePos0 + k) <= 1
+		const double currentSample = fl0 + double(m) * a.spp;
+		const double d0 = currentSample - samplePos0;
+		const double k = d0 > 1.0 ? ceil(d0 - 1.0) : 0.0;
+		const double delta = currentSample - (samplePos0 + k);
+		const long long base = (long long)a.n - (long long)fl0 - KernelSize + (long long)k; // index of kernel[0]
+		const double x = double(KernelSize) + delta;
+		const double fx = floor(x);
+		const int ib = int(fx);
+		const float* src = a.audio + uint64_t(s) * a.stride;
+		double acc = 0.0;
+		for (int i = ib - KernelSize + 1; i <= ib + KernelSize; ++i)
+		{
+			if (i < 0 || i >= KernelBufferSize) continue;
+			const long long idx = base + i;
+			float v = 0.f;
+			if (idx >= 0 && idx < (long long)a.n)
+			{
+				float l, r;
+				loadLR(src, a.layout, a.n, uint64_t(idx), l, r);
+				v = oscChannel(a.channel, l, r);
+			}
+			const double d = x - double(i);
+			double w = 0.0;
+			if (d > -double(KernelSize) && d < double(KernelSize)) w = sincD(d) * sincD(d / KernelSize);
+			acc += double(v) * w;
+		}
+		float* o = a.out + (uint64_t(s) * a.count + m) * 2;
+		o[0] = float(a.left + double(m) * a.inc);
+		o[1] = float(acc);
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// Oscilloscope: stream triggers.  One warp per stream, 32 samples per step.
+	// ------------------------------------------------------------------------------------------
+	struct TriggerArgs
+	{
+		const float* audio; int layout; uint64_t n; uint64_t stride; int channel; uint32_t nStreams;
+		double threshold, hysteresis; uint64_t steadyClock;
+		sgz_scope_trigger_state* states; uint64_t* peaks; uint32_t* counts; uint32_t maxPeaks;
+	};
+
+	// ZeroCrossingProcessor::process (StreamPreprocessing.h:331-347): the per-sample predicates are
+	// evaluated by the lanes, the tiny state machine then walks the two ballot masks
+	__global__ void k_scope_trigger_zero(TriggerArgs a)
+	{
+		const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+		if (warp >= a.nStreams) return;
+		const float* base = a.audio + uint64_t(warp) * a.stride;
+		sgz_scope_trigger_state st = a.states[warp];
+		double prev = st.state;
+		bool holding = st.is_peak_holding != 0;
+		uint64_t origin = st.cross_origin;
+		uint32_t count = 0;
+		for (uint64_t n0 = 0; n0 < a.n; n0 += 32)
+		{
+			float x = 0.f;
+			const bool valid = n0 + lane < a.n;
+			if (valid) { float l, r; loadLR(base, a.layout, a.n, n0 + lane, l, r); x = oscChannel(a.channel, l, r); }
+			const double sample = double(x);
+			double before = __shfl_up_sync(0xffffffffu, sample, 1);
+			if (lane == 0) before = prev;
+			const uint32_t cross = __ballot_sync(0xffffffffu, valid && sample > 0 && before < 0);
+			const uint32_t above = __ballot_sync(0xffffffffu, valid && sample > a.threshold);
+			uint32_t todo = cross | above;
+			while (todo)
+			{
+				const int j = __ffs(todo) - 1;
+				todo &= todo - 1;
+				if (cross & (1u << j)) { holding = true; origin = a.steadyClock + n0 + j; }
+				if (holding && (above & (1u << j)))
+				{
+					holding = false;
+					if (lane == 0 && count < a.maxPeaks) a.peaks[uint64_t(warp) * a.maxPeaks + count] = origin;
+					++count;
+				}
+			}
+			const int last = int(min(uint64_t(32), a.n - n0)) - 1;
+			prev = __shfl_sync(0xffffffffu, sample, last);
+		}
+		if (lane == 0)
+		{
+			st.state = a.n ? prev : st.state; st.is_peak_holding = holding ? 1 : 0; st.cross_origin = origin;
+			a.states[warp] = st;
+			a.counts[warp] = count;
+		}
+	}
+
+	// PeakHoldProcessor::process (StreamPreprocessing.h:284-311): a data-dependent double recurrence;
+	// lanes fetch, lane order is replayed sequentially
+	__global__ void k_scope_trigger_peak(TriggerArgs a)
+	{
+		const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+		if (warp >= a.nStreams) return;
+		const float* base = a.audio + uint64_t(warp) * a.stride;
+		sgz_scope_trigger_state st = a.states[warp];
+		double state = st.state;
+		bool holding = st.is_peak_holding != 0;
+		uint32_t count = 0;
+		const double thr2 = __dmul_rn(a.threshold, a.threshold);
+		for (uint64_t n0 = 0; n0 < a.n; n0 += 32)
+		{
+			float x = 0.f;
+			if (n0 + lane < a.n) { float l, r; loadLR(base, a.layout, a.n, n0 + lane, l, r); x = oscChannel(a.channel, l, r); }
+			const double sq = __dmul_rn(double(x), double(x));
+			const int cnt = int(min(uint64_t(32), a.n - n0));
+			for (int j = 0; j < cnt; ++j)
+			{
+				const double sample = __shfl_sync(0xffffffffu, sq, j);
+				const double delta = __dsub_rn(sample, state);
+				if (delta < 0)
+				{
+					state = __dmul_rn(state, 0.9999);
+					state = fmax(thr2, state);
+					if (holding)
+					{
+						if (lane == 0 && count < a.maxPeaks) a.peaks[uint64_t(warp) * a.maxPeaks + count] = a.steadyClock + n0 + j - 1;
+						++count;
+						holding = false;
+					}
+				}
+				else
+				{
+					if (delta > __dmul_rn(a.hysteresis, state)) holding = true;
+					state = sample;
+				}
+			}
+		}
+		if (lane == 0)
+		{
+			st.state = state; st.is_peak_holding = holding ? 1 : 0;
+			a.states[warp] = st;
+			a.counts[warp] = count;
+		}
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// Oscilloscope: spectral period search.  One CTA per stream: 8192-point float64 FFT in shared
+	// memory (128 KB), the sequential pick by one thread, then a second kernel for the Goertzel sum.
+	// ------------------------------------------------------------------------------------------
+	constexpr int kLookahead = 8192;
+
+	__device__ __forceinline__ double2 dmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+	__device__ __forceinline__ double dabs(double2 a) { return hypot(a.x, a.y); }
+
+	struct PeriodPickArgs
+	{
+		const float* audio; int layout; uint64_t n; uint64_t stride; int channel;
+		long long firstSample; // n - max(ceil(effectiveWindowSize), 8192)
+		double threshold, hysteresis;
+		sgz_scope_bin_record* picked; // [S]
+	};
+
+	__device__ double quadDelta(const double2* tb, int w)
+	{
+		const double2 x0 = tb[w], x1 = tb[w + 1], xm1 = tb[w == 0 ? 1 : w - 1];
+		const double2 denom = make_double2(x0.x * 2.0 - xm1.x - x1.x, x0.y * 2.0 - xm1.y - x1.y);
+		if ((denom.x + denom.y) == 0) return 0;
+		const double2 num = make_double2(xm1.x - x1.x, xm1.y - x1.y);
+		// Re(num / denom)
+		return (num.x * denom.x + num.y * denom.y) / (denom.x * denom.x + denom.y * denom.y);
+	}
+
+	__global__ void __launch_bounds__(512) k_scope_period_pick(PeriodPickArgs a)
+	{
+		extern __shared__ double2 tb[];
+		const uint32_t s = blockIdx.x;
+		const float* base = a.audio + uint64_t(s) * a.stride;
+		constexpr int N = kLookahead, bits = 13;
+		for (int i = threadIdx.x; i < N; i += blockDim.x)
+		{
+			const long long idx = a.firstSample + i;
+			float v = 0.f;
+			if (idx >= 0 && idx < (long long)a.n) { float l, r; loadLR(base, a.layout, a.n, uint64_t(idx), l, r); v = oscChannel(a.channel, l, r); }
+			tb[__brev(unsigned(i)) >> (32 - bits)] = make_double2(double(v), 0.0);
+		}
+		__syncthreads();
+		for (int half = 1; half < N; half <<= 1)
+		{
+			for (int b = threadIdx.x; b < (N >> 1); b += blockDim.x)
+			{
+				const int j = b & (half - 1);
+				const int i0 = ((b - j) << 1) + j;
+				double sn, cs;
+				sincospi(-double(j) / double(half), &sn, &cs); // W_(2 half)^j
+				const double2 u = tb[i0];
+				const double2 v = dmul(tb[i0 + half], make_double2(cs, sn));
+				tb[i0] = make_double2(u.x + v.x, u.y + v.y);
+				tb[i0 + half] = make_double2(u.x - v.x, u.y - v.y);
+			}
+			__syncthreads();
+		}
+		if (threadIdx.x != 0) return;
+		// OscilloscopeDSP.inl:128-184, one thread: the loop carries `max` from bin to bin
+		const double quarterSemitone = pow(2.0, 0.25 / 12.0) - 1;
+		const double invHysteresis = 1 - a.hysteresis;
+		uint64_t mIndex = 1; double mValue = fmax(a.threshold * N / 6.0, dabs(tb[1])), mOffset = quadDelta(tb, 1);
+		for (int i = 2; i < (N >> 1); ++i)
+		{
+			const double cValue = dabs(tb[i]);
+			if (invHysteresis * cValue > mValue * 2)
+			{
+				const double mOmega = double(mIndex) + mOffset;
+				if (mOmega > 0)
+				{
+					const double cOffset = quadDelta(tb, i);
+					const double factor = (double(i) + cOffset) / mOmega;
+					const double sensivity = cValue / mValue;
+					bool take = false;
+					if (invHysteresis * sensivity > 20) take = true;
+					else if (fabs(1 - factor) < invHysteresis * quarterSemitone) take = true;
+					else
+					{
+						const double multipleDeviation = fabs(factor - floor(factor + 0.5));
+						if (invHysteresis * fabs(multipleDeviation) > quarterSemitone) take = true;
+					}
+					if (take) { mIndex = i; mValue = cValue; mOffset = cOffset; }
+				}
+				else
+				{
+					mIndex = i; mValue = cValue; mOffset = quadDelta(tb, i);
+				}
+			}
+		}
+		a.picked[s].index = mIndex; a.picked[s].value = mValue; a.picked[s].offset = mOffset;
+	}
+
+	struct GoertzelArgs
+	{
+		const float* audio; int layout; uint64_t n; uint64_t stride; int channel;
+		const long long* firstSample; // [S]
+		const double* radians;        // [S]
+		double2* z;                   // [S]
+	};
+
+	// cpl::dsp::goertzel(buf, N, w) = sum x[n] exp(-i w n) over the 8192 newest samples (:271-277)
+	__global__ void __launch_bounds__(256) k_scope_goertzel(GoertzelArgs a)
+	{
+		__shared__ double2 red[256];
+		const uint32_t s = blockIdx.x;
+		const float* base = a.audio + uint64_t(s) * a.stride;
+		const double w = a.radians[s];
+		const long long first = a.firstSample[s];
+		double2 acc = make_double2(0.0, 0.0);
+		for (int i = threadIdx.x; i < kLookahead; i += blockDim.x)
+		{
+			const long long idx = first + i;
+			float v = 0.f;
+			if (idx >= 0 && idx < (long long)a.n) { float l, r; loadLR(base, a.layout, a.n, uint64_t(idx), l, r); v = oscChannel(a.channel, l, r); }
+			double sn, cs;
+			sincos(w * double(i), &sn, &cs);
+			acc.x += double(v) * cs; acc.y -= double(v) * sn;
+		}
+		red[threadIdx.x] = acc;
+		__syncthreads();
+		for (int stride = 128; stride > 0; stride >>= 1)
+		{
+			if (threadIdx.x < stride) { red[threadIdx.x].x += red[threadIdx.x + stride].x; red[threadIdx.x].y += red[threadIdx.x + stride].y; }
+			__syncthreads();
+		}
+		if (threadIdx.x == 0) a.z[s] = red[0];
+	}
+}
+
+using namespace sgz;
+
+#define SGZS_GUARD(ctx)                                                                  \
+	if (!(ctx)) return fail(SGZ_EINVAL, "null context");                                 \
+	CtxGuard g__((ctx)->device);                                                         \
+	if (!g__.ok) return fail(SGZ_ECUDA, "cudaSetDevice failed")
+
+extern "C"
+{
+	int sgz_context_create(int device, sgz_context** out)
+	{
+		if (!out) return fail(SGZ_EINVAL, "null argument");
+		*out = nullptr;
+		int count = 0;
+		if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return fail(SGZ_ECUDA, "no CUDA device (this library has no CPU fallback)");
+		if (device < 0 || device >= count) return fail(SGZ_EINVAL, "device %d out of range (%d devices)", device, count);
+		sgz_context* c = new (std::nothrow) sgz_context();
+		if (!c) return fail(SGZ_ENOMEM, "out of host memory");
+		c->device = device;
+		CtxGuard g(device);
+		if (!g.ok || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(SGZ_ECUDA, "cannot create a stream on device %d", device); }
+		c->ownStream = true;
+		*out = c;
+		return SGZ_OK;
+	}
+
+	void sgz_context_destroy(sgz_context* c)
+	{
+		if (!c) return;
+		{
+			CtxGuard g(c->device);
+			if (c->stream) cudaStreamSynchronize(c->stream);
+			for (void* p : c->stage) if (p) cudaFree(p);
+			if (c->ownStream && c->stream) cudaStreamDestroy(c->stream);
+		}
+		delete c;
+	}
+
+	int sgz_context_set_cuda_stream(sgz_context* c, void* cuda_stream)
+	{
+		SGZS_GUARD(c);
+		if (c->stream) cudaStreamSynchronize(c->stream);
+		if (c->ownStream && c->stream) cudaStreamDestroy(c->stream);
+		c->stream = static_cast<cudaStream_t>(cuda_stream);
+		c->ownStream = false;
+		return SGZ_OK;
+	}
+
+	int sgz_context_synchronize(sgz_context* c)
+	{
+		SGZS_GUARD(c);
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		return SGZ_OK;
+	}
+
+	static int vscopeCheck(const sgz_vscope_config* cfg)
+	{
+		if (!cfg || cfg->abi_version != SGZ_ABI_VERSION) return fail(SGZ_EINVAL, "bad vectorscope config");
+		if (cfg->width == 0 || cfg->height == 0 || cfg->width > 16384 || cfg->height > 16384) return fail(SGZ_EINVAL, "bad histogram size");
+		return SGZ_OK;
+	}
+
+	int sgz_vscope_vertices(sgz_context* c, const sgz_vscope_config* cfg, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, float* xyz, int out_mem)
+	{
+		int rc = vscopeCheck(cfg); if (rc != SGZ_OK) return rc;
+		if (!xyz) return fail(SGZ_EINVAL, "null output");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		if (n_samples == 0) return SGZ_OK;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		const size_t bytes = size_t(n_streams) * n_samples * 3 * sizeof(float);
+		float* dOut = xyz;
+		if (out_mem == SGZ_MEM_HOST) { void* p; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
+		const dim3 block(256), grid(unsigned((n_samples + 255) / 256), n_streams);
+		k_vscope_vertices<<<grid, block, 0, c->stream>>>(*cfg, d, layout, n_samples, stream_stride, dOut);
+		SGZS_CUDA(cudaGetLastError());
+		if (out_mem == SGZ_MEM_HOST)
+		{
+			SGZS_CUDA(cudaMemcpyAsync(xyz, dOut, bytes, cudaMemcpyDeviceToHost, c->stream));
+			SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		}
+		return SGZ_OK;
+	}
+
+	int sgz_vscope_histogram(sgz_context* c, const sgz_vscope_config* cfg, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, uint32_t* hist, int out_mem)
+	{
+		int rc = vscopeCheck(cfg); if (rc != SGZ_OK) return rc;
+		if (!hist) return fail(SGZ_EINVAL, "null output");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if (n_samples && (rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		const size_t bytes = size_t(n_streams) * cfg->width * cfg->height * sizeof(uint32_t);
+		uint32_t* dOut = hist;
+		if (out_mem == SGZ_MEM_HOST) { void* p; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<uint32_t*>(p); }
+		SGZS_CUDA(cudaMemsetAsync(dOut, 0, bytes, c->stream));
+		if (n_samples)
+		{
+			// enough CTAs per stream to fill the machine when there are few streams, grid-stride inside
+			unsigned perStream = unsigned(std::min<uint64_t>((n_samples + 255) / 256, std::max<uint64_t>(1, (148ull * 8 + n_streams - 1) / n_streams)));
+			k_vscope_histogram<<<dim3(perStream, n_streams), 256, 0, c->stream>>>(*cfg, d, layout, n_samples, stream_stride, dOut);
+			SGZS_CUDA(cudaGetLastError());
+		}
+		if (out_mem == SGZ_MEM_HOST)
+		{
+			SGZS_CUDA(cudaMemcpyAsync(hist, dOut, bytes, cudaMemcpyDeviceToHost, c->stream));
+			SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		}
+		return SGZ_OK;
+	}
+
+	int sgz_vscope_meters(sgz_context* c, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+		float envelope_coeff, float stereo_coeff, float second_stereo_filter_speed, sgz_vscope_filters* filters)
+	{
+		int rc;
+		if (!filters) return fail(SGZ_EINVAL, "null filters");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		if (n_samples == 0) return SGZ_OK;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		// host slot order: envelope[2], balance[slow][L,R], balance[fast][L,R], phase[slow], phase[fast] = struct order
+		void* p; if ((rc = ensure(c, 2, size_t(n_streams) * 8 * sizeof(float), &p)) != SGZ_OK) return rc;
+		SGZS_CUDA(cudaMemcpyAsync(p, filters, size_t(n_streams) * 8 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+		const float pole1 = static_cast<float>(std::pow(stereo_coeff, second_stereo_filter_speed)); // Vectorscope.cpp:279
+		const unsigned warpsPerBlock = 4;
+		k_vscope_meters<<<(n_streams + warpsPerBlock - 1) / warpsPerBlock, warpsPerBlock * 32, 0, c->stream>>>(d, layout, n_samples, stream_stride, n_streams,
+			envelope_coeff, stereo_coeff, pole1, static_cast<float*>(p));
+		SGZS_CUDA(cudaGetLastError());
+		SGZS_CUDA(cudaMemcpyAsync(filters, p, size_t(n_streams) * 8 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		return SGZ_OK;
+	}
+
+	uint64_t sgz_scope_resample_count(const sgz_scope_resample_config* cfg)
+	{
+		if (!cfg || !(cfg->inc > 0) || !(cfg->right >= cfg->left)) return 0;
+		// the do-while at OscilloscopeRendering.cpp:863-886, replayed so the count is exact
+		uint64_t count = 0;
+		double unitSpacePos = cfg->left;
+		do { ++count; unitSpacePos += cfg->inc; } while (unitSpacePos < (cfg->right + cfg->inc) && count < (1ull << 32));
+		return count;
+	}
+
+	int sgz_scope_resample(sgz_context* c, const sgz_scope_resample_config* cfg, const double* sample_pos, const float* audio, int mem, int layout,
+		uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride, float* out_xy, int out_mem)
+	{
+		int rc;
+		if (!cfg || cfg->abi_version != SGZ_ABI_VERSION || !sample_pos || !out_xy) return fail(SGZ_EINVAL, "bad resample arguments");
+		if (cfg->channel < SGZ_OSC_LEFT || cfg->channel > SGZ_OSC_SIDE) return fail(SGZ_EINVAL, "bad channel");
+		if (!(cfg->samples_per_pixel > 0)) return fail(SGZ_EINVAL, "samples_per_pixel must be positive");
+		const uint64_t count = sgz_scope_resample_count(cfg);
+		if (count == 0) return fail(SGZ_EINVAL, "empty output range");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		void* dPos; if ((rc = ensure(c, 2, size_t(n_streams) * sizeof(double), &dPos)) != SGZ_OK) return rc;
+		SGZS_CUDA(cudaMemcpyAsync(dPos, sample_pos, size_t(n_streams) * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+		const size_t bytes = size_t(n_streams) * count * 2 * sizeof(float);
+		float* dOut = out_xy;
+		if (out_mem == SGZ_MEM_HOST) { void* p; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
+		ResampleArgs a{};
+		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = cfg->channel;
+		a.samplePos = static_cast<const double*>(dPos); a.spp = cfg->samples_per_pixel; a.left = cfg->left; a.inc = cfg->inc; a.count = count; a.out = dOut;
+		k_scope_resample<<<dim3(unsigned((count + 127) / 128), n_streams), 128, 0, c->stream>>>(a);
+		SGZS_CUDA(cudaGetLastError());
+		if (out_mem == SGZ_MEM_HOST)
+		{
+			SGZS_CUDA(cudaMemcpyAsync(out_xy, dOut, bytes, cudaMemcpyDeviceToHost, c->stream));
+			SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		}
+		return SGZ_OK;
+	}
+
+	int sgz_scope_trigger(sgz_context* c, int mode, int channel, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, double threshold, double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* states, uint64_t* peaks,
+		uint32_t* counts, uint32_t max_peaks)
+	{
+		int rc;
+		if (!states || !counts || (max_peaks && !peaks)) return fail(SGZ_EINVAL, "null argument");
+		if (mode != 0 && mode != 1) return fail(SGZ_EINVAL, "mode must be 0 (zero crossing) or 1 (envelope hold)");
+		if (channel < SGZ_OSC_LEFT || channel > SGZ_OSC_SIDE) return fail(SGZ_EINVAL, "bad channel");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if (n_samples && (rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		const size_t stBytes = size_t(n_streams) * sizeof(sgz_scope_trigger_state), pkBytes = size_t(n_streams) * std::max<uint32_t>(max_peaks, 1) * sizeof(uint64_t),
+			cnBytes = size_t(n_streams) * sizeof(uint32_t);
+		void* p; if ((rc = ensure(c, 2, stBytes + pkBytes + cnBytes + 64, &p)) != SGZ_OK) return rc;
+		auto* dStates = static_cast<sgz_scope_trigger_state*>(p);
+		auto* dPeaks = reinterpret_cast<uint64_t*>(static_cast<char*>(p) + ((stBytes + 15) & ~size_t(15)));
+		auto* dCounts = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dPeaks) + pkBytes);
+		SGZS_CUDA(cudaMemcpyAsync(dStates, states, stBytes, cudaMemcpyHostToDevice, c->stream));
+		TriggerArgs a{};
+		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = channel; a.nStreams = n_streams;
+		a.threshold = threshold; a.hysteresis = hysteresis; a.steadyClock = steady_clock; a.states = dStates; a.peaks = dPeaks; a.counts = dCounts; a.maxPeaks = max_peaks;
+		const unsigned warpsPerBlock = 4, blocks = (n_streams + warpsPerBlock - 1) / warpsPerBlock;
+		if (mode == 0) k_scope_trigger_zero<<<blocks, warpsPerBlock * 32, 0, c->stream>>>(a);
+		else k_scope_trigger_peak<<<blocks, warpsPerBlock * 32, 0, c->stream>>>(a);
+		SGZS_CUDA(cudaGetLastError());
+		SGZS_CUDA(cudaMemcpyAsync(states, dStates, stBytes, cudaMemcpyDeviceToHost, c->stream));
+		if (max_peaks) SGZS_CUDA(cudaMemcpyAsync(peaks, dPeaks, size_t(n_streams) * max_peaks * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaMemcpyAsync(counts, dCounts, cnBytes, cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_scope_period(sgz_context* c, const sgz_scope_period_params* prm, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, sgz_scope_period_state* states, sgz_scope_period_result* results)
+	{
+		int rc;
+		if (!prm || prm->abi_version != SGZ_ABI_VERSION || !states || !results) return fail(SGZ_EINVAL, "bad period arguments");
+		if (prm->channel < SGZ_OSC_LEFT || prm->channel > SGZ_OSC_SIDE) return fail(SGZ_EINVAL, "bad channel");
+		if (!(prm->sample_rate > 0)) return fail(SGZ_EINVAL, "bad sample rate");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		constexpr size_t LookaheadSize = kLookahead, TransformSize = kLookahead;
+		// --- calculateFundamentalPeriod: FFT + pick on the device ---
+		const size_t recBytes = size_t(n_streams) * sizeof(sgz_scope_bin_record);
+		const size_t auxBytes = size_t(n_streams) * (sizeof(long long) + sizeof(double) + sizeof(double2));
+		void* p; if ((rc = ensure(c, 2, recBytes + auxBytes + 64, &p)) != SGZ_OK) return rc;
+		auto* dPicked = static_cast<sgz_scope_bin_record*>(p);
+		auto* dFirst = reinterpret_cast<long long*>(static_cast<char*>(p) + ((recBytes + 15) & ~size_t(15)));
+		auto* dRadians = reinterpret_cast<double*>(dFirst + n_streams);
+		auto* dZ = reinterpret_cast<double2*>(dRadians + n_streams); // 16 n bytes past dFirst: 16-byte aligned
+		PeriodPickArgs pa{};
+		pa.audio = d; pa.layout = layout; pa.n = n_samples; pa.stride = stream_stride; pa.channel = prm->channel;
+		const size_t offset1 = std::max<size_t>(static_cast<size_t>(std::ceil(prm->effective_window_size)), LookaheadSize); // :88
+		pa.firstSample = (long long)n_samples - (long long)offset1;
+		pa.threshold = prm->threshold; pa.hysteresis = prm->hysteresis; pa.picked = dPicked;
+		const size_t smem = TransformSize * sizeof(double2);
+		SGZS_CUDA(cudaFuncSetAttribute(k_scope_period_pick, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+		k_scope_period_pick<<<n_streams, 512, smem, c->stream>>>(pa);
+		SGZS_CUDA(cudaGetLastError());
+		std::vector<sgz_scope_bin_record> picked(n_streams);
+		SGZS_CUDA(cudaMemcpyAsync(picked.data(), dPicked, recBytes, cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		// --- median over the previous picks (:186-212) and the Goertzel parameters (:261-269), host side ---
+		std::vector<long long> first(n_streams);
+		std::vector<double> radians(n_streams), sampleDifference(n_streams);
+		const double tau = 6.283185307179586476925286766559;
+		for (uint32_t s = 0; s < n_streams; ++s)
+		{
+			sgz_scope_bin_record max = picked[s];
+			sgz_scope_period_state& st = states[s];
+			sgz_scope_bin_record local[8];
+			std::memcpy(local, st.median, sizeof(local));
+			st.median[st.median_pos & 7] = max;
+			st.median_pos = (st.median_pos + 1) & 7;
+			// std::nth_element leaves ties to the implementation; a stable order is the documented choice
+			std::stable_sort(local, local + 8, [](const sgz_scope_bin_record& a, const sgz_scope_bin_record& b) { return a.index < b.index; });
+			const sgz_scope_bin_record& old = local[4];
+			const double omegaMax = double(max.index) + max.offset, omegaOld = double(old.index) + old.offset;
+			if (old.index != uint64_t(-1) && std::abs(omegaMax - omegaOld) > 0.5) max = old;
+			sgz_scope_period_result& r = results[s];
+			r.record = max;
+			const double omega = double(max.index) + max.offset;
+			double fundamental = prm->sample_rate * omega / TransformSize;
+			r.fundamental = fundamental = std::max(5.0, fundamental);
+			r.cycle_samples = prm->sample_rate / fundamental;
+			radians[s] = tau * omega / TransformSize;
+			const double offsetReal = std::max<double>(double(LookaheadSize), prm->effective_window_size + r.cycle_samples);
+			const size_t offset2 = static_cast<size_t>(std::ceil(offsetReal));
+			sampleDifference[s] = double(offset2) - (prm->effective_window_size + r.cycle_samples);
+			first[s] = (long long)n_samples - (long long)offset2;
+		}
+		SGZS_CUDA(cudaMemcpyAsync(dFirst, first.data(), n_streams * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
+		SGZS_CUDA(cudaMemcpyAsync(dRadians, radians.data(), n_streams * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+		GoertzelArgs ga{};
+		ga.audio = d; ga.layout = layout; ga.n = n_samples; ga.stride = stream_stride; ga.channel = prm->channel; ga.firstSample = dFirst; ga.radians = dRadians; ga.z = dZ;
+		k_scope_goertzel<<<n_streams, 256, 0, c->stream>>>(ga);
+		SGZS_CUDA(cudaGetLastError());
+		std::vector<double2> z(n_streams);
+		SGZS_CUDA(cudaMemcpyAsync(z.data(), dZ, n_streams * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		for (uint32_t s = 0; s < n_streams; ++s)
+		{
+			// :283-306
+			sgz_scope_period_result& r = results[s];
+			const double rotation = -sampleDifference[s] * radians[s];
+			const double cr = std::cos(rotation), ci = -std::sin(rotation);
+			const double zr = z[s].x * cr - z[s].y * ci, zi = z[s].x * ci + z[s].y * cr;
+			double phase = tau - std::atan2(zi, zr);
+			phase += r.record.offset * tau;
+			phase -= 1.5707963267948966192313216916398;
+			phase += tau * prm->phase_offset_degrees / 360;
+			phase = std::fmod(phase, tau);
+			while (phase < 0) phase += tau;
+			r.phase = phase;
+			r.sample_offset = (phase / tau) * prm->sample_rate / r.fundamental - 1;
+		}
+		return SGZ_OK;
+	}
+}

@@ -1,0 +1,107 @@
+"""Host-side mirror of the secondary views' hot arithmetic (Vectorscope, Oscilloscope) over the C ABI.
+
+Reference call sites: `VectorScope::drawPolarPlot` / `drawRectPlot`
+(Source/Vectorscope/VectorscopeRendering.cpp:444-746), `VectorScope::Processor::audioProcessing`
+(Source/Vectorscope/Vectorscope.cpp:268-377), `Oscilloscope::drawWavePlot` Lanczos branch
+(Source/Oscilloscope/OscilloscopeRendering.cpp:790-891), `ZeroCrossingProcessor` / `PeakHoldProcessor`
+(Source/Oscilloscope/StreamPreprocessing.h:269-349) and `calculateFundamentalPeriod` /
+`calculateTriggeringOffset` (Source/Oscilloscope/OscilloscopeDSP.inl:61-308)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from ._lib import check, load
+from .spectrum import _buf
+
+
+def _geometry(audio, layout):
+    shape = tuple(audio.shape)
+    assert len(shape) == 3
+    n = shape[1] if layout == _abi.LAYOUT_INTERLEAVED else shape[2]
+    return shape[0], n, shape[1] * shape[2]
+
+
+class Context:
+    def __init__(self, device: int = 0):
+        self.lib = load()
+        self._h = C.c_void_p()
+        check(self.lib.sgz_context_create(int(device), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self.lib.sgz_context_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_cuda_stream(self, stream_ptr: int):
+        check(self.lib.sgz_context_set_cuda_stream(self._h, C.c_void_p(stream_ptr)))
+
+    def synchronize(self):
+        check(self.lib.sgz_context_synchronize(self._h))
+
+    # ---- Vectorscope ----------------------------------------------------------------------
+    def vscope_vertices(self, cfg, audio, layout=_abi.LAYOUT_INTERLEAVED):
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        out = np.empty((S, n, 3), dtype=np.float32)
+        check(self.lib.sgz_vscope_vertices(self._h, C.byref(cfg), ptr, mem, layout, S, n, stride, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
+    def vscope_histogram(self, cfg, audio, layout=_abi.LAYOUT_INTERLEAVED, out=None):
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        if out is None:
+            out = np.empty((S, cfg.height, cfg.width), dtype=np.uint32)
+            check(self.lib.sgz_vscope_histogram(self._h, C.byref(cfg), ptr, mem, layout, S, n, stride, out.ctypes.data, _abi.MEM_HOST))
+        else:  # device tensor (torch int32 view of the uint32 counts)
+            check(self.lib.sgz_vscope_histogram(self._h, C.byref(cfg), ptr, mem, layout, S, n, stride, out.data_ptr(), _abi.MEM_DEVICE))
+        return out
+
+    def vscope_meters(self, audio, filters, envelope_coeff, stereo_coeff, second_speed, layout=_abi.LAYOUT_INTERLEAVED):
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        assert len(filters) == S
+        check(self.lib.sgz_vscope_meters(self._h, ptr, mem, layout, S, n, stride, envelope_coeff, stereo_coeff, second_speed, filters))
+        return filters
+
+    # ---- Oscilloscope ---------------------------------------------------------------------
+    def scope_resample_count(self, cfg) -> int:
+        return int(self.lib.sgz_scope_resample_count(C.byref(cfg)))
+
+    def scope_resample(self, cfg, sample_pos, audio, layout=_abi.LAYOUT_INTERLEAVED, out=None):
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        pos = np.ascontiguousarray(sample_pos, dtype=np.float64)
+        assert pos.shape == (S,)
+        count = self.scope_resample_count(cfg)
+        if out is None:
+            out = np.empty((S, count, 2), dtype=np.float32)
+            optr, omem = out.ctypes.data, _abi.MEM_HOST
+        else:
+            optr, omem = out.data_ptr(), _abi.MEM_DEVICE
+        check(self.lib.sgz_scope_resample(self._h, C.byref(cfg), pos.ctypes.data_as(C.POINTER(C.c_double)), ptr, mem, layout, S, n, stride, optr, omem))
+        return out
+
+    def scope_trigger(self, mode, channel, audio, states, threshold, hysteresis=0.0, steady_clock=0, max_peaks=4096, layout=_abi.LAYOUT_INTERLEAVED):
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        assert len(states) == S
+        peaks = np.zeros((S, max_peaks), dtype=np.uint64)
+        counts = np.zeros(S, dtype=np.uint32)
+        check(self.lib.sgz_scope_trigger(self._h, mode, channel, ptr, mem, layout, S, n, stride, threshold, hysteresis, steady_clock, states,
+                                         peaks.ctypes.data_as(C.POINTER(C.c_uint64)), counts.ctypes.data_as(C.POINTER(C.c_uint32)), max_peaks))
+        return [peaks[s, :min(int(counts[s]), max_peaks)].copy() for s in range(S)], counts
+
+    def scope_period(self, params, audio, states, layout=_abi.LAYOUT_INTERLEAVED):
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        assert len(states) == S
+        results = (_abi.ScopePeriodResult * S)()
+        check(self.lib.sgz_scope_period(self._h, C.byref(params), ptr, mem, layout, S, n, stride, states, results))
+        return results
