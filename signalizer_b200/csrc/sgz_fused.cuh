@@ -30,7 +30,11 @@
 		static constexpr int N = 2 * M;
 		static constexpr int G = 16 / R3;
 		static constexpr size_t xbufBytes = size_t(M) * 16;          // float4[M]; csfmag[N+1] aliases its upper half (+4 B)
-		static constexpr size_t stateOffset = xbufBytes + 16;
+		// small twiddle tables kept in shared memory: A[16][16] = W_256^(n2 k1), B[16][R3] = W_M^(n3 k1),
+		// C[16][R3] = W_(16 R3)^(n3 k2)
+		static constexpr size_t twOffset = xbufBytes + 16;
+		static constexpr size_t twBytes = (256 + 2 * 16 * R3) * sizeof(float2);
+		static constexpr size_t stateOffset = twOffset + twBytes;
 		static size_t smemBytes(uint32_t P) { return stateOffset + size_t(P) * 16; }
 	};
 
@@ -48,6 +52,19 @@
 		return d > 0.f ? __log2f(d) * dyLn2 : clip;
 	}
 
+	// W_32^k, k = 0..15 (cos, -sin of 2 pi k / 32): the k3-dependent part of the last radix-2 twiddle
+	// W_N^(u + T g + 256 k3) = W_N^(u + T g) * W_(N/256)^k3
+	__device__ __forceinline__ float2 w32(int k)
+	{
+		constexpr float c[16] = { 1.f, 0.98078528040323044913f, 0.92387953251128675613f, 0.83146961230254523708f, 0.70710678118654752440f,
+			0.55557023301960222474f, 0.38268343236508977173f, 0.19509032201612826785f, 0.f, -0.19509032201612826785f, -0.38268343236508977173f,
+			-0.55557023301960222474f, -0.70710678118654752440f, -0.83146961230254523708f, -0.92387953251128675613f, -0.98078528040323044913f };
+		constexpr float s[16] = { 0.f, 0.19509032201612826785f, 0.38268343236508977173f, 0.55557023301960222474f, 0.70710678118654752440f,
+			0.83146961230254523708f, 0.92387953251128675613f, 0.98078528040323044913f, 1.f, 0.98078528040323044913f, 0.92387953251128675613f,
+			0.83146961230254523708f, 0.70710678118654752440f, 0.55557023301960222474f, 0.38268343236508977173f, 0.19509032201612826785f };
+		return make_float2(c[k], -s[k]);
+	}
+
 	__device__ __forceinline__ float csfTap(const float* csfmag, int i, int N) { return (i >= 0 && i <= N) ? csfmag[i] : 0.f; }
 
 	// MATRIX = 0: (L w, R w) (Separate and the other two-channel inputs); 1: runtime channel matrix
@@ -61,6 +78,9 @@
 		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
 		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
 		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
+		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);  // [16][16]  W_256^(n2 k1)
+		float2* twB = twA + 256;                                          // [16][R3]  W_M^(n3 k1)
+		float2* twC = twB + 16 * R3;                                      // [16][R3]  W_(16 R3)^(n3 k2)
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
 
 		const int u = threadIdx.x;
@@ -72,6 +92,13 @@
 
 		// peak-hold state of this stream lives in shared memory for the whole frame loop
 		for (int i = u; i < 2 * P; i += T) st[i] = a.states[uint64_t(stream) * 2 * P + i];
+		for (int i = u; i < 256; i += T) twA[i] = t.tw1[i];
+		for (int i = u; i < 16 * R3; i += T) { twB[i] = t.tw1[256 + i]; twC[i] = t.tw2[i]; }
+		// W_N^(u + T g): the thread-constant part of the last radix-2 twiddle, two registers per g
+		float2 wu[Gm::G];
+#pragma unroll
+		for (int g = 0; g < Gm::G; ++g) wu[g] = t.tw3[u + T * g];
+		__syncthreads();
 
 		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
 		const bool vec4 = a.layout == SGZ_LAYOUT_INTERLEAVED && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0);
@@ -130,7 +157,8 @@
 				float2 e = ve[perm16(k1)], o = vo[perm16(k1)];
 				if (k1 > 0)
 				{
-					const float2 w = ldg_f2(t.tw1 + k1 * T + u);
+					// W_M^(u k1) = W_256^(n2 k1) W_M^(n3 k1), u = n2 R3 + n3
+					const float2 w = cmul(twA[k1 * 16 + u / R3], twB[k1 * R3 + u % R3]);
 					e = cmul(e, w); o = cmul(o, w);
 				}
 				xbuf[k1 * T + (u ^ (k1 & 7))] = make_float4(e.x, e.y, o.x, o.y); // physAddr(k1, n2, n3), u = n2 R3 + n3
@@ -153,7 +181,7 @@
 					float2 e = ve[perm16(k2)], o = vo[perm16(k2)];
 					if (k2 > 0)
 					{
-						const float2 w = ldg_f2(t.tw2 + k2 * R3 + n3);
+						const float2 w = twC[k2 * R3 + n3];
 						e = cmul(e, w); o = cmul(o, w);
 					}
 					xbuf[physAddr<R3>(k1, k2, n3)] = make_float4(e.x, e.y, o.x, o.y);
@@ -186,8 +214,8 @@
 				for (int k3 = 0; k3 < R3; ++k3)
 				{
 					const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
-					const int k = u + T * g + 256 * k3;
-					const float2 wo = cmul(vo[slot], ldg_f2(t.tw3 + k));
+					// W_N^k, k = u + T g + 256 k3: W_N^256 = W_(2 R3)
+					const float2 wo = cmul(cmul(vo[slot], w32(R3 == 16 ? k3 : 2 * k3)), wu[g]);
 					const float2 e = ve[slot];
 					ve[slot] = cadd(e, wo); vo[slot] = csub(e, wo);
 				}

@@ -69,7 +69,7 @@ namespace sgz
 		const float* wR;         // [P][10]
 		const int* phaseNormPos; // [P]
 		const float2* twN;       // [N/2] W_N^k (generic FFT)
-		const float2* tw1;       // [16][T]  W_M^(u k1)          (fused FFT)
+		const float2* tw1;       // [256 + 16 R3] W_256^(n2 k1) | W_M^(n3 k1)   (fused FFT)
 		const float2* tw2;       // [16][R3] W_(16 R3)^(n3 k2)
 		const float2* tw3;       // [M]      W_N^k
 		const float2* resCoeff;  // [V][P] pole per vector and filter
@@ -751,11 +751,20 @@ extern "C"
 		{
 			const int R3 = t.N == 8192 ? 16 : 8;
 			const int T = 16 * R3, M = 16 * T;
-			std::vector<uint64_t> e1(size_t(16) * T), e2(size_t(16) * R3), e3(M);
-			for (int k1 = 0; k1 < 16; ++k1) for (int u = 0; u < T; ++u) e1[size_t(k1) * T + u] = uint64_t(u) * k1;
+			// tw1 = [A | B]: A[k1][n2] = W_256^(n2 k1) (256 entries), B[k1][n3] = W_M^(n3 k1) (16 R3 entries)
+			std::vector<float2> tw1(256 + size_t(16) * R3);
+			{
+				std::vector<uint64_t> eA(256), eB(size_t(16) * R3);
+				for (int k1 = 0; k1 < 16; ++k1) for (int n2 = 0; n2 < 16; ++n2) eA[k1 * 16 + n2] = uint64_t(n2) * k1;
+				for (int k1 = 0; k1 < 16; ++k1) for (int n3 = 0; n3 < R3; ++n3) eB[size_t(k1) * R3 + n3] = uint64_t(n3) * k1;
+				const auto A = twiddleTable(eA.size(), 256.0, eA), B = twiddleTable(eB.size(), double(M), eB);
+				std::copy(A.begin(), A.end(), tw1.begin());
+				std::copy(B.begin(), B.end(), tw1.begin() + 256);
+			}
+			std::vector<uint64_t> e2(size_t(16) * R3), e3(M);
 			for (int k2 = 0; k2 < 16; ++k2) for (int n3 = 0; n3 < R3; ++n3) e2[size_t(k2) * R3 + n3] = uint64_t(n3) * k2;
 			for (int k = 0; k < M; ++k) e3[k] = k;
-			SGZ_TRY(upload(h, twiddleTable(e1.size(), double(M), e1), &d.tw1));
+			SGZ_TRY(upload(h, tw1, &d.tw1));
 			SGZ_TRY(upload(h, twiddleTable(e2.size(), double(16 * R3), e2), &d.tw2));
 			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(2 * M), e3), &d.tw3));
 			h->fusedR3 = R3;
