@@ -100,3 +100,97 @@ namespace sgz
 		asm volatile("st.global.cs.v2.f32 [%0], {%1, %2};" :: "l"(p), "f"(v.x), "f"(v.y) : "memory");
 	}
 }
+
+// ------------------------------------------------------------------------------------------------
+// Packed FP32 (Blackwell add/sub/mul/fma.f32x2 -> SASS FADD2 / FMUL2 / FFMA2).  The fused kernel
+// carries two independent FFTs (the even- and odd-sample halves, E and O) through identical
+// arithmetic, so it keeps them as register pairs: re = (E.re, O.re), im = (E.im, O.im).  Every
+// butterfly add/sub and every twiddle multiply is then one packed instruction for both halves.
+// ------------------------------------------------------------------------------------------------
+namespace sgz
+{
+	typedef unsigned long long u64_t;
+	__device__ __forceinline__ u64_t pk(float2 v) { return reinterpret_cast<const u64_t&>(v); }
+	__device__ __forceinline__ float2 unpk(u64_t v) { return reinterpret_cast<const float2&>(v); }
+
+	__device__ __forceinline__ float2 add2(float2 a, float2 b) { u64_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return unpk(r); }
+	__device__ __forceinline__ float2 sub2(float2 a, float2 b) { u64_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return unpk(r); }
+	__device__ __forceinline__ float2 mul2(float2 a, float2 b) { u64_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return unpk(r); }
+	__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { u64_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c))); return unpk(r); }
+	__device__ __forceinline__ float2 bc2(float s) { return make_float2(s, s); }
+
+	// forward radix-4 on SoA pairs: (re, im)[0..3] -> X0..X3
+	__device__ __forceinline__ void radix4p(float2& r0, float2& i0, float2& r1, float2& i1, float2& r2, float2& i2, float2& r3, float2& i3)
+	{
+		const float2 s02r = add2(r0, r2), s02i = add2(i0, i2), d02r = sub2(r0, r2), d02i = sub2(i0, i2);
+		const float2 s13r = add2(r1, r3), s13i = add2(i1, i3), d13r = sub2(r1, r3), d13i = sub2(i1, i3);
+		r0 = add2(s02r, s13r); i0 = add2(s02i, s13i);
+		r2 = sub2(s02r, s13r); i2 = sub2(s02i, s13i);
+		r1 = add2(d02r, d13i); i1 = sub2(d02i, d13r); // d02 - i d13
+		r3 = sub2(d02r, d13i); i3 = add2(d02i, d13r); // d02 + i d13
+	}
+
+	// (re, im) *= (c - i s) with broadcast constants: re' = re c + im s, im' = im c - re s
+	__device__ __forceinline__ void mulCS(float2& re, float2& im, float c, float s)
+	{
+		const float2 C = bc2(c), S = bc2(s);
+		const float2 nr = fma2(im, S, mul2(re, C));
+		const float2 ni = sub2(mul2(im, C), mul2(re, S));
+		re = nr; im = ni;
+	}
+
+	template<int E> __device__ __forceinline__ void mulW16p(float2& re, float2& im)
+	{
+		constexpr float C1 = 0.92387953251128673848f, S1 = 0.38268343236508978178f, R = 0.70710678118654752440f;
+		if constexpr (E == 0) {}
+		else if constexpr (E == 1) mulCS(re, im, C1, S1);
+		else if constexpr (E == 2) { const float2 a = add2(re, im), b = sub2(im, re); re = mul2(a, bc2(R)); im = mul2(b, bc2(R)); }
+		else if constexpr (E == 3) mulCS(re, im, S1, C1);
+		else if constexpr (E == 4) { const float2 t = re; re = im; im = sub2(bc2(0.f), t); }
+		else if constexpr (E == 6) { const float2 a = sub2(im, re), b = add2(re, im); re = mul2(a, bc2(R)); im = mul2(b, bc2(-R)); }
+		else if constexpr (E == 9) mulCS(re, im, -C1, -S1);
+		else static_assert(E < 0, "unsupported W16 exponent");
+	}
+
+	__device__ __forceinline__ void dft16p(float2 (&re)[16], float2 (&im)[16])
+	{
+#pragma unroll
+		for (int j = 0; j < 4; ++j) radix4p(re[j], im[j], re[j + 4], im[j + 4], re[j + 8], im[j + 8], re[j + 12], im[j + 12]);
+		mulW16p<1>(re[5], im[5]); mulW16p<2>(re[9], im[9]); mulW16p<3>(re[13], im[13]);
+		mulW16p<2>(re[6], im[6]); mulW16p<4>(re[10], im[10]); mulW16p<6>(re[14], im[14]);
+		mulW16p<3>(re[7], im[7]); mulW16p<6>(re[11], im[11]); mulW16p<9>(re[15], im[15]);
+#pragma unroll
+		for (int m = 0; m < 4; ++m) radix4p(re[4 * m], im[4 * m], re[4 * m + 1], im[4 * m + 1], re[4 * m + 2], im[4 * m + 2], re[4 * m + 3], im[4 * m + 3]);
+	}
+
+	template<int O>
+	__device__ __forceinline__ void dft8p(float2 (&re)[16], float2 (&im)[16])
+	{
+		constexpr float R = 0.70710678118654752440f;
+		radix4p(re[O + 0], im[O + 0], re[O + 2], im[O + 2], re[O + 4], im[O + 4], re[O + 6], im[O + 6]);
+		radix4p(re[O + 1], im[O + 1], re[O + 3], im[O + 3], re[O + 5], im[O + 5], re[O + 7], im[O + 7]);
+		{
+			const float2 a = add2(re[O + 3], im[O + 3]), b = sub2(im[O + 3], re[O + 3]);   // W8^1
+			re[O + 3] = mul2(a, bc2(R)); im[O + 3] = mul2(b, bc2(R));
+			const float2 t = re[O + 5]; re[O + 5] = im[O + 5]; im[O + 5] = sub2(bc2(0.f), t); // W8^2 = -i
+			const float2 c = sub2(im[O + 7], re[O + 7]), d = add2(re[O + 7], im[O + 7]);   // W8^3
+			re[O + 7] = mul2(c, bc2(R)); im[O + 7] = mul2(d, bc2(-R));
+		}
+#pragma unroll
+		for (int m = 0; m < 4; ++m)
+		{
+			const float2 ar = re[O + 2 * m], ai = im[O + 2 * m], br = re[O + 2 * m + 1], bi = im[O + 2 * m + 1];
+			re[O + 2 * m] = add2(ar, br); im[O + 2 * m] = add2(ai, bi);
+			re[O + 2 * m + 1] = sub2(ar, br); im[O + 2 * m + 1] = sub2(ai, bi);
+		}
+	}
+
+	// (re, im) *= w for a table twiddle stored pre-broadcast as float4 (wx, wx, wy, wy)
+	__device__ __forceinline__ void mulTwiddleP(float2& re, float2& im, float4 w)
+	{
+		const float2 X = make_float2(w.x, w.y), Y = make_float2(w.z, w.w);
+		const float2 nr = sub2(mul2(re, X), mul2(im, Y));
+		const float2 ni = fma2(re, Y, mul2(im, X));
+		re = nr; im = ni;
+	}
+}

@@ -33,7 +33,7 @@
 		// small twiddle tables kept in shared memory: A[16][16] = W_256^(n2 k1), B[16][R3] = W_M^(n3 k1),
 		// C[16][R3] = W_(16 R3)^(n3 k2)
 		static constexpr size_t twOffset = xbufBytes + 16;
-		static constexpr size_t twBytes = (256 + 2 * 16 * R3) * sizeof(float2);
+		static constexpr size_t twBytes = (256 + 2 * 16 * R3) * sizeof(float2);   // C is read as float2 and broadcast in registers
 		static constexpr size_t stateOffset = twOffset + twBytes;
 		static size_t smemBytes(uint32_t P) { return stateOffset + size_t(P) * 16; }
 	};
@@ -131,7 +131,8 @@
 
 		for (uint32_t f = 0; f < a.nFrames; ++f)
 		{
-			float2 ve[16], vo[16];
+			// SoA register pairs: re[i] = (E.re, O.re), im[i] = (E.im, O.im)
+			float2 re[16], im[16];
 
 			// ---- pass 1: window + channel matrix, DFT16 over n1, twiddle W_M^(u k1) ----
 #pragma unroll
@@ -141,27 +142,27 @@
 				const float4 v = raw[n1];
 				if constexpr (MATRIX == 0)
 				{
-					ve[n1] = make_float2(v.x * w.x, v.y * w.x);
-					vo[n1] = make_float2(v.z * w.y, v.w * w.y);
+					re[n1] = make_float2(v.x * w.x, v.z * w.y);
+					im[n1] = make_float2(v.y * w.x, v.w * w.y);
 				}
 				else
 				{
-					ve[n1] = channelMatrix(conf, v.x, v.y, w.x);
-					vo[n1] = channelMatrix(conf, v.z, v.w, w.y);
+					const float2 e = channelMatrix(conf, v.x, v.y, w.x), o = channelMatrix(conf, v.z, v.w, w.y);
+					re[n1] = make_float2(e.x, o.x); im[n1] = make_float2(e.y, o.y);
 				}
 			}
-			dft16(ve); dft16(vo);
+			dft16p(re, im);
 #pragma unroll
 			for (int k1 = 0; k1 < 16; ++k1)
 			{
-				float2 e = ve[perm16(k1)], o = vo[perm16(k1)];
+				float2 r = re[perm16(k1)], i = im[perm16(k1)];
 				if (k1 > 0)
 				{
 					// W_M^(u k1) = W_256^(n2 k1) W_M^(n3 k1), u = n2 R3 + n3
 					const float2 w = cmul(twA[k1 * 16 + u / R3], twB[k1 * R3 + u % R3]);
-					e = cmul(e, w); o = cmul(o, w);
+					mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
 				}
-				xbuf[k1 * T + (u ^ (k1 & 7))] = make_float4(e.x, e.y, o.x, o.y); // physAddr(k1, n2, n3), u = n2 R3 + n3
+				xbuf[k1 * T + (u ^ (k1 & 7))] = make_float4(r.x, r.y, i.x, i.y); // physAddr(k1, n2, n3), u = n2 R3 + n3
 			}
 			__syncthreads();
 
@@ -172,19 +173,19 @@
 				for (int n2 = 0; n2 < 16; ++n2)
 				{
 					const float4 v = xbuf[physAddr<R3>(k1, n2, n3)];
-					ve[n2] = make_float2(v.x, v.y); vo[n2] = make_float2(v.z, v.w);
+					re[n2] = make_float2(v.x, v.y); im[n2] = make_float2(v.z, v.w);
 				}
-				dft16(ve); dft16(vo);
+				dft16p(re, im);
 #pragma unroll
 				for (int k2 = 0; k2 < 16; ++k2)
 				{
-					float2 e = ve[perm16(k2)], o = vo[perm16(k2)];
+					float2 r = re[perm16(k2)], i = im[perm16(k2)];
 					if (k2 > 0)
 					{
 						const float2 w = twC[k2 * R3 + n3];
-						e = cmul(e, w); o = cmul(o, w);
+						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
 					}
-					xbuf[physAddr<R3>(k1, k2, n3)] = make_float4(e.x, e.y, o.x, o.y);
+					xbuf[physAddr<R3>(k1, k2, n3)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 			}
 			__syncthreads();
@@ -199,14 +200,14 @@
 				for (int n3 = 0; n3 < R3; ++n3)
 				{
 					const float4 v = xbuf[physAddr<R3>(k1, k2, n3)];
-					ve[g * R3 + n3] = make_float2(v.x, v.y); vo[g * R3 + n3] = make_float2(v.z, v.w);
+					re[g * R3 + n3] = make_float2(v.x, v.y); im[g * R3 + n3] = make_float2(v.z, v.w);
 				}
 			}
-			if constexpr (R3 == 16) { dft16(ve); dft16(vo); }
-			else { dft8<0>(ve); dft8<8>(ve); dft8<0>(vo); dft8<8>(vo); }
+			if constexpr (R3 == 16) dft16p(re, im);
+			else { dft8p<0>(re, im); dft8p<8>(re, im); }
 
 			// ---- last radix-2: Zp[k] = E + W_N^k O (= Z[k]), Zm[k] = E - W_N^k O (= Z[k + M]) ----
-			// ve[] <- Zp, vo[] <- Zm, indexed by slot = g R3 + perm(k3)
+			// afterwards re[slot] = (Zp.re, Zm.re), im[slot] = (Zp.im, Zm.im), slot = g R3 + perm(k3)
 #pragma unroll
 			for (int g = 0; g < Gm::G; ++g)
 			{
@@ -215,9 +216,10 @@
 				{
 					const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
 					// W_N^k, k = u + T g + 256 k3: W_N^256 = W_(2 R3)
-					const float2 wo = cmul(cmul(vo[slot], w32(R3 == 16 ? k3 : 2 * k3)), wu[g]);
-					const float2 e = ve[slot];
-					ve[slot] = cadd(e, wo); vo[slot] = csub(e, wo);
+					const float2 o = make_float2(re[slot].y, im[slot].y), e = make_float2(re[slot].x, im[slot].x);
+					const float2 wo = cmul(cmul(o, w32(R3 == 16 ? k3 : 2 * k3)), wu[g]);
+					re[slot] = make_float2(e.x + wo.x, e.x - wo.x);
+					im[slot] = make_float2(e.y + wo.y, e.y - wo.y);
 				}
 			}
 			__syncthreads(); // every pass-3 read of xbuf is done before zm / csfmag overwrite it
@@ -230,7 +232,7 @@
 					for (int k3 = 0; k3 < R3; ++k3)
 					{
 						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
-						zm[u + T * g + 256 * k3] = vo[slot];
+						zm[u + T * g + 256 * k3] = make_float2(re[slot].y, im[slot].y);
 					}
 				__syncthreads();
 				// two-for-one split + |.| (or |.|^2 beyond linLimit) into the reference's csf layout:
@@ -242,11 +244,11 @@
 					{
 						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
 						const int j = u + T * g + 256 * k3;
-						const float2 zj = ve[slot];
+						const float2 zj = make_float2(re[slot].x, im[slot].x);
 						if (j == 0)
 						{
 							// :861-864: csf[N] = Im Z[0] / 2, csf[0] = Re Z[0] / 2, csf[N/2] *= .5 (packed Nyquists)
-							const float2 ny = vo[slot]; // Z[M] = Zm[0]
+							const float2 ny = make_float2(re[slot].y, im[slot].y); // Z[M] = Zm[0]
 							const float h = 0.5f * cabs(ny);
 							csfmag[0] = zj.x * 0.5f;   // linLimit >= 1: entries 0 and N are always magnitudes
 							csfmag[N] = zj.y * 0.5f;
@@ -273,11 +275,11 @@
 					{
 						const int slot = g * R3 + (R3 == 16 ? perm16(k3) : perm8(k3));
 						const int j = u + T * g + 256 * k3;
-						float2 zj = ve[slot];
+						float2 zj = make_float2(re[slot].x, im[slot].x);
 						if (j == 0)
 						{
 							zj.x *= 0.5f; zj.y *= 0.5f;
-							const float2 ny = vo[slot];
+							const float2 ny = make_float2(re[slot].y, im[slot].y);
 							const float h2 = 0.25f * cnorm(ny);
 							csfmag[M] = (M < linLimit) ? sqrtf(h2) : h2;
 						}
