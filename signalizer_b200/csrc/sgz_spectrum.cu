@@ -79,6 +79,7 @@ namespace sgz
 		int phaseNormFinal;
 		uint32_t N, W, P, M, linLimit;
 		uint32_t workStride; // float2 entries of workingMemory per stream
+		uint32_t safeFrom;   // fused kernel: interpolated points x >= safeFrom need no tap bounds checks
 		int conf, binpol;
 		float invSize, deltaYRecip, minFracRecip, lowerClip;
 		float deltaYLn2; // deltaYRecip * ln 2, for the log2-based display scale of the fused kernel
@@ -690,7 +691,7 @@ extern "C"
 			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
 			const int rc = buildTables(*cfg, h->tab);
 			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
-			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 4096) ? (h->tab.N == 8192 ? 16 : 8) : 0;
+			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 8192 ? 16 : 8) : 0;
 			*out = h;
 			return SGZ_OK;
 		}
@@ -718,6 +719,7 @@ extern "C"
 		d.invSize = t.invSize; d.deltaYRecip = t.deltaYRecip; d.minFracRecip = t.minFracRecip; d.lowerClip = t.lowerClip;
 		d.pole0 = t.pole[0]; d.pole1 = t.pole[1]; d.phasePole0 = t.phasePole[0]; d.phasePole1 = t.phasePole[1];
 		d.phaseNormFinal = t.phaseNormFinal;
+		d.safeFrom = t.safeFrom;
 		d.workStride = uint32_t(std::max<size_t>(t.N, size_t(2) * t.P));
 
 		std::vector<int4> binmap(t.P);
@@ -747,7 +749,7 @@ extern "C"
 			SGZ_TRY(upload(h, twiddleTable(e.size(), double(t.N), e), &d.twN));
 		}
 		h->fusedR3 = 0;
-		if (t.fusedOk && t.P <= 4096)
+		if (t.fusedOk && t.P <= 2048)
 		{
 			const int R3 = t.N == 8192 ? 16 : 8;
 			const int T = 16 * R3, M = 16 * T;

@@ -307,6 +307,22 @@ namespace sgz
 				}
 			}
 			t.linLimit = std::min<uint32_t>(L, M + 1);
+			// the fused kernel packs the bin map into 32 bits and derives fallback = first + count - 1 and the
+			// channel-1 Lanczos base = first - 4; verify those identities and the field widths
+			uint32_t safeFrom = 0;
+			for (uint32_t x = 0; x < P; ++x)
+			{
+				if (t.first[x] < 0 || t.first[x] > 0xFFFF || t.count[x] < 0 || t.count[x] > 0x7FFF) ok = false;
+				if (t.mode[x] == 1 && t.fallback[x] != t.first[x] + t.count[x] - 1) ok = false;
+				if (t.mode[x] == 0 && cfg.bin_polation == SGZ_BIN_LANCZOS)
+				{
+					if (t.baseL[x] != t.first[x] - (kLanczosSize - 1)) ok = false;
+					const bool inL = t.baseL[x] >= 0 && t.baseL[x] + kLanczosTaps - 1 <= int32_t(N);
+					const bool inR = mono || (t.baseR[x] >= 0 && t.baseR[x] + kLanczosTaps - 1 <= int32_t(N));
+					if (!(inL && inR)) safeFrom = x + 1;
+				}
+			}
+			t.safeFrom = safeFrom;
 			t.fusedOk = ok;
 		}
 

@@ -51,6 +51,8 @@ namespace sgz
 		// smallest L such that every interpolation tap index i of every point satisfies
 		// i < L or i > N - L (fused kernel keeps those entries as magnitudes, the rest squared)
 		uint32_t linLimit{ 0 };
+		// interpolated display points x >= safeFrom have every (Lanczos) tap of both channels inside [0, N]
+		uint32_t safeFrom{ 0 };
 		// true when the fused kernel reproduces the staged result for this configuration
 		bool fusedOk{ false };
 
