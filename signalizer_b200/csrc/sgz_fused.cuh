@@ -23,6 +23,7 @@
 	{
 		const float* audio; uint64_t nSamples; uint64_t streamStride; int layout;
 		uint32_t hop, nFrames;
+		uint32_t firstStream, numStreams; // the launch covers streams [firstStream, firstStream + numStreams)
 		float2* states;  // [S][2][P]
 		float2* results; // [S][F][2][P]
 	};
@@ -109,7 +110,7 @@
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
 
 		const int u = threadIdx.x;
-		const int stream = blockIdx.x;
+		const int stream = blockIdx.x + a.firstStream;
 		const int P = int(t.P);
 		const int W = int(t.W);
 		const int conf = t.conf;

@@ -500,6 +500,8 @@ struct sgz_spectrum
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
 	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
 	int fusedR3{ 0 };
+	cudaStream_t copyIn{ nullptr }, copyOut{ nullptr }; // host-buffer pipeline of process_frames
+	std::vector<cudaEvent_t> events;
 	bool fusedAttrSet{ false };
 	size_t fusedSmem{ 0 };
 };
@@ -567,7 +569,7 @@ namespace
 	int launchFusedBinpol(sgz_spectrum* h, const FusedArgs& a)
 	{
 		const size_t smem = FusedGeom<R3>::smemBytes(h->tab.P);
-		const dim3 grid(h->nStreams), block(16 * R3);
+		const dim3 grid(a.numStreams), block(16 * R3);
 #define SGZ_LAUNCH(BP)                                                                                              \
 		{                                                                                                           \
 			auto kern = k_fused<R3, STEREO, BP, MATRIX>;                                                            \
@@ -674,6 +676,9 @@ extern "C"
 			if (h->dAudioStage) cudaFree(h->dAudioStage);
 			if (h->dResultStage) cudaFree(h->dResultStage);
 			if (h->dResPartial) cudaFree(h->dResPartial);
+			for (cudaEvent_t e : h->events) cudaEventDestroy(e);
+			if (h->copyIn) cudaStreamDestroy(h->copyIn);
+			if (h->copyOut) cudaStreamDestroy(h->copyOut);
 			if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
 		}
 		delete h;
@@ -1102,6 +1107,57 @@ extern "C"
 		return SGZ_OK;
 	}
 
+	// Host-resident callers: the streams are cut into chunks so that the upload of chunk c+1, the
+	// kernel of chunk c and the download of chunk c-1 overlap (PCIe is full duplex); results are
+	// identical to the single launch because streams are independent.
+	static int processFramesPipelined(sgz_spectrum* h, const float* audio, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
+		uint32_t n_frames, float* results)
+	{
+		const uint32_t P = h->tab.P, S = h->nStreams;
+		const size_t audioFloats = size_t(stream_stride) * (S - 1) + size_t(n_samples) * 2;
+		const size_t resPerStream = size_t(n_frames) * 2 * P * 2;
+		int rc = ensureStage(h, &h->dAudioStage, &h->audioStageBytes, audioFloats * sizeof(float));
+		if (rc != SGZ_OK) return rc;
+		if ((rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, resPerStream * S * sizeof(float))) != SGZ_OK) return rc;
+		if (!h->copyIn) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyIn, cudaStreamNonBlocking));
+		if (!h->copyOut) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyOut, cudaStreamNonBlocking));
+		const uint32_t chunks = std::min<uint32_t>(8, S);
+		while (h->events.size() < 2 * chunks + 1)
+		{
+			cudaEvent_t e;
+			SGZ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+			h->events.push_back(e);
+		}
+		// the copy streams start after whatever the caller queued on the handle's stream
+		SGZ_CUDA(cudaEventRecord(h->events[2 * chunks], h->stream));
+		SGZ_CUDA(cudaStreamWaitEvent(h->copyIn, h->events[2 * chunks], 0));
+		for (uint32_t c = 0; c < chunks; ++c)
+		{
+			const uint32_t s0 = uint32_t(uint64_t(S) * c / chunks), s1 = uint32_t(uint64_t(S) * (c + 1) / chunks);
+			if (s1 == s0) continue;
+			const size_t off = size_t(s0) * stream_stride;
+			const size_t floats = size_t(stream_stride) * (s1 - s0 - 1) + size_t(n_samples) * 2;
+			SGZ_CUDA(cudaMemcpyAsync(h->dAudioStage + off, audio + off, floats * sizeof(float), cudaMemcpyHostToDevice, h->copyIn));
+			SGZ_CUDA(cudaEventRecord(h->events[2 * c], h->copyIn));
+			SGZ_CUDA(cudaStreamWaitEvent(h->stream, h->events[2 * c], 0));
+			FusedArgs a{};
+			a.audio = h->dAudioStage; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
+			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(h->dResultStage);
+			a.firstStream = s0; a.numStreams = s1 - s0;
+			if ((rc = launchFused(h, a)) != SGZ_OK) return rc;
+			SGZ_CUDA(cudaEventRecord(h->events[2 * c + 1], h->stream));
+			SGZ_CUDA(cudaStreamWaitEvent(h->copyOut, h->events[2 * c + 1], 0));
+			SGZ_CUDA(cudaMemcpyAsync(results + resPerStream * s0, h->dResultStage + resPerStream * s0, resPerStream * (s1 - s0) * sizeof(float),
+				cudaMemcpyDeviceToHost, h->copyOut));
+		}
+		// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
+		SGZ_CUDA(cudaMemcpy2DAsync(h->dResults, size_t(2) * P * sizeof(float2), h->dResultStage + size_t(n_frames - 1) * 2 * P * 2,
+			size_t(n_frames) * 2 * P * sizeof(float2), size_t(2) * P * sizeof(float2), S, cudaMemcpyDeviceToDevice, h->stream));
+		SGZ_CUDA(cudaStreamSynchronize(h->copyOut));
+		SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+
 	int sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
 		uint32_t n_frames, float* results, int results_mem)
 	{
@@ -1116,6 +1172,8 @@ extern "C"
 		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stream_stride & 1) || (reinterpret_cast<uintptr_t>(audio) & 7)))
 			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
 		SGZ_GUARD(h);
+		if (!rsnt && h->fusedR3 != 0 && mem == SGZ_MEM_HOST && results_mem == SGZ_MEM_HOST && h->nStreams >= 8)
+			return processFramesPipelined(h, audio, layout, n_samples, stream_stride, hop, n_frames, results);
 		const float* dAudio = nullptr;
 		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);
 		if (rc != SGZ_OK) return rc;
@@ -1145,6 +1203,7 @@ extern "C"
 			FusedArgs a{};
 			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
 			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(dRes);
+			a.firstStream = 0; a.numStreams = h->nStreams;
 			rc = launchFused(h, a);
 			if (rc != SGZ_OK) return rc;
 			// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)

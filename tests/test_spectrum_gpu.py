@@ -326,3 +326,24 @@ def test_resonator_clear_state():
     assert np.abs(g.get_resonator_state()).max() > 0
     g.clear_audio_state()
     assert np.all(g.get_resonator_state() == 0)
+
+
+def test_host_buffer_pipeline_equals_single_launch():
+    # >= 8 streams with host buffers take the chunked upload / compute / download pipeline
+    import torch
+    cfg = _abi.default_config()
+    S, F, hop = 19, 3, 2048
+    audio = frames_case(cfg, S, F, hop)
+    a = TransformPairBatch(cfg, S)
+    host = a.process_frames(audio, hop, F)                      # pipelined
+    b = TransformPairBatch(cfg, S)
+    dev = b.process_frames(torch.from_numpy(audio).cuda(), hop, F)
+    b.synchronize()
+    np.testing.assert_array_equal(host, dev.cpu().numpy())
+    for k in range(2):
+        np.testing.assert_array_equal(a.get_states(k), b.get_states(k))
+        np.testing.assert_array_equal(a.get_results(k), b.get_results(k))
+    again = a.process_frames(audio, hop, F)                     # state carried into a second pipelined call
+    again_dev = b.process_frames(torch.from_numpy(audio).cuda(), hop, F)
+    b.synchronize()
+    np.testing.assert_array_equal(again, again_dev.cpu().numpy())
