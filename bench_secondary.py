@@ -1,0 +1,111 @@
+#!/usr/bin/env python
+"""Device-time measurements of the other BASELINE.json configurations (not the driver's contract;
+bench.py is).  One JSON line per configuration: C1 (4096-pt Hann frames), C2 (resonator bank,
+fp32 FLOP/s), C4 (16x Lanczos resampling + zero-crossing trigger, 256 streams), C5 (polar transform
++ 512x512 histogram, 256 streams).  CUDA events on the launch stream, inputs resident in HBM."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from signalizer_b200 import _abi, signals  # noqa: E402
+from signalizer_b200.scope import Context  # noqa: E402
+from signalizer_b200.spectrum import TransformPairBatch  # noqa: E402
+
+PEAK = 6551.4
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+
+
+def timed(fn, sync, steps=10, warmup=3):
+    for _ in range(warmup):
+        fn()
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    sync()
+    return e0.elapsed_time(e1) / steps
+
+
+def tile(base, S):
+    reps = -(-S // base.shape[0])
+    return np.ascontiguousarray(np.tile(base, (reps, 1, 1))[:S])
+
+
+def c1():
+    cfg = _abi.default_config(window_size=4096, window_type=_abi.WIN_HANN)
+    S, F, hop = 1024, 64, 1024
+    n = signals.frames_length(4096, hop, F)
+    d = torch.from_numpy(tile(signals.batch(48, n), S)).cuda()
+    p = TransformPairBatch(cfg, S)
+    p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+    out = torch.empty((S, F, 2, 1024, 2), dtype=torch.float32, device="cuda")
+    ms = timed(lambda: p.process_frames(d, hop, F, out=out), torch.cuda.synchronize)
+    frames = S * F
+    bytes_per_frame = 2 * 4096 * 4 + 2 * 2 * 1024 * 8 + 2 * 1024 * 8  # 81 920 B, SURVEY.md §8(d)
+    return {"config": "C1 batched: 1024 streams x 4096-pt Hann, hop 1024, Separate, Lanczos, 1024 log bins", "frames_per_s": frames / ms * 1e3,
+            "ms": ms, "achieved_GBps": frames * bytes_per_frame / ms / 1e6, "frac_hbm": frames * bytes_per_frame / ms / 1e6 / PEAK}
+
+
+def c2():
+    cfg = _abi.default_config(algo=_abi.ALGO_RSNT, window_size=8192, window_type=_abi.WIN_HANN)
+    out = []
+    for S, n in ((1, 480000), (64, 48000)):
+        d = torch.from_numpy(tile(signals.batch(min(S, 16), n), S)).cuda()
+        p = TransformPairBatch(cfg, S)
+        p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+        ms = timed(lambda: p.resonating_dispatch(d), torch.cuda.synchronize, steps=5)
+        V = p.info.resonator_vectors
+        flops = 8.0 * 1024 * V * 2 * n * S   # 8 flop per complex one-pole update, filters x vectors x channels
+        out.append({"config": f"C2 resonator bank: {S} stereo stream(s), 1024 log bins, Hann (V={V}), {n} samples", "ms": ms,
+                    "samples_per_s_per_stream": n / ms * 1e3, "realtime_factor_48k": n / ms * 1e3 / 48000.0, "fp32_TFLOPs": flops / ms / 1e9})
+    return out
+
+
+def c4():
+    S, n = 256, 65536
+    d = torch.from_numpy(tile(signals.batch(32, n), S)).cuda()
+    ctx = Context()
+    ctx.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+    W = 4096  # window samples shown
+    cfg = _abi.resample_config(channel=_abi.OSC_LEFT, samples_per_pixel=1.0 / 16, left=0.0, right=1.0, inc=1.0 / (16 * W))
+    count = ctx.scope_resample_count(cfg)
+    pos = np.full(S, W + 100.25)
+    out = torch.empty((S, count, 2), dtype=torch.float32, device="cuda")
+    ms = timed(lambda: ctx.scope_resample(cfg, pos, d, out=out), torch.cuda.synchronize)
+    algo = S * (W * 4 + count * 8)   # read W samples of one channel, write 16 W vertices (x, y)
+    st = (_abi.ScopeTriggerState * S)()
+    ms_t = timed(lambda: ctx.scope_trigger(0, _abi.OSC_LEFT, d, st, 0.05, max_peaks=4096), torch.cuda.synchronize, steps=5)
+    return {"config": f"C4 oscilloscope: 256 streams, Lanczos-10 16x resampling of a {W}-sample window ({count} vertices) + zero-crossing trigger over {n} samples",
+            "resample_ms": ms, "vertices_per_s": S * count / ms * 1e3, "resample_achieved_GBps": algo / ms / 1e6, "resample_frac_hbm": algo / ms / 1e6 / PEAK,
+            "trigger_ms_incl_host_copies": ms_t, "trigger_samples_per_s": S * n / ms_t * 1e3}
+
+
+def c5():
+    S, n = 256, 65536
+    d = torch.from_numpy(tile(signals.batch(32, n), S)).cuda()
+    ctx = Context()
+    ctx.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+    cfg = _abi.vscope_config(gain=1.2)
+    hist = torch.empty((S, 512, 512), dtype=torch.int32, device="cuda")
+    ms = timed(lambda: ctx.vscope_histogram(cfg, d, out=hist), torch.cuda.synchronize)
+    algo = S * (2 * n * 4 + 512 * 512 * 4 * 2)   # read audio, clear + write-out the 1 MiB histogram
+    return {"config": f"C5 vectorscope: 256 stereo streams x {n} samples, polar transform + 512x512 histogram", "ms": ms,
+            "points_per_s": S * n / ms * 1e3, "achieved_GBps": algo / ms / 1e6, "frac_hbm": algo / ms / 1e6 / PEAK}
+
+
+if __name__ == "__main__":
+    for fn in (c1, c2, c4, c5):
+        r = fn()
+        for line in (r if isinstance(r, list) else [r]):
+            print(json.dumps(line), flush=True)

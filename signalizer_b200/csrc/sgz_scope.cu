@@ -237,13 +237,16 @@ namespace sgz
 		float* out;
 	};
 
-	__device__ __forceinline__ double sincD(double x)
-	{
-		if (x == 0.0) return 1.0;
-		const double px = 3.1415926535897932384626433832795 * x;
-		return sin(px) / px;
-	}
+	// cos(pi k / 10), sin(pi k / 10), k = 0..10
+	__constant__ double kCos10[11] = { 1.0, 0.95105651629515357212, 0.80901699437494742410, 0.58778525229247312917, 0.30901699437494742410, 0.0,
+		-0.30901699437494742410, -0.58778525229247312917, -0.80901699437494742410, -0.95105651629515357212, -1.0 };
+	__constant__ double kSin10[11] = { 0.0, 0.30901699437494742410, 0.58778525229247312917, 0.80901699437494742410, 0.95105651629515357212, 1.0,
+		0.95105651629515357212, 0.80901699437494742410, 0.58778525229247312917, 0.30901699437494742410, 0.0 };
 
+	// One thread per output vertex.  The 20 Lanczos weights sinc(d) sinc(d / 10), d = frac + j, share their
+	// transcendentals: sin(pi d) = (-1)^j sin(pi frac) and sin(pi d / 10) follows from sincospi(frac / 10)
+	// by the angle-addition formula with the constants above (two transcendental calls per vertex
+	// instead of forty).
 	__global__ void k_scope_resample(ResampleArgs a)
 	{
 		const uint64_t m = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -263,10 +266,17 @@ namespace sgz
 		const double x = double(KernelSize) + delta;
 		const double fx = floor(x);
 		const int ib = int(fx);
+		const double frac = x - fx;
 		const float* src = a.audio + uint64_t(s) * a.stride;
+		const double S1 = sinpi(frac);
+		double sa, ca;
+		sincospi(frac * 0.1, &sa, &ca);
+		const double invPi2x10 = 10.0 / (3.1415926535897932384626433832795 * 3.1415926535897932384626433832795);
 		double acc = 0.0;
-		for (int i = ib - KernelSize + 1; i <= ib + KernelSize; ++i)
+#pragma unroll
+		for (int j = 9; j >= -10; --j) // tap i = ib - j ascending, distance d = frac + j
 		{
+			const int i = ib - j;
 			if (i < 0 || i >= KernelBufferSize) continue;
 			const long long idx = base + i;
 			float v = 0.f;
@@ -276,9 +286,17 @@ namespace sgz
 				loadLR(src, a.layout, a.n, uint64_t(idx), l, r);
 				v = oscChannel(a.channel, l, r);
 			}
-			const double d = x - double(i);
-			double w = 0.0;
-			if (d > -double(KernelSize) && d < double(KernelSize)) w = sincD(d) * sincD(d / KernelSize);
+			const double d = frac + double(j);
+			double w;
+			if (d == 0.0) w = 1.0;
+			else
+			{
+				const int aj = j < 0 ? -j : j;
+				const double cj = kCos10[aj], sj = j < 0 ? -kSin10[aj] : kSin10[aj];
+				const double s10 = sa * cj + ca * sj;          // sin(pi d / 10)
+				const double s1 = (aj & 1) ? -S1 : S1;         // sin(pi d)
+				w = s1 * s10 * invPi2x10 / (d * d);
+			}
 			acc += double(v) * w;
 		}
 		float* o = a.out + (uint64_t(s) * a.count + m) * 2;
