@@ -1,0 +1,431 @@
+	// ------------------------------------------------------------------------------------------
+	// k_fused8 — the N = 8192 fused frame kernel with 512 threads per stream and 8 (E, O) pairs per
+	// thread (included inside namespace sgz from sgz_spectrum.cu).
+	//
+	// Same arithmetic and shared-memory budget as k_fused<16,...>, different shape: M = 4096 = 8^4, four
+	// register-resident radix-8 passes, 32 data registers per thread instead of 64, so that the kernel
+	// fits 64 registers and TWO 512-thread CTAs (32 warps) are resident per SM.  ncu on k_fused showed
+	// no pipe saturated and 16 warps/SM unable to cover shared-memory / L2 latency; this variant buys
+	// latency tolerance with warps instead of instruction-level parallelism.
+	//
+	//   n = n1 512 + n2 64 + n3 8 + n4,  k = k1 + 8 k2 + 64 k3 + 512 k4          (all digits 0..7)
+	//   pass 1: thread (n2 n3 n4) DFT8 over n1, twiddle W_M^((64 n2 + v) k1) = W_64^(n2 k1) W_M^(v k1), v = 8 n3 + n4
+	//   pass 2: thread (k1 n3 n4) DFT8 over n2, twiddle W_512^(v k2)
+	//   pass 3: thread (k1 k2 n4) DFT8 over n3, twiddle W_64^(n4 k3)
+	//   pass 4: thread (k3 k2 k1) DFT8 over n4  -> bins k = t + 512 k4, t = k1 + 8 k2 + 64 k3
+	// exchange element (k1, d2, d3, d4) lives at k1 512 + d2 64 + d3 8 + (d4 ^ k1): every pass reads and
+	// writes 128-bit words without bank conflicts and passes 2-3 run in place.
+	// ------------------------------------------------------------------------------------------
+	struct Fused8Geom
+	{
+		static constexpr int T = 512, M = 4096, N = 8192;
+		static constexpr size_t xbufBytes = size_t(M) * 16;
+		static constexpr size_t twOffset = xbufBytes + 16;
+		static constexpr int twEntries = 64 + 512 + 512;            // A[8][8] | B[8][64] | C[8][64]
+		static constexpr size_t twBytes = size_t(twEntries) * sizeof(float2);
+		static constexpr size_t stateOffset = twOffset + twBytes;
+		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
+		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12; }
+	};
+
+	// 8-point forward DFT on SoA pairs; X[k] ends up in v[perm8(k)]
+	__device__ __forceinline__ void dft8q(float2 (&re)[8], float2 (&im)[8])
+	{
+		constexpr float R = 0.70710678118654752440f;
+		radix4p(re[0], im[0], re[2], im[2], re[4], im[4], re[6], im[6]);
+		radix4p(re[1], im[1], re[3], im[3], re[5], im[5], re[7], im[7]);
+		{
+			const float2 a = add2(re[3], im[3]), b = sub2(im[3], re[3]);   // W8^1
+			re[3] = mul2(a, bc2(R)); im[3] = mul2(b, bc2(R));
+			const float2 t = re[5]; re[5] = im[5]; im[5] = sub2(bc2(0.f), t); // W8^2 = -i
+			const float2 c = sub2(im[7], re[7]), d = add2(re[7], im[7]);   // W8^3
+			re[7] = mul2(c, bc2(R)); im[7] = mul2(d, bc2(-R));
+		}
+#pragma unroll
+		for (int m = 0; m < 4; ++m)
+		{
+			const float2 ar = re[2 * m], ai = im[2 * m], br = re[2 * m + 1], bi = im[2 * m + 1];
+			re[2 * m] = add2(ar, br); im[2 * m] = add2(ai, bi);
+			re[2 * m + 1] = sub2(ar, br); im[2 * m + 1] = sub2(ai, bi);
+		}
+	}
+
+	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4) { return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ k1); }
+
+	template<bool STEREO, int BINPOL, int MATRIX>
+	__global__ void __launch_bounds__(512, 2)
+	k_fused8(DeviceTables t, FusedArgs a)
+	{
+		typedef Fused8Geom Gm;
+		constexpr int T = Gm::T, M = Gm::M, N = Gm::N;
+		extern __shared__ __align__(16) unsigned char smemRaw[];
+		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
+		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
+		float4* stage = reinterpret_cast<float4*>(smemRaw);               // [4][T] next frame's newest half
+		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
+		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);  // [8][8]   W_64^(a b)
+		float2* twB = twA + 64;                                           // [8][64]  W_M^(v k1)
+		float2* twC = twB + 512;                                          // [8][64]  W_512^(v k2)
+		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
+
+		const int u = threadIdx.x;
+		const int stream = blockIdx.x + a.firstStream;
+		const int P = int(t.P);
+		const int conf = t.conf;
+		const int linLimit = int(t.linLimit);
+		uint32_t* mapPacked = reinterpret_cast<uint32_t*>(smemRaw + Gm::mapOffset(t.P));
+		float* mapSlope = reinterpret_cast<float*>(mapPacked + P);
+		int* mapBaseR = reinterpret_cast<int*>(mapSlope + P);
+
+		for (int i = u; i < 2 * P; i += T) st[i] = a.states[uint64_t(stream) * 2 * P + i];
+		for (int i = u; i < P; i += T)
+		{
+			const int4 bm = t.binmap[i];
+			mapPacked[i] = packBinMap(bm.x, bm.y, bm.z);
+			mapSlope[i] = t.slope[i] * t.minFracRecip;
+			mapBaseR[i] = t.baseR[i];
+		}
+		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i];
+		const float2 wu = t.tw3[u]; // W_N^t, the thread-constant part of the last radix-2 twiddle
+		__syncthreads();
+
+		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
+		const bool vec4 = a.layout == SGZ_LAYOUT_INTERLEAVED && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0) && int(t.W) == N;
+		const int W = int(t.W);
+		bool staged = false;
+
+		for (uint32_t f = 0; f < a.nFrames; ++f)
+		{
+			float2 re[8], im[8];
+			const uint64_t start = uint64_t(f) * a.hop;
+
+			// ---- pass 1: load (all loads first), window + channel matrix, DFT8 over n1 ----
+			{
+				float2 wv[8];
+#pragma unroll
+				for (int n1 = 0; n1 < 8; ++n1) wv[n1] = ldg_f2(reinterpret_cast<const float2*>(t.window) + n1 * T + u);
+				float4 rv[8];
+				if (vec4)
+				{
+					const float4* src = reinterpret_cast<const float4*>(sbase + 2 * start) + u;
+#pragma unroll
+					for (int n1 = 0; n1 < 4; ++n1) rv[n1] = ldg_stream_f4(src + n1 * T);
+					if (staged)
+					{
+						cpAsyncWaitAll();
+#pragma unroll
+						for (int n1 = 4; n1 < 8; ++n1) rv[n1] = stage[(n1 - 4) * T + u];
+					}
+					else
+					{
+#pragma unroll
+						for (int n1 = 4; n1 < 8; ++n1) rv[n1] = ldg_stream_f4(src + n1 * T);
+					}
+				}
+				else
+				{
+#pragma unroll
+					for (int n1 = 0; n1 < 8; ++n1)
+					{
+						const int n = 2 * (n1 * T + u);
+						float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+						if (n < W) fetchLR(sbase, a.layout, a.nSamples, start + n, v.x, v.y);
+						if (n + 1 < W) fetchLR(sbase, a.layout, a.nSamples, start + n + 1, v.z, v.w);
+						rv[n1] = v;
+					}
+				}
+#pragma unroll
+				for (int n1 = 0; n1 < 8; ++n1)
+				{
+					const float4 v = rv[n1];
+					const float2 w = wv[n1];
+					if constexpr (MATRIX == 0)
+					{
+						re[n1] = make_float2(v.x * w.x, v.z * w.y);
+						im[n1] = make_float2(v.y * w.x, v.w * w.y);
+					}
+					else
+					{
+						const float2 e = channelMatrix(conf, v.x, v.y, w.x), o = channelMatrix(conf, v.z, v.w, w.y);
+						re[n1] = make_float2(e.x, o.x); im[n1] = make_float2(e.y, o.y);
+					}
+				}
+			}
+			dft8q(re, im);
+			{
+				const int n2 = u >> 6, v = u & 63;
+#pragma unroll
+				for (int k1 = 1; k1 < 8; ++k1)
+				{
+					const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
+					mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
+				}
+			}
+			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+			{
+				const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
+#pragma unroll
+				for (int k1 = 0; k1 < 8; ++k1)
+				{
+					const float2 r = re[perm8(k1)], i = im[perm8(k1)];
+					xbuf[phys8(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+			}
+			__syncthreads();
+
+			// ---- pass 2 (in place): thread (k1 n3 n4), DFT8 over n2, twiddle W_512^(v k2) ----
+			{
+				const int k1 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7, v = u & 63;
+#pragma unroll
+				for (int n2 = 0; n2 < 8; ++n2)
+				{
+					const float4 x = xbuf[phys8(k1, n2, n3, n4)];
+					re[n2] = make_float2(x.x, x.y); im[n2] = make_float2(x.z, x.w);
+				}
+				dft8q(re, im);
+#pragma unroll
+				for (int k2 = 0; k2 < 8; ++k2)
+				{
+					float2 r = re[perm8(k2)], i = im[perm8(k2)];
+					if (k2 > 0)
+					{
+						const float2 w = twC[k2 * 64 + v];
+						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
+					}
+					xbuf[phys8(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+			}
+			__syncthreads();
+
+			// ---- pass 3 (in place): thread (k1 k2 n4), DFT8 over n3, twiddle W_64^(n4 k3) ----
+			{
+				const int k1 = u >> 6, k2 = (u >> 3) & 7, n4 = u & 7;
+#pragma unroll
+				for (int n3 = 0; n3 < 8; ++n3)
+				{
+					const float4 x = xbuf[phys8(k1, k2, n3, n4)];
+					re[n3] = make_float2(x.x, x.y); im[n3] = make_float2(x.z, x.w);
+				}
+				dft8q(re, im);
+#pragma unroll
+				for (int k3 = 0; k3 < 8; ++k3)
+				{
+					float2 r = re[perm8(k3)], i = im[perm8(k3)];
+					if (k3 > 0)
+					{
+						const float2 w = twA[k3 * 8 + n4];
+						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
+					}
+					xbuf[phys8(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+			}
+			__syncthreads();
+
+			// ---- pass 4: thread t = k1 + 8 k2 + 64 k3, DFT8 over n4; owns bins k = t + 512 k4 ----
+			{
+				const int k1 = u & 7, k2 = (u >> 3) & 7, k3 = u >> 6;
+#pragma unroll
+				for (int n4 = 0; n4 < 8; ++n4)
+				{
+					const float4 x = xbuf[phys8(k1, k2, k3, n4)];
+					re[n4] = make_float2(x.x, x.y); im[n4] = make_float2(x.z, x.w);
+				}
+			}
+			dft8q(re, im);
+			// last radix-2: re[slot] = (Zp.re, Zm.re), im[slot] = (Zp.im, Zm.im); W_N^(t + 512 k4) = W_N^t W_16^k4
+#pragma unroll
+			for (int k4 = 0; k4 < 8; ++k4)
+			{
+				const int slot = perm8(k4);
+				const float2 o = make_float2(re[slot].y, im[slot].y), e = make_float2(re[slot].x, im[slot].x);
+				const float2 wo = cmul(cmul(o, w32(2 * k4)), wu);
+				re[slot] = make_float2(e.x + wo.x, e.x - wo.x);
+				im[slot] = make_float2(e.y + wo.y, e.y - wo.y);
+			}
+			__syncthreads(); // every pass-4 read of xbuf is done before zm / csfmag overwrite it
+
+			if constexpr (STEREO)
+			{
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4) zm[u + 512 * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
+				__syncthreads();
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4)
+				{
+					const int slot = perm8(k4);
+					const int j = u + 512 * k4;
+					const float2 zj = make_float2(re[slot].x, im[slot].x);
+					if (j == 0)
+					{
+						const float2 ny = make_float2(re[slot].y, im[slot].y); // Z[M] = Zm[0]
+						const float h2 = 0.25f * cnorm(ny);
+						csfmag[0] = zj.x * 0.5f;
+						csfmag[N] = zj.y * 0.5f;
+						csfmag[M] = (M < linLimit) ? approxSqrt(h2) : h2;
+						continue;
+					}
+					const float2 zn = zm[M - j]; // Z[N - j]
+					float ax = (zj.x + zn.x) * 0.5f, ay = (zj.y - zn.y) * 0.5f;
+					const float dx = (zj.x - zn.x) * 0.5f, dy = (zj.y + zn.y) * 0.5f;
+					if (j == M - 1) { ax *= 0.5f; ay *= 0.5f; }
+					float a2 = ax * ax + ay * ay, b2 = dx * dx + dy * dy;
+					if (j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
+					csfmag[j] = a2;
+					csfmag[N - j] = b2;
+				}
+			}
+			else
+			{
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4)
+				{
+					const int slot = perm8(k4);
+					const int j = u + 512 * k4;
+					float2 zj = make_float2(re[slot].x, im[slot].x);
+					if (j == 0)
+					{
+						zj.x *= 0.5f; zj.y *= 0.5f;
+						const float2 ny = make_float2(re[slot].y, im[slot].y);
+						const float h2 = 0.25f * cnorm(ny);
+						csfmag[M] = (M < linLimit) ? approxSqrt(h2) : h2;
+					}
+					const float m2 = cnorm(zj);
+					csfmag[j] = (j < linLimit) ? approxSqrt(m2) : m2;
+				}
+			}
+			__syncthreads();
+
+			// newest half of the next frame -> lower half of the exchange buffer, behind the display points
+			staged = false;
+			if (vec4 && f + 1 < a.nFrames)
+			{
+				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
+#pragma unroll
+				for (int n1 = 4; n1 < 8; ++n1) cpAsync16(stage + (n1 - 4) * T + u, src + n1 * T);
+				cpAsyncCommit();
+				staged = true;
+			}
+
+			// ---- display points: one per thread per step ----
+			float2* resOut = a.results + ((uint64_t(stream) * a.nFrames + f) * 2) * P;
+			const float poles[2] = { t.pole0, t.pole1 };
+			const int safeFrom = int(t.safeFrom);
+			for (int x = u; x < P; x += T)
+			{
+				const uint32_t pkd = mapPacked[x];
+				const int first = int(pkd & 0xFFFFu), count = int((pkd >> 16) & 0x7FFFu);
+				float vL, vR = 0.f;
+				if (!(pkd >> 31))
+				{
+					if constexpr (BINPOL == SGZ_BIN_NONE)
+					{
+						vL = csfmag[first];
+						if constexpr (STEREO) vR = csfmag[N - first];
+					}
+					else if constexpr (BINPOL == SGZ_BIN_LINEAR)
+					{
+						{
+							const float pos = __ldg(t.posL + x); const float fl = floorf(pos); const int k = int(fl); const float fr = pos - fl;
+							vL = csfTap(csfmag, k, N) * (1.f - fr) + csfTap(csfmag, k + 1, N) * fr;
+						}
+						if constexpr (STEREO)
+						{
+							const float pos = __ldg(t.posR + x); const float fl = floorf(pos); const int k = int(fl); const float fr = pos - fl;
+							vR = csfTap(csfmag, k, N) * (1.f - fr) + csfTap(csfmag, k + 1, N) * fr;
+						}
+					}
+					else
+					{
+						const int bl = first - (kLanczosSize - 1);
+						const float4* wl4 = reinterpret_cast<const float4*>(t.wL + size_t(x) * kLanczosStride);
+						const float4 w0 = __ldg(wl4), w1 = __ldg(wl4 + 1), w2 = __ldg(wl4 + 2);
+						float4 r0, r1, r2; int br = 0;
+						if constexpr (STEREO)
+						{
+							const float4* wr4 = reinterpret_cast<const float4*>(t.wR + size_t(x) * kLanczosStride);
+							r0 = __ldg(wr4); r1 = __ldg(wr4 + 1); r2 = __ldg(wr4 + 2);
+							br = mapBaseR[x];
+						}
+						const float w[10] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y };
+						vL = 0.f;
+						if (x >= safeFrom)
+						{
+#pragma unroll
+							for (int k = 0; k < kLanczosTaps; ++k) vL += csfmag[bl + k] * w[k];
+						}
+						else
+						{
+#pragma unroll
+							for (int k = 0; k < kLanczosTaps; ++k) vL += csfTap(csfmag, bl + k, N) * w[k];
+						}
+						if constexpr (STEREO)
+						{
+							const float v[10] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y };
+							if (x >= safeFrom)
+							{
+#pragma unroll
+								for (int k = 0; k < kLanczosTaps; ++k) vR += csfmag[br + k] * v[k];
+							}
+							else
+							{
+#pragma unroll
+								for (int k = 0; k < kLanczosTaps; ++k) vR += csfTap(csfmag, br + k, N) * v[k];
+							}
+						}
+					}
+				}
+				else
+				{
+					float bestL = 0.f, bestR = 0.f;
+					if (first >= linLimit)
+					{
+						for (int c = 0; c < count; ++c)
+						{
+							bestL = fmaxf(bestL, csfmag[first + c]);
+							if constexpr (STEREO) bestR = fmaxf(bestR, csfmag[N - first - c]);
+						}
+					}
+					else
+					{
+						for (int c = 0; c < count; ++c)
+						{
+							const int off = first + c;
+							const float v = csfmag[off];
+							bestL = fmaxf(bestL, off < linLimit ? v * v : v);
+							if constexpr (STEREO) { const float vr = csfmag[N - off]; bestR = fmaxf(bestR, off < linLimit ? vr * vr : vr); }
+						}
+					}
+					const int fb = first + count - 1;
+					const float fv = csfmag[fb];
+					const float fbMag = (fb < linLimit || fb > N - linLimit) ? fv : approxSqrt(fv);
+					vL = bestL > 0.f ? approxSqrt(bestL) : fbMag;
+					if constexpr (STEREO) vR = bestR > 0.f ? approxSqrt(bestR) : fbMag;
+				}
+				const float lmag = fabsf(t.invSize * vL);
+				const float rmag = fabsf(t.invSize * vR);
+				const float sm = mapSlope[x];
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+				{
+					float2 sv = st[k * P + x];
+					sv.x *= poles[k];
+					if (lmag > sv.x) sv.x = lmag;
+					float2 res;
+					const float dl = sm * sv.x;
+					res.x = dl > 0.f ? __log2f(dl) * t.deltaYLn2 : t.lowerClip;
+					if constexpr (STEREO)
+					{
+						sv.y *= poles[k];
+						if (rmag > sv.y) sv.y = rmag;
+						const float dr = sm * sv.y;
+						res.y = dr > 0.f ? __log2f(dr) * t.deltaYLn2 : t.lowerClip;
+					}
+					else res.y = 0.f;
+					st[k * P + x] = sv;
+					stg_stream_f2(resOut + k * P + x, res);
+				}
+			}
+		}
+		__syncthreads();
+		for (int i = u; i < 2 * P; i += T) a.states[uint64_t(stream) * 2 * P + i] = st[i];
+	}

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -29,6 +30,9 @@
 
 namespace sgz
 {
+	// which N = 8192 fused kernel runs unless SGZ_FUSED_VARIANT=8|16 overrides it (set from measurement)
+	constexpr bool kDefaultVariant8 = true;
+
 	// ------------------------------------------------------------------------------------------
 	// error plumbing
 	// ------------------------------------------------------------------------------------------
@@ -72,6 +76,7 @@ namespace sgz
 		const float2* tw1;       // [256 + 16 R3] W_256^(n2 k1) | W_M^(n3 k1)   (fused FFT)
 		const float2* tw2;       // [16][R3] W_(16 R3)^(n3 k2)
 		const float2* tw3;       // [M]      W_N^k
+		const float2* tw8;       // k_fused8: [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2)
 		const float2* resCoeff;  // [V][P] pole per vector and filter
 		const float* resGain;    // [P]
 		const float* resTaps;    // [V]
@@ -469,6 +474,7 @@ namespace sgz
 	}
 
 #include "sgz_fused.cuh"
+#include "sgz_fused8.cuh"
 #include "sgz_resonator.cuh"
 
 } // namespace sgz
@@ -500,6 +506,7 @@ struct sgz_spectrum
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
 	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
 	int fusedR3{ 0 };
+	bool fusedVariant8{ false }; // N = 8192: use k_fused8 (512 threads, radix-8 x 4) instead of k_fused<16> (256 threads, radix-16 x 3)
 	cudaStream_t copyIn{ nullptr }, copyOut{ nullptr }; // host-buffer pipeline of process_frames
 	std::vector<cudaEvent_t> events;
 	bool fusedAttrSet{ false };
@@ -591,8 +598,39 @@ namespace
 		return SGZ_OK;
 	}
 
+	template<bool STEREO, int MATRIX>
+	int launchFused8Binpol(sgz_spectrum* h, const FusedArgs& a)
+	{
+		const size_t smem = Fused8Geom::smemBytes(h->tab.P);
+		const dim3 grid(a.numStreams), block(Fused8Geom::T);
+#define SGZ_LAUNCH8(BP)                                                                                             \
+		{                                                                                                           \
+			auto kern = k_fused8<STEREO, BP, MATRIX>;                                                               \
+			if (!h->fusedAttrSet)                                                                                   \
+			{                                                                                                       \
+				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
+				h->fusedAttrSet = true;                                                                             \
+			}                                                                                                       \
+			kern<<<grid, block, smem, h->stream>>>(h->dev, a);                                                      \
+		}
+		switch (h->cfg.bin_polation)
+		{
+		case SGZ_BIN_NONE: SGZ_LAUNCH8(SGZ_BIN_NONE); break;
+		case SGZ_BIN_LINEAR: SGZ_LAUNCH8(SGZ_BIN_LINEAR); break;
+		default: SGZ_LAUNCH8(SGZ_BIN_LANCZOS); break;
+		}
+#undef SGZ_LAUNCH8
+		SGZ_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
 	int launchFused(sgz_spectrum* h, const FusedArgs& a)
 	{
+		if (h->fusedR3 == 16 && h->fusedVariant8)
+		{
+			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<true, 0>(h, a);
+			return h->tab.stateChannels == 2 ? launchFused8Binpol<true, 1>(h, a) : launchFused8Binpol<false, 1>(h, a);
+		}
 		const bool stereo = h->tab.stateChannels == 2;
 		const bool passthru = h->cfg.configuration == SGZ_CH_SEPARATE;
 		if (h->fusedR3 == 16)
@@ -774,6 +812,18 @@ extern "C"
 			SGZ_TRY(upload(h, tw1, &d.tw1));
 			SGZ_TRY(upload(h, twiddleTable(e2.size(), double(16 * R3), e2), &d.tw2));
 			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(2 * M), e3), &d.tw3));
+			if (R3 == 16)
+			{
+				std::vector<uint64_t> eA(64), eB(512), eC(512);
+				for (int x = 0; x < 8; ++x) for (int y = 0; y < 8; ++y) eA[x * 8 + y] = uint64_t(x) * y;
+				for (int k = 0; k < 8; ++k) for (int v = 0; v < 64; ++v) { eB[k * 64 + v] = uint64_t(v) * k; eC[k * 64 + v] = uint64_t(v) * k; }
+				std::vector<float2> tw8;
+				const auto A = twiddleTable(64, 64.0, eA), B = twiddleTable(512, 4096.0, eB), C = twiddleTable(512, 512.0, eC);
+				tw8.insert(tw8.end(), A.begin(), A.end()); tw8.insert(tw8.end(), B.begin(), B.end()); tw8.insert(tw8.end(), C.begin(), C.end());
+				SGZ_TRY(upload(h, tw8, &d.tw8));
+				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
+				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
+			}
 			h->fusedR3 = R3;
 			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
 		}
