@@ -252,11 +252,11 @@ def run_ours(args):
                          "algorithmic_bytes_per_frame": ALGO_BYTES_PER_FRAME,
                          "unique_bytes_per_frame": UNIQUE_BYTES_PER_FRAME,
                          "unique_bytes_frac": S * F * UNIQUE_BYTES_PER_FRAME / (kernel_ms * 1e-3) / 1e9 / peak,
-                         "kernel": "sgz::k_fused<16,true,2>", "kernel_ms": kernel_ms},
+                         "kernel": "sgz::k_fused8<true,2,0>", "kernel_ms": kernel_ms},
             "e2e": {"value": frames_per_step / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(h_audio.numel() * 4), "d2h_bytes_per_step": int(h_out.numel() * 4),
                     "ms_per_step": e2e_ms, "steps": e2e_steps},
-            "gpu_launches": args.steps,  # one k_fused launch per step (plus one D2D memcpy node)
+            "gpu_launches": args.steps,  # one k_fused8 launch per device-resident step (plus one D2D memcpy node)
             "clocks": clocks, "checksum": checksum,
         }
         if world == 1 and not args.no_cpu_baseline:
