@@ -249,27 +249,31 @@
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4) zm[u + 512 * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
 				__syncthreads();
+				// A = (Z[j] + conj Z[N-j]) / 2, B = (Z[j] - conj Z[N-j]) / 2i.  With S = Z[j] + Z[N-j] and
+				// D = Z[j] - Z[N-j]: 2A = (S.x, D.y), 2|B| components = (D.x, S.y).  The halving is folded into the
+				// display scale (magScale = invSize / 2), so entries hold 2|.| (or 4|.|^2 beyond linLimit).
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
 					const int slot = perm8(k4);
 					const int j = u + 512 * k4;
 					const float2 zj = make_float2(re[slot].x, im[slot].x);
-					if (j == 0)
+					if (k4 == 0 && j == 0)
 					{
+						// :861-864: csf[N] = Im Z[0] / 2, csf[0] = Re Z[0] / 2, csf[N/2] = packed Nyquists / 2
 						const float2 ny = make_float2(re[slot].y, im[slot].y); // Z[M] = Zm[0]
-						const float h2 = 0.25f * cnorm(ny);
-						csfmag[0] = zj.x * 0.5f;
-						csfmag[N] = zj.y * 0.5f;
+						const float h2 = cnorm(ny);
+						csfmag[0] = zj.x;
+						csfmag[N] = zj.y;
 						csfmag[M] = (M < linLimit) ? approxSqrt(h2) : h2;
 						continue;
 					}
 					const float2 zn = zm[M - j]; // Z[N - j]
-					float ax = (zj.x + zn.x) * 0.5f, ay = (zj.y - zn.y) * 0.5f;
-					const float dx = (zj.x - zn.x) * 0.5f, dy = (zj.y + zn.y) * 0.5f;
-					if (j == M - 1) { ax *= 0.5f; ay *= 0.5f; }
-					float a2 = ax * ax + ay * ay, b2 = dx * dx + dy * dy;
-					if (j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
+					const float2 S = add2(zj, zn), D = sub2(zj, zn);
+					const float2 SS = mul2(S, S), DD = mul2(D, D);
+					float a2 = SS.x + DD.y, b2 = DD.x + SS.y;
+					if (k4 == 7 && j == M - 1) a2 *= 0.25f; // csf[(N >> 1) - 1] *= 0.5, channel 1 only
+					if ((k4 == 0 || linLimit > 512) && j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
 					csfmag[j] = a2;
 					csfmag[N - j] = b2;
 				}
@@ -310,6 +314,7 @@
 			float2* resOut = a.results + ((uint64_t(stream) * a.nFrames + f) * 2) * P;
 			const float poles[2] = { t.pole0, t.pole1 };
 			const int safeFrom = int(t.safeFrom);
+			const float magScale = STEREO ? 0.5f * t.invSize : t.invSize; // the stereo split stores 2 |.|
 			for (int x = u; x < P; x += T)
 			{
 				const uint32_t pkd = mapPacked[x];
@@ -401,24 +406,22 @@
 					vL = bestL > 0.f ? approxSqrt(bestL) : fbMag;
 					if constexpr (STEREO) vR = bestR > 0.f ? approxSqrt(bestR) : fbMag;
 				}
-				const float lmag = fabsf(t.invSize * vL);
-				const float rmag = fabsf(t.invSize * vR);
+				const float lmag = fabsf(magScale * vL);
+				const float rmag = fabsf(magScale * vR);
 				const float sm = mapSlope[x];
 #pragma unroll
 				for (int k = 0; k < 2; ++k)
 				{
 					float2 sv = st[k * P + x];
-					sv.x *= poles[k];
-					if (lmag > sv.x) sv.x = lmag;
+					// st = max(st * pole, mag); y = d > 0 ? ln(d) dy : clip  ==  max(log2(d) dy ln2, clip)
+					// (log2(0) = -inf and NaN both fall to clip, exactly like the reference's `d > 0 ?`)
+					sv.x = fmaxf(sv.x * poles[k], lmag);
 					float2 res;
-					const float dl = sm * sv.x;
-					res.x = dl > 0.f ? __log2f(dl) * t.deltaYLn2 : t.lowerClip;
+					res.x = fmaxf(__log2f(sm * sv.x) * t.deltaYLn2, t.lowerClip);
 					if constexpr (STEREO)
 					{
-						sv.y *= poles[k];
-						if (rmag > sv.y) sv.y = rmag;
-						const float dr = sm * sv.y;
-						res.y = dr > 0.f ? __log2f(dr) * t.deltaYLn2 : t.lowerClip;
+						sv.y = fmaxf(sv.y * poles[k], rmag);
+						res.y = fmaxf(__log2f(sm * sv.y) * t.deltaYLn2, t.lowerClip);
 					}
 					else res.y = 0.f;
 					st[k * P + x] = sv;
