@@ -215,6 +215,40 @@ int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, i
                                  uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
                                  uint32_t n_frames, float* results, int results_mem);
 
+/* ---- audioEntryPoint ------------------------------------------------------
+ * Replaces `template<ISA> void audioEntryPoint(const Constant&, const
+ * optional<AudioPair>&, array<AFloat*, 2> buffer, size_t numSamples)`
+ * (TransformDSP.inl:1165-1211) as called by AudioDispatcher::dispatch
+ * (SpectrumDSP.cpp:81-100) for one callback block, statement by statement:
+ * in ColourSpectrum display mode the block is cut at `sample_buffer_size`
+ * boundaries (the counter `processedSamplesSinceLastFrame` is carried in the
+ * handle); RSNT resonates each piece; at every boundary FFT runs
+ * prepareTransform(history, buffer, availableSamples) + doTransform, then
+ * addAudioFrame (:1139-1148) appends LineMain's results.  In LineGraph mode
+ * only RSNT resonates the block.  `history` is the audio-history view (FFT
+ * only; may be NULL for RSNT), `block` the callback buffer, both laid out
+ * like sgz_spectrum_prepare.  frames: HOST [stream][max_frames][P][2];
+ * *n_emitted receives the number of frames produced (the sfbuf size). */
+int  sgz_spectrum_audio_entry_point(sgz_spectrum* h, const float* history, uint64_t n_history,
+                                    uint64_t history_stride, const float* block, uint64_t n_block,
+                                    uint64_t block_stride, int mem, int layout, float* frames,
+                                    uint32_t max_frames, uint32_t* n_emitted);
+
+/* ---- spectrogram colour columns -----------------------------------------
+ * Replaces `AudioDispatcher::blendAndDispatchSpectrums`
+ * (Source/Spectrum/SpectrumDSP.cpp:110-206): every frame of `results`
+ * ([stream][frame][graph][P][2], as written by sgz_spectrum_process_frames;
+ * LineMain's .magnitude is the intensity) becomes one RGBA8 column of P
+ * pixels.  `pairs_per_view` consecutive streams are the stereo pairs of one
+ * view and are screen-blended (c += (1 - c) * colour, :162-166) into the same
+ * column; n_streams must be a multiple of it.  `ratios` is
+ * Constant::normalizedSpecRatios (6 floats, [0] = 0, Spectrum.cpp:226-246),
+ * `colours` the per-pair SpectrumColourArray [pairs_per_view][6][3] (background
+ * + 5 gradient colours, RGB floats).  rgba: [n_streams / pairs_per_view][frame][P][4]. */
+int  sgz_spectrum_colour_columns(sgz_spectrum* h, const float* results, int mem, uint32_t n_frames,
+                                 uint32_t pairs_per_view, const float* ratios, const float* colours,
+                                 uint8_t* rgba, int out_mem);
+
 /* ---- resonator bank (algo = SGZ_ALGO_RSNT) ------------------------------
  * Replaces `template<ISA> void resonatingDispatch(const Constant&,
  * std::array<AFloat*, 2> buffer, size_t numSamples)` (TransformDSP.inl:1215-1295):

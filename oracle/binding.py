@@ -290,3 +290,25 @@ class OracleScope:
         results = (_abi.ScopePeriodResult * S)()
         self.lib.sgzo_scope_period(C.byref(params), p, layout, S, n, stride, states, results)
         return results
+
+
+def colour_ratios(spec_ratios):
+    lib = load()
+    lib.sgzo_colour_ratios.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_float)]
+    a = np.ascontiguousarray(spec_ratios, dtype=np.float64)
+    out = np.empty(6, dtype=np.float32)
+    lib.sgzo_colour_ratios(a.ctypes.data_as(C.POINTER(C.c_double)), out.ctypes.data_as(C.POINTER(C.c_float)))
+    return out
+
+
+def colour_columns(results, pairs, ratios, colours):
+    lib = load()
+    lib.sgzo_colour_columns.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_float),
+                                        C.POINTER(C.c_float), C.POINTER(C.c_uint8)]
+    r, rp = _f32(results)
+    S, F, _, P, _ = r.shape
+    ra, rap = _f32(ratios)
+    co, cop = _f32(colours)
+    out = np.empty((S // pairs, F, P, 4), dtype=np.uint8)
+    lib.sgzo_colour_columns(rp, S, F, P, pairs, rap, cop, out.ctypes.data_as(C.POINTER(C.c_uint8)))
+    return out

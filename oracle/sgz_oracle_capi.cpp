@@ -11,6 +11,7 @@
 #include "../include/sgz.h"
 
 #include <atomic>
+#include <limits>
 #include <memory>
 #include <thread>
 
@@ -565,4 +566,69 @@ extern "C"
 			results[s].fundamental = r.fundamental; results[s].cycle_samples = r.cycleSamples; results[s].phase = r.phase; results[s].sample_offset = r.sampleOffset;
 		}
 	}
+}
+
+// blendAndDispatchSpectrums — Source/Spectrum/SpectrumDSP.cpp:110-206, restated over flat arrays:
+// results [S][F][2][P][2] (LineMain .magnitude = intensity), pairs of one view = consecutive streams.
+extern "C" void sgzo_colour_columns(const float* results, uint32_t S, uint32_t F, uint32_t P, uint32_t pairs, const float* ratios, const float* colours, uint8_t* rgba)
+{
+	const uint32_t views = S / pairs;
+	std::vector<std::array<float, 3>> colourBuffer(P);
+	for (uint32_t v = 0; v < views; ++v)
+		for (uint32_t s = 0; s < F; ++s)
+		{
+			for (auto& c : colourBuffer) c = { 0.f, 0.f, 0.f };
+			for (uint32_t p = 0; p < pairs; ++p)
+			{
+				const float* sca = colours + p * 18; // generateSpectrogramColourRotation(p)
+				const float* input = results + (((uint64_t(v) * pairs + p) * F + s) * 2 + 0) * P * 2;
+				for (uint32_t i = 0; i < P; ++i)
+				{
+					const auto intensity = input[2 * i];
+					if (intensity < 0) continue;
+					std::array<float, 3> colour{ 0.f, 0.f, 0.f };
+					if (intensity < 0.999f)
+					{
+						float accumulatedSum = 0;
+						for (std::size_t c = 1; c < 6; ++c)
+						{
+							const auto nextScale = ratios[c];
+							accumulatedSum += nextScale;
+							if (accumulatedSum >= intensity)
+							{
+								const auto min = accumulatedSum - nextScale;
+								const auto max = accumulatedSum;
+								const auto mix = (intensity - min) / (max - min);
+								const auto imix = 1 - mix;
+								for (int k = 0; k < 3; ++k) colour[k] = sca[(c - 1) * 3 + k] * imix + sca[c * 3 + k] * mix;
+								break;
+							}
+						}
+					}
+					else
+					{
+						for (int k = 0; k < 3; ++k) colour[k] = sca[15 + k];
+					}
+					for (std::size_t c = 0; c < 3; ++c) colourBuffer[i][c] += (1 - colourBuffer[i][c]) * colour[c];
+				}
+			}
+			uint8_t* px = rgba + ((uint64_t(v) * F + s) * P) * 4;
+			for (uint32_t p = 0; p < P; ++p)
+			{
+				px[4 * p + 0] = static_cast<uint8_t>(colourBuffer[p][0] * 255);
+				px[4 * p + 1] = static_cast<uint8_t>(colourBuffer[p][1] * 255);
+				px[4 * p + 2] = static_cast<uint8_t>(colourBuffer[p][2] * 255);
+				px[4 * p + 3] = 255;
+			}
+		}
+}
+
+// calculateSpectrumColourRatios — Source/Spectrum/Spectrum.cpp:226-246
+extern "C" void sgzo_colour_ratios(const double* specRatios, float* out)
+{
+	double acc = 0.0, vals[5];
+	for (int i = 0; i < 5; ++i) { vals[i] = std::max(0.0001, specRatios[i]); acc += vals[i]; }
+	acc += std::numeric_limits<float>::epsilon();
+	out[0] = 0;
+	for (int i = 0; i < 5; ++i) out[i + 1] = static_cast<float>(vals[i] / acc);
 }

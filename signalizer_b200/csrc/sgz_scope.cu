@@ -610,7 +610,7 @@ extern "C"
 		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
 		const size_t bytes = size_t(n_streams) * n_samples * 3 * sizeof(float);
 		float* dOut = xyz;
-		if (out_mem == SGZ_MEM_HOST) { void* p; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
+		if (out_mem == SGZ_MEM_HOST) { void* p = nullptr; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
 		const dim3 block(256), grid(unsigned((n_samples + 255) / 256), n_streams);
 		k_vscope_vertices<<<grid, block, 0, c->stream>>>(*cfg, d, layout, n_samples, stream_stride, dOut);
 		SGZS_CUDA(cudaGetLastError());
@@ -633,7 +633,7 @@ extern "C"
 		if (n_samples && (rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
 		const size_t bytes = size_t(n_streams) * cfg->width * cfg->height * sizeof(uint32_t);
 		uint32_t* dOut = hist;
-		if (out_mem == SGZ_MEM_HOST) { void* p; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<uint32_t*>(p); }
+		if (out_mem == SGZ_MEM_HOST) { void* p = nullptr; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<uint32_t*>(p); }
 		SGZS_CUDA(cudaMemsetAsync(dOut, 0, bytes, c->stream));
 		if (n_samples)
 		{
@@ -661,7 +661,7 @@ extern "C"
 		const float* d = nullptr;
 		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
 		// host slot order: envelope[2], balance[slow][L,R], balance[fast][L,R], phase[slow], phase[fast] = struct order
-		void* p; if ((rc = ensure(c, 2, size_t(n_streams) * 8 * sizeof(float), &p)) != SGZ_OK) return rc;
+		void* p = nullptr; if ((rc = ensure(c, 2, size_t(n_streams) * 8 * sizeof(float), &p)) != SGZ_OK) return rc;
 		SGZS_CUDA(cudaMemcpyAsync(p, filters, size_t(n_streams) * 8 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
 		const float pole1 = static_cast<float>(std::pow(stereo_coeff, second_stereo_filter_speed)); // Vectorscope.cpp:279
 		const unsigned warpsPerBlock = 4;
@@ -696,11 +696,11 @@ extern "C"
 		SGZS_GUARD(c);
 		const float* d = nullptr;
 		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
-		void* dPos; if ((rc = ensure(c, 2, size_t(n_streams) * sizeof(double), &dPos)) != SGZ_OK) return rc;
+		void* dPos = nullptr; if ((rc = ensure(c, 2, size_t(n_streams) * sizeof(double), &dPos)) != SGZ_OK) return rc;
 		SGZS_CUDA(cudaMemcpyAsync(dPos, sample_pos, size_t(n_streams) * sizeof(double), cudaMemcpyHostToDevice, c->stream));
 		const size_t bytes = size_t(n_streams) * count * 2 * sizeof(float);
 		float* dOut = out_xy;
-		if (out_mem == SGZ_MEM_HOST) { void* p; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
+		if (out_mem == SGZ_MEM_HOST) { void* p = nullptr; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
 		ResampleArgs a{};
 		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = cfg->channel;
 		a.samplePos = static_cast<const double*>(dPos); a.spp = cfg->samples_per_pixel; a.left = cfg->left; a.inc = cfg->inc; a.count = count; a.out = dOut;
@@ -728,7 +728,7 @@ extern "C"
 		if (n_samples && (rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
 		const size_t stBytes = size_t(n_streams) * sizeof(sgz_scope_trigger_state), pkBytes = size_t(n_streams) * std::max<uint32_t>(max_peaks, 1) * sizeof(uint64_t),
 			cnBytes = size_t(n_streams) * sizeof(uint32_t);
-		void* p; if ((rc = ensure(c, 2, stBytes + pkBytes + cnBytes + 64, &p)) != SGZ_OK) return rc;
+		void* p = nullptr; if ((rc = ensure(c, 2, stBytes + pkBytes + cnBytes + 64, &p)) != SGZ_OK) return rc;
 		auto* dStates = static_cast<sgz_scope_trigger_state*>(p);
 		auto* dPeaks = reinterpret_cast<uint64_t*>(static_cast<char*>(p) + ((stBytes + 15) & ~size_t(15)));
 		auto* dCounts = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dPeaks) + pkBytes);
@@ -762,7 +762,7 @@ extern "C"
 		// --- calculateFundamentalPeriod: FFT + pick on the device ---
 		const size_t recBytes = size_t(n_streams) * sizeof(sgz_scope_bin_record);
 		const size_t auxBytes = size_t(n_streams) * (sizeof(long long) + sizeof(double) + sizeof(double2));
-		void* p; if ((rc = ensure(c, 2, recBytes + auxBytes + 64, &p)) != SGZ_OK) return rc;
+		void* p = nullptr; if ((rc = ensure(c, 2, recBytes + auxBytes + 64, &p)) != SGZ_OK) return rc;
 		auto* dPicked = static_cast<sgz_scope_bin_record*>(p);
 		auto* dFirst = reinterpret_cast<long long*>(static_cast<char*>(p) + ((recBytes + 15) & ~size_t(15)));
 		auto* dRadians = reinterpret_cast<double*>(dFirst + n_streams);

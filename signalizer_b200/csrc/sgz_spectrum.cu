@@ -473,6 +473,64 @@ namespace sgz
 		}
 	}
 
+	// ------------------------------------------------------------------------------------------
+	// spectrogram colour columns: blendAndDispatchSpectrums (SpectrumDSP.cpp:110-206).  uint8 output,
+	// so the float arithmetic that decides it uses non-contractable round-to-nearest intrinsics.
+	// ------------------------------------------------------------------------------------------
+	struct ColourArgs
+	{
+		const float2* results; // [S][F][2][P]
+		uint32_t nFrames, pairs, P;
+		float ratios[6];
+		const float* colours;  // [pairs][6][3]
+		uchar4* rgba;          // [S / pairs][F][P]
+	};
+
+	__global__ void k_colour_columns(ColourArgs a)
+	{
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		const uint32_t f = blockIdx.y, view = blockIdx.z;
+		if (i >= a.P) return;
+		float cb[3] = { 0.f, 0.f, 0.f };
+		for (uint32_t p = 0; p < a.pairs; ++p)
+		{
+			const uint32_t s = view * a.pairs + p;
+			const float intensity = a.results[((uint64_t(s) * a.nFrames + f) * 2 + 0) * a.P + i].x; // LineMain .magnitude
+			if (intensity < 0) continue;
+			const float* sca = a.colours + p * 18;
+			float colour[3] = { 0.f, 0.f, 0.f };
+			if (intensity < 0.999f)
+			{
+				float accumulatedSum = 0;
+				for (int c = 1; c < 6; ++c)
+				{
+					const float nextScale = a.ratios[c];
+					accumulatedSum = __fadd_rn(accumulatedSum, nextScale);
+					if (accumulatedSum >= intensity)
+					{
+						const float mn = __fsub_rn(accumulatedSum, nextScale), mx = accumulatedSum;
+						const float mix = __fdiv_rn(__fsub_rn(intensity, mn), __fsub_rn(mx, mn));
+						const float imix = __fsub_rn(1.f, mix);
+						for (int k = 0; k < 3; ++k)
+							colour[k] = __fadd_rn(__fmul_rn(sca[(c - 1) * 3 + k], imix), __fmul_rn(sca[c * 3 + k], mix));
+						break;
+					}
+				}
+			}
+			else
+			{
+				for (int k = 0; k < 3; ++k) colour[k] = sca[15 + k];
+			}
+			for (int k = 0; k < 3; ++k) cb[k] = __fadd_rn(cb[k], __fmul_rn(__fsub_rn(1.f, cb[k]), colour[k])); // GL_ONE_MINUS_SRC_COLOR
+		}
+		uchar4 px;
+		px.x = static_cast<unsigned char>(__fmul_rn(cb[0], 255.f));
+		px.y = static_cast<unsigned char>(__fmul_rn(cb[1], 255.f));
+		px.z = static_cast<unsigned char>(__fmul_rn(cb[2], 255.f));
+		px.w = 255;
+		a.rgba[(uint64_t(view) * a.nFrames + f) * a.P + i] = px;
+	}
+
 #include "sgz_fused.cuh"
 #include "sgz_fused8.cuh"
 #include "sgz_resonator.cuh"
@@ -505,6 +563,7 @@ struct sgz_spectrum
 	float* dAudioStage{ nullptr }; size_t audioStageBytes{ 0 };
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
 	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
+	uint64_t processedSamplesSinceLastFrame{ 0 }; // TransformPair.h:189 (one authority counter for all pairs, SpectrumDSP.cpp:81,93)
 	int fusedR3{ 0 };
 	bool fusedVariant8{ false }; // N = 8192: use k_fused8 (512 threads, radix-8 x 4) instead of k_fused<16> (256 threads, radix-16 x 3)
 	cudaStream_t copyIn{ nullptr }, copyOut{ nullptr }; // host-buffer pipeline of process_frames
@@ -1127,6 +1186,113 @@ extern "C"
 		k_resonate<<<dim3(blocksX, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
 		if (a.chunks > 1) k_resonate_combine<<<dim3(blocksX, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
 		SGZ_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_audio_entry_point(sgz_spectrum* h, const float* history, uint64_t n_history, uint64_t history_stride, const float* block, uint64_t n_block,
+		uint64_t block_stride, int mem, int layout, float* frames, uint32_t max_frames, uint32_t* n_emitted)
+	{
+		if (!h || !block || !n_emitted || (max_frames && !frames)) return fail(SGZ_EINVAL, "null argument");
+		*n_emitted = 0;
+		const bool fft = h->cfg.algo == SGZ_ALGO_FFT, rsnt = h->cfg.algo == SGZ_ALGO_RSNT;
+		if (fft && h->cfg.display_mode == SGZ_DISPLAY_COLOURSPECTRUM && !history) return fail(SGZ_EINVAL, "the FFT algorithm needs the audio-history view");
+		const uint32_t P = h->tab.P;
+		const uint64_t sampleBufferSize = h->cfg.sample_buffer_size;
+		if (h->cfg.display_mode == SGZ_DISPLAY_COLOURSPECTRUM)
+		{
+			// TransformDSP.inl:1169-1204
+			int64_t n = int64_t(n_block);
+			uint64_t offset = 0;
+			uint32_t emitted = 0;
+			while (n > 0)
+			{
+				const int64_t numRemainingSamples = h->processedSamplesSinceLastFrame > sampleBufferSize ? 0 : int64_t(sampleBufferSize - h->processedSamplesSinceLastFrame);
+				const int64_t availableSamples = numRemainingSamples + std::min<int64_t>(0, n - numRemainingSamples);
+				int rc;
+				if (rsnt && availableSamples > 0)
+				{
+					// resonatingDispatch(constant, { buffer[0] + offset, buffer[1] + offset }, availableSamples)
+					SGZ_GUARD(h);
+					const float* dBlock = nullptr;
+					if ((rc = stageAudio(h, block, mem, n_block, block_stride, &dBlock, &h->dAudioStage, &h->audioStageBytes)) != SGZ_OK) return rc;
+					if ((rc = resonateBlock(h, dBlock, layout, n_block, block_stride, offset, uint32_t(availableSamples))) != SGZ_OK) return rc;
+				}
+				h->processedSamplesSinceLastFrame += uint64_t(availableSamples);
+				if (h->processedSamplesSinceLastFrame >= sampleBufferSize)
+				{
+					bool transformReady = true;
+					if (fft)
+					{
+						// NOTE: `buffer`, not buffer + offset, exactly like the reference (:1192)
+						rc = sgz_spectrum_prepare_preliminary(h, history, n_history, history_stride, block, uint64_t(availableSamples), block_stride, mem, layout);
+						if (rc < 0) return rc;
+						transformReady = rc == SGZ_OK;
+						if (transformReady && (rc = sgz_spectrum_transform(h)) != SGZ_OK) return rc;
+					}
+					if (transformReady)
+					{
+						// addAudioFrame: mapToLinearSpace + postProcessStdTransform + sfbuf.emplace_back(LineMain results)
+						if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return rc;
+						if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return rc;
+						if (emitted < max_frames)
+						{
+							SGZ_GUARD(h);
+							SGZ_CUDA(cudaMemcpy2DAsync(frames + size_t(emitted) * P * 2, size_t(max_frames) * P * sizeof(float2), h->dResults, size_t(2) * P * sizeof(float2),
+								size_t(P) * sizeof(float2), h->nStreams, cudaMemcpyDeviceToHost, h->stream));
+						}
+						++emitted;
+					}
+					h->processedSamplesSinceLastFrame = 0;
+				}
+				if (availableSamples <= 0 && numRemainingSamples <= 0 && sampleBufferSize == 0) break; // degenerate configuration
+				offset += uint64_t(availableSamples);
+				n -= availableSamples;
+			}
+			*n_emitted = emitted;
+			SGZ_GUARD(h);
+			SGZ_CUDA(cudaStreamSynchronize(h->stream));
+			return SGZ_OK;
+		}
+		if (rsnt) return sgz_resonator_process(h, block, mem, layout, n_block, block_stride); // :1206-1209
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_colour_columns(sgz_spectrum* h, const float* results, int mem, uint32_t n_frames, uint32_t pairs_per_view, const float* ratios,
+		const float* colours, uint8_t* rgba, int out_mem)
+	{
+		if (!h || !results || !ratios || !colours || !rgba) return fail(SGZ_EINVAL, "null argument");
+		if (pairs_per_view == 0 || h->nStreams % pairs_per_view != 0) return fail(SGZ_EINVAL, "n_streams must be a multiple of pairs_per_view");
+		if (n_frames == 0) return SGZ_OK;
+		if (n_frames > 65535 || h->nStreams / pairs_per_view > 65535) return fail(SGZ_EINVAL, "too many frames or views for one launch");
+		SGZ_GUARD(h);
+		const uint32_t P = h->tab.P, views = h->nStreams / pairs_per_view;
+		const size_t resFloats = size_t(h->nStreams) * n_frames * 2 * P * 2;
+		const size_t outBytes = size_t(views) * n_frames * P * 4;
+		const size_t colBytes = size_t(pairs_per_view) * 18 * sizeof(float);
+		const float* dRes = results;
+		int rc;
+		if (mem == SGZ_MEM_HOST)
+		{
+			if ((rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, resFloats * sizeof(float))) != SGZ_OK) return rc;
+			SGZ_CUDA(cudaMemcpyAsync(h->dResultStage, results, resFloats * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+			dRes = h->dResultStage;
+		}
+		// colours + (for host callers) the output columns share the audio staging slot
+		const size_t need = ((colBytes + 255) & ~size_t(255)) + (out_mem == SGZ_MEM_HOST ? outBytes : 0);
+		if ((rc = ensureStage(h, &h->dAudioStage, &h->audioStageBytes, need)) != SGZ_OK) return rc;
+		SGZ_CUDA(cudaMemcpyAsync(h->dAudioStage, colours, colBytes, cudaMemcpyHostToDevice, h->stream));
+		uint8_t* dOut = out_mem == SGZ_MEM_HOST ? reinterpret_cast<uint8_t*>(h->dAudioStage) + ((colBytes + 255) & ~size_t(255)) : rgba;
+		ColourArgs a{};
+		a.results = reinterpret_cast<const float2*>(dRes); a.nFrames = n_frames; a.pairs = pairs_per_view; a.P = P;
+		for (int k = 0; k < 6; ++k) a.ratios[k] = ratios[k];
+		a.colours = h->dAudioStage; a.rgba = reinterpret_cast<uchar4*>(dOut);
+		k_colour_columns<<<dim3((P + 255) / 256, n_frames, views), 256, 0, h->stream>>>(a);
+		SGZ_CUDA(cudaGetLastError());
+		if (out_mem == SGZ_MEM_HOST)
+		{
+			SGZ_CUDA(cudaMemcpyAsync(rgba, dOut, outBytes, cudaMemcpyDeviceToHost, h->stream));
+			SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		}
 		return SGZ_OK;
 	}
 

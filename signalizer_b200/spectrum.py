@@ -159,6 +159,37 @@ class TransformPairBatch:
     def clear_audio_state(self):
         check(self.lib.sgz_spectrum_clear_audio_state(self._h))
 
+    # -- audioEntryPoint ---------------------------------------------------------------------
+    def audio_entry_point(self, history, block, layout=_abi.LAYOUT_INTERLEAVED, max_frames=64):
+        """template<ISA> void audioEntryPoint(const Constant&, const optional<AudioPair>&, array<AFloat*, 2>, size_t)
+        (TransformDSP.inl:1165-1211) for every pair; returns the emitted sfbuf frames [streams, n, P, 2]."""
+        bk, bptr, mem = _buf(block)
+        s, nb, bstride = self._geometry(bk, layout)
+        assert s == self.n_streams
+        if history is not None:
+            hk, hptr, hmem = _buf(history)
+            assert hmem == mem
+            _, nh, hstride = self._geometry(hk, layout)
+        else:
+            hptr, nh, hstride = None, 0, 0
+        out = np.zeros((self.n_streams, max_frames, self.P, 2), dtype=np.float32)
+        n = C.c_uint32(0)
+        check(self.lib.sgz_spectrum_audio_entry_point(self._h, hptr, nh, hstride, bptr, nb, bstride, mem, layout, out.ctypes.data, max_frames, C.byref(n)))
+        return out[:, :min(n.value, max_frames)]
+
+    # -- spectrogram colour columns ----------------------------------------------------------
+    def blend_and_dispatch_spectrums(self, results, pairs_per_view, ratios, colours):
+        """AudioDispatcher::blendAndDispatchSpectrums (SpectrumDSP.cpp:110-206): results
+        [streams, frames, 2, P, 2] -> RGBA8 columns [streams / pairs_per_view, frames, P, 4]."""
+        keep, ptr, mem = _buf(results)
+        n_frames = keep.shape[1]
+        ratios = np.ascontiguousarray(ratios, dtype=np.float32); colours = np.ascontiguousarray(colours, dtype=np.float32)
+        assert ratios.shape == (6,) and colours.shape == (pairs_per_view, 6, 3)
+        out = np.empty((self.n_streams // pairs_per_view, n_frames, self.P, 4), dtype=np.uint8)
+        check(self.lib.sgz_spectrum_colour_columns(self._h, ptr, mem, n_frames, pairs_per_view, ratios.ctypes.data, colours.ctypes.data,
+                                                   out.ctypes.data, _abi.MEM_HOST))
+        return out
+
     # -- resonator bank (algo = RSNT) ------------------------------------------------------
     def resonating_dispatch(self, audio, layout=_abi.LAYOUT_INTERLEAVED):
         """template<ISA> void resonatingDispatch(const Constant&, array<AFloat*, 2> buffer, size_t n)

@@ -347,3 +347,59 @@ def test_host_buffer_pipeline_equals_single_launch():
     again_dev = b.process_frames(torch.from_numpy(audio).cuda(), hop, F)
     b.synchronize()
     np.testing.assert_array_equal(again, again_dev.cpu().numpy())
+
+
+def test_spectrogram_colour_columns_bit_exact():
+    # §8(f) row 1: blendAndDispatchSpectrums (SpectrumDSP.cpp:110-206) over process_frames results
+    from oracle.binding import colour_columns, colour_ratios
+    cfg = _abi.default_config(window_size=4096, window_type=_abi.WIN_HANN, display_mode=_abi.DISPLAY_COLOURSPECTRUM)
+    S, F, hop, pairs = 6, 5, 1024, 3
+    audio = frames_case(cfg, S, F, hop)
+    g = TransformPairBatch(cfg, S)
+    res = g.process_frames(audio, hop, F)
+    ratios = colour_ratios([0.1, 0.2, 0.3, 0.25, 0.15])
+    assert ratios[0] == 0 and abs(ratios.sum() - 1) < 1e-6
+    rng = np.random.default_rng(5)
+    colours = rng.random((pairs, 6, 3)).astype(np.float32)
+    res[0, 0, 0, :7, 0] = [-1.0, 0.0, 0.9989, 0.999, 1.0, 1.5, 0.5]   # skipped, floor, near-top, top colour, ...
+    got = g.blend_and_dispatch_spectrums(res, pairs, ratios, colours)
+    want = colour_columns(res, pairs, ratios, colours)
+    assert got.shape == (S // pairs, F, cfg.axis_points, 4)
+    np.testing.assert_array_equal(got, want)
+    assert np.all(got[..., 3] == 255) and got[..., :3].max() > 0
+
+
+@pytest.mark.parametrize("algo", [_abi.ALGO_FFT, _abi.ALGO_RSNT])
+@pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_SEPARATE, _abi.CH_MIDSIDE])
+def test_audio_entry_point_frame_scheduler(algo, conf):
+    # audioEntryPoint (TransformDSP.inl:1165-1211): blocks cut at sampleBufferSize boundaries, frames into sfbuf
+    cfg = _abi.default_config(algo=algo, window_size=2048, window_type=_abi.WIN_HANN, configuration=conf,
+                              display_mode=_abi.DISPLAY_COLOURSPECTRUM, sample_buffer_size=300, axis_points=256)
+    S = 3
+    o = OracleSpectrum(cfg, S)
+    g = TransformPairBatch(cfg, S)
+    hist = signals.batch(S, 2048, first_stream=1)
+    total = signals.batch(S, 5000, first_stream=4)
+    pos = 0
+    emitted = 0
+    for block in (100, 250, 1024, 299, 301, 1500):   # boundaries fall inside, at the end of, and across blocks
+        chunk = np.ascontiguousarray(total[:, pos:pos + block]); pos += block
+        want = o.audio_entry_point(hist, chunk)
+        got = g.audio_entry_point(hist if algo == _abi.ALGO_FFT else None, chunk)
+        assert got.shape == want.shape, (block, got.shape, want.shape)
+        emitted += got.shape[1]
+        if got.shape[1]:
+            used = 1 if conf == _abi.CH_LEFT else 2
+            lin = np.where(want > -300, 1e-6 * np.exp(want.astype(np.float64) * np.log(1e6)), 0.0)
+            for s in range(S):
+                for f in range(got.shape[1]):
+                    m = want[s, f, :, :used] > -300
+                    assert_log_close(got[s, f, :, :used][m], want[s, f, :, :used][m], lin=lin[s, f, :, :used][m], peak=lin[s, f].max(),
+                                     floor=2e-5 if algo == _abi.ALGO_RSNT else FLOOR, what=f"block {block} frame {f}")
+    assert emitted == sum((100, 250, 1024, 299, 301, 1500)) // 300
+    # LineGraph mode: FFT does nothing here, RSNT resonates the whole block
+    cfg2 = _abi.copy_config(cfg, display_mode=_abi.DISPLAY_LINEGRAPH)
+    g2 = TransformPairBatch(cfg2, S)
+    assert g2.audio_entry_point(hist if algo == _abi.ALGO_FFT else None, total[:, :700].copy()).shape[1] == 0
+    if algo == _abi.ALGO_RSNT:
+        assert np.abs(g2.get_resonator_state()).max() > 0
