@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""Regenerates tests/golden/spectrum_golden.npz from the CPU oracle (oracle/, float32 build).
+
+The reference ships no golden vectors and cannot be run, so these fixtures pin the
+ORACLE (a regression guard for the checker itself) and give the GPU tests a committed target that
+does not depend on the oracle being rebuilt identically.  Inputs are the seeded synthetic signals of
+signalizer_b200/signals.py; every case records its configuration overrides.
+
+    python tests/golden/make_golden.py"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+
+from oracle.binding import OracleSpectrum  # noqa: E402
+from signalizer_b200 import _abi, signals  # noqa: E402
+
+CASES = {
+    "c1_hann4096_separate_lanczos": dict(window_size=4096, window_type=_abi.WIN_HANN),
+    "c3_bh8192_separate_lanczos": dict(),
+    "bh8192_left_linear": dict(configuration=_abi.CH_LEFT, bin_polation=_abi.BIN_LINEAR),
+    "hamming6000_midside_none": dict(window_size=6000, window_type=_abi.WIN_HAMMING, configuration=_abi.CH_MIDSIDE, bin_polation=_abi.BIN_NONE),
+    "phase2048_lanczos_p256": dict(window_size=2048, configuration=_abi.CH_PHASE, axis_points=256),
+}
+S, F = 3, 3
+
+
+def run(overrides):
+    cfg = _abi.default_config(**overrides)
+    hop = cfg.window_size // 4
+    audio = signals.batch(S, signals.frames_length(cfg.window_size, hop, F), first_stream=1)
+    o = OracleSpectrum(cfg, S)
+    res = o.process_frames(audio, hop, F)
+    return res, np.stack([o.states(0), o.states(1)])
+
+
+if __name__ == "__main__":
+    out = {}
+    for name, ov in CASES.items():
+        res, st = run(ov)
+        out[name + "/results"] = res
+        out[name + "/states"] = st
+    out["meta"] = np.frombuffer(json.dumps({"streams": S, "frames": F, "first_stream": 1, "cases": CASES}).encode(), dtype=np.uint8)
+    np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "spectrum_golden.npz"), **out)
+    print("wrote", len(CASES), "cases")

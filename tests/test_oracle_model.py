@@ -185,3 +185,18 @@ def test_resonator_oracle_known_answers():
     assert np.abs(o.resonator_state()).max() < 1e-3 * np.abs(whole).max()
     o.clear_audio_state()
     assert np.all(o.resonator_state() == 0)
+
+
+def test_window_kernels_match_scipy():
+    # pins the cosine-sum window family (a cpl decision) to scipy.signal's definitions
+    from scipy.signal import get_window
+    names = {_abi.WIN_HANN: "hann", _abi.WIN_HAMMING: "hamming", _abi.WIN_BLACKMAN: "blackman",
+             _abi.WIN_BLACKMAN_HARRIS: "blackmanharris", _abi.WIN_FLATTOP: "flattop", _abi.WIN_RECTANGULAR: "boxcar"}
+    for W in (64, 1000, 4096):
+        for wt, name in names.items():
+            for shape, fftbins in ((_abi.WINSHAPE_PERIODIC, True), (_abi.WINSHAPE_SYMMETRIC, False)):
+                cfg = _abi.default_config(window_size=W, window_type=wt, window_shape=shape)
+                o = OracleSpectrum(cfg, 1)
+                want = get_window(name, W, fftbins=fftbins)
+                np.testing.assert_allclose(o.window_kernel()[:W], want, rtol=0, atol=2e-7, err_msg=f"{name} {W} {fftbins}")
+                assert abs(o.info.window_kernel_scale - W / want.sum()) < 1e-5 * W / want.sum()
