@@ -36,6 +36,13 @@ struct sgz_context
 	bool ownStream{ false };
 	void* stage[4]{ nullptr, nullptr, nullptr, nullptr };
 	size_t stageBytes[4]{ 0, 0, 0, 0 };
+	// x positions of the resampler's vertices for the last (left, right, inc): the reference accumulates
+	// unitSpacePos += inc serially (OscilloscopeRendering.cpp:863-886), which left + m * inc only
+	// reproduces for dyadic inc, so the host replays the accumulation once per view and caches it
+	float* xTable{ nullptr };
+	size_t xCapacity{ 0 };
+	uint64_t xCount{ 0 };
+	double xKey[3]{ 0, 0, 0 };
 };
 
 namespace sgz
@@ -233,7 +240,8 @@ namespace sgz
 	{
 		const float* audio; int layout; uint64_t n; uint64_t stride; int channel;
 		const double* samplePos; // [S] device
-		double spp, left, inc; uint64_t count;
+		double spp; uint64_t count;
+		const float* xs; // [count] device, float(unitSpacePos) per vertex
 		float* out;
 	};
 
@@ -300,8 +308,132 @@ namespace sgz
 			acc += double(v) * w;
 		}
 		float* o = a.out + (uint64_t(s) * a.count + m) * 2;
-		o[0] = float(a.left + double(m) * a.inc);
+		o[0] = a.xs[m];
 		o[1] = float(acc);
+	}
+
+	// Polyphase variant for integer oversampling ratios R = 1 / spp (BASELINE config 4: R = 16): in steady
+	// state the fractional position of output m depends only on m mod R (and on the stream's
+	// samplePos), so a CTA evaluates the R x 20 double weights once into shared memory and every
+	// vertex is 20 double FMAs.  A vertex whose delta differs from its phase's (the first R outputs,
+	// before the window starts sliding) takes the direct evaluation.
+	constexpr int kMaxPhases = 64;
+	constexpr int kPolyVerticesPerThread = 8;
+	__device__ __forceinline__ double lanczosWeight10(double frac, int ib, int t)
+	{
+		// weight of tap i = ib - 9 + t at distance d = frac + (9 - t); same closed form as k_scope_resample's fast weights
+		const int j = 9 - t;
+		const int i = ib - j;
+		const double d = frac + double(j);
+		if (i < 0 || i >= 21) return 0.0;
+		if (d == 0.0) return 1.0;
+		const double S1 = sinpi(frac);
+		double sa, ca;
+		sincospi(frac * 0.1, &sa, &ca);
+		const int aj = j < 0 ? -j : j;
+		const double cj = kCos10[aj], sj = j < 0 ? -kSin10[aj] : kSin10[aj];
+		const double invPi2x10 = 10.0 / (3.1415926535897932384626433832795 * 3.1415926535897932384626433832795);
+		return ((aj & 1) ? -S1 : S1) * (sa * cj + ca * sj) * invPi2x10 / (d * d);
+	}
+
+	__device__ __noinline__ double resampleVertexDirect(const ResampleArgs& a, const float* src, long long base, double delta)
+	{
+		const double x = 10.0 + delta;
+		const double fx = floor(x);
+		const int ib = int(fx);
+		double acc = 0.0;
+		for (int t = 0; t < 20; ++t)
+		{
+			const int i = ib - 9 + t;
+			const long long idx = base + i;
+			if (i >= 0 && i < 21 && idx >= 0 && idx < (long long)a.n)
+			{
+				float l, rr;
+				loadLR(src, a.layout, a.n, uint64_t(idx), l, rr);
+				acc += double(oscChannel(a.channel, l, rr)) * lanczosWeight10(x - fx, ib, t);
+			}
+		}
+		return acc;
+	}
+
+	template <int LAYOUT, int CHANNEL>
+	__global__ void __launch_bounds__(256) k_scope_resample_poly(ResampleArgs a, int R)
+	{
+		__shared__ double wts[20][kMaxPhases]; // [tap][phase]: the lanes of a warp read consecutive phases
+		__shared__ double deltaOf[kMaxPhases];
+		__shared__ int ibOf[kMaxPhases];
+		const uint32_t s = blockIdx.y;
+		const double samplePos0 = a.samplePos[s];
+		const double fl0 = floor(samplePos0);
+		// one (phase, tap) weight per thread; steady-state delta of phase r taken at an output far enough
+		// along that the window slides (q = 2)
+		for (int e = threadIdx.x; e < R * 20; e += blockDim.x)
+		{
+			const int r = e / 20, t = e - r * 20;
+			const double currentSample = fl0 + double(2 * R + r) * a.spp;
+			const double d0 = currentSample - samplePos0;
+			const double k = d0 > 1.0 ? ceil(d0 - 1.0) : 0.0;
+			const double delta = currentSample - (samplePos0 + k);
+			const double x = 10.0 + delta;
+			const double fx = floor(x);
+			if (t == 0) { deltaOf[r] = delta; ibOf[r] = int(fx); }
+			wts[t][r] = lanczosWeight10(x - fx, int(fx), t);
+		}
+		__syncthreads();
+		const float* src = a.audio + uint64_t(s) * a.stride;
+		const uint64_t m0 = uint64_t(blockIdx.x) * (256 * kPolyVerticesPerThread) + threadIdx.x;
+		for (int it = 0; it < kPolyVerticesPerThread; ++it)
+		{
+			const uint64_t m = m0 + uint64_t(it) * 256;
+			if (m >= a.count) return;
+			const double currentSample = fl0 + double(m) * a.spp;
+			const double d0 = currentSample - samplePos0;
+			const double k = d0 > 1.0 ? ceil(d0 - 1.0) : 0.0;
+			const double delta = currentSample - (samplePos0 + k);
+			const long long base = (long long)a.n - (long long)fl0 - 10 + (long long)k; // index of kernel[0]
+			const int r = int(uint32_t(m) & uint32_t(R - 1)); // R is a power of two
+			// samplePos + k rounds differently as k grows, so the deltas of one phase agree to ~1e-12 rather
+			// than exactly; the weights are smooth in delta (|dw/d delta| < 4), far inside the float32 output ulp
+			const bool table = fabs(delta - deltaOf[r]) < 1e-9;
+			double acc = 0.0;
+			if (table)
+			{
+				const int ib = ibOf[r];
+				const long long first = base + ib - 9;
+				const double* wp = &wts[0][r];
+				if (first >= 0 && first + 19 < (long long)a.n)
+				{
+					// interior vertex: all 20 taps are inside the audio window; ib is 10, or 11 when the vertex
+					// sits exactly on a sample (delta == 1), where the last tap falls outside the kernel
+#pragma unroll
+					for (int t = 0; t < 20; ++t)
+					{
+						float l, rr;
+						loadLR(src, LAYOUT, a.n, uint64_t(first + t), l, rr);
+						if (t < 19 || ib == 10) acc += double(oscChannel(CHANNEL, l, rr)) * wp[t * kMaxPhases];
+					}
+				}
+				else
+				{
+					for (int t = 0; t < 20; ++t)
+					{
+						const int i = ib - 9 + t;
+						const long long idx = first + t;
+						if (i >= 0 && i < 21 && idx >= 0 && idx < (long long)a.n)
+						{
+							float l, rr;
+							loadLR(src, LAYOUT, a.n, uint64_t(idx), l, rr);
+							acc += double(oscChannel(CHANNEL, l, rr)) * wp[t * kMaxPhases];
+						}
+					}
+				}
+			}
+			else
+				acc = resampleVertexDirect(a, src, base, delta);
+			float* o = a.out + (uint64_t(s) * a.count + m) * 2;
+			o[0] = a.xs[m];
+			o[1] = float(acc);
+		}
 	}
 
 	// ------------------------------------------------------------------------------------------
@@ -569,6 +701,7 @@ extern "C"
 			CtxGuard g(c->device);
 			if (c->stream) cudaStreamSynchronize(c->stream);
 			for (void* p : c->stage) if (p) cudaFree(p);
+			if (c->xTable) cudaFree(c->xTable);
 			if (c->ownStream && c->stream) cudaStreamDestroy(c->stream);
 		}
 		delete c;
@@ -690,7 +823,9 @@ extern "C"
 		if (!cfg || cfg->abi_version != SGZ_ABI_VERSION || !sample_pos || !out_xy) return fail(SGZ_EINVAL, "bad resample arguments");
 		if (cfg->channel < SGZ_OSC_LEFT || cfg->channel > SGZ_OSC_SIDE) return fail(SGZ_EINVAL, "bad channel");
 		if (!(cfg->samples_per_pixel > 0)) return fail(SGZ_EINVAL, "samples_per_pixel must be positive");
-		const uint64_t count = sgz_scope_resample_count(cfg);
+		if (!c) return fail(SGZ_EINVAL, "null context");
+		const bool sameView = c->xTable && c->xCount && c->xKey[0] == cfg->left && c->xKey[1] == cfg->right && c->xKey[2] == cfg->inc;
+		const uint64_t count = sameView ? c->xCount : sgz_scope_resample_count(cfg);
 		if (count == 0) return fail(SGZ_EINVAL, "empty output range");
 		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
 		SGZS_GUARD(c);
@@ -703,8 +838,39 @@ extern "C"
 		if (out_mem == SGZ_MEM_HOST) { void* p = nullptr; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
 		ResampleArgs a{};
 		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = cfg->channel;
-		a.samplePos = static_cast<const double*>(dPos); a.spp = cfg->samples_per_pixel; a.left = cfg->left; a.inc = cfg->inc; a.count = count; a.out = dOut;
-		k_scope_resample<<<dim3(unsigned((count + 127) / 128), n_streams), 128, 0, c->stream>>>(a);
+		if (!(c->xTable && c->xCount == count && c->xKey[0] == cfg->left && c->xKey[1] == cfg->right && c->xKey[2] == cfg->inc))
+		{
+			std::vector<float> xs(count);
+			double unitSpacePos = cfg->left;
+			for (uint64_t m = 0; m < count; ++m) { xs[m] = static_cast<float>(unitSpacePos); unitSpacePos += cfg->inc; }
+			if (c->xCapacity < count)
+			{
+				if (c->xTable) { cudaFree(c->xTable); c->xTable = nullptr; c->xCapacity = 0; }
+				SGZS_CUDA(cudaMalloc(&c->xTable, size_t(count) * sizeof(float)));
+				c->xCapacity = count;
+			}
+			c->xCount = 0;
+			SGZS_CUDA(cudaMemcpyAsync(c->xTable, xs.data(), size_t(count) * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+			SGZS_CUDA(cudaStreamSynchronize(c->stream)); // xs is a local
+			c->xCount = count; c->xKey[0] = cfg->left; c->xKey[1] = cfg->right; c->xKey[2] = cfg->inc;
+		}
+		a.samplePos = static_cast<const double*>(dPos); a.spp = cfg->samples_per_pixel; a.count = count; a.xs = c->xTable; a.out = dOut;
+		// integer oversampling ratio (a power of two keeps m * spp exact) -> polyphase weights
+		const double ratio = 1.0 / cfg->samples_per_pixel;
+		const int R = int(ratio);
+		if (double(R) == ratio && R >= 1 && R <= kMaxPhases && (R & (R - 1)) == 0)
+		{
+			const dim3 grid(unsigned((count + 256 * kPolyVerticesPerThread - 1) / (256 * kPolyVerticesPerThread)), n_streams);
+#define SGZ_POLY(L, C) k_scope_resample_poly<L, C><<<grid, 256, 0, c->stream>>>(a, R)
+#define SGZ_POLY_CH(L) \
+			switch (cfg->channel) { case SGZ_OSC_LEFT: SGZ_POLY(L, SGZ_OSC_LEFT); break; case SGZ_OSC_RIGHT: SGZ_POLY(L, SGZ_OSC_RIGHT); break; \
+				case SGZ_OSC_MID: SGZ_POLY(L, SGZ_OSC_MID); break; default: SGZ_POLY(L, SGZ_OSC_SIDE); break; }
+			if (layout == SGZ_LAYOUT_INTERLEAVED) { SGZ_POLY_CH(SGZ_LAYOUT_INTERLEAVED) } else { SGZ_POLY_CH(SGZ_LAYOUT_PLANAR) }
+#undef SGZ_POLY_CH
+#undef SGZ_POLY
+		}
+		else
+			k_scope_resample<<<dim3(unsigned((count + 127) / 128), n_streams), 128, 0, c->stream>>>(a);
 		SGZS_CUDA(cudaGetLastError());
 		if (out_mem == SGZ_MEM_HOST)
 		{

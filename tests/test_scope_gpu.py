@@ -87,6 +87,22 @@ def test_scope_lanczos_resampler(channel, spp, inc):
     assert np.max(np.abs(got[..., 1] - want[..., 1])) < 2e-6           # values: double sums rounded to float
 
 
+@pytest.mark.parametrize("layout", [_abi.LAYOUT_INTERLEAVED, _abi.LAYOUT_PLANAR])
+@pytest.mark.parametrize("ratio", [1, 2, 4, 64, 128, 3])
+def test_scope_resampler_polyphase_path_edges(layout, ratio):
+    # power-of-two oversampling ratios <= 64 take the polyphase kernel, the rest the direct one; a short
+    # buffer makes most vertices touch the buffer edges, and the positions include exact sample alignment
+    S, n = 5, 48
+    a = signals.batch(S, n)
+    buf = a if layout == _abi.LAYOUT_INTERLEAVED else np.ascontiguousarray(a.transpose(0, 2, 1))
+    cfg = _abi.resample_config(channel=_abi.OSC_MID, samples_per_pixel=1.0 / ratio, left=-0.5, right=1.5, inc=1.0 / (ratio * 40))
+    pos = np.array([30.0, 12.5, 47.0625, 0.0, 5.333])
+    o, g = OracleScope(), Context()
+    want, got = o.scope_resample(cfg, pos, buf, layout=layout), g.scope_resample(cfg, pos, buf, layout=layout)
+    np.testing.assert_array_equal(got[..., 0], want[..., 0])
+    assert np.max(np.abs(got[..., 1] - want[..., 1])) < 2e-6
+
+
 def test_scope_c4_16x_resample_full_size():
     # BASELINE config 4: 256 streams, 16x windowed-sinc resampling; a band-limited sine is reproduced
     S, n = 256, 4096
