@@ -234,6 +234,44 @@ int  sgz_spectrum_audio_entry_point(sgz_spectrum* h, const float* history, uint6
                                     uint64_t block_stride, int mem, int layout, float* frames,
                                     uint32_t max_frames, uint32_t* n_emitted);
 
+/* ---- device-resident audio history --------------------
+ * Replaces the audio-history side of the path: the reference reads the last
+ * `windowSize` samples of a `cpl::AudioStream` history through its two-segment
+ * views (`audio[c].getItIndex(k)` over two ranges, TransformDSP.inl:49,65-88;
+ * the ring wraps, hence two segments) and is called back per block
+ * (audioEntryPoint, :1165-1211).  Here the history is a per-stream ring in
+ * HBM: only new samples are uploaded, windows are never re-sent, and the
+ * fused frame kernel reads the ring in place.
+ *   reserve : allocate `capacity` (>= window_size) samples per stream,
+ *             cleared to silence; resets the counters.  Calling it again
+ *             clears the history.
+ *   append  : add one callback block ([stream][n_block] stereo, HOST or
+ *             DEVICE, either layout) at the write head, wrapping as needed.
+ *   view    : device pointer to the last n_last (<= capacity) samples of
+ *             stream 0 as ONE contiguous interleaved run (the two segments
+ *             linearised), `*stream_stride` floats between streams; valid
+ *             until the next append; usable with every entry point that
+ *             takes SGZ_MEM_DEVICE audio (prepare, audio_entry_point ...).
+ *   read    : copy of that run, [stream][n_last][2] floats.
+ *   process : every frame that fell due since the last call — one per `hop`
+ *             appended samples, the frame at boundary b transforming samples
+ *             [b - window_size, b) (silence before time zero), exactly the
+ *             frames audioEntryPoint emits when sample_buffer_size == hop —
+ *             runs through the fused path of sgz_spectrum_process_frames;
+ *             at most max_frames per call (the rest stay pending);
+ *             results as there, [stream][*n_frames][graph][P][2].  SGZ_ESTATE
+ *             if a pending frame's window has already been overwritten. */
+int  sgz_spectrum_history_reserve(sgz_spectrum* h, uint64_t capacity);
+int  sgz_spectrum_history_append(sgz_spectrum* h, const float* block, int mem, int layout,
+                                 uint64_t n_block, uint64_t stream_stride);
+int  sgz_spectrum_history_info(sgz_spectrum* h, uint64_t* capacity, uint64_t* total_appended,
+                               uint64_t* last_frame_position);
+int  sgz_spectrum_history_view(sgz_spectrum* h, uint64_t n_last, const float** device_audio,
+                               uint64_t* stream_stride);
+int  sgz_spectrum_history_read(sgz_spectrum* h, uint64_t n_last, float* out, int mem);
+int  sgz_spectrum_history_process(sgz_spectrum* h, uint32_t hop, uint32_t max_frames,
+                                  float* results, int results_mem, uint32_t* n_frames);
+
 /* ---- spectrogram colour columns -----------------------------------------
  * Replaces `AudioDispatcher::blendAndDispatchSpectrums`
  * (Source/Spectrum/SpectrumDSP.cpp:110-206): every frame of `results`

@@ -153,6 +153,21 @@ namespace sgz
 				static_cast<uint32_t>(numFrames), reinterpret_cast<float*>(results), resultsMem));
 		}
 
+		/// Device-resident audio history (the cpl::AudioStream side of TransformDSP.inl:49,65-88): reserve once,
+		/// append each callback block, then run the frames that fell due (audioEntryPoint's scheduling, :1165-1211).
+		void historyReserve(std::size_t capacity) { check(sgz_spectrum_history_reserve(handle, capacity)); }
+		void historyAppend(const float* block, std::size_t numSamples, std::size_t pairStride, int layout = SGZ_LAYOUT_PLANAR, int mem = SGZ_MEM_HOST)
+		{
+			check(sgz_spectrum_history_append(handle, block, mem, layout, numSamples, pairStride));
+		}
+		/// returns the number of frames written to `results` ([pair][frames][graph][axisPoints])
+		std::size_t historyProcess(std::size_t hop, std::size_t maxFrames, UComplex* results, int resultsMem = SGZ_MEM_HOST)
+		{
+			uint32_t n = 0;
+			check(sgz_spectrum_history_process(handle, static_cast<uint32_t>(hop), static_cast<uint32_t>(maxFrames), reinterpret_cast<float*>(results), resultsMem, &n));
+			return n;
+		}
+
 		sgz_spectrum* handle{ nullptr };
 		sgz_spectrum_info info{};
 	};

@@ -147,6 +147,22 @@ namespace sgz
 		csf[uint64_t(s) * (t.N + 1) + i] = out; // zero-pad, including the extra element N
 	}
 
+	// audio history ring: sample `skip + j` of the block goes to ring position (head + skip + j) mod C and to
+	// its mirror at + C
+	__global__ void k_history_append(float2* __restrict__ ring, uint64_t C, uint64_t head, const float* __restrict__ block, int layout, uint64_t nBlock,
+		uint64_t stride, uint64_t skip)
+	{
+		const uint64_t j = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+		if (skip + j >= nBlock) return;
+		const uint32_t s = blockIdx.y;
+		float l, r;
+		fetchLR(block + s * stride, layout, nBlock, skip + j, l, r);
+		const uint64_t pos = (head + skip + j) % C;
+		float2* dst = ring + uint64_t(s) * 2 * C;
+		dst[pos] = make_float2(l, r);
+		dst[pos + C] = make_float2(l, r);
+	}
+
 	// ------------------------------------------------------------------------------------------
 	// staged kernel 2: doTransform — generic power-of-two forward FFT, natural order, in place
 	// ------------------------------------------------------------------------------------------
@@ -570,6 +586,13 @@ struct sgz_spectrum
 	std::vector<cudaEvent_t> events;
 	bool fusedAttrSet{ false };
 	size_t fusedSmem{ 0 };
+	// device-resident audio history (sgz_spectrum_history_*): per stream a ring of `ringCapacity` stereo
+	// samples stored twice back to back ([S][2 C] float2), so that any run of <= C samples ending at the
+	// write head is one contiguous span whatever the wrap position
+	float2* dRing{ nullptr };
+	uint64_t ringCapacity{ 0 };
+	uint64_t ringTotal{ 0 };      // samples appended since reserve (absolute time of the write head)
+	uint64_t ringLastFrame{ 0 };  // absolute time of the last frame boundary consumed by history_process
 };
 
 namespace
@@ -770,6 +793,7 @@ extern "C"
 			DeviceGuard g(h->device);
 			if (h->stream) cudaStreamSynchronize(h->stream);
 			for (void* p : h->allocations) cudaFree(p);
+			if (h->dRing) cudaFree(h->dRing);
 			if (h->dAudioStage) cudaFree(h->dAudioStage);
 			if (h->dResultStage) cudaFree(h->dResultStage);
 			if (h->dResPartial) cudaFree(h->dResPartial);
@@ -1451,6 +1475,119 @@ extern "C"
 			SGZ_CUDA(cudaMemcpyAsync(results, dRes, resFloats * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
 			SGZ_CUDA(cudaStreamSynchronize(h->stream));
 		}
+		return SGZ_OK;
+	}
+
+	// ---- device-resident audio history ---------------------------------------------------------
+	int sgz_spectrum_history_reserve(sgz_spectrum* h, uint64_t capacity)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (capacity < h->tab.W) return fail(SGZ_EINVAL, "history capacity %llu is smaller than the window (%u)", (unsigned long long)capacity, h->tab.W);
+		if (capacity > (1ull << 28)) return fail(SGZ_EINVAL, "history capacity %llu exceeds 2^28 samples", (unsigned long long)capacity);
+		SGZ_GUARD(h);
+		const size_t bytes = size_t(h->nStreams) * 2 * capacity * sizeof(float2);
+		if (h->ringCapacity != capacity)
+		{
+			if (h->dRing) { SGZ_CUDA(cudaStreamSynchronize(h->stream)); cudaFree(h->dRing); h->dRing = nullptr; h->ringCapacity = 0; }
+			SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dRing), bytes));
+			h->ringCapacity = capacity;
+		}
+		SGZ_CUDA(cudaMemsetAsync(h->dRing, 0, bytes, h->stream)); // a fresh history is silence
+		h->ringTotal = 0;
+		h->ringLastFrame = 0;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_history_append(sgz_spectrum* h, const float* block, int mem, int layout, uint64_t n_block, uint64_t stream_stride)
+	{
+		if (!h || !block) return fail(SGZ_EINVAL, "null argument");
+		if (!h->dRing) return fail(SGZ_ESTATE, "history_append before history_reserve");
+		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
+		if (n_block == 0) return SGZ_OK;
+		if (h->nStreams > 1 && stream_stride < 2 * n_block) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stream_stride & 1) || (reinterpret_cast<uintptr_t>(block) & 7)))
+			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
+		SGZ_GUARD(h);
+		const float* dBlock = nullptr;
+		int rc = stageAudio(h, block, mem, n_block, stream_stride, &dBlock, &h->dAudioStage, &h->audioStageBytes);
+		if (rc != SGZ_OK) return rc;
+		const uint64_t C = h->ringCapacity;
+		const uint64_t skip = n_block > C ? n_block - C : 0; // only the last C samples of an oversized block survive
+		const uint64_t n = n_block - skip;
+		const dim3 grid(unsigned((n + 255) / 256), h->nStreams);
+		k_history_append<<<grid, 256, 0, h->stream>>>(h->dRing, C, h->ringTotal % C, dBlock, layout, n_block, stream_stride, skip);
+		SGZ_CUDA(cudaGetLastError());
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream)); // the caller may reuse its buffer on return
+		h->ringTotal += n_block;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_history_info(sgz_spectrum* h, uint64_t* capacity, uint64_t* total_appended, uint64_t* last_frame_position)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (capacity) *capacity = h->ringCapacity;
+		if (total_appended) *total_appended = h->ringTotal;
+		if (last_frame_position) *last_frame_position = h->ringLastFrame;
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_history_view(sgz_spectrum* h, uint64_t n_last, const float** device_audio, uint64_t* stream_stride)
+	{
+		if (!h || !device_audio || !stream_stride) return fail(SGZ_EINVAL, "null argument");
+		if (!h->dRing) return fail(SGZ_ESTATE, "history_view before history_reserve");
+		const uint64_t C = h->ringCapacity;
+		if (n_last > C) return fail(SGZ_EINVAL, "history holds %llu samples, %llu requested", (unsigned long long)C, (unsigned long long)n_last);
+		// the run ends at the write head; before the first wrap the samples ahead of time zero are the silence
+		// the ring was cleared to
+		const uint64_t head = h->ringTotal % C;
+		const uint64_t start = (head + C - n_last) % C;
+		*device_audio = reinterpret_cast<const float*>(h->dRing + start);
+		*stream_stride = 4 * C; // floats between streams: 2 C stereo samples
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_history_read(sgz_spectrum* h, uint64_t n_last, float* out, int mem)
+	{
+		if (!out) return fail(SGZ_EINVAL, "null argument");
+		const float* view = nullptr; uint64_t stride = 0;
+		int rc = sgz_spectrum_history_view(h, n_last, &view, &stride);
+		if (rc != SGZ_OK) return rc;
+		if (n_last == 0) return SGZ_OK;
+		SGZ_GUARD(h);
+		SGZ_CUDA(cudaMemcpy2DAsync(out, size_t(n_last) * sizeof(float2), view, size_t(stride) * sizeof(float), size_t(n_last) * sizeof(float2), h->nStreams,
+			mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_history_process(sgz_spectrum* h, uint32_t hop, uint32_t max_frames, float* results, int results_mem, uint32_t* n_frames)
+	{
+		if (!h || !n_frames || (max_frames && !results)) return fail(SGZ_EINVAL, "null argument");
+		*n_frames = 0;
+		if (!h->dRing) return fail(SGZ_ESTATE, "history_process before history_reserve");
+		if (hop == 0) return fail(SGZ_EINVAL, "hop must be positive");
+		if (h->cfg.algo != SGZ_ALGO_FFT) return fail(SGZ_EUNSUPPORTED, "history_process is the FFT path; the resonator consumes blocks directly (sgz_spectrum_audio_entry_point)");
+		const uint64_t C = h->ringCapacity, W = h->tab.W, T = h->ringTotal;
+		// frames fall due every `hop` samples after the last one (the processedSamplesSinceLastFrame counter of
+		// audioEntryPoint, TransformDSP.inl:1172-1204); the frame at boundary b transforms samples [b - W, b)
+		const uint64_t pending = (T - h->ringLastFrame) / hop;
+		const uint64_t n = std::min<uint64_t>(pending, max_frames);
+		if (n == 0) return SGZ_OK;
+		const uint64_t firstBoundary = h->ringLastFrame + hop;
+		const uint64_t span = (n - 1) * hop + W;
+		// every sample of [firstBoundary - W, T) must still be in the ring (times before zero are the silence
+		// the ring was cleared to, and need their slots unwritten just the same)
+		if (T + W - firstBoundary > C)
+			return fail(SGZ_ESTATE, "history overrun: the window of the oldest pending frame was overwritten (capacity %llu, %llu samples behind); "
+				"process more often or reserve a longer history", (unsigned long long)C, (unsigned long long)(T + W - firstBoundary));
+		// ring position of absolute time firstBoundary - W (may be negative in absolute terms: add multiples of C)
+		const uint64_t start = (firstBoundary % C + C - W % C) % C;
+		const float* audio = reinterpret_cast<const float*>(h->dRing + start);
+		// start + span <= 2 C: span <= C by the overrun check
+		int rc = sgz_spectrum_process_frames(h, audio, SGZ_MEM_DEVICE, SGZ_LAYOUT_INTERLEAVED, span, 4 * C, hop, uint32_t(n), results, results_mem);
+		if (rc != SGZ_OK) return rc;
+		h->ringLastFrame += n * hop;
+		*n_frames = uint32_t(n);
 		return SGZ_OK;
 	}
 }

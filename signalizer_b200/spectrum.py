@@ -225,6 +225,62 @@ class TransformPairBatch:
         check(self.lib.sgz_spectrum_process_frames(self._h, ptr, mem, layout, n, stride, hop, n_frames, optr, omem))
         return out
 
+    # -- device-resident audio history -------------------------------------
+    def history_reserve(self, capacity: int) -> None:
+        """Allocate (or clear) the per-stream history ring: the device-side stand-in for the
+        cpl::AudioStream history the reference reads at TransformDSP.inl:49,65-88."""
+        check(self.lib.sgz_spectrum_history_reserve(self._h, capacity))
+
+    def history_append(self, block, layout=_abi.LAYOUT_INTERLEAVED) -> None:
+        """Append one callback block ([streams, n, 2] or planar [streams, 2, n])."""
+        keep, ptr, mem = _buf(block)
+        s, n, stride = self._geometry(keep, layout)
+        assert s == self.n_streams
+        check(self.lib.sgz_spectrum_history_append(self._h, ptr, mem, layout, n, stride))
+
+    def history_info(self):
+        """(capacity, total samples appended, position of the last processed frame boundary)"""
+        c, t, f = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(self.lib.sgz_spectrum_history_info(self._h, C.byref(c), C.byref(t), C.byref(f)))
+        return c.value, t.value, f.value
+
+    def history_read(self, n_last: int) -> np.ndarray:
+        """The last `n_last` samples of every stream, oldest first, [streams, n_last, 2]."""
+        out = np.empty((self.n_streams, n_last, 2), dtype=np.float32)
+        check(self.lib.sgz_spectrum_history_read(self._h, n_last, out.ctypes.data, _abi.MEM_HOST))
+        return out
+
+    def history_view(self, n_last: int):
+        """(device address, stream stride in floats) of the last `n_last` samples as one contiguous
+        interleaved run per stream; valid until the next append."""
+        p, stride = C.c_void_p(), C.c_uint64()
+        check(self.lib.sgz_spectrum_history_view(self._h, n_last, C.byref(p), C.byref(stride)))
+        return p.value, stride.value
+
+    def prepare_transform_device_view(self, ptr: int, n: int, stride: int) -> bool:
+        """prepareTransform on a raw device view (as returned by history_view)."""
+        rc = self.lib.sgz_spectrum_prepare(self._h, ptr, _abi.MEM_DEVICE, _abi.LAYOUT_INTERLEAVED, n, stride)
+        check(rc, allow=(_abi.OK, _abi.SKIPPED))
+        return rc == _abi.OK
+
+    def history_process(self, hop: int, max_frames: int, out=None, device=False):
+        """Run every frame that fell due since the last call (at most `max_frames`); returns
+        (results[:, :n], n) with results laid out like process_frames."""
+        shape = (self.n_streams, max_frames, 2, self.P, 2)
+        if out is None:
+            if device:
+                import torch
+                out = torch.empty(shape, dtype=torch.float32, device=f"cuda:{self.device}")
+            else:
+                out = np.empty(shape, dtype=np.float32)
+        okeep, optr, omem = _buf(out, writable=True)
+        n = C.c_uint32(0)
+        check(self.lib.sgz_spectrum_history_process(self._h, hop, max_frames, optr, omem, C.byref(n)))
+        # the library packs [stream][n][graph][P][2] with n, not max_frames, as the frame stride
+        flat = out.reshape(-1)
+        got = flat[: self.n_streams * n.value * 2 * self.P * 2].reshape(self.n_streams, n.value, 2, self.P, 2)
+        return got, n.value
+
 
 def fft_forward_noalloc(d_in, d_out, n: int, batch: int, cuda_stream: int = 0) -> None:
     """Forward FFT of `batch` complex sequences of `n` points on DEVICE tensors, for callers that may
