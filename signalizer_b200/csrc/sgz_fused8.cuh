@@ -16,6 +16,11 @@
 	// exchange element (k1, d2, d3, d4) lives at k1 512 + d2 64 + d3 8 + (d4 ^ k1): every pass reads and
 	// writes 128-bit words without bank conflicts and passes 2-3 run in place.
 	// ------------------------------------------------------------------------------------------
+// SGZ8_TW_POWERS: 0 = every twiddle from the shared-memory tables, 1 = passes 1-2 derive w^2..w^7 from w^1 in
+// registers (measured +2.0 % on BASELINE config 3), 2 = pass 3 as well (no further gain; tools/ab_bench.sh)
+#ifndef SGZ8_TW_POWERS
+#define SGZ8_TW_POWERS 1
+#endif
 	struct Fused8Geom
 	{
 		static constexpr int T = 512, M = 4096, N = 8192;
@@ -51,6 +56,27 @@
 	}
 
 	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4) { return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ k1); }
+
+	// Multiplies output k of a radix-8 butterfly (held in slot perm8(k)) by w1^k, k = 1..7.  The powers are
+	// derived in registers (depth <= 3 complex products: w2 = w1^2, w3 = w2 w1, w4 = w2^2, w5 = w4 w1,
+	// w6 = w3^2, w7 = w4 w3) instead of being read from a [8][64] table: the kernel is bound by the
+	// shared-memory pipe, not by FP issue, and this trades 7 LDS.64 for 6 complex products.
+	__device__ __forceinline__ void applyTwiddlePowers(float2 w1, float2 (&re)[8], float2 (&im)[8])
+	{
+		const float2 w2 = cmul(w1, w1);
+		mulTwiddleP(re[perm8(1)], im[perm8(1)], make_float4(w1.x, w1.x, w1.y, w1.y));
+		mulTwiddleP(re[perm8(2)], im[perm8(2)], make_float4(w2.x, w2.x, w2.y, w2.y));
+		const float2 w3 = cmul(w2, w1);
+		mulTwiddleP(re[perm8(3)], im[perm8(3)], make_float4(w3.x, w3.x, w3.y, w3.y));
+		const float2 w4 = cmul(w2, w2);
+		mulTwiddleP(re[perm8(4)], im[perm8(4)], make_float4(w4.x, w4.x, w4.y, w4.y));
+		const float2 w5 = cmul(w4, w1);
+		mulTwiddleP(re[perm8(5)], im[perm8(5)], make_float4(w5.x, w5.x, w5.y, w5.y));
+		const float2 w6 = cmul(w3, w3);
+		mulTwiddleP(re[perm8(6)], im[perm8(6)], make_float4(w6.x, w6.x, w6.y, w6.y));
+		const float2 w7 = cmul(w4, w3);
+		mulTwiddleP(re[perm8(7)], im[perm8(7)], make_float4(w7.x, w7.x, w7.y, w7.y));
+	}
 
 	template<bool STEREO, int BINPOL, int MATRIX>
 	__global__ void __launch_bounds__(512, 2)
@@ -152,6 +178,9 @@
 				}
 			}
 			dft8q(re, im);
+#if SGZ8_TW_POWERS
+			applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
+#else
 			{
 				const int n2 = u >> 6, v = u & 63;
 #pragma unroll
@@ -161,6 +190,7 @@
 					mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
 				}
 			}
+#endif
 			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
 			{
 				const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
@@ -183,6 +213,15 @@
 					re[n2] = make_float2(x.x, x.y); im[n2] = make_float2(x.z, x.w);
 				}
 				dft8q(re, im);
+#if SGZ8_TW_POWERS
+				applyTwiddlePowers(twC[64 + v], re, im); // W_512^(v k2) = (W_512^v)^k2
+#pragma unroll
+				for (int k2 = 0; k2 < 8; ++k2)
+				{
+					const float2 r = re[perm8(k2)], i = im[perm8(k2)];
+					xbuf[phys8(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+#else
 #pragma unroll
 				for (int k2 = 0; k2 < 8; ++k2)
 				{
@@ -194,6 +233,7 @@
 					}
 					xbuf[phys8(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
+#endif
 			}
 			__syncthreads();
 
@@ -207,6 +247,15 @@
 					re[n3] = make_float2(x.x, x.y); im[n3] = make_float2(x.z, x.w);
 				}
 				dft8q(re, im);
+#if SGZ8_TW_POWERS >= 2
+				applyTwiddlePowers(twA[8 + n4], re, im); // W_64^(n4 k3) = (W_64^n4)^k3
+#pragma unroll
+				for (int k3 = 0; k3 < 8; ++k3)
+				{
+					const float2 r = re[perm8(k3)], i = im[perm8(k3)];
+					xbuf[phys8(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+#else
 #pragma unroll
 				for (int k3 = 0; k3 < 8; ++k3)
 				{
@@ -218,6 +267,7 @@
 					}
 					xbuf[phys8(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
+#endif
 			}
 			__syncthreads();
 
