@@ -272,6 +272,39 @@ int  sgz_spectrum_history_read(sgz_spectrum* h, uint64_t n_last, float* out, int
 int  sgz_spectrum_history_process(sgz_spectrum* h, uint32_t hop, uint32_t max_frames,
                                   float* results, int results_mem, uint32_t* n_frames);
 
+/* ---- frequency tracker --------------------------------
+ * Replaces the peak search of `Spectrum::drawFrequencyTracking`
+ * (Source/Spectrum/SpectrumRendering.cpp:301-469, 494-519) and
+ * `SmoothedPeakState` (Source/Spectrum/Spectrum.h:405-459) for every stream at
+ * once; the mouse read-out, the scalloping-loss estimate and the text box
+ * around it are GUI and stay with the caller.
+ * `graph` = state.frequencyTrackingGraph.  SGZ_TRACK_TRANSFORM with the FFT
+ * algorithm and a non-Complex configuration searches the raw FFT
+ * (`transform.getRawFFT`, :376-469: |z|^2 argmax in the bins around the
+ * mouse, rising-edge scan at the window borders, log-domain parabolic fit);
+ * that needs the handle's audioMemory as the staged calls leave it, i.e.
+ * after sgz_spectrum_transform / _map.  Every other case searches
+ * lineGraphs[graph].getResults() (:306-374; TRANSFORM falls back to
+ * LINE_MAIN).  mouse_fraction: HOST [stream] = mouseX / (width - 1).
+ * states: HOST [stream], in/out, NULL = no smoothing (the smoothed_* fields
+ * then repeat the raw values); smoothing_ms = trackerSmoothing * 1000, fps as
+ * passed to drawFrequencyTracking.  results: HOST [stream]. */
+enum { SGZ_TRACK_LINE_MAIN = 0, SGZ_TRACK_LINE_SECOND = 1, SGZ_TRACK_TRANSFORM = 2 };
+typedef struct sgz_tracker_result {
+    int64_t peak_offset;        /* index into the searched array */
+    int32_t searched_raw_fft;   /* 1 = the raw-FFT branch ran */
+    int32_t peak_is_complex;    /* peakFrequency was above Nyquist and got folded (:494-496) */
+    double  peak_frequency, peak_dbs, peak_deviance, peak_slope, peak_x, peak_fraction;
+    double  smoothed_frequency, smoothed_dbs; /* peakState.getFrequency() / getPeakDBs() */
+} sgz_tracker_result;
+typedef struct sgz_tracker_state {  /* SmoothedPeakState's members (Spectrum.h:452-455) */
+    double frequency_state[8], peak_dbs_state[8];
+    double current_frequency, current_peak_dbs, current_peak;
+} sgz_tracker_state;
+int  sgz_spectrum_track_peaks(sgz_spectrum* h, int graph, const double* mouse_fraction,
+                              double smoothing_ms, double fps, sgz_tracker_state* states,
+                              sgz_tracker_result* results);
+
 /* ---- spectrogram colour columns -----------------------------------------
  * Replaces `AudioDispatcher::blendAndDispatchSpectrums`
  * (Source/Spectrum/SpectrumDSP.cpp:110-206): every frame of `results`

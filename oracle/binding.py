@@ -312,3 +312,25 @@ def colour_columns(results, pairs, ratios, colours):
     out = np.empty((S // pairs, F, P, 4), dtype=np.uint8)
     lib.sgzo_colour_columns(rp, S, F, P, pairs, rap, cop, out.ctypes.data_as(C.POINTER(C.c_uint8)))
     return out
+
+
+def track_peaks(cfg, graph, transform_size, window_scale, mapped_freq, slope_map, mouse_fraction, results=None, raw_fft=None,
+                smoothing_ms=0.0, fps=60.0, states=None):
+    """oracle/sgz_oracle_tracker.hpp on caller-supplied arrays: results [S, P, 2] float32 or raw_fft
+    [S, N + 1, 2] float32 (the searched array is handed in so that both sides search the same data)."""
+    lib = load()
+    src = results if results is not None else raw_fft
+    S = src.shape[0]
+    mf = np.ascontiguousarray(np.broadcast_to(np.asarray(mouse_fraction, dtype=np.float64), (S,)))
+    f = np.ascontiguousarray(mapped_freq, dtype=np.float32); sl = np.ascontiguousarray(slope_map, dtype=np.float32)
+    out = (_abi.TrackerResult * S)()
+    fp = C.POINTER(C.c_float)
+    lib.sgzo_track_peaks.restype = None
+    lib.sgzo_track_peaks.argtypes = [C.POINTER(_abi.SpectrumConfig), C.c_int, C.c_uint32, C.c_uint32, C.c_double, fp, fp, fp, fp, C.POINTER(C.c_double),
+                                     C.c_double, C.c_double, C.POINTER(_abi.TrackerState), C.POINTER(_abi.TrackerResult)]
+    r = np.ascontiguousarray(results, dtype=np.float32) if results is not None else None
+    w = np.ascontiguousarray(raw_fft, dtype=np.float32) if raw_fft is not None else None
+    lib.sgzo_track_peaks(C.byref(cfg), graph, S, transform_size, window_scale, f.ctypes.data_as(fp), sl.ctypes.data_as(fp),
+                         r.ctypes.data_as(fp) if r is not None else None, w.ctypes.data_as(fp) if w is not None else None,
+                         mf.ctypes.data_as(C.POINTER(C.c_double)), smoothing_ms, fps, states, out)
+    return out

@@ -632,3 +632,19 @@ extern "C" void sgzo_colour_ratios(const double* specRatios, float* out)
 	out[0] = 0;
 	for (int i = 0; i < 5; ++i) out[i + 1] = static_cast<float>(vals[i] / acc);
 }
+
+// ---- frequency tracker (oracle/sgz_oracle_tracker.hpp) --------------------------------------------
+#include "sgz_oracle_tracker.hpp"
+extern "C" void sgzo_track_peaks(const sgz_spectrum_config* cfg, int graph, uint32_t S, uint32_t transformSize, double windowScale, const float* mappedFreq,
+	const float* slopeMap, const float* results /*[S][P][2] or NULL*/, const float* rawFFT /*[S][N+1][2] or NULL*/, const double* mouseFraction,
+	double smoothingMs, double fps, sgz_tracker_state* states, sgz_tracker_result* out)
+{
+	sgz_oracle::TrackerView v{};
+	v.graph = graph; v.fft = cfg->algo == SGZ_ALGO_FFT; v.configuration = cfg->configuration; v.binPolation = cfg->bin_polation;
+	v.viewScale = cfg->view_scaling; v.viewLeft = cfg->view_left; v.viewRight = cfg->view_right; v.minLogFreq = cfg->min_freq;
+	v.sampleRate = cfg->sample_rate; v.transformSize = transformSize; v.windowSize = cfg->window_size; v.axisPoints = cfg->axis_points;
+	v.windowScale = windowScale; v.lowDbs = cfg->low_dbs; v.highDbs = cfg->high_dbs; v.mappedFrequencies = mappedFreq; v.slopeMap = slopeMap;
+	for (uint32_t s = 0; s < S; ++s)
+		sgz_oracle::trackPeak(v, results ? results + size_t(s) * cfg->axis_points * 2 : nullptr, rawFFT ? rawFFT + size_t(s) * (size_t(transformSize) + 1) * 2 : nullptr,
+			mouseFraction[s], smoothingMs, fps, states ? states + s : nullptr, out + s);
+}

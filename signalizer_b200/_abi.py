@@ -157,3 +157,18 @@ def vscope_config(polar=True, scale_polar=False, gain=1.0, width=512, height=512
 
 def resample_config(channel=OSC_LEFT, samples_per_pixel=1.0 / 16, left=0.0, right=1.0, inc=1.0 / 1024) -> ScopeResampleConfig:
     return ScopeResampleConfig(ABI_VERSION, channel, samples_per_pixel, left, right, inc)
+
+
+# frequency tracker (include/sgz.h: sgz_tracker_result / sgz_tracker_state)
+TRACK_LINE_MAIN, TRACK_LINE_SECOND, TRACK_TRANSFORM = range(3)
+
+
+class TrackerResult(C.Structure):
+    _fields_ = [("peak_offset", C.c_int64), ("searched_raw_fft", C.c_int32), ("peak_is_complex", C.c_int32),
+                ("peak_frequency", C.c_double), ("peak_dbs", C.c_double), ("peak_deviance", C.c_double), ("peak_slope", C.c_double),
+                ("peak_x", C.c_double), ("peak_fraction", C.c_double), ("smoothed_frequency", C.c_double), ("smoothed_dbs", C.c_double)]
+
+
+class TrackerState(C.Structure):
+    _fields_ = [("frequency_state", C.c_double * 8), ("peak_dbs_state", C.c_double * 8),
+                ("current_frequency", C.c_double), ("current_peak_dbs", C.c_double), ("current_peak", C.c_double)]

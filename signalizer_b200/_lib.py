@@ -23,7 +23,7 @@ EXPORTS = [
     "sgz_spectrum_set_states", "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state",
     "sgz_spectrum_process_frames", "sgz_fft_forward_noalloc",
     "sgz_spectrum_history_reserve", "sgz_spectrum_history_append", "sgz_spectrum_history_info", "sgz_spectrum_history_view",
-    "sgz_spectrum_history_read", "sgz_spectrum_history_process",
+    "sgz_spectrum_history_read", "sgz_spectrum_history_process", "sgz_spectrum_track_peaks",
     "sgz_resonator_process", "sgz_resonator_get_state", "sgz_spectrum_colour_columns", "sgz_spectrum_audio_entry_point",
     "sgz_context_create", "sgz_context_destroy", "sgz_context_set_cuda_stream", "sgz_context_synchronize",
     "sgz_vscope_vertices", "sgz_vscope_histogram", "sgz_vscope_meters",
@@ -100,6 +100,7 @@ def load():
     lib.sgz_resonator_process.argtypes = [vp, fp, i32, i32, u64, u64]
     lib.sgz_resonator_get_state.argtypes = [vp, fp, i32]
     lib.sgz_fft_forward_noalloc.argtypes = [fp, fp, u32, u32, vp]
+    lib.sgz_spectrum_track_peaks.argtypes = [vp, i32, C.POINTER(C.c_double), C.c_double, C.c_double, C.POINTER(_abi.TrackerState), C.POINTER(_abi.TrackerResult)]
     lib.sgz_spectrum_history_reserve.argtypes = [vp, u64]
     lib.sgz_spectrum_history_append.argtypes = [vp, fp, i32, i32, u64, u64]
     lib.sgz_spectrum_history_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]

@@ -22,6 +22,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <complex>
 #include <vector>
 
 #include "../../include/sgz.h"
@@ -161,6 +162,78 @@ namespace sgz
 		float2* dst = ring + uint64_t(s) * 2 * C;
 		dst[pos] = make_float2(l, r);
 		dst[pos + C] = make_float2(l, r);
+	}
+
+	// ------------------------------------------------------------------------------------------
+	// frequency tracker: per stream, first maximum of key(i) over [lo, hiEx), then the reference's
+	// "continuously rising" walk when the maximum sits on a border of the window
+	// (SpectrumRendering.cpp:320-350, 391-421).  key = .leftMagnitude of a results graph, or |z|^2 of
+	// the raw FFT.  One warp per stream; the handful of scalars the caller derives from the peak
+	// (parabolic fit, dB conversion, smoothing) are finished on the host from the record written here.
+	// ------------------------------------------------------------------------------------------
+	struct TrackBounds { long long lo, hiEx, rightBorder, end; };
+	struct TrackRecord { long long peak; float2 prev, at, next; };
+
+	template<bool RAW>
+	__device__ __forceinline__ float trackKey(const float2* d, long long i)
+	{
+		const float2 v = d[i];
+		if (RAW) return __fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y));
+		return v.x;
+	}
+
+	template<bool RAW>
+	__global__ void k_track_peaks(const float2* __restrict__ data, uint64_t stride, const TrackBounds* __restrict__ bounds, TrackRecord* __restrict__ out, uint32_t nStreams)
+	{
+		const uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+		const int lane = threadIdx.x & 31;
+		if (s >= nStreams) return;
+		const float2* d = data + uint64_t(s) * stride;
+		const TrackBounds b = bounds[s];
+		float best = -INFINITY;
+		long long at = 0x7fffffffffffffffll;
+		for (long long i = b.lo + lane; i < b.hiEx; i += 32)
+		{
+			const float v = trackKey<RAW>(d, i);
+			if (at == 0x7fffffffffffffffll || best < v) { best = v; at = i; } // strict: the earliest of equal maxima stays
+		}
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1)
+		{
+			const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+			const long long oa = __shfl_xor_sync(0xffffffffu, at, o);
+			const bool mine = at != 0x7fffffffffffffffll, theirs = oa != 0x7fffffffffffffffll;
+			if (theirs && (!mine || best < ov || (best == ov && oa < at))) { best = ov; at = oa; }
+		}
+		if (lane != 0) return;
+		long long peak = at;
+		if (peak == b.lo && b.lo != 0)
+		{
+			while (true)
+			{
+				const long long next = peak - 1;
+				if (next == 0) break;
+				if (trackKey<RAW>(d, next) < trackKey<RAW>(d, peak)) break;
+				peak = next;
+			}
+		}
+		else if (peak == b.rightBorder)
+		{
+			while (true)
+			{
+				const long long next = peak + 1;
+				if (next == b.end) break;
+				if (trackKey<RAW>(d, next) < trackKey<RAW>(d, peak)) break;
+				peak = next;
+			}
+		}
+		TrackRecord r;
+		r.peak = peak;
+		r.at = d[peak];
+		r.prev = d[peak == 0 ? 0 : peak - 1];
+		// RAW: the reference reads source[peak + 1] up to index N, which audioMemory carries; results graphs end at P - 1
+		r.next = d[RAW ? (peak == b.end ? peak : peak + 1) : (peak + 1 < b.end ? peak + 1 : peak)];
+		out[s] = r;
 	}
 
 	// ------------------------------------------------------------------------------------------
@@ -586,6 +659,7 @@ struct sgz_spectrum
 	std::vector<cudaEvent_t> events;
 	bool fusedAttrSet{ false };
 	size_t fusedSmem{ 0 };
+	void* dTrack{ nullptr }; // frequency tracker: [S] bounds in, [S] records out
 	// device-resident audio history (sgz_spectrum_history_*): per stream a ring of `ringCapacity` stereo
 	// samples stored twice back to back ([S][2 C] float2), so that any run of <= C samples ending at the
 	// write head is one contiguous span whatever the wrap position
@@ -794,6 +868,7 @@ extern "C"
 			if (h->stream) cudaStreamSynchronize(h->stream);
 			for (void* p : h->allocations) cudaFree(p);
 			if (h->dRing) cudaFree(h->dRing);
+			if (h->dTrack) cudaFree(h->dTrack);
 			if (h->dAudioStage) cudaFree(h->dAudioStage);
 			if (h->dResultStage) cudaFree(h->dResultStage);
 			if (h->dResPartial) cudaFree(h->dResPartial);
@@ -1588,6 +1663,132 @@ extern "C"
 		if (rc != SGZ_OK) return rc;
 		h->ringLastFrame += n * hop;
 		*n_frames = uint32_t(n);
+		return SGZ_OK;
+	}
+
+	// ---- frequency tracker ---------------------------------------------------------------------
+	int sgz_spectrum_track_peaks(sgz_spectrum* h, int graph, const double* mouse_fraction, double smoothing_ms, double fps, sgz_tracker_state* states,
+		sgz_tracker_result* results)
+	{
+		if (!h || !mouse_fraction || !results) return fail(SGZ_EINVAL, "null argument");
+		if (graph < SGZ_TRACK_LINE_MAIN || graph > SGZ_TRACK_TRANSFORM) return fail(SGZ_EINVAL, "bad graph");
+		const Tables& t = h->tab;
+		const bool fft = h->cfg.algo == SGZ_ALGO_FFT;
+		const bool raw = h->cfg.configuration != SGZ_CH_COMPLEX && fft && graph == SGZ_TRACK_TRANSFORM;
+		if (raw && h->stage < 2) return fail(SGZ_ESTATE, "the raw-FFT tracker reads audioMemory: call sgz_spectrum_transform first");
+		if (states && !(fps > 0)) return fail(SGZ_EINVAL, "fps must be positive");
+		const long long P = t.P, N = t.N;
+		if (P < 2) return fail(SGZ_EINVAL, "the tracker needs at least two display points");
+		SGZ_GUARD(h);
+		const uint32_t S = h->nStreams;
+		const size_t boundsBytes = size_t(S) * sizeof(TrackBounds), recBytes = size_t(S) * sizeof(TrackRecord);
+		if (!h->dTrack) SGZ_CUDA(cudaMalloc(&h->dTrack, boundsBytes + recBytes));
+		TrackBounds* dBounds = static_cast<TrackBounds*>(h->dTrack);
+		TrackRecord* dRec = reinterpret_cast<TrackRecord*>(static_cast<char*>(h->dTrack) + boundsBytes);
+		const double sampleRate = double(h->cfg.sample_rate);
+		auto roundHalfUp = [](double x) { return (long long)std::floor(x + 0.5); };
+		auto clampTo = [](long long x, long long lo, long long hi) { return x < lo ? lo : (x > hi ? hi : x); };
+		std::vector<TrackBounds> bounds(S);
+		std::vector<double> mouse(S);
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			const double mf = std::min(1.0, std::max(0.0, mouse_fraction[s]));
+			mouse[s] = mf;
+			TrackBounds b{};
+			if (!raw)
+			{
+				// window of +-3 % of the axis around the mouse, in display points
+				const unsigned long long pivot = (unsigned long long)roundHalfUp(double(P) * mf), range = (unsigned long long)roundHalfUp(double(P) * 0.03);
+				b.lo = range > pivot ? 0 : (long long)(pivot - range);
+				b.hiEx = range + pivot > (unsigned long long)P ? P : (long long)(range + pivot);
+				b.rightBorder = b.hiEx - 1;
+				b.end = P;
+				if (b.lo >= b.hiEx) return fail(SGZ_EINVAL, "empty tracker window (axis_points too small)");
+			}
+			else
+			{
+				// the same window expressed in FFT bins through the display-point frequencies
+				long long lo = roundHalfUp(double(P) * (mf - 0.03)), hi = roundHalfUp(double(P) * (mf + 0.03));
+				lo = roundHalfUp(double(N) * t.mappedFreq[size_t(clampTo(lo, 0, P - 1))] / sampleRate);
+				hi = roundHalfUp(double(N) * t.mappedFreq[size_t(clampTo(hi, 0, P - 1))] / sampleRate);
+				lo = clampTo(lo, 0, N); hi = clampTo(hi, 0, N);
+				b.lo = lo; b.hiEx = hi + 1; b.rightBorder = hi - 1; b.end = N;
+				if (b.lo >= b.hiEx) return fail(SGZ_EINVAL, "empty tracker window");
+			}
+			bounds[s] = b;
+		}
+		SGZ_CUDA(cudaMemcpyAsync(dBounds, bounds.data(), boundsBytes, cudaMemcpyHostToDevice, h->stream));
+		const int shownGraph = graph == SGZ_TRACK_TRANSFORM ? SGZ_TRACK_LINE_MAIN : graph;
+		const dim3 block(128), grid((S * 32 + 127) / 128);
+		if (raw) k_track_peaks<true><<<grid, block, 0, h->stream>>>(h->dCsf, uint64_t(N) + 1, dBounds, dRec, S);
+		else k_track_peaks<false><<<grid, block, 0, h->stream>>>(h->dResults + size_t(shownGraph) * P, uint64_t(2) * P, dBounds, dRec, S);
+		SGZ_CUDA(cudaGetLastError());
+		std::vector<TrackRecord> rec(S);
+		SGZ_CUDA(cudaMemcpyAsync(rec.data(), dRec, recBytes, cudaMemcpyDeviceToHost, h->stream));
+		SGZ_CUDA(cudaStreamSynchronize(h->stream));
+
+		const double nyquist = sampleRate * 0.5;
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			const TrackRecord& r = rec[s];
+			sgz_tracker_result o{};
+			o.peak_offset = r.peak;
+			o.searched_raw_fft = raw ? 1 : 0;
+			double freq, dbs;
+			if (!raw)
+			{
+				const size_t k = size_t(r.peak);
+				freq = t.mappedFreq[k];
+				const bool last = r.peak == P - 1;
+				const float width = t.mappedFreq[last ? k : k + 1] - t.mappedFreq[last ? k - 1 : k]; // float difference, as the reference
+				o.peak_deviance = width;
+				if (fft && h->cfg.bin_polation != SGZ_BIN_LANCZOS) o.peak_deviance = std::max(o.peak_deviance, 0.5 * double(t.N) / double(P));
+				o.peak_x = double(r.peak);
+				o.peak_slope = t.slope[k];
+				dbs = double(r.at.x) * (h->cfg.high_dbs - h->cfg.low_dbs) + h->cfg.low_dbs; // results are fractions of the dB range
+			}
+			else
+			{
+				const float invSize = static_cast<float>(double(t.windowKernelScale) / (double(t.W) * 0.5));
+				auto levelDb = [invSize](float2 z) -> float { return 20 * std::log10(std::abs(std::complex<float>(z.x, z.y) * invSize)); };
+				const float a = levelDb(r.prev), bb = levelDb(r.at), c = levelDb(r.next);
+				const double phi = 0.5 * (a - c) / (a - 2 * bb + c); // vertex of the parabola through the three log magnitudes
+				o.peak_fraction = 2 * (double(r.peak) + (std::isnormal(phi) ? phi : 0)) / double(N);
+				freq = 0.5 * o.peak_fraction * sampleRate;
+				dbs = bb - 0.25 * (a - c) * phi;
+				if (!std::isnormal(dbs)) dbs = 20 * std::log10(std::abs(std::complex<float>(r.at.x, r.at.y)) / (double(N) * 0.5));
+				// display coordinate of that frequency: inverse of the axis mapping (TransformConstant.h:125-182)
+				double arg = o.peak_fraction;
+				if (h->cfg.view_scaling == SGZ_VIEW_LOGARITHMIC) arg = std::log(o.peak_fraction * nyquist / h->cfg.min_freq) / std::log(nyquist / h->cfg.min_freq);
+				o.peak_x = (arg - h->cfg.view_left) / (h->cfg.view_right - h->cfg.view_left) * double(P - 1);
+				o.peak_slope = t.slope[size_t(clampTo(roundHalfUp(o.peak_x), 0, P - 1))];
+				dbs += 20 * std::log10(o.peak_slope);
+				o.peak_deviance = 2 * 0.01 * ((1.0 - o.peak_fraction) / double(N)) * sampleRate + 0.001;
+			}
+			o.peak_is_complex = freq > nyquist ? 1 : 0;
+			if (o.peak_is_complex) freq = sampleRate - freq;
+			if (dbs > 1000) dbs = INFINITY; else if (dbs < -1000) dbs = -INFINITY;
+			o.peak_frequency = freq; o.peak_dbs = dbs;
+			o.smoothed_frequency = freq; o.smoothed_dbs = dbs;
+			if (states)
+			{
+				sgz_tracker_state& st = states[s];
+				if (!std::isnormal(st.current_peak)) st.current_peak = 0;
+				if (!std::isnormal(st.frequency_state[7])) std::fill(st.frequency_state, st.frequency_state + 8, 0.0);
+				if (!std::isnormal(st.peak_dbs_state[7])) std::fill(st.peak_dbs_state, st.peak_dbs_state + 8, 0.0);
+				const double holdPole = std::exp(-1.0 / (smoothing_ms * 10 * 0.001 * fps)), smoothPole = std::exp(-1.0 / (smoothing_ms / 5 * 0.001 * fps));
+				const double linear = std::pow(10, dbs / 20);
+				st.current_peak *= holdPole;
+				if (linear > st.current_peak) { st.current_peak = 1.2 * (linear / holdPole); st.current_frequency = freq; st.current_peak_dbs = dbs; }
+				double in = st.current_frequency;
+				for (double& x : st.frequency_state) { x = in + smoothPole * (x - in); in = x; }
+				in = st.current_peak_dbs;
+				for (double& x : st.peak_dbs_state) { x = in + smoothPole * (x - in); in = x; }
+				o.smoothed_frequency = st.frequency_state[7];
+				o.smoothed_dbs = st.peak_dbs_state[7];
+			}
+			results[s] = o;
+		}
 		return SGZ_OK;
 	}
 }

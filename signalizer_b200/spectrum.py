@@ -281,6 +281,16 @@ class TransformPairBatch:
         got = flat[: self.n_streams * n.value * 2 * self.P * 2].reshape(self.n_streams, n.value, 2, self.P, 2)
         return got, n.value
 
+    # -- frequency tracker --------------------------------------------------
+    def track_peaks(self, graph: int, mouse_fraction, smoothing_ms: float = 0.0, fps: float = 60.0, states=None):
+        """The peak search of Spectrum::drawFrequencyTracking (SpectrumRendering.cpp:301-469) for every
+        stream: returns a ctypes array of TrackerResult.  `states` = (TrackerState * streams)() to
+        run SmoothedPeakState (Spectrum.h:405-459) as well."""
+        mf = np.ascontiguousarray(np.broadcast_to(np.asarray(mouse_fraction, dtype=np.float64), (self.n_streams,)))
+        out = (_abi.TrackerResult * self.n_streams)()
+        check(self.lib.sgz_spectrum_track_peaks(self._h, graph, mf.ctypes.data_as(C.POINTER(C.c_double)), smoothing_ms, fps, states, out))
+        return out
+
 
 def fft_forward_noalloc(d_in, d_out, n: int, batch: int, cuda_stream: int = 0) -> None:
     """Forward FFT of `batch` complex sequences of `n` points on DEVICE tensors, for callers that may
