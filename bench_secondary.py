@@ -91,6 +91,22 @@ def c4():
             "trigger_ms_incl_host_copies": ms_t, "trigger_samples_per_s": S * n / ms_t * 1e3}
 
 
+def c4_colour():
+    out = []
+    for S, n in ((256, 65536), (4096, 8192)):
+        d = torch.from_numpy(tile(signals.batch(32, n), S)).cuda()
+        ctx = Context()
+        ctx.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+        cfg = _abi.colour_config(channel_mode=_abi.OSC_SEPARATE, envelope_mode=_abi.ENVELOPE_RMS)
+        st = (_abi.ScopeColourState * (2 * S))()
+        rgba = torch.empty((S, 4, n, 4), dtype=torch.uint8, device="cuda")
+        ms = timed(lambda: ctx.scope_colour(cfg, d, st, out=rgba), torch.cuda.synchronize, steps=3, warmup=1)
+        out.append({"config": f"C4 oscilloscope colouring: {S} stereo streams x {n} samples, 3-band Linkwitz-Riley + 4 colour planes + RMS envelope",
+                    "ms": ms, "samples_per_s": S * n / ms * 1e3, "algorithmic_GBps": S * n * 24 / ms / 1e6, "frac_hbm": S * n * 24 / ms / 1e6 / PEAK,
+                    "note": "recursive filters: one dependent chain per channel, parallel over streams only"})
+    return out
+
+
 def c5():
     S, n = 256, 65536
     d = torch.from_numpy(tile(signals.batch(32, n), S)).cuda()
@@ -105,7 +121,7 @@ def c5():
 
 
 if __name__ == "__main__":
-    for fn in (c1, c2, c4, c5):
+    for fn in (c1, c2, c4, c4_colour, c5):
         r = fn()
         for line in (r if isinstance(r, list) else [r]):
             print(json.dumps(line), flush=True)

@@ -344,7 +344,8 @@ int  sgz_context_set_cuda_stream(sgz_context* ctx, void* cuda_stream);
 int  sgz_context_synchronize(sgz_context* ctx);
 
 /* channel views of Source/Oscilloscope/SampleColourEvaluators.h:57-320 */
-enum { SGZ_OSC_LEFT = 0, SGZ_OSC_RIGHT = 1, SGZ_OSC_MID = 2, SGZ_OSC_SIDE = 3 };
+enum { SGZ_OSC_LEFT = 0, SGZ_OSC_RIGHT = 1, SGZ_OSC_MID = 2, SGZ_OSC_SIDE = 3,
+       SGZ_OSC_SEPARATE = 4, SGZ_OSC_MIDSIDE = 5 /* the two-trace modes: envelopes only (sgz_scope_colour, sgz_scope_peak_envelope) */ };
 
 /* ---- Vectorscope ----------------------------------------------------------
  * Replaces the per-sample vertex arithmetic of `VectorScope::drawPolarPlot`
@@ -420,6 +421,52 @@ typedef struct sgz_scope_period_result { sgz_scope_bin_record record; double fun
 int  sgz_scope_period(sgz_context* ctx, const sgz_scope_period_params* params, const float* audio, int mem,
                       int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
                       sgz_scope_period_state* states, sgz_scope_period_result* results);
+
+/* ---- oscilloscope colouring and envelopes -------------
+ * sgz_scope_colour replaces the per-sample work of
+ * `Oscilloscope::StreamState::audioProcessing`
+ * (Source/Oscilloscope/OscilloscopeDSP.inl:426-710) for every stereo pair:
+ * the RMS envelope of the selected channel mode (:505-586, stored only in
+ * SGZ_ENVELOPE_RMS mode, :682-699), the 3-band crossover at 300 / 3000 Hz
+ * (`channelData.tuneCrossOver`, ChannelData.h:163-166), the one-pole
+ * smoothing of the squared bands (`filterStates`, :462-470) for left, right,
+ * mid (= left + right bands) and side, and `accumulateColour` (:474-497)
+ * into four RGBA8 colour streams per pair (colourData of the two channels,
+ * auxColourData for mid / side, :606-651).
+ * states: HOST [stream][2] (index 0 = left / mid, 1 = right / side; the
+ * ChannelState of ChannelData.h:68-77), in/out.  rgba: [stream][4][n][4]
+ * bytes, planes in the order left, right, mid, side, r g b a per pixel.
+ * envelope_gain: HOST [stream] `envelopeGain` (0 unless RMS mode), may be
+ * NULL.
+ * sgz_scope_peak_envelope replaces `Oscilloscope::runPeakFilter` (:712-886):
+ * the largest |sample| of the window (whole groups of 8 samples, as the AVX
+ * loop) per channel mode folded into the two envelope states with
+ * `coeff` (:742-743, computed by the caller), and `state.autoGain`.
+ * envelopes: HOST [stream][2] floats in/out; auto_gain: HOST [stream]. */
+enum { SGZ_ENVELOPE_NONE = 0, SGZ_ENVELOPE_RMS = 1, SGZ_ENVELOPE_PEAK = 2 };
+typedef struct sgz_scope_colour_config {
+    uint32_t abi_version;
+    int32_t  channel_mode;        /* SGZ_OSC_* (all six) */
+    int32_t  envelope_mode;       /* SGZ_ENVELOPE_* */
+    double   sample_rate;
+    double   colour_smoothing_ms; /* content->colourSmoothing.getTransformedValue() */
+    double   envelope_window;     /* content->envelopeWindow.getNormalizedValue() */
+    double   colouring_blend;     /* content->frequencyColouringBlend */
+    float    colours[3][3];       /* low, mid, high colour as r g b in 0..1 */
+    uint8_t  key_left[4], key_right[4]; /* ChannelState::defaultKey of the two channels, r g b a */
+} sgz_scope_colour_config;
+typedef struct sgz_scope_colour_state {
+    float smooth_filters[3];      /* ChannelState::smoothFilters */
+    float aux_smooth_filter[3];   /* ChannelState::auxSmoothFilter */
+    float network[24];            /* ChannelState::network: 12 second-order sections x 2 */
+    float envelope;               /* ChannelState::envelope */
+} sgz_scope_colour_state;
+int  sgz_scope_colour(sgz_context* ctx, const sgz_scope_colour_config* cfg, const float* audio, int mem,
+                      int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+                      sgz_scope_colour_state* states, uint8_t* rgba, int rgba_mem, double* envelope_gain);
+int  sgz_scope_peak_envelope(sgz_context* ctx, int channel_mode, const float* audio, int mem, int layout,
+                             uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride, double coeff,
+                             float* envelopes, double* auto_gain);
 
 /* ---- allocation-free forward FFT ------------------------------------------
  * No counterpart in the reference.  For callers that cannot allocate device

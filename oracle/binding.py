@@ -275,6 +275,26 @@ class OracleScope:
         self.lib.sgzo_scope_resample(C.byref(cfg), pos.ctypes.data_as(C.POINTER(C.c_double)), p, layout, S, n, stride, out.ctypes.data_as(C.POINTER(C.c_float)))
         return out
 
+    def scope_colour(self, cfg, audio, states, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        rgba = np.empty((S, 4, n, 4), dtype=np.uint8)
+        gain = np.zeros(S, dtype=np.float64)
+        self.lib.sgzo_scope_colour.restype = None
+        self.lib.sgzo_scope_colour.argtypes = [C.POINTER(_abi.ScopeColourConfig), C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_uint64,
+                                               C.POINTER(_abi.ScopeColourState), C.c_void_p, C.POINTER(C.c_double)]
+        self.lib.sgzo_scope_colour(C.byref(cfg), p, layout, S, n, stride, states, rgba.ctypes.data, gain.ctypes.data_as(C.POINTER(C.c_double)))
+        return rgba, gain
+
+    def scope_peak_envelope(self, channel_mode, audio, envelopes, coeff, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        gain = np.zeros(S, dtype=np.float64)
+        self.lib.sgzo_scope_peak_envelope.restype = None
+        self.lib.sgzo_scope_peak_envelope.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_uint64, C.c_double, C.c_void_p, C.POINTER(C.c_double)]
+        self.lib.sgzo_scope_peak_envelope(channel_mode, p, layout, S, n, stride, coeff, envelopes.ctypes.data, gain.ctypes.data_as(C.POINTER(C.c_double)))
+        return gain
+
     def scope_trigger(self, mode, channel, audio, states, threshold, hysteresis=0.0, steady_clock=0, max_peaks=4096, layout=_abi.LAYOUT_INTERLEAVED):
         a, p = _f32(audio)
         S, n, stride = _geom(a, layout)

@@ -648,3 +648,48 @@ extern "C" void sgzo_track_peaks(const sgz_spectrum_config* cfg, int graph, uint
 		sgz_oracle::trackPeak(v, results ? results + size_t(s) * cfg->axis_points * 2 : nullptr, rawFFT ? rawFFT + size_t(s) * (size_t(transformSize) + 1) * 2 : nullptr,
 			mouseFraction[s], smoothingMs, fps, states ? states + s : nullptr, out + s);
 }
+
+// ---- oscilloscope colouring and envelopes (oracle/sgz_oracle_colour.hpp) ----------------------------
+#include "sgz_oracle_colour.hpp"
+extern "C" void sgzo_scope_colour(const sgz_scope_colour_config* cfg, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride,
+	sgz_scope_colour_state* states, uint8_t* rgba, double* gain)
+{
+	std::vector<float> l(n), r(n);
+	for (uint32_t s = 0; s < S; ++s)
+	{
+		const float* base = audio + size_t(s) * stride;
+		for (uint64_t i = 0; i < n; ++i)
+		{
+			if (layout == SGZ_LAYOUT_INTERLEAVED) { l[i] = base[2 * i]; r[i] = base[2 * i + 1]; }
+			else { l[i] = base[i]; r[i] = base[n + i]; }
+		}
+		const double g = sgz_oracle::audioProcessing(*cfg, l.data(), r.data(), n, states + 2 * size_t(s), rgba + size_t(s) * 16 * n);
+		if (gain) gain[s] = g;
+	}
+}
+extern "C" void sgzo_scope_peak_envelope(int channelMode, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, double coeff, float* env, double* gain)
+{
+	std::vector<float> l(n), r(n);
+	for (uint32_t s = 0; s < S; ++s)
+	{
+		const float* base = audio + size_t(s) * stride;
+		for (uint64_t i = 0; i < n; ++i)
+		{
+			if (layout == SGZ_LAYOUT_INTERLEAVED) { l[i] = base[2 * i]; r[i] = base[2 * i + 1]; }
+			else { l[i] = base[i]; r[i] = base[n + i]; }
+		}
+		gain[s] = sgz_oracle::runPeakFilter(channelMode, l.data(), r.data(), n, coeff, env + 2 * size_t(s));
+	}
+}
+// the crossover alone, for the tests that pin it against scipy: bands [n][3]
+extern "C" void sgzo_scope_crossover(double sampleRate, const float* x, uint64_t n, float* bands)
+{
+	const sgz_oracle::CrossoverCoeffs c = sgz_oracle::designCrossover(sampleRate);
+	float z[24] = {};
+	for (uint64_t i = 0; i < n; ++i)
+	{
+		float b[3];
+		sgz_oracle::runNetwork(c, z, x[i], b);
+		bands[3 * i] = b[0]; bands[3 * i + 1] = b[1]; bands[3 * i + 2] = b[2];
+	}
+}

@@ -172,3 +172,32 @@ class TrackerResult(C.Structure):
 class TrackerState(C.Structure):
     _fields_ = [("frequency_state", C.c_double * 8), ("peak_dbs_state", C.c_double * 8),
                 ("current_frequency", C.c_double), ("current_peak_dbs", C.c_double), ("current_peak", C.c_double)]
+
+
+# oscilloscope colouring / envelopes (include/sgz.h: sgz_scope_colour_config / _state)
+OSC_SEPARATE, OSC_MIDSIDE = 4, 5
+ENVELOPE_NONE, ENVELOPE_RMS, ENVELOPE_PEAK = range(3)
+
+
+class ScopeColourConfig(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("channel_mode", C.c_int32), ("envelope_mode", C.c_int32), ("sample_rate", C.c_double),
+                ("colour_smoothing_ms", C.c_double), ("envelope_window", C.c_double), ("colouring_blend", C.c_double),
+                ("colours", (C.c_float * 3) * 3), ("key_left", C.c_uint8 * 4), ("key_right", C.c_uint8 * 4)]
+
+
+class ScopeColourState(C.Structure):
+    _fields_ = [("smooth_filters", C.c_float * 3), ("aux_smooth_filter", C.c_float * 3), ("network", C.c_float * 24), ("envelope", C.c_float)]
+
+
+def colour_config(channel_mode=OSC_LEFT, envelope_mode=ENVELOPE_RMS, sample_rate=48000.0, colour_smoothing_ms=1.0, envelope_window=0.1,
+                  colouring_blend=1.0, colours=((1.0, 0.0, 0.0), (0.0, 1.0, 0.0), (0.0, 0.0, 1.0)), key_left=(0, 255, 0, 255), key_right=(255, 0, 0, 255)):
+    c = ScopeColourConfig()
+    c.abi_version = ABI_VERSION
+    c.channel_mode, c.envelope_mode, c.sample_rate = channel_mode, envelope_mode, sample_rate
+    c.colour_smoothing_ms, c.envelope_window, c.colouring_blend = colour_smoothing_ms, envelope_window, colouring_blend
+    for i in range(3):
+        for k in range(3):
+            c.colours[i][k] = colours[i][k]
+    for k in range(4):
+        c.key_left[k], c.key_right[k] = key_left[k], key_right[k]
+    return c

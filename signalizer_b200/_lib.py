@@ -27,7 +27,7 @@ EXPORTS = [
     "sgz_resonator_process", "sgz_resonator_get_state", "sgz_spectrum_colour_columns", "sgz_spectrum_audio_entry_point",
     "sgz_context_create", "sgz_context_destroy", "sgz_context_set_cuda_stream", "sgz_context_synchronize",
     "sgz_vscope_vertices", "sgz_vscope_histogram", "sgz_vscope_meters",
-    "sgz_scope_resample_count", "sgz_scope_resample", "sgz_scope_trigger", "sgz_scope_period",
+    "sgz_scope_resample_count", "sgz_scope_resample", "sgz_scope_trigger", "sgz_scope_period", "sgz_scope_colour", "sgz_scope_peak_envelope",
 ]
 
 
@@ -95,6 +95,8 @@ def load():
                                       C.POINTER(_abi.ScopeTriggerState), C.POINTER(C.c_uint64), C.POINTER(u32), u32]
     lib.sgz_scope_period.argtypes = [vp, C.POINTER(_abi.ScopePeriodParams), fp, i32, i32, u32, u64, u64,
                                      C.POINTER(_abi.ScopePeriodState), C.POINTER(_abi.ScopePeriodResult)]
+    lib.sgz_scope_colour.argtypes = [vp, C.POINTER(_abi.ScopeColourConfig), fp, i32, i32, u32, u64, u64, C.POINTER(_abi.ScopeColourState), fp, i32, C.POINTER(C.c_double)]
+    lib.sgz_scope_peak_envelope.argtypes = [vp, i32, fp, i32, i32, u32, u64, u64, C.c_double, C.POINTER(C.c_float), C.POINTER(C.c_double)]
     lib.sgz_spectrum_audio_entry_point.argtypes = [vp, fp, u64, u64, fp, u64, u64, i32, i32, fp, u32, C.POINTER(u32)]
     lib.sgz_spectrum_colour_columns.argtypes = [vp, fp, i32, u32, u32, fp, fp, fp, i32]
     lib.sgz_resonator_process.argtypes = [vp, fp, i32, i32, u64, u64]

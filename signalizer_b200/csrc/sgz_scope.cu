@@ -666,6 +666,7 @@ namespace sgz
 		}
 		if (threadIdx.x == 0) a.z[s] = red[0];
 	}
+#include "sgz_colour.cuh"
 }
 
 using namespace sgz;
@@ -998,6 +999,108 @@ extern "C"
 			while (phase < 0) phase += tau;
 			r.phase = phase;
 			r.sample_offset = (phase / tau) * prm->sample_rate / r.fundamental - 1;
+		}
+		return SGZ_OK;
+	}
+
+	// ---- oscilloscope colouring and envelopes --------------------------------------------------
+	static void designSections(double fNorm, ColourSection& lp, ColourSection& hp)
+	{
+		// 2nd-order Butterworth pair through the bilinear transform; two passes of each make the 4th-order
+		// Linkwitz-Riley crossover (cpl decisions)
+		const double w0 = 6.283185307179586476925286766559 * fNorm, c = std::cos(w0), alpha = std::sin(w0) / 1.4142135623730950488016887242097;
+		const double norm = 1.0 + alpha;
+		lp.b0 = float((1 - c) * 0.5 / norm); lp.b1 = float((1 - c) / norm); lp.b2 = lp.b0;
+		hp.b0 = float((1 + c) * 0.5 / norm); hp.b1 = float(-(1 + c) / norm); hp.b2 = hp.b0;
+		lp.a1 = hp.a1 = float(-2 * c / norm);
+		lp.a2 = hp.a2 = float((1 - alpha) / norm);
+	}
+
+	int sgz_scope_colour(sgz_context* c, const sgz_scope_colour_config* cfg, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, sgz_scope_colour_state* states, uint8_t* rgba, int rgba_mem, double* envelope_gain)
+	{
+		int rc;
+		if (!cfg || cfg->abi_version != SGZ_ABI_VERSION || !states || !rgba) return fail(SGZ_EINVAL, "bad colour arguments");
+		if (cfg->channel_mode < SGZ_OSC_LEFT || cfg->channel_mode > SGZ_OSC_MIDSIDE) return fail(SGZ_EINVAL, "bad channel mode");
+		if (cfg->envelope_mode < SGZ_ENVELOPE_NONE || cfg->envelope_mode > SGZ_ENVELOPE_PEAK) return fail(SGZ_EINVAL, "bad envelope mode");
+		if (!(cfg->sample_rate > 0)) return fail(SGZ_EINVAL, "sample_rate must be positive");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		if (n_samples == 0) return SGZ_OK;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		const size_t stateBytes = size_t(n_streams) * 2 * sizeof(sgz_scope_colour_state);
+		void* dStates = nullptr; if ((rc = ensure(c, 2, stateBytes, &dStates)) != SGZ_OK) return rc;
+		SGZS_CUDA(cudaMemcpyAsync(dStates, states, stateBytes, cudaMemcpyHostToDevice, c->stream));
+		const size_t bytes = size_t(n_streams) * 4 * n_samples * 4;
+		uint8_t* dOut = rgba;
+		if (rgba_mem == SGZ_MEM_HOST) { void* p = nullptr; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<uint8_t*>(p); }
+		if (reinterpret_cast<uintptr_t>(dOut) & 3) return fail(SGZ_EINVAL, "rgba must be 4-byte aligned");
+		ColourArgs a{};
+		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.nStreams = n_streams;
+		designSections(double(static_cast<float>(300.0 / cfg->sample_rate)), a.lp[0], a.hp[0]);   // tuneCrossOver(300, 3000, sampleRate), ChannelData.h:163-166
+		designSections(double(static_cast<float>(3000.0 / cfg->sample_rate)), a.lp[1], a.hp[1]);
+		a.pole = static_cast<float>(std::exp(-1.0 / (cfg->colour_smoothing_ms * 0.001 * cfg->sample_rate)));
+		a.envelopeCoeff = static_cast<float>(std::exp(-1.0 / (cfg->envelope_window * cfg->sample_rate))); // :448
+		a.blend = 1 - static_cast<float>(cfg->colouring_blend);                                            // :503
+		for (int i = 0; i < 3; ++i) for (int k = 0; k < 3; ++k) a.colours[i][k] = cfg->colours[i][k];
+		for (int k = 0; k < 4; ++k) { a.keyL[k] = float(cfg->key_left[k]); a.keyR[k] = float(cfg->key_right[k]); }
+		a.channelMode = cfg->channel_mode; a.envelopeMode = cfg->envelope_mode;
+		a.states = static_cast<sgz_scope_colour_state*>(dStates); a.rgba = dOut;
+		// few pairs: a warp per pair (recursions on two lanes, colouring by all 32); thousands of pairs: the recursions
+		// alone fill the GPU, so pack 16 pairs per warp (measured crossover between 256 and 4096 pairs)
+		if (n_streams >= kColourPackedFrom) k_scope_colour_packed<<<(2 * n_streams + 63) / 64, 64, 0, c->stream>>>(a);
+		else k_scope_colour<<<(n_streams + kColourWarps - 1) / kColourWarps, 32 * kColourWarps, 0, c->stream>>>(a);
+		SGZS_CUDA(cudaGetLastError());
+		SGZS_CUDA(cudaMemcpyAsync(states, dStates, stateBytes, cudaMemcpyDeviceToHost, c->stream));
+		if (rgba_mem == SGZ_MEM_HOST) SGZS_CUDA(cudaMemcpyAsync(rgba, dOut, bytes, cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		if (envelope_gain)
+			for (uint32_t s = 0; s < n_streams; ++s)
+			{
+				// :682-699: 1 / the larger of the two channels' RMS
+				double g = 0;
+				if (cfg->envelope_mode == SGZ_ENVELOPE_RMS)
+					g = 1.0 / std::max(std::sqrt(states[2 * s].envelope), std::sqrt(states[2 * s + 1].envelope));
+				envelope_gain[s] = g;
+			}
+		return SGZ_OK;
+	}
+
+	int sgz_scope_peak_envelope(sgz_context* c, int channel_mode, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, double coeff, float* envelopes, double* auto_gain)
+	{
+		int rc;
+		if (!envelopes || !auto_gain) return fail(SGZ_EINVAL, "null argument");
+		if (channel_mode < SGZ_OSC_LEFT || channel_mode > SGZ_OSC_MIDSIDE) return fail(SGZ_EINVAL, "bad channel mode");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		void* dMax = nullptr; if ((rc = ensure(c, 2, size_t(n_streams) * sizeof(float2), &dMax)) != SGZ_OK) return rc;
+		const uint64_t stop = n_samples - (n_samples & 7); // whole 8-float vectors only (:738-740)
+		k_scope_peak_max<<<n_streams, 256, 0, c->stream>>>(d, layout, n_samples, stream_stride, stop, channel_mode, static_cast<float2*>(dMax));
+		SGZS_CUDA(cudaGetLastError());
+		std::vector<float2> hi(n_streams);
+		SGZS_CUDA(cudaMemcpyAsync(hi.data(), dMax, size_t(n_streams) * sizeof(float2), cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		for (uint32_t s = 0; s < n_streams; ++s)
+		{
+			float* env = envelopes + 2 * size_t(s);
+			if (channel_mode == SGZ_OSC_SEPARATE)
+			{
+				// float arithmetic here (std::max<float>), and the second channel inherits the first one's running maximum
+				const float first = hi[s].x, second = std::max(hi[s].x, hi[s].y);
+				env[0] = std::max<float>(float(env[0] * coeff), first * first);
+				env[1] = std::max<float>(float(env[1] * coeff), second * second);
+			}
+			else
+			{
+				const double a = hi[s].x, b = hi[s].y;
+				env[0] = static_cast<float>(std::max(env[0] * coeff, a * a));
+				env[1] = static_cast<float>(std::max(env[1] * coeff, b * b));
+			}
+			auto_gain[s] = 1.0 / std::max(std::sqrt(env[0]), std::sqrt(env[1])); // :877-885
 		}
 		return SGZ_OK;
 	}

@@ -105,3 +105,32 @@ class Context:
         results = (_abi.ScopePeriodResult * S)()
         check(self.lib.sgz_scope_period(self._h, C.byref(params), ptr, mem, layout, S, n, stride, states, results))
         return results
+
+    def scope_colour(self, cfg, audio, states, layout=_abi.LAYOUT_INTERLEAVED, out=None):
+        """Per-sample colouring + RMS envelope of StreamState::audioProcessing (OscilloscopeDSP.inl:426-710).
+        states: (ScopeColourState * (2 * streams))(), in/out.  Returns (rgba [streams, 4, n, 4] uint8 with planes
+        left, right, mid, side; envelope gains [streams])."""
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        assert len(states) == 2 * S
+        gain = np.zeros(S, dtype=np.float64)
+        if out is None:
+            rgba = np.empty((S, 4, n, 4), dtype=np.uint8)
+            optr, omem = rgba.ctypes.data, _abi.MEM_HOST
+        else:   # a CUDA uint8 tensor [S, 4, n, 4]: the colour planes stay on the device
+            rgba = out
+            assert tuple(out.shape) == (S, 4, n, 4) and out.is_contiguous()
+            optr, omem = out.data_ptr(), _abi.MEM_DEVICE
+        check(self.lib.sgz_scope_colour(self._h, C.byref(cfg), ptr, mem, layout, S, n, stride, states, optr, omem,
+                                        gain.ctypes.data_as(C.POINTER(C.c_double))))
+        return rgba, gain
+
+    def scope_peak_envelope(self, channel_mode, audio, envelopes, coeff, layout=_abi.LAYOUT_INTERLEAVED):
+        """Oscilloscope::runPeakFilter (OscilloscopeDSP.inl:712-886): envelopes [streams, 2] float32 in/out; returns autoGain [streams]."""
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        assert envelopes.dtype == np.float32 and envelopes.shape == (S, 2) and envelopes.flags.c_contiguous
+        gain = np.zeros(S, dtype=np.float64)
+        check(self.lib.sgz_scope_peak_envelope(self._h, channel_mode, ptr, mem, layout, S, n, stride, coeff,
+                                               envelopes.ctypes.data_as(C.POINTER(C.c_float)), gain.ctypes.data_as(C.POINTER(C.c_double))))
+        return gain
