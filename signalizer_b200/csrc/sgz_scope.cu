@@ -318,7 +318,18 @@ namespace sgz
 	// vertex is 20 double FMAs.  A vertex whose delta differs from its phase's (the first R outputs,
 	// before the window starts sliding) takes the direct evaluation.
 	constexpr int kMaxPhases = 64;
-	constexpr int kPolyVerticesPerThread = 8;
+#ifndef SGZ_POLY_VPT
+#define SGZ_POLY_VPT 8
+#endif
+#ifndef SGZ_POLY_MINB
+#define SGZ_POLY_MINB 2
+#endif
+#ifndef SGZ_POLY_GROUPS
+#define SGZ_POLY_GROUPS 8
+#endif
+	constexpr int kPolyVerticesPerThread = SGZ_POLY_VPT;       // vertices a thread keeps in flight at once
+	constexpr int kPolyGroups = SGZ_POLY_GROUPS;               // such sweeps per CTA: the block prologue is paid once for all of them
+	constexpr int kPolyBlockVertices = 256 * kPolyVerticesPerThread * kPolyGroups;
 	__device__ __forceinline__ double lanczosWeight10(double frac, int ib, int t)
 	{
 		// weight of tap i = ib - 9 + t at distance d = frac + (9 - t); same closed form as k_scope_resample's fast weights
@@ -356,83 +367,133 @@ namespace sgz
 		return acc;
 	}
 
-	template <int LAYOUT, int CHANNEL>
-	__global__ void __launch_bounds__(256) k_scope_resample_poly(ResampleArgs a, int R)
+	// per stream: the R x 20 steady-state weights (+ delta and kernel index of each phase), evaluated once per call
+	// instead of once per CTA - the sinpi / sincospi / divide chain is ~20x the cost of using the weights
+	struct PolyPhase { double w[20]; double delta; long long ib; }; // 176 bytes
+	__global__ void k_scope_poly_weights(ResampleArgs a, int R, PolyPhase* __restrict__ table)
 	{
-		__shared__ double wts[20][kMaxPhases]; // [tap][phase]: the lanes of a warp read consecutive phases
-		__shared__ double deltaOf[kMaxPhases];
-		__shared__ int ibOf[kMaxPhases];
-		const uint32_t s = blockIdx.y;
+		const uint32_t s = blockIdx.x;
 		const double samplePos0 = a.samplePos[s];
 		const double fl0 = floor(samplePos0);
-		// one (phase, tap) weight per thread; steady-state delta of phase r taken at an output far enough
-		// along that the window slides (q = 2)
 		for (int e = threadIdx.x; e < R * 20; e += blockDim.x)
 		{
 			const int r = e / 20, t = e - r * 20;
+			// steady-state delta of phase r: taken at an output far enough along that the window slides (q = 2)
 			const double currentSample = fl0 + double(2 * R + r) * a.spp;
 			const double d0 = currentSample - samplePos0;
 			const double k = d0 > 1.0 ? ceil(d0 - 1.0) : 0.0;
 			const double delta = currentSample - (samplePos0 + k);
 			const double x = 10.0 + delta;
 			const double fx = floor(x);
-			if (t == 0) { deltaOf[r] = delta; ibOf[r] = int(fx); }
-			wts[t][r] = lanczosWeight10(x - fx, int(fx), t);
+			PolyPhase& ph = table[uint64_t(s) * R + r];
+			if (t == 0) { ph.delta = delta; ph.ib = (long long)fx; }
+			ph.w[t] = lanczosWeight10(x - fx, int(fx), t);
 		}
-		__syncthreads();
+	}
+
+	template <int LAYOUT, int CHANNEL>
+	__global__ void __launch_bounds__(256, SGZ_POLY_MINB) k_scope_resample_poly(ResampleArgs a, int R, const PolyPhase* __restrict__ table)
+	{
+		extern __shared__ double xsamples[]; // kPolyBlockVertices / R + 32
+		const uint32_t s = blockIdx.y;
+		const double samplePos0 = a.samplePos[s];
+		const double fl0 = floor(samplePos0);
 		const float* src = a.audio + uint64_t(s) * a.stride;
-		const uint64_t m0 = uint64_t(blockIdx.x) * (256 * kPolyVerticesPerThread) + threadIdx.x;
-		for (int it = 0; it < kPolyVerticesPerThread; ++it)
+		const uint64_t mBlock = uint64_t(blockIdx.x) * kPolyBlockVertices;
+		const uint64_t mLast = min(mBlock + kPolyBlockVertices, a.count) - 1;
+		// window slide k of a vertex (closed form of the reference's while (delta > 1) loop), nondecreasing in m
+		auto slideOf = [&](uint64_t m, double& delta) -> long long
 		{
-			const uint64_t m = m0 + uint64_t(it) * 256;
-			if (m >= a.count) return;
 			const double currentSample = fl0 + double(m) * a.spp;
 			const double d0 = currentSample - samplePos0;
 			const double k = d0 > 1.0 ? ceil(d0 - 1.0) : 0.0;
-			const double delta = currentSample - (samplePos0 + k);
-			const long long base = (long long)a.n - (long long)fl0 - 10 + (long long)k; // index of kernel[0]
-			const int r = int(uint32_t(m) & uint32_t(R - 1)); // R is a power of two
-			// samplePos + k rounds differently as k grows, so the deltas of one phase agree to ~1e-12 rather
-			// than exactly; the weights are smooth in delta (|dw/d delta| < 4), far inside the float32 output ulp
-			const bool table = fabs(delta - deltaOf[r]) < 1e-9;
-			double acc = 0.0;
-			if (table)
-			{
-				const int ib = ibOf[r];
-				const long long first = base + ib - 9;
-				const double* wp = &wts[0][r];
-				if (first >= 0 && first + 19 < (long long)a.n)
-				{
-					// interior vertex: all 20 taps are inside the audio window; ib is 10, or 11 when the vertex
-					// sits exactly on a sample (delta == 1), where the last tap falls outside the kernel
+			delta = currentSample - (samplePos0 + k);
+			return (long long)k;
+		};
+		// every global read of the block is issued up front so that their latencies overlap: this thread's phase
+		// weights, the x coordinates of its vertices, then (below) the block's samples
+		const int r = int(uint32_t(mBlock + threadIdx.x) & uint32_t(R - 1));
+		const PolyPhase& ph = table[uint64_t(s) * R + r];
+		double w[20];
 #pragma unroll
-					for (int t = 0; t < 20; ++t)
-					{
-						float l, rr;
-						loadLR(src, LAYOUT, a.n, uint64_t(first + t), l, rr);
-						if (t < 19 || ib == 10) acc += double(oscChannel(CHANNEL, l, rr)) * wp[t * kMaxPhases];
-					}
-				}
-				else
-				{
-					for (int t = 0; t < 20; ++t)
-					{
-						const int i = ib - 9 + t;
-						const long long idx = first + t;
-						if (i >= 0 && i < 21 && idx >= 0 && idx < (long long)a.n)
-						{
-							float l, rr;
-							loadLR(src, LAYOUT, a.n, uint64_t(idx), l, rr);
-							acc += double(oscChannel(CHANNEL, l, rr)) * wp[t * kMaxPhases];
-						}
-					}
-				}
+		for (int t = 0; t < 20; ++t) w[t] = ph.w[t];
+		const int ib = int(ph.ib);
+		const double deltaR = ph.delta;
+		// the samples this block's vertices can touch, converted to double ONCE (the float -> double conversion
+		// unit is 8x narrower than the fp64 FMA pipe, and every sample feeds ~20 R taps); outside the buffer = 0
+		double unused;
+		const long long origin = (long long)a.n - (long long)fl0 - 10; // index of kernel[0] before any slide
+		const long long lo = origin + slideOf(mBlock, unused) + 1;     // table taps start at kernel index ib - 9 >= 1
+		const long long hi = origin + slideOf(mLast, unused) + 21;
+		const int span = int(hi - lo + 1);                             // <= kPolyBlockVertices / R + 23
+		for (int e = threadIdx.x; e < span; e += blockDim.x)
+		{
+			const long long idx = lo + e;
+			float v = 0.f;
+			if (idx >= 0 && idx < (long long)a.n)
+			{
+				float l, rr;
+				loadLR(src, LAYOUT, a.n, uint64_t(idx), l, rr);
+				v = oscChannel(CHANNEL, l, rr);
 			}
-			else
-				acc = resampleVertexDirect(a, src, base, delta);
-			float* o = a.out + (uint64_t(s) * a.count + m) * 2;
-			o[0] = a.xs[m];
-			o[1] = float(acc);
+			xsamples[e] = double(v);
+		}
+		__syncthreads();
+		// vertices m = mBlock + tid + 256 j: one phase per thread (256 is a multiple of R), so its 20 weights live in
+		// registers; neighbouring lanes read the same or neighbouring samples (broadcast / conflict-free)
+		// three sweeps over the thread's vertices so that independent work interleaves (the kernel is latency-bound,
+		// not throughput-bound): window slides, then the 20-tap sums with one accumulator chain per vertex, then stores
+		for (int g = 0; g < kPolyGroups; ++g)
+		{
+			const uint64_t mGroup = mBlock + uint64_t(g) * (256 * kPolyVerticesPerThread);
+			if (mGroup >= a.count) break;
+			float xv[kPolyVerticesPerThread];
+#pragma unroll
+			for (int it = 0; it < kPolyVerticesPerThread; ++it)
+			{
+				const uint64_t m = mGroup + threadIdx.x + uint64_t(it) * 256;
+				xv[it] = m < a.count ? a.xs[m] : 0.f;
+			}
+			int offs[kPolyVerticesPerThread];   // sample index of tap 0 relative to xsamples; < 0: not a table vertex
+			double accs[kPolyVerticesPerThread];
+#pragma unroll
+			for (int it = 0; it < kPolyVerticesPerThread; ++it)
+			{
+				const uint64_t m = mGroup + threadIdx.x + uint64_t(it) * 256;
+				double delta;
+				const long long base = origin + slideOf(m, delta);
+				// samplePos + k rounds differently as k grows, so the deltas of one phase agree to ~1e-12 rather
+				// than exactly; the weights are smooth in delta (|dw/d delta| < 4), far inside the float32 output ulp
+				const bool table = m < a.count && fabs(delta - deltaR) < 1e-9;
+				offs[it] = table ? int(base + ib - 9 - lo) : -1;
+				accs[it] = 0.0;
+			}
+			// ib is 10, or 11 when the vertex sits exactly on a sample (delta == 1): then the last tap falls outside the
+			// 21-sample kernel and is skipped, as the reference's bounds check does
+			const int taps = ib == 10 ? 20 : 19;
+#pragma unroll
+			for (int t = 0; t < 20; ++t)
+			{
+				const double wt = w[t];
+#pragma unroll
+				for (int it = 0; it < kPolyVerticesPerThread; ++it)
+					if (offs[it] >= 0 && t < taps) accs[it] += xsamples[offs[it] + t] * wt;
+			}
+#pragma unroll
+			for (int it = 0; it < kPolyVerticesPerThread; ++it)
+			{
+				const uint64_t m = mGroup + threadIdx.x + uint64_t(it) * 256;
+				if (m >= a.count) break;
+				double acc = accs[it];
+				if (offs[it] < 0)
+				{
+					double delta;
+					const long long base = origin + slideOf(m, delta);
+					acc = resampleVertexDirect(a, src, base, delta); // the first outputs, before the window starts sliding
+				}
+				reinterpret_cast<float2*>(a.out)[uint64_t(s) * a.count + m] = make_float2(xv[it], float(acc));
+			}
+	
 		}
 	}
 
@@ -837,6 +898,7 @@ extern "C"
 		const size_t bytes = size_t(n_streams) * count * 2 * sizeof(float);
 		float* dOut = out_xy;
 		if (out_mem == SGZ_MEM_HOST) { void* p = nullptr; if ((rc = ensure(c, 1, bytes, &p)) != SGZ_OK) return rc; dOut = static_cast<float*>(p); }
+		if (reinterpret_cast<uintptr_t>(dOut) & 7) return fail(SGZ_EINVAL, "out_xy must be 8-byte aligned");
 		ResampleArgs a{};
 		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = cfg->channel;
 		if (!(c->xTable && c->xCount == count && c->xKey[0] == cfg->left && c->xKey[1] == cfg->right && c->xKey[2] == cfg->inc))
@@ -861,8 +923,13 @@ extern "C"
 		const int R = int(ratio);
 		if (double(R) == ratio && R >= 1 && R <= kMaxPhases && (R & (R - 1)) == 0)
 		{
-			const dim3 grid(unsigned((count + 256 * kPolyVerticesPerThread - 1) / (256 * kPolyVerticesPerThread)), n_streams);
-#define SGZ_POLY(L, C) k_scope_resample_poly<L, C><<<grid, 256, 0, c->stream>>>(a, R)
+			const dim3 grid(unsigned((count + kPolyBlockVertices - 1) / kPolyBlockVertices), n_streams);
+			const size_t polySmem = (size_t(kPolyBlockVertices) / R + 32) * sizeof(double);
+			void* tp = nullptr; if ((rc = ensure(c, 3, size_t(n_streams) * R * sizeof(PolyPhase), &tp)) != SGZ_OK) return rc;
+			PolyPhase* table = static_cast<PolyPhase*>(tp);
+			k_scope_poly_weights<<<n_streams, 320, 0, c->stream>>>(a, R, table);
+#define SGZ_POLY(L, C) { if (polySmem > 48 * 1024) SGZS_CUDA(cudaFuncSetAttribute(k_scope_resample_poly<L, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(polySmem))); \
+			k_scope_resample_poly<L, C><<<grid, 256, polySmem, c->stream>>>(a, R, table); }
 #define SGZ_POLY_CH(L) \
 			switch (cfg->channel) { case SGZ_OSC_LEFT: SGZ_POLY(L, SGZ_OSC_LEFT); break; case SGZ_OSC_RIGHT: SGZ_POLY(L, SGZ_OSC_RIGHT); break; \
 				case SGZ_OSC_MID: SGZ_POLY(L, SGZ_OSC_MID); break; default: SGZ_POLY(L, SGZ_OSC_SIDE); break; }

@@ -12,5 +12,8 @@ for spp, inc in ((1/16, 1/(16*W)), (1/15, 1/(15*W)), (1/16, 1/(16*W))):
     for _ in range(3): ctx.scope_resample(cfg, pos, d, out=out)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    w0 = time.perf_counter(); e0.record(); ctx.scope_resample(cfg, pos, d, out=out); e1.record(); w1 = time.perf_counter(); torch.cuda.synchronize()
-    print(f"spp=1/{round(1/spp)} count={count} count_call={1e3*(t1-t0):.3f} ms  host_call={1e3*(w1-w0):.3f} ms  gpu={e0.elapsed_time(e1):.3f} ms")
+    K = 20
+    w0 = time.perf_counter(); e0.record()
+    for _ in range(K): ctx.scope_resample(cfg, pos, d, out=out)
+    e1.record(); w1 = time.perf_counter(); torch.cuda.synchronize()
+    print(f"spp=1/{round(1/spp)} count={count} count_call={1e3*(t1-t0):.3f} ms  host_call={1e3*(w1-w0)/K:.3f} ms  gpu={e0.elapsed_time(e1)/K:.4f} ms per call ({K} calls)")
