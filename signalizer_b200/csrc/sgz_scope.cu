@@ -507,50 +507,151 @@ namespace sgz
 		sgz_scope_trigger_state* states; uint64_t* peaks; uint32_t* counts; uint32_t maxPeaks;
 	};
 
-	// ZeroCrossingProcessor::process (StreamPreprocessing.h:331-347): the per-sample predicates are
-	// evaluated by the lanes, the tiny state machine then walks the two ballot masks
-	__global__ void k_scope_trigger_zero(TriggerArgs a)
+	// ZeroCrossingProcessor::process (StreamPreprocessing.h:331-347).  Per sample: a rising zero crossing arms the
+	// trigger and remembers where (holding = true, origin = position); a sample above the threshold while armed
+	// emits that origin and disarms.  The state entering a stretch of samples only matters up to the stretch's first
+	// event: a crossing overwrites it, and an above-threshold sample that comes before any crossing emits the
+	// INCOMING origin (if armed) and disarms.  So a stream is cut into kTrigWarps contiguous chunks, one warp each:
+	//   pass A  every warp runs the automaton over its chunk from the disarmed state (coalesced 32-sample steps,
+	//           predicates by ballot, all 32 positions resolved by one carry-chain addition) and records: emits inside the chunk, whether an
+	//           above-threshold sample precedes every crossing, whether there was any event, and its final state;
+	//   pass B  one lane chains the kTrigWarps summaries (16 steps) into each chunk's true incoming state and the
+	//           output offset of its first emit;
+	//   pass C  every warp replays its chunk (now from L2) from the true incoming state and writes its origins.
+	// Positions come out in ascending order and bit-identical to the sequential scan.
+	constexpr int kTrigWarps = 16;
+	constexpr int kTrigRows = 8; // 32-sample rows fetched per trip
+	struct TrigSummary { uint32_t emits; int aboveFirst, anyEvent, holdingOut; uint64_t originOut; };
+
+	template<bool WRITE>
+	__device__ __forceinline__ void trigZeroChunk(const TriggerArgs& a, const float* base, uint64_t begin, uint64_t end, float prev, float aboveFrom, bool holding,
+		uint64_t origin, uint64_t* out, uint32_t outPos, int lane, TrigSummary& sum, float& lastSample)
 	{
-		const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-		if (warp >= a.nStreams) return;
-		const float* base = a.audio + uint64_t(warp) * a.stride;
-		sgz_scope_trigger_state st = a.states[warp];
-		double prev = st.state;
-		bool holding = st.is_peak_holding != 0;
-		uint64_t origin = st.cross_origin;
-		uint32_t count = 0;
-		for (uint64_t n0 = 0; n0 < a.n; n0 += 32)
+		uint32_t emits = 0;
+		int aboveFirst = 0, anyEvent = 0;
+		// the rows of a trip are fetched together, one trip ahead of the scan, so that memory latency overlaps both
+		// itself and the scan (which is a handful of integer operations per row; what it waits for is memory)
+		auto fetch = [&](uint64_t n1, float (&dst)[kTrigRows])
 		{
-			float x = 0.f;
-			const bool valid = n0 + lane < a.n;
-			if (valid) { float l, r; loadLR(base, a.layout, a.n, n0 + lane, l, r); x = oscChannel(a.channel, l, r); }
-			const double sample = double(x);
-			double before = __shfl_up_sync(0xffffffffu, sample, 1);
-			if (lane == 0) before = prev;
-			const uint32_t cross = __ballot_sync(0xffffffffu, valid && sample > 0 && before < 0);
-			const uint32_t above = __ballot_sync(0xffffffffu, valid && sample > a.threshold);
-			uint32_t todo = cross | above;
-			while (todo)
+#pragma unroll
+			for (int k = 0; k < kTrigRows; ++k)
 			{
-				const int j = __ffs(todo) - 1;
-				todo &= todo - 1;
-				if (cross & (1u << j)) { holding = true; origin = a.steadyClock + n0 + j; }
-				if (holding && (above & (1u << j)))
-				{
-					holding = false;
-					if (lane == 0 && count < a.maxPeaks) a.peaks[uint64_t(warp) * a.maxPeaks + count] = origin;
-					++count;
-				}
+				const uint64_t i = n1 + 32 * k + lane;
+				dst[k] = 0.f;
+				if (i < end) { float l, r; loadLR(base, a.layout, a.n, i, l, r); dst[k] = oscChannel(a.channel, l, r); }
 			}
-			const int last = int(min(uint64_t(32), a.n - n0)) - 1;
+		};
+		float xs[kTrigRows], ahead[kTrigRows];
+		fetch(begin, ahead);
+		for (uint64_t n1 = begin; n1 < end; n1 += 32 * kTrigRows)
+		{
+#pragma unroll
+		for (int k = 0; k < kTrigRows; ++k) xs[k] = ahead[k];
+		if (n1 + 32 * kTrigRows < end) fetch(n1 + 32 * kTrigRows, ahead);
+#pragma unroll
+		for (int k = 0; k < kTrigRows; ++k)
+		{
+			const uint64_t n0 = n1 + 32 * k;
+			if (n0 >= end) break;
+			const bool valid = n0 + lane < end;
+			// float comparisons that decide exactly like the reference's double ones: the signs are the same, and
+			// sample > threshold <=> sample >= aboveFrom, the smallest float strictly greater than the threshold
+			const float sample = xs[k];
+			float before = __shfl_up_sync(0xffffffffu, sample, 1);
+			if (lane == 0) before = prev;
+			const uint32_t cross = __ballot_sync(0xffffffffu, valid && sample > 0.f && before < 0.f);
+			const uint32_t above = __ballot_sync(0xffffffffu, valid && sample >= aboveFrom);
+			uint32_t todo = cross | above;
+			if (todo && !anyEvent)
+			{
+				// first event of the chunk: is it an above-threshold sample with no crossing at or before it?
+				const int j = __ffs(todo) - 1;
+				aboveFirst = ((above >> j) & 1u) && !((cross >> j) & 1u);
+				anyEvent = 1;
+			}
+			if (todo)
+			{
+				// the armed flag through the 32 samples is a carry chain: a crossing that is not also above the threshold
+				// generates it, an above-threshold sample kills it, every other sample propagates it - so one 64-bit
+				// addition resolves all 32 positions at once (bit j of `carries` = armed after sample j - 1)
+				const uint32_t gen = cross & ~above, prop = ~(cross | above);
+				const uint64_t X = uint64_t(gen | prop), Y = uint64_t(gen);
+				const uint64_t carries = (X + Y + (holding ? 1u : 0u)) ^ X ^ Y;
+				const uint32_t fires = above & (cross | uint32_t(carries)); // armed (or arming right now) and above
+				const int nFires = __popc(fires);
+				if (WRITE && ((fires >> lane) & 1u))
+				{
+					// the lane of a firing sample reports it: its rank among the firing samples gives the slot, the
+					// latest crossing at or before it the origin
+					const uint32_t slot = outPos + emits + __popc(fires & ((1u << lane) - 1u));
+					const uint32_t earlier = cross & (0xffffffffu >> (31 - lane));
+					if (slot < a.maxPeaks) out[slot] = earlier ? a.steadyClock + n0 + (31 - __clz(earlier)) : origin;
+				}
+				emits += nFires;
+				if (cross) origin = a.steadyClock + n0 + (31 - __clz(cross));
+				holding = ((carries >> 32) & 1u) != 0;
+			}
+			const int last = int(min(uint64_t(32), end - n0)) - 1;
 			prev = __shfl_sync(0xffffffffu, sample, last);
 		}
-		if (lane == 0)
-		{
-			st.state = a.n ? prev : st.state; st.is_peak_holding = holding ? 1 : 0; st.cross_origin = origin;
-			a.states[warp] = st;
-			a.counts[warp] = count;
 		}
+		sum.emits = emits; sum.aboveFirst = aboveFirst; sum.anyEvent = anyEvent; sum.holdingOut = holding ? 1 : 0; sum.originOut = origin;
+		lastSample = prev;
+	}
+
+	__global__ void __launch_bounds__(32 * kTrigWarps) k_scope_trigger_zero(TriggerArgs a)
+	{
+		__shared__ TrigSummary sums[kTrigWarps];
+		__shared__ int holdIn[kTrigWarps];
+		__shared__ uint64_t originIn[kTrigWarps];
+		__shared__ uint32_t offset[kTrigWarps + 1];
+		const uint32_t stream = blockIdx.x;
+		const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+		const float* base = a.audio + uint64_t(stream) * a.stride;
+		const sgz_scope_trigger_state st = a.states[stream];
+		// chunk bounds: multiples of 32 samples so every step is a whole aligned row
+		const uint64_t per = ((a.n + kTrigWarps - 1) / kTrigWarps + 31) & ~uint64_t(31);
+		const uint64_t begin = min(uint64_t(warp) * per, a.n), end = min(begin + per, a.n);
+		// the sample before the chunk (the crossing test of its first sample): the carried state for chunk 0 (a float
+		// widened to double by the previous call; any other double keeps at least its sign through the conversion)
+		float prev = float(st.state);
+		if (st.state != 0.0 && prev == 0.f) prev = st.state < 0 ? -1.f : 1.f;
+		if (begin > 0 && begin < a.n) { float l, r; loadLR(base, a.layout, a.n, begin - 1, l, r); prev = oscChannel(a.channel, l, r); }
+		// smallest float strictly greater than the (double) threshold
+		float aboveFrom = float(a.threshold);
+		if (!(double(aboveFrom) > a.threshold)) aboveFrom = nextafterf(aboveFrom, INFINITY);
+		TrigSummary mine;
+		float lastSample = prev;
+		trigZeroChunk<false>(a, base, begin, end, prev, aboveFrom, false, 0, nullptr, 0, lane, mine, lastSample);
+		if (lane == 0) sums[warp] = mine;
+		__syncthreads();
+		if (threadIdx.x == 0)
+		{
+			int holding = st.is_peak_holding != 0;
+			uint64_t origin = st.cross_origin;
+			uint32_t total = 0;
+			for (int w = 0; w < kTrigWarps; ++w)
+			{
+				holdIn[w] = holding; originIn[w] = origin; offset[w] = total;
+				const TrigSummary& c = sums[w];
+				total += c.emits + ((c.aboveFirst && holding) ? 1u : 0u);
+				if (c.anyEvent) { holding = c.holdingOut; origin = c.holdingOut || c.emits ? c.originOut : origin; }
+			}
+			offset[kTrigWarps] = total;
+			a.counts[stream] = total;
+			// .state (the last sample of the block) is written by the warp that owns the end of the stream, below
+			a.states[stream].is_peak_holding = holding;
+			a.states[stream].cross_origin = origin;
+		}
+		__syncthreads();
+		// replay with the true incoming state only where something is written
+		const bool extra = sums[warp].aboveFirst && holdIn[warp];
+		if ((sums[warp].emits || extra) && offset[warp] < a.maxPeaks)
+		{
+			TrigSummary again; float ls;
+			trigZeroChunk<true>(a, base, begin, end, prev, aboveFrom, holdIn[warp] != 0, originIn[warp], a.peaks + uint64_t(stream) * a.maxPeaks, offset[warp], lane, again, ls);
+		}
+		if (lane == 0 && end == a.n && begin < end) a.states[stream].state = double(lastSample);
 	}
 
 	// PeakHoldProcessor::process (StreamPreprocessing.h:284-311): a data-dependent double recurrence;
@@ -971,7 +1072,7 @@ extern "C"
 		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = channel; a.nStreams = n_streams;
 		a.threshold = threshold; a.hysteresis = hysteresis; a.steadyClock = steady_clock; a.states = dStates; a.peaks = dPeaks; a.counts = dCounts; a.maxPeaks = max_peaks;
 		const unsigned warpsPerBlock = 4, blocks = (n_streams + warpsPerBlock - 1) / warpsPerBlock;
-		if (mode == 0) k_scope_trigger_zero<<<blocks, warpsPerBlock * 32, 0, c->stream>>>(a);
+		if (mode == 0) k_scope_trigger_zero<<<n_streams, 32 * kTrigWarps, 0, c->stream>>>(a);
 		else k_scope_trigger_peak<<<blocks, warpsPerBlock * 32, 0, c->stream>>>(a);
 		SGZS_CUDA(cudaGetLastError());
 		SGZS_CUDA(cudaMemcpyAsync(states, dStates, stBytes, cudaMemcpyDeviceToHost, c->stream));

@@ -123,6 +123,43 @@ def test_scope_c4_16x_resample_full_size():
     assert np.max(np.abs(got[:4, :, 1] - sub[..., 1])) < 2e-6
 
 
+def test_zero_crossing_trigger_chunked_scan_equals_sequential():
+    """the GPU cuts each stream into 16 chunks and chains their summaries: sparse, bursty and DC-shifted signals put
+    the arming crossing, the firing sample and long event-free stretches on every side of the chunk borders"""
+    rng = np.random.default_rng(11)
+    o, g = OracleScope(), Context()
+    for n in (1, 7, 32, 33, 511, 512, 513, 4096, 10007, 65536):
+        S = 12
+        a = np.zeros((S, n, 2), np.float32)
+        for s in range(S):
+            kind = s % 6
+            if kind == 0:      # sparse spikes of either sign
+                idx = rng.integers(0, n, size=max(1, n // 40)); a[s, idx, 0] = rng.uniform(-1, 1, size=len(idx))
+            elif kind == 1:    # always above the threshold, never crossing: only the carried-in armed state can fire
+                a[s, :, 0] = 0.5
+            elif kind == 2:    # crossings but never above the threshold: stays armed through every chunk
+                a[s, :, 0] = 0.01 * np.sign(np.sin(np.arange(n) * 0.37 + s))
+            elif kind == 3:    # dense noise
+                a[s, :, 0] = rng.uniform(-1, 1, size=n)
+            elif kind == 4:    # one burst in the middle of silence
+                m = n // 2; a[s, m: m + 5, 0] = [-0.3, 0.02, 0.04, 0.9, -0.2][: max(0, min(5, n - m))]
+            else:              # slow sine: arming and firing far apart
+                a[s, :, 0] = 0.8 * np.sin(np.arange(n) * 2 * np.pi / 3000.0 + s)
+        so, sg = (_abi.ScopeTriggerState * S)(), (_abi.ScopeTriggerState * S)()
+        for s in range(S):     # half of the streams come in armed
+            for st in (so, sg):
+                st[s].state = -0.25 if s % 2 else 0.3
+                st[s].is_peak_holding = s % 2
+                st[s].cross_origin = 1000 + s
+        for cap in (4096, 3):
+            po, co = o.scope_trigger(0, _abi.OSC_LEFT, a, so, threshold=0.05, steady_clock=5000, max_peaks=cap)
+            pg, cg = g.scope_trigger(0, _abi.OSC_LEFT, a, sg, threshold=0.05, steady_clock=5000, max_peaks=cap)
+            np.testing.assert_array_equal(cg, co)
+            for s in range(S):
+                np.testing.assert_array_equal(pg[s], po[s])
+            assert bytes(sg) == bytes(so), n
+
+
 @pytest.mark.parametrize("mode", [0, 1])
 @pytest.mark.parametrize("channel", [_abi.OSC_LEFT, _abi.OSC_MID, _abi.OSC_SIDE])
 def test_scope_triggers_bit_exact(mode, channel):
