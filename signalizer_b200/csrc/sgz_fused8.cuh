@@ -1,6 +1,6 @@
 	// ------------------------------------------------------------------------------------------
-	// k_fused8 — the N = 8192 fused frame kernel with 512 threads per stream and 8 (E, O) pairs per
-	// thread (included inside namespace sgz from sgz_spectrum.cu).
+	// k_fused8<K1> — the fused frame kernel with 64 K1 threads per stream and 8 (E, O) pairs per thread: K1 = 8 is
+	// N = 8192 (described below), K1 = 4 is N = 4096 (same passes 2-4, a radix-4 first pass; see Fused8GeomT) (included inside namespace sgz from sgz_spectrum.cu).
 	//
 	// Same arithmetic and shared-memory budget as k_fused<16,...>, different shape: M = 4096 = 8^4, four
 	// register-resident radix-8 passes, 32 data registers per thread instead of 64, so that the kernel
@@ -21,9 +21,12 @@
 #ifndef SGZ8_TW_POWERS
 #define SGZ8_TW_POWERS 1
 #endif
-	struct Fused8Geom
+	// K1 = radix of the first pass: 8 -> N = 8192 (M = 8^4, 512 threads); 4 -> N = 4096 (M = 4 x 8^3, 256 threads, whose
+	// first pass is two radix-4 butterflies per thread; passes 2-4 and everything after are the same code)
+	template<int K1>
+	struct Fused8GeomT
 	{
-		static constexpr int T = 512, M = 4096, N = 8192;
+		static constexpr int T = 64 * K1, M = 512 * K1, N = 2 * M;
 		static constexpr size_t xbufBytes = size_t(M) * 16;
 		static constexpr size_t twOffset = xbufBytes + 16;
 		static constexpr int twEntries = 64 + 512 + 512;            // A[8][8] | B[8][64] | C[8][64]
@@ -32,6 +35,7 @@
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
 		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12; }
 	};
+	typedef Fused8GeomT<8> Fused8Geom;
 
 	// 8-point forward DFT on SoA pairs; X[k] ends up in v[perm8(k)]
 	__device__ __forceinline__ void dft8q(float2 (&re)[8], float2 (&im)[8])
@@ -55,7 +59,14 @@
 		}
 	}
 
-	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4) { return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ k1); }
+	// exchange element (k1, d2, d3, d4) of the 512-point sub-transform k1.  The XOR keeps every pass free of bank
+	// conflicts on 128-bit words: the lanes of a quarter warp differ in d4 (passes 1-3) or, in pass 4, in k1 and - when
+	// k1 has only two bits (K1 = 4) - in the low bit of d2 as well
+	template<int K1>
+	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4)
+	{
+		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 == 8 ? k1 : (k1 | ((d2 & 1) << 2))));
+	}
 
 	// Multiplies output k of a radix-8 butterfly (held in slot perm8(k)) by w1^k, k = 1..7.  The powers are
 	// derived in registers (depth <= 3 complex products: w2 = w1^2, w3 = w2 w1, w4 = w2^2, w5 = w4 w1,
@@ -78,11 +89,11 @@
 		mulTwiddleP(re[perm8(7)], im[perm8(7)], make_float4(w7.x, w7.x, w7.y, w7.y));
 	}
 
-	template<bool STEREO, int BINPOL, int MATRIX>
-	__global__ void __launch_bounds__(512, 2)
+	template<int K1, bool STEREO, int BINPOL, int MATRIX>
+	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : 3)
 	k_fused8(DeviceTables t, FusedArgs a)
 	{
-		typedef Fused8Geom Gm;
+		typedef Fused8GeomT<K1> Gm;
 		constexpr int T = Gm::T, M = Gm::M, N = Gm::N;
 		extern __shared__ __align__(16) unsigned char smemRaw[];
 		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
@@ -177,28 +188,63 @@
 					}
 				}
 			}
-			dft8q(re, im);
-#if SGZ8_TW_POWERS
-			applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
-#else
+			if constexpr (K1 == 8)
 			{
-				const int n2 = u >> 6, v = u & 63;
-#pragma unroll
-				for (int k1 = 1; k1 < 8; ++k1)
+				dft8q(re, im);
+#if SGZ8_TW_POWERS
+				applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
+#else
 				{
-					const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
-					mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
+					const int n2 = u >> 6, v = u & 63;
+#pragma unroll
+					for (int k1 = 1; k1 < 8; ++k1)
+					{
+						const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
+						mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
+					}
+				}
+#endif
+			}
+			else
+			{
+				// two radix-4 butterflies: loaded element e sits at pair index e T + u = n1 (M / 4) + v with n1 = e >> 1 and
+				// v = u + T (e & 1); output k1 of group g = e & 1 lands in slot g + 2 k1 and takes the twiddle (W_M^v)^k1
+				constexpr float R = 0.70710678118654752440f;
+				const float2 wa = cmul(wu, wu);                                           // W_M^u
+				const float2 wb = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));      // W_M^(u + M / 8) = W_M^u W_8^1
+#pragma unroll
+				for (int g = 0; g < 2; ++g)
+				{
+					radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
+					const float2 w1 = g ? wb : wa, w2 = cmul(w1, w1), w3 = cmul(w2, w1);
+					mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
+					mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
+					mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
 				}
 			}
-#endif
 			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+			if constexpr (K1 == 8)
 			{
 				const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
 #pragma unroll
 				for (int k1 = 0; k1 < 8; ++k1)
 				{
 					const float2 r = re[perm8(k1)], i = im[perm8(k1)];
-					xbuf[phys8(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+			}
+			else
+			{
+#pragma unroll
+				for (int g = 0; g < 2; ++g)
+				{
+					const int v = u + T * g, n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
+#pragma unroll
+					for (int k1 = 0; k1 < 4; ++k1)
+					{
+						const float2 r = re[g + 2 * k1], i = im[g + 2 * k1];
+						xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					}
 				}
 			}
 			__syncthreads();
@@ -209,7 +255,7 @@
 #pragma unroll
 				for (int n2 = 0; n2 < 8; ++n2)
 				{
-					const float4 x = xbuf[phys8(k1, n2, n3, n4)];
+					const float4 x = xbuf[phys8<K1>(k1, n2, n3, n4)];
 					re[n2] = make_float2(x.x, x.y); im[n2] = make_float2(x.z, x.w);
 				}
 				dft8q(re, im);
@@ -219,7 +265,7 @@
 				for (int k2 = 0; k2 < 8; ++k2)
 				{
 					const float2 r = re[perm8(k2)], i = im[perm8(k2)];
-					xbuf[phys8(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					xbuf[phys8<K1>(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 #else
 #pragma unroll
@@ -231,7 +277,7 @@
 						const float2 w = twC[k2 * 64 + v];
 						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
 					}
-					xbuf[phys8(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					xbuf[phys8<K1>(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 #endif
 			}
@@ -243,7 +289,7 @@
 #pragma unroll
 				for (int n3 = 0; n3 < 8; ++n3)
 				{
-					const float4 x = xbuf[phys8(k1, k2, n3, n4)];
+					const float4 x = xbuf[phys8<K1>(k1, k2, n3, n4)];
 					re[n3] = make_float2(x.x, x.y); im[n3] = make_float2(x.z, x.w);
 				}
 				dft8q(re, im);
@@ -253,7 +299,7 @@
 				for (int k3 = 0; k3 < 8; ++k3)
 				{
 					const float2 r = re[perm8(k3)], i = im[perm8(k3)];
-					xbuf[phys8(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					xbuf[phys8<K1>(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 #else
 #pragma unroll
@@ -265,7 +311,7 @@
 						const float2 w = twA[k3 * 8 + n4];
 						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
 					}
-					xbuf[phys8(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					xbuf[phys8<K1>(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 #endif
 			}
@@ -273,11 +319,11 @@
 
 			// ---- pass 4: thread t = k1 + 8 k2 + 64 k3, DFT8 over n4; owns bins k = t + 512 k4 ----
 			{
-				const int k1 = u & 7, k2 = (u >> 3) & 7, k3 = u >> 6;
+				const int k1 = u & (K1 - 1), k2 = (u / K1) & 7, k3 = u / (8 * K1);
 #pragma unroll
 				for (int n4 = 0; n4 < 8; ++n4)
 				{
-					const float4 x = xbuf[phys8(k1, k2, k3, n4)];
+					const float4 x = xbuf[phys8<K1>(k1, k2, k3, n4)];
 					re[n4] = make_float2(x.x, x.y); im[n4] = make_float2(x.z, x.w);
 				}
 			}
@@ -297,7 +343,7 @@
 			if constexpr (STEREO)
 			{
 #pragma unroll
-				for (int k4 = 0; k4 < 8; ++k4) zm[u + 512 * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
+				for (int k4 = 0; k4 < 8; ++k4) zm[u + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
 				__syncthreads();
 				// A = (Z[j] + conj Z[N-j]) / 2, B = (Z[j] - conj Z[N-j]) / 2i.  With S = Z[j] + Z[N-j] and
 				// D = Z[j] - Z[N-j]: 2A = (S.x, D.y), 2|B| components = (D.x, S.y).  The halving is folded into the
@@ -306,7 +352,7 @@
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
 					const int slot = perm8(k4);
-					const int j = u + 512 * k4;
+					const int j = u + T * k4;
 					const float2 zj = make_float2(re[slot].x, im[slot].x);
 					if (k4 == 0 && j == 0)
 					{
@@ -323,7 +369,7 @@
 					const float2 SS = mul2(S, S), DD = mul2(D, D);
 					float a2 = SS.x + DD.y, b2 = DD.x + SS.y;
 					if (k4 == 7 && j == M - 1) a2 *= 0.25f; // csf[(N >> 1) - 1] *= 0.5, channel 1 only
-					if ((k4 == 0 || linLimit > 512) && j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
+					if ((k4 == 0 || linLimit > T) && j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
 					csfmag[j] = a2;
 					csfmag[N - j] = b2;
 				}
@@ -334,7 +380,7 @@
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
 					const int slot = perm8(k4);
-					const int j = u + 512 * k4;
+					const int j = u + T * k4;
 					float2 zj = make_float2(re[slot].x, im[slot].x);
 					if (j == 0)
 					{

@@ -654,7 +654,7 @@ struct sgz_spectrum
 	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
 	uint64_t processedSamplesSinceLastFrame{ 0 }; // TransformPair.h:189 (one authority counter for all pairs, SpectrumDSP.cpp:81,93)
 	int fusedR3{ 0 };
-	bool fusedVariant8{ false }; // N = 8192: use k_fused8 (512 threads, radix-8 x 4) instead of k_fused<16> (256 threads, radix-16 x 3)
+	bool fusedVariant8{ false }; // use k_fused8<K1> (64 K1 threads, 8 pairs per thread, radix-K1 x 8 x 8 x 8) instead of k_fused<R3> (16 R3 threads, 16 pairs per thread)
 	cudaStream_t copyIn{ nullptr }, copyOut{ nullptr }; // host-buffer pipeline of process_frames
 	std::vector<cudaEvent_t> events;
 	bool fusedAttrSet{ false };
@@ -754,14 +754,14 @@ namespace
 		return SGZ_OK;
 	}
 
-	template<bool STEREO, int MATRIX>
+	template<int K1, bool STEREO, int MATRIX>
 	int launchFused8Binpol(sgz_spectrum* h, const FusedArgs& a)
 	{
-		const size_t smem = Fused8Geom::smemBytes(h->tab.P);
-		const dim3 grid(a.numStreams), block(Fused8Geom::T);
+		const size_t smem = Fused8GeomT<K1>::smemBytes(h->tab.P);
+		const dim3 grid(a.numStreams), block(Fused8GeomT<K1>::T);
 #define SGZ_LAUNCH8(BP)                                                                                             \
 		{                                                                                                           \
-			auto kern = k_fused8<STEREO, BP, MATRIX>;                                                               \
+			auto kern = k_fused8<K1, STEREO, BP, MATRIX>;                                                           \
 			if (!h->fusedAttrSet)                                                                                   \
 			{                                                                                                       \
 				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
@@ -784,8 +784,13 @@ namespace
 	{
 		if (h->fusedR3 == 16 && h->fusedVariant8)
 		{
-			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<true, 0>(h, a);
-			return h->tab.stateChannels == 2 ? launchFused8Binpol<true, 1>(h, a) : launchFused8Binpol<false, 1>(h, a);
+			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<8, true, 0>(h, a);
+			return h->tab.stateChannels == 2 ? launchFused8Binpol<8, true, 1>(h, a) : launchFused8Binpol<8, false, 1>(h, a);
+		}
+		if (h->fusedR3 == 8 && h->fusedVariant8)
+		{
+			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<4, true, 0>(h, a);
+			return h->tab.stateChannels == 2 ? launchFused8Binpol<4, true, 1>(h, a) : launchFused8Binpol<4, false, 1>(h, a);
 		}
 		const bool stereo = h->tab.stateChannels == 2;
 		const bool passthru = h->cfg.configuration == SGZ_CH_SEPARATE;
@@ -970,7 +975,6 @@ extern "C"
 			SGZ_TRY(upload(h, tw1, &d.tw1));
 			SGZ_TRY(upload(h, twiddleTable(e2.size(), double(16 * R3), e2), &d.tw2));
 			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(2 * M), e3), &d.tw3));
-			if (R3 == 16)
 			{
 				std::vector<uint64_t> eA(64), eB(512), eC(512);
 				for (int x = 0; x < 8; ++x) for (int y = 0; y < 8; ++y) eA[x * 8 + y] = uint64_t(x) * y;
