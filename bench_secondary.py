@@ -43,18 +43,22 @@ def tile(base, S):
 
 
 def c1():
-    cfg = _abi.default_config(window_size=4096, window_type=_abi.WIN_HANN)
-    S, F, hop = 1024, 64, 1024
-    n = signals.frames_length(4096, hop, F)
-    d = torch.from_numpy(tile(signals.batch(48, n), S)).cuda()
-    p = TransformPairBatch(cfg, S)
-    p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
-    out = torch.empty((S, F, 2, 1024, 2), dtype=torch.float32, device="cuda")
-    ms = timed(lambda: p.process_frames(d, hop, F, out=out), torch.cuda.synchronize)
-    frames = S * F
-    bytes_per_frame = 2 * 4096 * 4 + 2 * 2 * 1024 * 8 + 2 * 1024 * 8  # 81 920 B, SURVEY.md §8(d)
-    return {"config": "C1 batched: 1024 streams x 4096-pt Hann, hop 1024, Separate, Lanczos, 1024 log bins", "frames_per_s": frames / ms * 1e3,
-            "ms": ms, "achieved_GBps": frames * bytes_per_frame / ms / 1e6, "frac_hbm": frames * bytes_per_frame / ms / 1e6 / PEAK}
+    out_lines = []
+    for W in (4096, 2048):
+        cfg = _abi.default_config(window_size=W, window_type=_abi.WIN_HANN)
+        S, F, hop = 1024, 64, W // 4
+        n = signals.frames_length(W, hop, F)
+        d = torch.from_numpy(tile(signals.batch(48, n), S)).cuda()
+        p = TransformPairBatch(cfg, S)
+        p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+        out = torch.empty((S, F, 2, 1024, 2), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: p.process_frames(d, hop, F, out=out), torch.cuda.synchronize)
+        frames = S * F
+        bytes_per_frame = 2 * W * 4 + 2 * 2 * 1024 * 8 + 2 * 1024 * 8  # W = 4096: 81 920 B, SURVEY.md §8(d)
+        name = "C1 batched" if W == 4096 else "C1 at half the window"
+        out_lines.append({"config": f"{name}: 1024 streams x {W}-pt Hann, hop {hop}, Separate, Lanczos, 1024 log bins", "frames_per_s": frames / ms * 1e3,
+                          "ms": ms, "achieved_GBps": frames * bytes_per_frame / ms / 1e6, "frac_hbm": frames * bytes_per_frame / ms / 1e6 / PEAK})
+    return out_lines
 
 
 def c2():

@@ -22,7 +22,8 @@
 #define SGZ8_TW_POWERS 1
 #endif
 	// K1 = radix of the first pass: 8 -> N = 8192 (M = 8^4, 512 threads); 4 -> N = 4096 (M = 4 x 8^3, 256 threads, whose
-	// first pass is two radix-4 butterflies per thread; passes 2-4 and everything after are the same code)
+	// first pass is two radix-4 butterflies per thread); 2 -> N = 2048 (128 threads, four radix-2 butterflies); passes 2-4
+	// and everything after are the same code
 	template<int K1>
 	struct Fused8GeomT
 	{
@@ -61,11 +62,11 @@
 
 	// exchange element (k1, d2, d3, d4) of the 512-point sub-transform k1.  The XOR keeps every pass free of bank
 	// conflicts on 128-bit words: the lanes of a quarter warp differ in d4 (passes 1-3) or, in pass 4, in k1 and - when
-	// k1 has only two bits (K1 = 4) - in the low bit of d2 as well
+	// k1 has fewer than three bits (K1 = 4, 2) - in the low bit(s) of d2 as well
 	template<int K1>
 	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4)
 	{
-		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 == 8 ? k1 : (k1 | ((d2 & 1) << 2))));
+		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 == 8 ? k1 : K1 == 4 ? (k1 | ((d2 & 1) << 2)) : (k1 | ((d2 & 3) << 1))));
 	}
 
 	// Multiplies output k of a radix-8 butterfly (held in slot perm8(k)) by w1^k, k = 1..7.  The powers are
@@ -90,7 +91,7 @@
 	}
 
 	template<int K1, bool STEREO, int BINPOL, int MATRIX>
-	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : 3)
+	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : K1 == 4 ? 3 : 4)
 	k_fused8(DeviceTables t, FusedArgs a)
 	{
 		typedef Fused8GeomT<K1> Gm;
@@ -207,19 +208,34 @@
 			}
 			else
 			{
-				// two radix-4 butterflies: loaded element e sits at pair index e T + u = n1 (M / 4) + v with n1 = e >> 1 and
-				// v = u + T (e & 1); output k1 of group g = e & 1 lands in slot g + 2 k1 and takes the twiddle (W_M^v)^k1
+				// G = 8 / K1 radix-K1 butterflies: loaded element e sits at pair index e T + u = n1 (M / K1) + v with
+				// n1 = e / G and v = u + T (e % G); output k1 of group g = e % G lands in slot g + G k1 and takes the twiddle
+				// (W_M^v)^k1, where W_M^v = W_M^u W_8^g because M / T = 8
+				constexpr int G = 8 / K1;
 				constexpr float R = 0.70710678118654752440f;
-				const float2 wa = cmul(wu, wu);                                           // W_M^u
-				const float2 wb = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));      // W_M^(u + M / 8) = W_M^u W_8^1
+				const float2 wa = cmul(wu, wu); // W_M^u
 #pragma unroll
-				for (int g = 0; g < 2; ++g)
+				for (int g = 0; g < G; ++g)
 				{
-					radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
-					const float2 w1 = g ? wb : wa, w2 = cmul(w1, w1), w3 = cmul(w2, w1);
-					mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
-					mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
-					mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
+					float2 w1 = wa;
+					if (g == 1) w1 = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));   // W_8^1 = (1 - i) / sqrt 2
+					if (g == 2) w1 = make_float2(wa.y, -wa.x);                            // W_8^2 = -i
+					if (g == 3) w1 = make_float2(R * (wa.y - wa.x), -R * (wa.x + wa.y));  // W_8^3 = -(1 + i) / sqrt 2
+					if constexpr (K1 == 4)
+					{
+						radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
+						const float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1);
+						mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
+						mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
+						mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
+					}
+					else
+					{
+						const float2 ar = re[g], ai = im[g], br = re[g + 4], bi = im[g + 4];
+						re[g] = add2(ar, br); im[g] = add2(ai, bi);
+						re[g + 4] = sub2(ar, br); im[g + 4] = sub2(ai, bi);
+						mulTwiddleP(re[g + 4], im[g + 4], make_float4(w1.x, w1.x, w1.y, w1.y));
+					}
 				}
 			}
 			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
@@ -235,14 +251,15 @@
 			}
 			else
 			{
+				constexpr int G = 8 / K1;
 #pragma unroll
-				for (int g = 0; g < 2; ++g)
+				for (int g = 0; g < G; ++g)
 				{
 					const int v = u + T * g, n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
 #pragma unroll
-					for (int k1 = 0; k1 < 4; ++k1)
+					for (int k1 = 0; k1 < K1; ++k1)
 					{
-						const float2 r = re[g + 2 * k1], i = im[g + 2 * k1];
+						const float2 r = re[g + G * k1], i = im[g + G * k1];
 						xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 					}
 				}

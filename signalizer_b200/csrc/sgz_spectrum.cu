@@ -787,6 +787,11 @@ namespace
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<8, true, 0>(h, a);
 			return h->tab.stateChannels == 2 ? launchFused8Binpol<8, true, 1>(h, a) : launchFused8Binpol<8, false, 1>(h, a);
 		}
+		if (h->fusedR3 == 4)
+		{
+			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<2, true, 0>(h, a);
+			return h->tab.stateChannels == 2 ? launchFused8Binpol<2, true, 1>(h, a) : launchFused8Binpol<2, false, 1>(h, a);
+		}
 		if (h->fusedR3 == 8 && h->fusedVariant8)
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<4, true, 0>(h, a);
@@ -897,7 +902,7 @@ extern "C"
 			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
 			const int rc = buildTables(*cfg, h->tab);
 			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
-			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 8192 ? 16 : 8) : 0;
+			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : 4) : 0;
 			*out = h;
 			return SGZ_OK;
 		}
@@ -957,7 +962,7 @@ extern "C"
 		h->fusedR3 = 0;
 		if (t.fusedOk && t.P <= 2048)
 		{
-			const int R3 = t.N == 8192 ? 16 : 8;
+			const int R3 = t.N == 8192 ? 16 : t.N == 4096 ? 8 : 4; // N = 2048 (R3 = 4) exists as k_fused8<2> only
 			const int T = 16 * R3, M = 16 * T;
 			// tw1 = [A | B]: A[k1][n2] = W_256^(n2 k1) (256 entries), B[k1][n3] = W_M^(n3 k1) (16 R3 entries)
 			std::vector<float2> tw1(256 + size_t(16) * R3);
@@ -986,7 +991,7 @@ extern "C"
 				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
 				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
 			}
-			h->fusedR3 = R3;
+			h->fusedR3 = (R3 == 4 && !h->fusedVariant8) ? 0 : R3;
 			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
 		}
 		const size_t workPerStream = std::max<size_t>(t.N, size_t(2) * t.P);

@@ -111,7 +111,8 @@ def compare_frames(got, want, cfg, what):
                 assert_log_close(g[m], w[m], lin=l[m], peak=l.max(), dy=dy, what=f"{what} stream {s} frame {f}")
 
 
-FUSED_SIZES = [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (6000, _abi.WIN_HAMMING), (3000, _abi.WIN_BLACKMAN)]
+FUSED_SIZES = [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (6000, _abi.WIN_HAMMING), (3000, _abi.WIN_BLACKMAN),
+               (2048, _abi.WIN_HANN), (1500, _abi.WIN_HAMMING)]   # N = 8192, 4096, 8192, 4096, 2048, 2048
 
 
 @pytest.mark.parametrize("size", FUSED_SIZES)
