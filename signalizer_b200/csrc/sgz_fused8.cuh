@@ -90,6 +90,224 @@
 		mulTwiddleP(re[perm8(7)], im[perm8(7)], make_float4(w7.x, w7.x, w7.y, w7.y));
 	}
 
+	// The FFT of one frame once its 8 windowed (E, O) pairs per thread sit in registers: first pass in registers,
+	// three in-place radix-8 passes through the exchange buffer, the last radix-2 that joins the even and odd halves.
+	// On return re[perm8(k4)] = (Z[k].re, Z[k + M].re), im[...] likewise, for the bins k = u + T k4.  Contains the
+	// block-wide barriers of the exchanges; the first one also orders whatever the caller still had in xbuf before it.
+	template<int K1>
+	__device__ __forceinline__ void fusedFftCore(float2 (&re)[8], float2 (&im)[8], float4* xbuf, const float2* twA, const float2* twB, const float2* twC,
+		float2 wu, int u)
+	{
+		constexpr int T = Fused8GeomT<K1>::T;
+
+		if constexpr (K1 == 8)
+		{
+			dft8q(re, im);
+#if SGZ8_TW_POWERS
+			applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
+#else
+			{
+				const int n2 = u >> 6, v = u & 63;
+#pragma unroll
+				for (int k1 = 1; k1 < 8; ++k1)
+				{
+					const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
+					mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
+				}
+			}
+#endif
+		}
+		else
+		{
+			// G = 8 / K1 radix-K1 butterflies: loaded element e sits at pair index e T + u = n1 (M / K1) + v with
+			// n1 = e / G and v = u + T (e % G); output k1 of group g = e % G lands in slot g + G k1 and takes the twiddle
+			// (W_M^v)^k1, where W_M^v = W_M^u W_8^g because M / T = 8
+			constexpr int G = 8 / K1;
+			constexpr float R = 0.70710678118654752440f;
+			const float2 wa = cmul(wu, wu); // W_M^u
+#pragma unroll
+			for (int g = 0; g < G; ++g)
+			{
+				float2 w1 = wa;
+				if (g == 1) w1 = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));   // W_8^1 = (1 - i) / sqrt 2
+				if (g == 2) w1 = make_float2(wa.y, -wa.x);                            // W_8^2 = -i
+				if (g == 3) w1 = make_float2(R * (wa.y - wa.x), -R * (wa.x + wa.y));  // W_8^3 = -(1 + i) / sqrt 2
+				if constexpr (K1 == 4)
+				{
+					radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
+					const float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1);
+					mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
+					mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
+					mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
+				}
+				else
+				{
+					const float2 ar = re[g], ai = im[g], br = re[g + 4], bi = im[g + 4];
+					re[g] = add2(ar, br); im[g] = add2(ai, bi);
+					re[g + 4] = sub2(ar, br); im[g + 4] = sub2(ai, bi);
+					mulTwiddleP(re[g + 4], im[g + 4], make_float4(w1.x, w1.x, w1.y, w1.y));
+				}
+			}
+		}
+		__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+		if constexpr (K1 == 8)
+		{
+			const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
+#pragma unroll
+			for (int k1 = 0; k1 < 8; ++k1)
+			{
+				const float2 r = re[perm8(k1)], i = im[perm8(k1)];
+				xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+			}
+		}
+		else
+		{
+			constexpr int G = 8 / K1;
+#pragma unroll
+			for (int g = 0; g < G; ++g)
+			{
+				const int v = u + T * g, n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
+#pragma unroll
+				for (int k1 = 0; k1 < K1; ++k1)
+				{
+					const float2 r = re[g + G * k1], i = im[g + G * k1];
+					xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+			}
+		}
+		__syncthreads();
+
+		// ---- pass 2 (in place): thread (k1 n3 n4), DFT8 over n2, twiddle W_512^(v k2) ----
+		{
+			const int k1 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7, v = u & 63;
+#pragma unroll
+			for (int n2 = 0; n2 < 8; ++n2)
+			{
+				const float4 x = xbuf[phys8<K1>(k1, n2, n3, n4)];
+				re[n2] = make_float2(x.x, x.y); im[n2] = make_float2(x.z, x.w);
+			}
+			dft8q(re, im);
+#if SGZ8_TW_POWERS
+			applyTwiddlePowers(twC[64 + v], re, im); // W_512^(v k2) = (W_512^v)^k2
+#pragma unroll
+			for (int k2 = 0; k2 < 8; ++k2)
+			{
+				const float2 r = re[perm8(k2)], i = im[perm8(k2)];
+				xbuf[phys8<K1>(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+			}
+#else
+#pragma unroll
+			for (int k2 = 0; k2 < 8; ++k2)
+			{
+				float2 r = re[perm8(k2)], i = im[perm8(k2)];
+				if (k2 > 0)
+				{
+					const float2 w = twC[k2 * 64 + v];
+					mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
+				}
+				xbuf[phys8<K1>(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+			}
+#endif
+		}
+		__syncthreads();
+
+		// ---- pass 3 (in place): thread (k1 k2 n4), DFT8 over n3, twiddle W_64^(n4 k3) ----
+		{
+			const int k1 = u >> 6, k2 = (u >> 3) & 7, n4 = u & 7;
+#pragma unroll
+			for (int n3 = 0; n3 < 8; ++n3)
+			{
+				const float4 x = xbuf[phys8<K1>(k1, k2, n3, n4)];
+				re[n3] = make_float2(x.x, x.y); im[n3] = make_float2(x.z, x.w);
+			}
+			dft8q(re, im);
+#if SGZ8_TW_POWERS >= 2
+			applyTwiddlePowers(twA[8 + n4], re, im); // W_64^(n4 k3) = (W_64^n4)^k3
+#pragma unroll
+			for (int k3 = 0; k3 < 8; ++k3)
+			{
+				const float2 r = re[perm8(k3)], i = im[perm8(k3)];
+				xbuf[phys8<K1>(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+			}
+#else
+#pragma unroll
+			for (int k3 = 0; k3 < 8; ++k3)
+			{
+				float2 r = re[perm8(k3)], i = im[perm8(k3)];
+				if (k3 > 0)
+				{
+					const float2 w = twA[k3 * 8 + n4];
+					mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
+				}
+				xbuf[phys8<K1>(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+			}
+#endif
+		}
+		__syncthreads();
+
+		// ---- pass 4: thread t = k1 + 8 k2 + 64 k3, DFT8 over n4; owns bins k = t + 512 k4 ----
+		{
+			const int k1 = u & (K1 - 1), k2 = (u / K1) & 7, k3 = u / (8 * K1);
+#pragma unroll
+			for (int n4 = 0; n4 < 8; ++n4)
+			{
+				const float4 x = xbuf[phys8<K1>(k1, k2, k3, n4)];
+				re[n4] = make_float2(x.x, x.y); im[n4] = make_float2(x.z, x.w);
+			}
+		}
+		dft8q(re, im);
+		// last radix-2: re[slot] = (Zp.re, Zm.re), im[slot] = (Zp.im, Zm.im); W_N^(t + 512 k4) = W_N^t W_16^k4
+#pragma unroll
+		for (int k4 = 0; k4 < 8; ++k4)
+		{
+			const int slot = perm8(k4);
+			const float2 o = make_float2(re[slot].y, im[slot].y), e = make_float2(re[slot].x, im[slot].x);
+			const float2 wo = cmul(cmul(o, w32(2 * k4)), wu);
+			re[slot] = make_float2(e.x + wo.x, e.x - wo.x);
+			im[slot] = make_float2(e.y + wo.y, e.y - wo.y);
+		}
+	}
+
+
+	// doTransform for the staged calls at N = 2048 / 4096 / 8192: the same register-resident FFT as the fused kernel,
+	// in place on audioMemory (csf, [stream][N + 1], element N untouched), one CTA per stream.  The complex input
+	// z[n] is read as the (even, odd) pairs the core works on; bins come out in natural order.
+	template<int K1>
+	struct Fft8Smem { static constexpr size_t bytes = Fused8GeomT<K1>::twOffset + Fused8GeomT<K1>::twBytes; };
+
+	template<int K1>
+	__global__ void __launch_bounds__(64 * K1) k_fft8(DeviceTables t, float2* __restrict__ csf)
+	{
+		typedef Fused8GeomT<K1> Gm;
+		constexpr int T = Gm::T, M = Gm::M;
+		extern __shared__ __align__(16) unsigned char smemRaw[];
+		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
+		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);
+		float2* twB = twA + 64;
+		float2* twC = twB + 512;
+		const int u = threadIdx.x;
+		float2* z = csf + uint64_t(blockIdx.x) * (t.N + 1);
+		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i];
+		const float2 wu = t.tw3[u];
+		float2 re[8], im[8];
+#pragma unroll
+		for (int e = 0; e < 8; ++e)
+		{
+			const int p = e * T + u;
+			const float2 ev = z[2 * p], od = z[2 * p + 1];
+			re[e] = make_float2(ev.x, od.x); im[e] = make_float2(ev.y, od.y);
+		}
+		__syncthreads(); // the twiddle tables are in place
+		fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u);
+#pragma unroll
+		for (int k4 = 0; k4 < 8; ++k4)
+		{
+			const int slot = perm8(k4), k = u + T * k4;
+			z[k] = make_float2(re[slot].x, im[slot].x);
+			z[k + M] = make_float2(re[slot].y, im[slot].y);
+		}
+	}
+
 	template<int K1, bool STEREO, int BINPOL, int MATRIX>
 	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : K1 == 4 ? 3 : 4)
 	k_fused8(DeviceTables t, FusedArgs a)
@@ -189,172 +407,7 @@
 					}
 				}
 			}
-			if constexpr (K1 == 8)
-			{
-				dft8q(re, im);
-#if SGZ8_TW_POWERS
-				applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
-#else
-				{
-					const int n2 = u >> 6, v = u & 63;
-#pragma unroll
-					for (int k1 = 1; k1 < 8; ++k1)
-					{
-						const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
-						mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
-					}
-				}
-#endif
-			}
-			else
-			{
-				// G = 8 / K1 radix-K1 butterflies: loaded element e sits at pair index e T + u = n1 (M / K1) + v with
-				// n1 = e / G and v = u + T (e % G); output k1 of group g = e % G lands in slot g + G k1 and takes the twiddle
-				// (W_M^v)^k1, where W_M^v = W_M^u W_8^g because M / T = 8
-				constexpr int G = 8 / K1;
-				constexpr float R = 0.70710678118654752440f;
-				const float2 wa = cmul(wu, wu); // W_M^u
-#pragma unroll
-				for (int g = 0; g < G; ++g)
-				{
-					float2 w1 = wa;
-					if (g == 1) w1 = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));   // W_8^1 = (1 - i) / sqrt 2
-					if (g == 2) w1 = make_float2(wa.y, -wa.x);                            // W_8^2 = -i
-					if (g == 3) w1 = make_float2(R * (wa.y - wa.x), -R * (wa.x + wa.y));  // W_8^3 = -(1 + i) / sqrt 2
-					if constexpr (K1 == 4)
-					{
-						radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
-						const float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1);
-						mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
-						mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
-						mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
-					}
-					else
-					{
-						const float2 ar = re[g], ai = im[g], br = re[g + 4], bi = im[g + 4];
-						re[g] = add2(ar, br); im[g] = add2(ai, bi);
-						re[g + 4] = sub2(ar, br); im[g + 4] = sub2(ai, bi);
-						mulTwiddleP(re[g + 4], im[g + 4], make_float4(w1.x, w1.x, w1.y, w1.y));
-					}
-				}
-			}
-			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
-			if constexpr (K1 == 8)
-			{
-				const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
-#pragma unroll
-				for (int k1 = 0; k1 < 8; ++k1)
-				{
-					const float2 r = re[perm8(k1)], i = im[perm8(k1)];
-					xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-				}
-			}
-			else
-			{
-				constexpr int G = 8 / K1;
-#pragma unroll
-				for (int g = 0; g < G; ++g)
-				{
-					const int v = u + T * g, n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
-#pragma unroll
-					for (int k1 = 0; k1 < K1; ++k1)
-					{
-						const float2 r = re[g + G * k1], i = im[g + G * k1];
-						xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-					}
-				}
-			}
-			__syncthreads();
-
-			// ---- pass 2 (in place): thread (k1 n3 n4), DFT8 over n2, twiddle W_512^(v k2) ----
-			{
-				const int k1 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7, v = u & 63;
-#pragma unroll
-				for (int n2 = 0; n2 < 8; ++n2)
-				{
-					const float4 x = xbuf[phys8<K1>(k1, n2, n3, n4)];
-					re[n2] = make_float2(x.x, x.y); im[n2] = make_float2(x.z, x.w);
-				}
-				dft8q(re, im);
-#if SGZ8_TW_POWERS
-				applyTwiddlePowers(twC[64 + v], re, im); // W_512^(v k2) = (W_512^v)^k2
-#pragma unroll
-				for (int k2 = 0; k2 < 8; ++k2)
-				{
-					const float2 r = re[perm8(k2)], i = im[perm8(k2)];
-					xbuf[phys8<K1>(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-				}
-#else
-#pragma unroll
-				for (int k2 = 0; k2 < 8; ++k2)
-				{
-					float2 r = re[perm8(k2)], i = im[perm8(k2)];
-					if (k2 > 0)
-					{
-						const float2 w = twC[k2 * 64 + v];
-						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
-					}
-					xbuf[phys8<K1>(k1, k2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-				}
-#endif
-			}
-			__syncthreads();
-
-			// ---- pass 3 (in place): thread (k1 k2 n4), DFT8 over n3, twiddle W_64^(n4 k3) ----
-			{
-				const int k1 = u >> 6, k2 = (u >> 3) & 7, n4 = u & 7;
-#pragma unroll
-				for (int n3 = 0; n3 < 8; ++n3)
-				{
-					const float4 x = xbuf[phys8<K1>(k1, k2, n3, n4)];
-					re[n3] = make_float2(x.x, x.y); im[n3] = make_float2(x.z, x.w);
-				}
-				dft8q(re, im);
-#if SGZ8_TW_POWERS >= 2
-				applyTwiddlePowers(twA[8 + n4], re, im); // W_64^(n4 k3) = (W_64^n4)^k3
-#pragma unroll
-				for (int k3 = 0; k3 < 8; ++k3)
-				{
-					const float2 r = re[perm8(k3)], i = im[perm8(k3)];
-					xbuf[phys8<K1>(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-				}
-#else
-#pragma unroll
-				for (int k3 = 0; k3 < 8; ++k3)
-				{
-					float2 r = re[perm8(k3)], i = im[perm8(k3)];
-					if (k3 > 0)
-					{
-						const float2 w = twA[k3 * 8 + n4];
-						mulTwiddleP(r, i, make_float4(w.x, w.x, w.y, w.y));
-					}
-					xbuf[phys8<K1>(k1, k2, k3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-				}
-#endif
-			}
-			__syncthreads();
-
-			// ---- pass 4: thread t = k1 + 8 k2 + 64 k3, DFT8 over n4; owns bins k = t + 512 k4 ----
-			{
-				const int k1 = u & (K1 - 1), k2 = (u / K1) & 7, k3 = u / (8 * K1);
-#pragma unroll
-				for (int n4 = 0; n4 < 8; ++n4)
-				{
-					const float4 x = xbuf[phys8<K1>(k1, k2, k3, n4)];
-					re[n4] = make_float2(x.x, x.y); im[n4] = make_float2(x.z, x.w);
-				}
-			}
-			dft8q(re, im);
-			// last radix-2: re[slot] = (Zp.re, Zm.re), im[slot] = (Zp.im, Zm.im); W_N^(t + 512 k4) = W_N^t W_16^k4
-#pragma unroll
-			for (int k4 = 0; k4 < 8; ++k4)
-			{
-				const int slot = perm8(k4);
-				const float2 o = make_float2(re[slot].y, im[slot].y), e = make_float2(re[slot].x, im[slot].x);
-				const float2 wo = cmul(cmul(o, w32(2 * k4)), wu);
-				re[slot] = make_float2(e.x + wo.x, e.x - wo.x);
-				im[slot] = make_float2(e.y + wo.y, e.y - wo.y);
-			}
+			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u);
 			__syncthreads(); // every pass-4 read of xbuf is done before zm / csfmag overwrite it
 
 			if constexpr (STEREO)

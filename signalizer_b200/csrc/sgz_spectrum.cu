@@ -959,6 +959,22 @@ extern "C"
 			for (size_t k = 0; k < e.size(); ++k) e[k] = k;
 			SGZ_TRY(upload(h, twiddleTable(e.size(), double(t.N), e), &d.twN));
 		}
+		if (t.N == 2048 || t.N == 4096 || t.N == 8192)
+		{
+			// tables of the radix-8 register FFT (k_fused8 and the staged k_fft8): W_N^k for the last radix-2, and
+			// [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2)
+			const uint32_t M = t.N / 2;
+			std::vector<uint64_t> e3(M);
+			for (uint32_t k = 0; k < M; ++k) e3[k] = k;
+			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(t.N), e3), &d.tw3));
+			std::vector<uint64_t> eA(64), eB(512), eC(512);
+			for (int x = 0; x < 8; ++x) for (int y = 0; y < 8; ++y) eA[x * 8 + y] = uint64_t(x) * y;
+			for (int k = 0; k < 8; ++k) for (int v = 0; v < 64; ++v) { eB[k * 64 + v] = uint64_t(v) * k; eC[k * 64 + v] = uint64_t(v) * k; }
+			std::vector<float2> tw8;
+			const auto A = twiddleTable(64, 64.0, eA), B = twiddleTable(512, 4096.0, eB), C = twiddleTable(512, 512.0, eC);
+			tw8.insert(tw8.end(), A.begin(), A.end()); tw8.insert(tw8.end(), B.begin(), B.end()); tw8.insert(tw8.end(), C.begin(), C.end());
+			SGZ_TRY(upload(h, tw8, &d.tw8));
+		}
 		h->fusedR3 = 0;
 		if (t.fusedOk && t.P <= 2048)
 		{
@@ -974,20 +990,11 @@ extern "C"
 				std::copy(A.begin(), A.end(), tw1.begin());
 				std::copy(B.begin(), B.end(), tw1.begin() + 256);
 			}
-			std::vector<uint64_t> e2(size_t(16) * R3), e3(M);
+			std::vector<uint64_t> e2(size_t(16) * R3);
 			for (int k2 = 0; k2 < 16; ++k2) for (int n3 = 0; n3 < R3; ++n3) e2[size_t(k2) * R3 + n3] = uint64_t(n3) * k2;
-			for (int k = 0; k < M; ++k) e3[k] = k;
 			SGZ_TRY(upload(h, tw1, &d.tw1));
 			SGZ_TRY(upload(h, twiddleTable(e2.size(), double(16 * R3), e2), &d.tw2));
-			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(2 * M), e3), &d.tw3));
 			{
-				std::vector<uint64_t> eA(64), eB(512), eC(512);
-				for (int x = 0; x < 8; ++x) for (int y = 0; y < 8; ++y) eA[x * 8 + y] = uint64_t(x) * y;
-				for (int k = 0; k < 8; ++k) for (int v = 0; v < 64; ++v) { eB[k * 64 + v] = uint64_t(v) * k; eC[k * 64 + v] = uint64_t(v) * k; }
-				std::vector<float2> tw8;
-				const auto A = twiddleTable(64, 64.0, eA), B = twiddleTable(512, 4096.0, eB), C = twiddleTable(512, 512.0, eC);
-				tw8.insert(tw8.end(), A.begin(), A.end()); tw8.insert(tw8.end(), B.begin(), B.end()); tw8.insert(tw8.end(), C.begin(), C.end());
-				SGZ_TRY(upload(h, tw8, &d.tw8));
 				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
 				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
 			}
@@ -1136,7 +1143,17 @@ extern "C"
 		if (h->stage < 1) return fail(SGZ_ESTATE, "call prepareTransform() first (TransformPair.h:123-124)");
 		SGZ_GUARD(h);
 		const uint32_t N = h->tab.N;
-		if (N <= 16384)
+		if (h->dev.tw8 && (N == 2048 || N == 4096 || N == 8192) && !std::getenv("SGZ_STAGED_FFT_GENERIC"))
+		{
+#define SGZ_FFT8(K1)                                                                                                          \
+			{                                                                                                                     \
+				SGZ_CUDA(cudaFuncSetAttribute(k_fft8<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Fft8Smem<K1>::bytes))); \
+				k_fft8<K1><<<h->nStreams, 64 * K1, Fft8Smem<K1>::bytes, h->stream>>>(h->dev, h->dCsf);                              \
+			}
+			if (N == 8192) SGZ_FFT8(8) else if (N == 4096) SGZ_FFT8(4) else SGZ_FFT8(2)
+#undef SGZ_FFT8
+		}
+		else if (N <= 16384)
 		{
 			const size_t smem = size_t(N) * sizeof(float2);
 			SGZ_CUDA(cudaFuncSetAttribute(k_fft_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
