@@ -239,7 +239,9 @@ namespace sgz
 	// ------------------------------------------------------------------------------------------
 	// staged kernel 2: doTransform — generic power-of-two forward FFT, natural order, in place
 	// ------------------------------------------------------------------------------------------
-	// N <= 16384: one CTA per stream, radix-2 DIT in shared memory
+	// N <= 16384 (other than the sizes k_fft8 takes): one CTA per stream, decimation in time in shared memory on the
+	// bit-reversed input, two radix-2 stages per sweep (one barrier and one round trip through shared memory for both);
+	// an odd log2 N starts with a single radix-2 stage
 	__global__ void __launch_bounds__(256) k_fft_smem(DeviceTables t, float2* __restrict__ csf)
 	{
 		extern __shared__ float2 sm[];
@@ -249,18 +251,36 @@ namespace sgz
 		for (uint32_t i = threadIdx.x; i < N; i += blockDim.x)
 			sm[__brev(i) >> (32 - bits)] = x[i];
 		__syncthreads();
-		for (uint32_t half = 1; half < N; half <<= 1)
+		uint32_t half = 1;
+		if (bits & 1)
 		{
-			const uint32_t step = (N >> 1) / half; // twiddle stride: W_(2 half)^j = W_N^(j step)
 			for (uint32_t b = threadIdx.x; b < (N >> 1); b += blockDim.x)
 			{
+				const float2 u = sm[2 * b], v = sm[2 * b + 1]; // W_2^0 = 1
+				sm[2 * b] = cadd(u, v);
+				sm[2 * b + 1] = csub(u, v);
+			}
+			__syncthreads();
+			half = 2;
+		}
+		for (; half < N; half <<= 2)
+		{
+			// stages of size 2 half and 4 half on the four elements base + {0, 1, 2, 3} half
+			const uint32_t step1 = (N >> 1) / half, step2 = step1 >> 1; // W_(2 half)^j = W_N^(j step1), W_(4 half)^j = W_N^(j step2)
+			for (uint32_t b = threadIdx.x; b < (N >> 2); b += blockDim.x)
+			{
 				const uint32_t j = b & (half - 1);
-				const uint32_t i0 = ((b - j) << 1) + j;
-				const float2 w = t.twN[j * step];
-				const float2 u = sm[i0];
-				const float2 v = cmul(sm[i0 + half], w);
-				sm[i0] = cadd(u, v);
-				sm[i0 + half] = csub(u, v);
+				const uint32_t base = ((b - j) << 2) + j;
+				const float2 w1 = t.twN[j * step1], w2 = t.twN[j * step2];
+				const float2 a0 = sm[base], a1 = cmul(sm[base + half], w1), a2 = sm[base + 2 * half], a3 = cmul(sm[base + 3 * half], w1);
+				const float2 u0 = cadd(a0, a1), u1 = csub(a0, a1);
+				const float2 u2 = cmul(cadd(a2, a3), w2), u3 = cmul(csub(a2, a3), w2);
+				sm[base] = cadd(u0, u2);
+				sm[base + 2 * half] = csub(u0, u2);
+				// the odd outputs take W_(4 half)^(j + half) = -i W_(4 half)^j: -i (x + i y) = y - i x
+				const float2 r3 = make_float2(u3.y, -u3.x);
+				sm[base + half] = cadd(u1, r3);
+				sm[base + 3 * half] = csub(u1, r3);
 			}
 			__syncthreads();
 		}
