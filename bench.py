@@ -253,7 +253,7 @@ def run_ours(args):
                          "algorithmic_bytes_per_frame": ALGO_BYTES_PER_FRAME,
                          "unique_bytes_per_frame": UNIQUE_BYTES_PER_FRAME,
                          "unique_bytes_frac": S * F * UNIQUE_BYTES_PER_FRAME / (kernel_ms * 1e-3) / 1e9 / peak,
-                         "kernel": "sgz::k_fused8<true,2,0>", "kernel_ms": kernel_ms},
+                         "kernel": "sgz::k_fused8<8,true,2,0>", "kernel_ms": kernel_ms},
             "e2e": {"value": frames_per_step / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(h_audio.numel() * 4), "d2h_bytes_per_step": int(h_out.numel() * 4),
                     "ms_per_step": e2e_ms, "steps": e2e_steps},
