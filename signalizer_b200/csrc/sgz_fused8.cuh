@@ -30,7 +30,13 @@
 		static constexpr int T = 64 * K1, M = 512 * K1, N = 2 * M;
 		static constexpr size_t xbufBytes = size_t(M) * 16;
 		static constexpr size_t twOffset = xbufBytes + 16;
+#if SGZ8_TW_POWERS >= 1
+		// with the powers derived in registers only A[8][8] (pass 3) and row 1 of C (the base W_512^v of pass 2) are
+		// read: 1 KB instead of 8.5 KB per CTA, which goes back to the L1 that the window and weight tables live in
+		static constexpr int twEntries = 64 + 64;
+#else
 		static constexpr int twEntries = 64 + 512 + 512;            // A[8][8] | B[8][64] | C[8][64]
+#endif
 		static constexpr size_t twBytes = size_t(twEntries) * sizeof(float2);
 		static constexpr size_t stateOffset = twOffset + twBytes;
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
@@ -283,11 +289,20 @@
 		extern __shared__ __align__(16) unsigned char smemRaw[];
 		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
 		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);
+#if SGZ8_TW_POWERS >= 1
+		float2* twB = nullptr;
+		float2* twC = twA;                                                // twC[64 + v] is W_512^v
+#else
 		float2* twB = twA + 64;
 		float2* twC = twB + 512;
+#endif
 		const int u = threadIdx.x;
 		float2* z = csf + uint64_t(blockIdx.x) * (t.N + 1);
+#if SGZ8_TW_POWERS >= 1
+		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i < 64 ? i : 64 + 512 + i]; // A, then row 1 of C
+#else
 		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i];
+#endif
 		const float2 wu = t.tw3[u];
 		float2 re[8], im[8];
 #pragma unroll
@@ -320,8 +335,13 @@
 		float4* stage = reinterpret_cast<float4*>(smemRaw);               // [4][T] next frame's newest half
 		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
 		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);  // [8][8]   W_64^(a b)
+#if SGZ8_TW_POWERS >= 1
+		float2* twB = nullptr;
+		float2* twC = twA;                                                // twC[64 + v] is W_512^v
+#else
 		float2* twB = twA + 64;                                           // [8][64]  W_M^(v k1)
 		float2* twC = twB + 512;                                          // [8][64]  W_512^(v k2)
+#endif
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
 
 		const int u = threadIdx.x;
@@ -341,7 +361,11 @@
 			mapSlope[i] = t.slope[i] * t.minFracRecip;
 			mapBaseR[i] = t.baseR[i];
 		}
+#if SGZ8_TW_POWERS >= 1
+		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i < 64 ? i : 64 + 512 + i]; // A, then row 1 of C
+#else
 		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i];
+#endif
 		const float2 wu = t.tw3[u]; // W_N^t, the thread-constant part of the last radix-2 twiddle
 		__syncthreads();
 
