@@ -21,6 +21,11 @@
 #ifndef SGZ8_TW_POWERS
 #define SGZ8_TW_POWERS 1
 #endif
+// SGZ8_STATES_GLOBAL: 1 = the peak-hold states stay in global memory (each thread owns fixed display points, so the
+// accesses are coalesced and private) instead of a 16 KB shared-memory copy
+#ifndef SGZ8_STATES_GLOBAL
+#define SGZ8_STATES_GLOBAL 0
+#endif
 	// K1 = radix of the first pass: 8 -> N = 8192 (M = 8^4, 512 threads); 4 -> N = 4096 (M = 4 x 8^3, 256 threads, whose
 	// first pass is two radix-4 butterflies per thread); 2 -> N = 2048 (128 threads, four radix-2 butterflies); passes 2-4
 	// and everything after are the same code
@@ -39,7 +44,11 @@
 #endif
 		static constexpr size_t twBytes = size_t(twEntries) * sizeof(float2);
 		static constexpr size_t stateOffset = twOffset + twBytes;
+#if SGZ8_STATES_GLOBAL
+		__host__ __device__ static size_t mapOffset(uint32_t) { return stateOffset; }
+#else
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
+#endif
 		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12; }
 	};
 	typedef Fused8GeomT<8> Fused8Geom;
@@ -342,7 +351,11 @@
 		float2* twB = twA + 64;                                           // [8][64]  W_M^(v k1)
 		float2* twC = twB + 512;                                          // [8][64]  W_512^(v k2)
 #endif
+#if SGZ8_STATES_GLOBAL
+		float2* st = a.states + uint64_t(blockIdx.x + a.firstStream) * 2 * t.P; // [2][P], read and written in place
+#else
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
+#endif
 
 		const int u = threadIdx.x;
 		const int stream = blockIdx.x + a.firstStream;
@@ -353,7 +366,9 @@
 		float* mapSlope = reinterpret_cast<float*>(mapPacked + P);
 		int* mapBaseR = reinterpret_cast<int*>(mapSlope + P);
 
+#if !SGZ8_STATES_GLOBAL
 		for (int i = u; i < 2 * P; i += T) st[i] = a.states[uint64_t(stream) * 2 * P + i];
+#endif
 		for (int i = u; i < P; i += T)
 		{
 			const int4 bm = t.binmap[i];
@@ -620,5 +635,7 @@
 			}
 		}
 		__syncthreads();
+#if !SGZ8_STATES_GLOBAL
 		for (int i = u; i < 2 * P; i += T) a.states[uint64_t(stream) * 2 * P + i] = st[i];
+#endif
 	}
