@@ -846,12 +846,6 @@ namespace
 		return SGZ_OK;
 	}
 
-	int copyOut(sgz_spectrum* h, void* dst, const void* src, size_t bytes, int mem)
-	{
-		SGZ_CUDA(cudaMemcpyAsync(dst, src, bytes, mem == SGZ_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
-		if (mem == SGZ_MEM_HOST) SGZ_CUDA(cudaStreamSynchronize(h->stream));
-		return SGZ_OK;
-	}
 }
 
 #define SGZ_GUARD(h)                                                                                        \
