@@ -141,6 +141,20 @@ def test_fused_frames_match_oracle(size, conf, bp):
         np.testing.assert_array_equal(g.get_results(k), got[:, -1, k])
 
 
+@pytest.mark.parametrize("window", [8192, 4096, 2048])
+@pytest.mark.parametrize("points", [300, 777, 2048])
+def test_fused_other_axis_sizes_and_hops_beyond_the_window(window, points):
+    # display-point counts that are not a multiple of the CTA size, and frames that do not overlap at all
+    cfg = _abi.default_config(window_size=window, axis_points=points)
+    S, F, hop = 3, 3, window + 37
+    g = TransformPairBatch(cfg, S)
+    assert g.info.fused_available == 1
+    audio = frames_case(cfg, S, F, hop)
+    got = g.process_frames(audio, hop, F)
+    want = OracleSpectrum(cfg, S).process_frames(audio, hop, F)
+    compare_frames(got, want, cfg, f"window {window} points {points}")
+
+
 @pytest.mark.parametrize("layout", [_abi.LAYOUT_INTERLEAVED, _abi.LAYOUT_PLANAR])
 @pytest.mark.parametrize("hop", [2048, 1023, 1])
 def test_fused_layouts_and_unaligned_hops(layout, hop):
