@@ -143,6 +143,21 @@ def test_fused_frames_match_oracle(size, conf, bp):
         np.testing.assert_array_equal(g.get_results(k), got[:, -1, k])
 
 
+@pytest.mark.parametrize("win", range(_abi.WIN_END))
+@pytest.mark.parametrize("shape", [_abi.WINSHAPE_SYMMETRIC, _abi.WINSHAPE_PERIODIC])
+@pytest.mark.parametrize("rate,window", [(44100.0, 4096), (96000.0, 8192), (48000.0, 2048)])
+def test_fused_window_families_and_sample_rates(win, shape, rate, window):
+    cfg = _abi.default_config(window_size=window, window_type=win, window_shape=shape, sample_rate=rate, min_freq=20.0)
+    cfg.pole[0], cfg.pole[1] = 0.5, 0.999
+    S, F, hop = 2, 4, window // 8
+    g = TransformPairBatch(cfg, S)
+    assert g.info.fused_available == 1
+    audio = frames_case(cfg, S, F, hop)
+    got = g.process_frames(audio, hop, F)
+    want = OracleSpectrum(cfg, S).process_frames(audio, hop, F)
+    compare_frames(got, want, cfg, f"window type {win} shape {shape} rate {rate}")
+
+
 VIEWS = [dict(view_scaling=_abi.VIEW_LINEAR), dict(view_left=0.2, view_right=0.4), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.03),
          dict(view_left=0.6, view_right=1.0, low_dbs=-60.0, high_dbs=6.0), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.9, view_right=1.0, slope_a=0.5, slope_b=0.02)]
 
