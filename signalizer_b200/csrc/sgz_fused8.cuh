@@ -290,8 +290,13 @@
 	template<int K1>
 	struct Fft8Smem { static constexpr size_t bytes = Fused8GeomT<K1>::twOffset + Fused8GeomT<K1>::twBytes; };
 
+	// Sub-transform q = blockIdx.y of `subs` interleaved ones: input element n at src[q + subs n], bin k to dst[q + subs k]
+	// (subs = 1: the whole transform, in place when src == dst - every thread has read its inputs before the first
+	// barrier inside the core, and stores only after the last).  With subs > 1 this finishes a transform of
+	// subs * 2 * M points whose first log2(subs) Stockham passes ran through global memory (k_fft_global_pass leaves
+	// exactly this layout).  The tables in `t` are those of the 2 M-point transform.
 	template<int K1>
-	__global__ void __launch_bounds__(64 * K1) k_fft8(DeviceTables t, float2* __restrict__ csf)
+	__global__ void __launch_bounds__(64 * K1) k_fft8(DeviceTables t, const float2* src, uint64_t srcStreamStride, float2* dst, uint64_t dstStreamStride, uint32_t subs)
 	{
 		typedef Fused8GeomT<K1> Gm;
 		constexpr int T = Gm::T, M = Gm::M;
@@ -306,7 +311,8 @@
 		float2* twC = twB + 512;
 #endif
 		const int u = threadIdx.x;
-		float2* z = csf + uint64_t(blockIdx.x) * (t.N + 1);
+		const float2* z = src + uint64_t(blockIdx.x) * srcStreamStride + blockIdx.y;
+		float2* y = dst + uint64_t(blockIdx.x) * dstStreamStride + blockIdx.y;
 #if SGZ8_TW_POWERS >= 1
 		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i < 64 ? i : 64 + 512 + i]; // A, then row 1 of C
 #else
@@ -317,8 +323,8 @@
 #pragma unroll
 		for (int e = 0; e < 8; ++e)
 		{
-			const int p = e * T + u;
-			const float2 ev = z[2 * p], od = z[2 * p + 1];
+			const uint64_t p = uint64_t(e * T + u) * 2;
+			const float2 ev = z[p * subs], od = z[(p + 1) * subs];
 			re[e] = make_float2(ev.x, od.x); im[e] = make_float2(ev.y, od.y);
 		}
 		__syncthreads(); // the twiddle tables are in place
@@ -326,9 +332,10 @@
 #pragma unroll
 		for (int k4 = 0; k4 < 8; ++k4)
 		{
-			const int slot = perm8(k4), k = u + T * k4;
-			z[k] = make_float2(re[slot].x, im[slot].x);
-			z[k + M] = make_float2(re[slot].y, im[slot].y);
+			const int slot = perm8(k4);
+			const uint64_t k = uint64_t(u + T * k4);
+			y[k * subs] = make_float2(re[slot].x, im[slot].x);
+			y[(k + M) * subs] = make_float2(re[slot].y, im[slot].y);
 		}
 	}
 

@@ -973,14 +973,14 @@ extern "C"
 			for (size_t k = 0; k < e.size(); ++k) e[k] = k;
 			SGZ_TRY(upload(h, twiddleTable(e.size(), double(t.N), e), &d.twN));
 		}
-		if (t.N == 2048 || t.N == 4096 || t.N == 8192)
+		if (t.N == 2048 || t.N == 4096 || t.N >= 8192)
 		{
-			// tables of the radix-8 register FFT (k_fused8 and the staged k_fft8): W_N^k for the last radix-2, and
-			// [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2)
-			const uint32_t M = t.N / 2;
+			// tables of the radix-8 register FFT (k_fused8 and the staged k_fft8): W_n^k for the last radix-2, and
+			// [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2); n = N, or 8192 for the sub-transforms of a larger N
+			const uint32_t subN = std::min<uint32_t>(t.N, 8192), M = subN / 2;
 			std::vector<uint64_t> e3(M);
 			for (uint32_t k = 0; k < M; ++k) e3[k] = k;
-			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(t.N), e3), &d.tw3));
+			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(subN), e3), &d.tw3));
 			std::vector<uint64_t> eA(64), eB(512), eC(512);
 			for (int x = 0; x < 8; ++x) for (int y = 0; y < 8; ++y) eA[x * 8 + y] = uint64_t(x) * y;
 			for (int k = 0; k < 8; ++k) for (int v = 0; v < 64; ++v) { eB[k * 64 + v] = uint64_t(v) * k; eC[k * 64 + v] = uint64_t(v) * k; }
@@ -1157,16 +1157,39 @@ extern "C"
 		if (h->stage < 1) return fail(SGZ_ESTATE, "call prepareTransform() first (TransformPair.h:123-124)");
 		SGZ_GUARD(h);
 		const uint32_t N = h->tab.N;
-		if (h->dev.tw8 && (N == 2048 || N == 4096 || N == 8192) && !std::getenv("SGZ_STAGED_FFT_GENERIC"))
-		{
-#define SGZ_FFT8(K1)                                                                                                          \
-			{                                                                                                                     \
-				SGZ_CUDA(cudaFuncSetAttribute(k_fft8<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Fft8Smem<K1>::bytes))); \
-				k_fft8<K1><<<h->nStreams, 64 * K1, Fft8Smem<K1>::bytes, h->stream>>>(h->dev, h->dCsf);                              \
-			}
-			if (N == 8192) SGZ_FFT8(8) else if (N == 4096) SGZ_FFT8(4) else SGZ_FFT8(2)
-#undef SGZ_FFT8
+		const bool generic = std::getenv("SGZ_STAGED_FFT_GENERIC") != nullptr;
+		const uint64_t csfStride = uint64_t(N) + 1, workStride = std::max<size_t>(N, size_t(2) * h->tab.P);
+#define SGZ_FFT8(K1, SRC, SSTRIDE, DST, DSTRIDE, SUBS)                                                                        \
+		{                                                                                                                     \
+			SGZ_CUDA(cudaFuncSetAttribute(k_fft8<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Fft8Smem<K1>::bytes))); \
+			k_fft8<K1><<<dim3(h->nStreams, SUBS), 64 * K1, Fft8Smem<K1>::bytes, h->stream>>>(h->dev, SRC, SSTRIDE, DST, DSTRIDE, SUBS); \
 		}
+		if (h->dev.tw8 && !generic && (N == 2048 || N == 4096 || N == 8192))
+		{
+			if (N == 8192) SGZ_FFT8(8, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+			else if (N == 4096) SGZ_FFT8(4, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+			else SGZ_FFT8(2, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+		}
+		else if (h->dev.tw8 && !generic && N > 8192 && N / 8192 <= 65535)
+		{
+			// N = subs * 8192: log2(subs) Stockham passes through global memory split the transform into `subs` interleaved
+			// 8192-point ones, which the register FFT then finishes straight into audioMemory (out of place when an odd
+			// number of passes left the data in the work buffer, in place otherwise): no copy back
+			const uint32_t subs = N / 8192;
+			int passes = 0; for (uint32_t v = subs; v > 1; v >>= 1) ++passes;
+			const float2* src = h->dCsf; float2* dst = h->dWork;
+			uint64_t sStride = csfStride, dStride = workStride;
+			const dim3 block(256), grid((N / 2 + 255) / 256, h->nStreams);
+			uint32_t n = N, st = 1;
+			for (int pass = 0; pass < passes; ++pass, n >>= 1, st <<= 1)
+			{
+				k_fft_global_pass<<<grid, block, 0, h->stream>>>(h->dev.twN, src, dst, N, n, st, sStride, dStride);
+				const float2* nsrc = dst; dst = const_cast<float2*>(src); src = nsrc;
+				std::swap(sStride, dStride);
+			}
+			SGZ_FFT8(8, src, sStride, h->dCsf, csfStride, subs)
+		}
+#undef SGZ_FFT8
 		else if (N <= 16384)
 		{
 			const size_t smem = size_t(N) * sizeof(float2);

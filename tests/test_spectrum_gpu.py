@@ -38,8 +38,9 @@ def run_staged(obj, audio, oracle=False):
 
 
 SIZES = [(4096, _abi.WIN_HANN, 1024), (8192, _abi.WIN_BLACKMAN_HARRIS, 1024), (700, _abi.WIN_BLACKMAN, 300),
-         (20, _abi.WIN_HANN, 40), (20000, _abi.WIN_NUTTALL, 512), (400, _abi.WIN_HANN, 128), (10000, _abi.WIN_HANN, 512)]
-# transform sizes 4096, 8192 (k_fft8), 1024, 32, 512, 16384 (shared-memory FFT, even and odd log2), 32768 (global passes)
+         (20, _abi.WIN_HANN, 40), (20000, _abi.WIN_NUTTALL, 512), (400, _abi.WIN_HANN, 128), (10000, _abi.WIN_HANN, 512), (40000, _abi.WIN_BLACKMAN_HARRIS, 700)]
+# transform sizes 4096, 8192 (k_fft8), 1024, 32, 512 (shared-memory FFT, even and odd log2), 16384, 32768, 65536 (1, 2, 3
+# global passes, then 8192-point sub-transforms in k_fft8)
 # (W = 12000 Hamming would also give 16384, but in the Phase configuration stream 1 has two bins, 3238 and 3241, whose
 # channel-2 magnitudes tie to 1.1e-6 inside one max-of-bins range: which one wins depends on the FFT's rounding,
 # tools/phase_probe.py)
