@@ -27,8 +27,8 @@
 #define SGZ8_STATES_GLOBAL 0
 #endif
 	// K1 = radix of the first pass: 8 -> N = 8192 (M = 8^4, 512 threads); 4 -> N = 4096 (M = 4 x 8^3, 256 threads, whose
-	// first pass is two radix-4 butterflies per thread); 2 -> N = 2048 (128 threads, four radix-2 butterflies); passes 2-4
-	// and everything after are the same code
+	// first pass is two radix-4 butterflies per thread); 2 -> N = 2048 (128 threads, four radix-2 butterflies); 1 -> N = 1024
+	// (64 threads, no first pass: M = 512 is the sub-transform itself); passes 2-4 and everything after are the same code
 	template<int K1>
 	struct Fused8GeomT
 	{
@@ -81,7 +81,7 @@
 	template<int K1>
 	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4)
 	{
-		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 == 8 ? k1 : K1 == 4 ? (k1 | ((d2 & 1) << 2)) : (k1 | ((d2 & 3) << 1))));
+		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 == 8 ? k1 : K1 == 4 ? (k1 | ((d2 & 1) << 2)) : K1 == 2 ? (k1 | ((d2 & 3) << 1)) : (d2 & 7)));
 	}
 
 	// Multiplies output k of a radix-8 butterfly (held in slot perm8(k)) by w1^k, k = 1..7.  The powers are
@@ -132,7 +132,7 @@
 			}
 #endif
 		}
-		else
+		else if constexpr (K1 > 1)
 		{
 			// G = 8 / K1 radix-K1 butterflies: loaded element e sits at pair index e T + u = n1 (M / K1) + v with
 			// n1 = e / G and v = u + T (e % G); output k1 of group g = e % G lands in slot g + G k1 and takes the twiddle
@@ -340,7 +340,7 @@
 	}
 
 	template<int K1, bool STEREO, int BINPOL, int MATRIX>
-	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : K1 == 4 ? 3 : 4)
+	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
 	k_fused8(DeviceTables t, FusedArgs a)
 	{
 		typedef Fused8GeomT<K1> Gm;

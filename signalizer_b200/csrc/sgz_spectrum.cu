@@ -807,6 +807,11 @@ namespace
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<8, true, 0>(h, a);
 			return h->tab.stateChannels == 2 ? launchFused8Binpol<8, true, 1>(h, a) : launchFused8Binpol<8, false, 1>(h, a);
 		}
+		if (h->fusedR3 == 2)
+		{
+			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<1, true, 0>(h, a);
+			return h->tab.stateChannels == 2 ? launchFused8Binpol<1, true, 1>(h, a) : launchFused8Binpol<1, false, 1>(h, a);
+		}
 		if (h->fusedR3 == 4)
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<2, true, 0>(h, a);
@@ -916,7 +921,7 @@ extern "C"
 			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
 			const int rc = buildTables(*cfg, h->tab);
 			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
-			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : 4) : 0;
+			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : h->tab.N == 2048 ? 4 : 2) : 0;
 			*out = h;
 			return SGZ_OK;
 		}
@@ -973,7 +978,7 @@ extern "C"
 			for (size_t k = 0; k < e.size(); ++k) e[k] = k;
 			SGZ_TRY(upload(h, twiddleTable(e.size(), double(t.N), e), &d.twN));
 		}
-		if (t.N == 2048 || t.N == 4096 || t.N >= 8192)
+		if (t.N == 1024 || t.N == 2048 || t.N == 4096 || t.N >= 8192)
 		{
 			// tables of the radix-8 register FFT (k_fused8 and the staged k_fft8): W_n^k for the last radix-2, and
 			// [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2); n = N, or 8192 for the sub-transforms of a larger N
@@ -992,7 +997,7 @@ extern "C"
 		h->fusedR3 = 0;
 		if (t.fusedOk && t.P <= 2048)
 		{
-			const int R3 = t.N == 8192 ? 16 : t.N == 4096 ? 8 : 4; // N = 2048 (R3 = 4) exists as k_fused8<2> only
+			const int R3 = t.N == 8192 ? 16 : t.N == 4096 ? 8 : t.N == 2048 ? 4 : 2; // N = 2048 / 1024 (R3 = 4 / 2) exist as k_fused8<2 / 1> only
 			const int T = 16 * R3, M = 16 * T;
 			// tw1 = [A | B]: A[k1][n2] = W_256^(n2 k1) (256 entries), B[k1][n3] = W_M^(n3 k1) (16 R3 entries)
 			std::vector<float2> tw1(256 + size_t(16) * R3);
@@ -1012,7 +1017,7 @@ extern "C"
 				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
 				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
 			}
-			h->fusedR3 = (R3 == 4 && !h->fusedVariant8) ? 0 : R3;
+			h->fusedR3 = (R3 <= 4 && !h->fusedVariant8) ? 0 : R3;
 			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
 		}
 		const size_t workPerStream = std::max<size_t>(t.N, size_t(2) * t.P);
@@ -1164,11 +1169,12 @@ extern "C"
 			SGZ_CUDA(cudaFuncSetAttribute(k_fft8<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Fft8Smem<K1>::bytes))); \
 			k_fft8<K1><<<dim3(h->nStreams, SUBS), 64 * K1, Fft8Smem<K1>::bytes, h->stream>>>(h->dev, SRC, SSTRIDE, DST, DSTRIDE, SUBS); \
 		}
-		if (h->dev.tw8 && !generic && (N == 2048 || N == 4096 || N == 8192))
+		if (h->dev.tw8 && !generic && (N == 1024 || N == 2048 || N == 4096 || N == 8192))
 		{
 			if (N == 8192) SGZ_FFT8(8, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
 			else if (N == 4096) SGZ_FFT8(4, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
-			else SGZ_FFT8(2, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+			else if (N == 2048) SGZ_FFT8(2, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+			else SGZ_FFT8(1, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
 		}
 		else if (h->dev.tw8 && !generic && N > 8192 && N / 8192 <= 65535)
 		{

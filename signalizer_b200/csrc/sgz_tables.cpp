@@ -265,7 +265,7 @@ namespace sgz
 			const uint32_t M = numBins;
 			uint32_t L = 1;
 			bool ok = cfg.algo == SGZ_ALGO_FFT && (isMono(cfg.configuration) || cfg.configuration == SGZ_CH_SEPARATE || cfg.configuration == SGZ_CH_MIDSIDE);
-			ok = ok && (N == 2048 || N == 4096 || N == 8192);
+			ok = ok && (N == 1024 || N == 2048 || N == 4096 || N == 8192);
 			const bool mono = isMono(cfg.configuration);
 			auto tapL = [&](std::ptrdiff_t i)
 			{

@@ -119,7 +119,8 @@ def compare_frames(got, want, cfg, what, peak_floor=None):
 
 
 FUSED_SIZES = [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (6000, _abi.WIN_HAMMING), (3000, _abi.WIN_BLACKMAN),
-               (2048, _abi.WIN_HANN), (1500, _abi.WIN_HAMMING)]   # N = 8192, 4096, 8192, 4096, 2048, 2048
+               (2048, _abi.WIN_HANN), (1500, _abi.WIN_HAMMING), (1024, _abi.WIN_BLACKMAN_HARRIS), (700, _abi.WIN_HANN)]
+# N = 8192, 4096, 8192, 4096, 2048, 2048, 1024, 1024
 
 
 @pytest.mark.parametrize("size", FUSED_SIZES)
@@ -165,7 +166,7 @@ VIEWS = [dict(view_scaling=_abi.VIEW_LINEAR), dict(view_left=0.2, view_right=0.4
 
 @pytest.mark.parametrize("view", VIEWS)
 @pytest.mark.parametrize("bp", INTERPS)
-@pytest.mark.parametrize("window", [8192, 4096, 2048])
+@pytest.mark.parametrize("window", [8192, 4096, 2048, 1024])
 def test_fused_views(view, bp, window):
     # zoomed / linear axes move the break between interpolated and max-of-bins points anywhere from "none" to "all",
     # which is what decides which shared-memory entries the fused kernels keep as magnitudes and which squared
@@ -183,7 +184,7 @@ def test_fused_views(view, bp, window):
     compare_frames(got, want, cfg, f"view {view} bp {bp} window {window} fused {g.info.fused_available}", peak_floor=peak_floor)
 
 
-@pytest.mark.parametrize("window", [8192, 4096, 2048])
+@pytest.mark.parametrize("window", [8192, 4096, 2048, 1024])
 @pytest.mark.parametrize("points", [300, 777, 2048])
 def test_fused_other_axis_sizes_and_hops_beyond_the_window(window, points):
     # display-point counts that are not a multiple of the CTA size, and frames that do not overlap at all

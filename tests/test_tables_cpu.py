@@ -101,5 +101,6 @@ def test_fused_eligibility():
     assert fused(configuration=_abi.CH_PHASE) == 0
     assert fused(configuration=_abi.CH_COMPLEX) == 0
     assert fused(window_size=2048) == 1                             # k_fused8<2>
-    assert fused(window_size=1024) == 0
+    assert fused(window_size=1024) == 1                             # k_fused8<1>
+    assert fused(window_size=512) == 0
     assert fused(algo=_abi.ALGO_RSNT) == 0
