@@ -350,6 +350,7 @@
 		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
 		float4* stage = reinterpret_cast<float4*>(smemRaw);               // [4][T] next frame's newest half
 		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
+		float2* z0c = reinterpret_cast<float2*>(smemRaw + Gm::xbufBytes + 8);  // Complex configuration: the halved DC bin (in the pad behind csfmag[N])
 		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);  // [8][8]   W_64^(a b)
 #if SGZ8_TW_POWERS >= 1
 		float2* twB = nullptr;
@@ -441,7 +442,7 @@
 				{
 					const float4 v = rv[n1];
 					const float2 w = wv[n1];
-					if constexpr (MATRIX == 0)
+					if constexpr (MATRIX != 1)
 					{
 						re[n1] = make_float2(v.x * w.x, v.z * w.y);
 						im[n1] = make_float2(v.y * w.x, v.w * w.y);
@@ -488,6 +489,23 @@
 					if ((k4 == 0 || linLimit > T) && j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
 					csfmag[j] = a2;
 					csfmag[N - j] = b2;
+				}
+			}
+			else if constexpr (MATRIX == 2)
+			{
+				// Complex configuration (TransformDSP.inl:993-1002): one channel over all N bins, csf[0] halved and left
+				// complex, every other bin replaced by its magnitude; csf[N] is the zero pad.  Entry 0 keeps its complex
+				// value in `z0c` for the few display points whose interpolation taps reach it.
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4)
+				{
+					const int slot = perm8(k4);
+					const int j = u + T * k4;
+					float2 zp = make_float2(re[slot].x, im[slot].x);
+					const float2 zq = make_float2(re[slot].y, im[slot].y);
+					if (j == 0) { zp.x *= 0.5f; zp.y *= 0.5f; *z0c = zp; csfmag[N] = 0.f; }
+					csfmag[j] = approxSqrt(cnorm(zp));
+					csfmag[j + M] = approxSqrt(cnorm(zq));
 				}
 			}
 			else
@@ -544,6 +562,15 @@
 						{
 							const float pos = __ldg(t.posL + x); const float fl = floorf(pos); const int k = int(fl); const float fr = pos - fl;
 							vL = csfTap(csfmag, k, N) * (1.f - fr) + csfTap(csfmag, k + 1, N) * fr;
+							if constexpr (MATRIX == 2)
+								if (k == 0 || k == -1)
+								{
+									// a tap on the complex DC bin: swap its magnitude for its value, then take the magnitude of the sum
+									const float w0 = k == 0 ? 1.f - fr : fr;
+									const float2 z0 = *z0c;
+									const float vr = vL + w0 * (z0.x - csfmag[0]), vi = w0 * z0.y;
+									vL = sqrtf(vr * vr + vi * vi);
+								}
 						}
 						if constexpr (STEREO)
 						{
@@ -575,6 +602,17 @@
 #pragma unroll
 							for (int k = 0; k < kLanczosTaps; ++k) vL += csfTap(csfmag, bl + k, N) * w[k];
 						}
+						if constexpr (MATRIX == 2)
+							if (bl <= 0 && bl > -kLanczosTaps)
+							{
+								// a tap on the complex DC bin (see the linear case)
+								float w0 = 0.f;
+#pragma unroll
+								for (int k = 0; k < kLanczosTaps; ++k) if (bl + k == 0) w0 = w[k];
+								const float2 z0 = *z0c;
+								const float vr = vL + w0 * (z0.x - csfmag[0]), vi = w0 * z0.y;
+								vL = sqrtf(vr * vr + vi * vi);
+							}
 						if constexpr (STEREO)
 						{
 							const float v[10] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y };

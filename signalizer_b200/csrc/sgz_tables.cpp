@@ -264,9 +264,11 @@ namespace sgz
 		{
 			const uint32_t M = numBins;
 			uint32_t L = 1;
-			bool ok = cfg.algo == SGZ_ALGO_FFT && (isMono(cfg.configuration) || cfg.configuration == SGZ_CH_SEPARATE || cfg.configuration == SGZ_CH_MIDSIDE);
+			const bool cplx = cfg.configuration == SGZ_CH_COMPLEX; // one channel over all N bins, magnitudes throughout
+			bool ok = cfg.algo == SGZ_ALGO_FFT && (isMono(cfg.configuration) || cplx || cfg.configuration == SGZ_CH_SEPARATE || cfg.configuration == SGZ_CH_MIDSIDE);
 			ok = ok && (N == 1024 || N == 2048 || N == 4096 || N == 8192);
 			const bool mono = isMono(cfg.configuration);
+			const bool single = mono || cplx;
 			auto tapL = [&](std::ptrdiff_t i)
 			{
 				if (i < 0 || i > std::ptrdiff_t(N)) return;
@@ -282,31 +284,32 @@ namespace sgz
 			{
 				if (t.mode[x] == 0)
 				{
-					if (cfg.bin_polation == SGZ_BIN_NONE) { tapL(t.first[x]); if (!mono) tapR(std::ptrdiff_t(N) - t.first[x]); }
+					if (cfg.bin_polation == SGZ_BIN_NONE) { tapL(t.first[x]); if (!single) tapR(std::ptrdiff_t(N) - t.first[x]); }
 					else if (cfg.bin_polation == SGZ_BIN_LINEAR)
 					{
 						const std::ptrdiff_t il = static_cast<std::ptrdiff_t>(std::floor(t.posL[x]));
 						const std::ptrdiff_t ir = static_cast<std::ptrdiff_t>(std::floor(t.posR[x]));
 						tapL(il); tapL(il + 1);
-						if (!mono) { tapR(ir); tapR(ir + 1); }
+						if (!single) { tapR(ir); tapR(ir + 1); }
 					}
 					else
 					{
 						for (int k = 0; k < kLanczosTaps; ++k)
 						{
 							tapL(t.baseL[x] + k);
-							if (!mono) tapR(t.baseR[x] + k);
+							if (!single) tapR(t.baseR[x] + k);
 						}
 					}
 				}
 				else
 				{
-					// scanned bins must stay inside [0, N/2]
-					if (t.first[x] < 0 || t.first[x] + t.count[x] - 1 > int32_t(M)) ok = false;
-					if (t.fallback[x] < 0 || t.fallback[x] > int32_t(M)) ok = false;
+					// scanned bins must stay inside [0, N/2] ([0, N] for Complex)
+					const int32_t top = cplx ? int32_t(N) : int32_t(M);
+					if (t.first[x] < 0 || t.first[x] + t.count[x] - 1 > top) ok = false;
+					if (t.fallback[x] < 0 || t.fallback[x] > top) ok = false;
 				}
 			}
-			t.linLimit = std::min<uint32_t>(L, M + 1);
+			t.linLimit = cplx ? N + 1 : std::min<uint32_t>(L, M + 1);
 			// the fused kernel packs the bin map into 32 bits and derives fallback = first + count - 1 and the
 			// channel-1 Lanczos base = first - 4; verify those identities and the field widths
 			uint32_t safeFrom = 0;
@@ -318,7 +321,7 @@ namespace sgz
 				{
 					if (t.baseL[x] != t.first[x] - (kLanczosSize - 1)) ok = false;
 					const bool inL = t.baseL[x] >= 0 && t.baseL[x] + kLanczosTaps - 1 <= int32_t(N);
-					const bool inR = mono || (t.baseR[x] >= 0 && t.baseR[x] + kLanczosTaps - 1 <= int32_t(N));
+					const bool inR = single || (t.baseR[x] >= 0 && t.baseR[x] + kLanczosTaps - 1 <= int32_t(N));
 					if (!(inL && inR)) safeFrom = x + 1;
 				}
 			}

@@ -124,7 +124,7 @@ FUSED_SIZES = [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (6000, _
 
 
 @pytest.mark.parametrize("size", FUSED_SIZES)
-@pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_RIGHT, _abi.CH_MERGE, _abi.CH_SIDE, _abi.CH_SEPARATE, _abi.CH_MIDSIDE])
+@pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_RIGHT, _abi.CH_MERGE, _abi.CH_SIDE, _abi.CH_SEPARATE, _abi.CH_MIDSIDE, _abi.CH_COMPLEX])
 @pytest.mark.parametrize("bp", INTERPS)
 def test_fused_frames_match_oracle(size, conf, bp):
     cfg = _abi.default_config(window_size=size[0], window_type=size[1], configuration=conf, bin_polation=bp)
@@ -158,6 +158,24 @@ def test_fused_window_families_and_sample_rates(win, shape, rate, window):
     got = g.process_frames(audio, hop, F)
     want = OracleSpectrum(cfg, S).process_frames(audio, hop, F)
     compare_frames(got, want, cfg, f"window type {win} shape {shape} rate {rate}")
+
+
+@pytest.mark.parametrize("bp", INTERPS)
+@pytest.mark.parametrize("window", [8192, 1024])
+@pytest.mark.parametrize("view", [dict(view_scaling=_abi.VIEW_LINEAR), dict(), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.002)])
+def test_fused_complex_configuration_keeps_the_dc_bin_complex(bp, window, view):
+    # Complex leaves csf[0] a complex number (halved) among magnitudes; with a DC offset on both channels the display
+    # points whose taps reach bin 0 depend on its imaginary part
+    cfg = _abi.default_config(window_size=window, configuration=_abi.CH_COMPLEX, bin_polation=bp, **view)
+    S, F, hop = 3, 2, window // 2
+    g = TransformPairBatch(cfg, S)
+    assert g.info.fused_available == 1
+    audio = frames_case(cfg, S, F, hop) * np.float32(0.2)
+    audio[..., 0] += np.float32(0.3); audio[..., 1] -= np.float32(0.2)
+    got = g.process_frames(audio, hop, F)
+    want = OracleSpectrum(cfg, S).process_frames(audio, hop, F)
+    compare_frames(got[..., :1], want[..., :1], cfg, f"complex dc {view} bp {bp}")
+    assert np.all(got[..., 1] == 0)
 
 
 VIEWS = [dict(view_scaling=_abi.VIEW_LINEAR), dict(view_left=0.2, view_right=0.4), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.03),
@@ -245,9 +263,9 @@ def test_device_resident_buffers_and_stream():
 
 
 def test_staged_fallback_for_unfused_configs_in_process_frames():
-    for conf in (_abi.CH_PHASE, _abi.CH_COMPLEX):
-        cfg = _abi.default_config(window_size=2048, configuration=conf, axis_points=256)
-        S, F, hop = 2, 3, 512
+    for conf, size in ((_abi.CH_PHASE, 2048), (_abi.CH_COMPLEX, 512)):   # no fused kernel for Phase, nor below 1024 points
+        cfg = _abi.default_config(window_size=size, configuration=conf, axis_points=256)
+        S, F, hop = 2, 3, size // 4
         g = TransformPairBatch(cfg, S)
         assert g.info.fused_available == 0
         audio = frames_case(cfg, S, F, hop)
