@@ -339,6 +339,16 @@
 		}
 	}
 
+	// ---- Phase configuration (MATRIX == 3): the display works on the complex split spectra themselves ----
+	// csf as the reference's magnitude pass sees it once the `np` lowest indices and their mirrors have been replaced by
+	// their magnitudes (the lazy in-place normalisation of TransformDSP.inl:709-727)
+	__device__ __forceinline__ float2 phaseSeen(float2 v, int i, int N, int np)
+	{
+		return (i < np || i > N - np) ? make_float2(sqrtf(v.x * v.x + v.y * v.y), 0.f) : v;
+	}
+	__device__ __forceinline__ float2 phaseEntry(const float2* csf, int i, int N) { return (i >= 0 && i <= N) ? csf[i] : make_float2(0.f, 0.f); }
+	__device__ __forceinline__ float mag2(float2 v) { return sqrtf(v.x * v.x + v.y * v.y); }
+
 	template<int K1, bool STEREO, int BINPOL, int MATRIX>
 	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
 	k_fused8(DeviceTables t, FusedArgs a)
@@ -350,6 +360,7 @@
 		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
 		float4* stage = reinterpret_cast<float4*>(smemRaw);               // [4][T] next frame's newest half
 		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
+		float2* csfC = reinterpret_cast<float2*>(smemRaw);                 // Phase configuration: [N+1] complex csf = the whole xbuf (+8 B of the pad)
 		float2* z0c = reinterpret_cast<float2*>(smemRaw + Gm::xbufBytes + 8);  // Complex configuration: the halved DC bin (in the pad behind csfmag[N])
 		float2* twA = reinterpret_cast<float2*>(smemRaw + Gm::twOffset);  // [8][8]   W_64^(a b)
 #if SGZ8_TW_POWERS >= 1
@@ -457,7 +468,38 @@
 			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u);
 			__syncthreads(); // every pass-4 read of xbuf is done before zm / csfmag overwrite it
 
-			if constexpr (STEREO)
+			if constexpr (MATRIX == 3)
+			{
+				// Phase keeps the split spectra complex: A (channel 1) at csfC[j], B (channel 2) at csfC[N - j], the whole
+				// exchange buffer (TransformDSP.inl:649-652 + separateTransformsIPL).  Z[j + M] is parked at slot M + j first;
+				// the partner Z[N - j] of bin j then sits at slot N - j, which is also where B_j goes - every upper slot is
+				// read and rewritten by one thread only, and the lower half (the A's) holds nothing that is still needed.
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4) csfC[M + u + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
+				__syncthreads();
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4)
+				{
+					const int slot = perm8(k4);
+					const int j = u + T * k4;
+					const float2 zj = make_float2(re[slot].x, im[slot].x);
+					if (k4 == 0 && j == 0)
+					{
+						const float2 ny = make_float2(re[slot].y, im[slot].y); // Z[M]
+						csfC[N] = make_float2(zj.y * 0.5f, 0.f);
+						csfC[0] = make_float2(zj.x * 0.5f, 0.f);
+						csfC[M] = make_float2(ny.x * 0.5f, ny.y * 0.5f);
+						continue;
+					}
+					const float2 zn = csfC[N - j];
+					float2 A = make_float2((zj.x + zn.x) * 0.5f, (zj.y - zn.y) * 0.5f);
+					const float2 D = make_float2((zj.x - zn.x) * 0.5f, (zj.y + zn.y) * 0.5f);
+					if (k4 == 7 && j == M - 1) { A.x *= 0.5f; A.y *= 0.5f; } // csf[(N >> 1) - 1] *= 0.5
+					csfC[j] = A;
+					csfC[N - j] = make_float2(D.y, -D.x);
+				}
+			}
+			else 			if constexpr (STEREO)
 			{
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4) zm[u + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
@@ -531,7 +573,7 @@
 
 			// newest half of the next frame -> lower half of the exchange buffer, behind the display points
 			staged = false;
-			if (vec4 && f + 1 < a.nFrames)
+			if (MATRIX != 3 && vec4 && f + 1 < a.nFrames) // (Phase: the display still reads the whole buffer)
 			{
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -549,6 +591,96 @@
 			{
 				const uint32_t pkd = mapPacked[x];
 				const int first = int(pkd & 0xFFFFu), count = int((pkd >> 16) & 0x7FFFu);
+				if constexpr (MATRIX == 3)
+				{
+					// Phase (TransformDSP.inl:643-853 + :1395-1424): wsp[2x] = invSize (|A| + |B|) from the partly
+					// normalised view of csf, wsp[2x+1] = 1 - |A + B| / (|A| + |B|) from the raw one
+					const float invSize = t.invSize;
+					float mid, cancelOut;
+					if (!(pkd >> 31))
+					{
+						float2 iL, iR, mL, mR;
+						if constexpr (BINPOL == SGZ_BIN_NONE)
+						{
+							iL = csfC[first]; iR = csfC[N - first]; mL = iL; mR = iR;
+						}
+						else if constexpr (BINPOL == SGZ_BIN_LINEAR)
+						{
+							const int np = __ldg(t.phaseNormPos + x);
+							{
+								const float pos = __ldg(t.posL + x); const float fl = floorf(pos); const int k = int(fl); const float fr = pos - fl;
+								const float2 a0 = phaseEntry(csfC, k, N), b0 = phaseEntry(csfC, k + 1, N);
+								const float2 a1 = phaseSeen(a0, k, N, np), b1 = phaseSeen(b0, k + 1, N, np);
+								iL = make_float2(a0.x * (1.f - fr) + b0.x * fr, a0.y * (1.f - fr) + b0.y * fr);
+								mL = make_float2(a1.x * (1.f - fr) + b1.x * fr, a1.y * (1.f - fr) + b1.y * fr);
+							}
+							{
+								const float pos = __ldg(t.posR + x); const float fl = floorf(pos); const int k = int(fl); const float fr = pos - fl;
+								const float2 a0 = phaseEntry(csfC, k, N), b0 = phaseEntry(csfC, k + 1, N);
+								const float2 a1 = phaseSeen(a0, k, N, np), b1 = phaseSeen(b0, k + 1, N, np);
+								iR = make_float2(a0.x * (1.f - fr) + b0.x * fr, a0.y * (1.f - fr) + b0.y * fr);
+								mR = make_float2(a1.x * (1.f - fr) + b1.x * fr, a1.y * (1.f - fr) + b1.y * fr);
+							}
+						}
+						else
+						{
+							const int np = __ldg(t.phaseNormPos + x);
+							const int bl = first - (kLanczosSize - 1), br = mapBaseR[x];
+							const float4* wl4 = reinterpret_cast<const float4*>(t.wL + size_t(x) * kLanczosStride);
+							const float4* wr4 = reinterpret_cast<const float4*>(t.wR + size_t(x) * kLanczosStride);
+							const float4 w0 = __ldg(wl4), w1 = __ldg(wl4 + 1), w2 = __ldg(wl4 + 2);
+							const float4 r0 = __ldg(wr4), r1 = __ldg(wr4 + 1), r2 = __ldg(wr4 + 2);
+							const float w[10] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y };
+							const float v[10] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y };
+							iL = iR = mL = mR = make_float2(0.f, 0.f);
+#pragma unroll
+							for (int k = 0; k < kLanczosTaps; ++k)
+							{
+								const float2 a0 = phaseEntry(csfC, bl + k, N), b0 = phaseEntry(csfC, br + k, N);
+								const float2 a1 = phaseSeen(a0, bl + k, N, np), b1 = phaseSeen(b0, br + k, N, np);
+								iL.x += a0.x * w[k]; iL.y += a0.y * w[k]; mL.x += a1.x * w[k]; mL.y += a1.y * w[k];
+								iR.x += b0.x * v[k]; iR.y += b0.y * v[k]; mR.x += b1.x * v[k]; mR.y += b1.y * v[k];
+							}
+						}
+						const float cancellation = invSize * mag2(make_float2(iL.x + iR.x, iL.y + iR.y));
+						const float midRaw = invSize * (mag2(iL) + mag2(iR));
+						cancelOut = 1.f - (midRaw > 0.f ? cancellation / midRaw : 0.f);
+						mid = invSize * (mag2(mL) + mag2(mR));
+					}
+					else
+					{
+						const int np = t.phaseNormFinal;
+						int maxBin = 0; float maxValue = 0.f;
+						for (int c = 0; c < count; ++c)
+						{
+							const int off = first + c;
+							const float m = fmaxf(cnorm(phaseSeen(csfC[off], off, N, np)), cnorm(phaseSeen(csfC[N - off], N - off, N, np)));
+							if (m > maxValue) { maxValue = m; maxBin = off; }
+						}
+						const float2 l = phaseSeen(csfC[maxBin], maxBin, N, np), r = phaseSeen(csfC[N - maxBin], N - maxBin, N, np);
+						const float interference = invSize * mag2(make_float2(l.x + r.x, l.y + r.y));
+						mid = invSize * (mag2(l) + mag2(r));
+						cancelOut = 1.f - (mid > 0.f ? interference / mid : 0.f);
+					}
+					const float mag = mid * 0.5f;
+					float ph = cancelOut;
+					const float sm = mapSlope[x];
+					const float phasePoles[2] = { t.phasePole0, t.phasePole1 };
+#pragma unroll
+					for (int k = 0; k < 2; ++k)
+					{
+						float2 sv = st[k * P + x];
+						sv.x = fmaxf(sv.x * poles[k], mag);
+						ph *= mag; // inside the graph loop, as the reference (:1417)
+						sv.y = ph + phasePoles[k] * (sv.y - ph);
+						st[k * P + x] = sv;
+						float2 res;
+						res.x = fmaxf(__log2f(sm * sv.x) * t.deltaYLn2, t.lowerClip);
+						res.y = fmaxf(__log2f(sm * sv.y) * t.deltaYLn2, t.lowerClip);
+						stg_stream_f2(resOut + k * P + x, res);
+					}
+					continue;
+				}
 				float vL, vR = 0.f;
 				if (!(pkd >> 31))
 				{

@@ -806,24 +806,28 @@ namespace
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<8, true, 0>(h, a);
 			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<8, false, 2>(h, a);
+			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<8, true, 3>(h, a);
 			return h->tab.stateChannels == 2 ? launchFused8Binpol<8, true, 1>(h, a) : launchFused8Binpol<8, false, 1>(h, a);
 		}
 		if (h->fusedR3 == 2)
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<1, true, 0>(h, a);
 			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<1, false, 2>(h, a);
+			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<1, true, 3>(h, a);
 			return h->tab.stateChannels == 2 ? launchFused8Binpol<1, true, 1>(h, a) : launchFused8Binpol<1, false, 1>(h, a);
 		}
 		if (h->fusedR3 == 4)
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<2, true, 0>(h, a);
 			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<2, false, 2>(h, a);
+			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<2, true, 3>(h, a);
 			return h->tab.stateChannels == 2 ? launchFused8Binpol<2, true, 1>(h, a) : launchFused8Binpol<2, false, 1>(h, a);
 		}
 		if (h->fusedR3 == 8 && h->fusedVariant8)
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<4, true, 0>(h, a);
 			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<4, false, 2>(h, a);
+			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<4, true, 3>(h, a);
 			return h->tab.stateChannels == 2 ? launchFused8Binpol<4, true, 1>(h, a) : launchFused8Binpol<4, false, 1>(h, a);
 		}
 		const bool stereo = h->tab.stateChannels == 2;
@@ -1021,7 +1025,7 @@ extern "C"
 				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
 				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
 			}
-			h->fusedR3 = ((R3 <= 4 || cfg->configuration == SGZ_CH_COMPLEX) && !h->fusedVariant8) ? 0 : R3; // k_fused8 only
+			h->fusedR3 = ((R3 <= 4 || cfg->configuration == SGZ_CH_COMPLEX || cfg->configuration == SGZ_CH_PHASE) && !h->fusedVariant8) ? 0 : R3; // k_fused8 only
 			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
 		}
 		const size_t workPerStream = std::max<size_t>(t.N, size_t(2) * t.P);

@@ -265,7 +265,8 @@ namespace sgz
 			const uint32_t M = numBins;
 			uint32_t L = 1;
 			const bool cplx = cfg.configuration == SGZ_CH_COMPLEX; // one channel over all N bins, magnitudes throughout
-			bool ok = cfg.algo == SGZ_ALGO_FFT && (isMono(cfg.configuration) || cplx || cfg.configuration == SGZ_CH_SEPARATE || cfg.configuration == SGZ_CH_MIDSIDE);
+			bool ok = cfg.algo == SGZ_ALGO_FFT && (isMono(cfg.configuration) || cplx || cfg.configuration == SGZ_CH_SEPARATE || cfg.configuration == SGZ_CH_MIDSIDE
+				|| cfg.configuration == SGZ_CH_PHASE);
 			ok = ok && (N == 1024 || N == 2048 || N == 4096 || N == 8192);
 			const bool mono = isMono(cfg.configuration);
 			const bool single = mono || cplx;
@@ -316,7 +317,8 @@ namespace sgz
 			for (uint32_t x = 0; x < P; ++x)
 			{
 				if (t.first[x] < 0 || t.first[x] > 0xFFFF || t.count[x] < 0 || t.count[x] > 0x7FFF) ok = false;
-				if (t.mode[x] == 1 && t.fallback[x] != t.first[x] + t.count[x] - 1) ok = false;
+				// (Phase starts its scan from bin 0 instead, TransformDSP.inl:789: the fused kernel does the same)
+				if (t.mode[x] == 1 && t.fallback[x] != (phase ? 0 : t.first[x] + t.count[x] - 1)) ok = false;
 				if (t.mode[x] == 0 && cfg.bin_polation == SGZ_BIN_LANCZOS)
 				{
 					if (t.baseL[x] != t.first[x] - (kLanczosSize - 1)) ok = false;

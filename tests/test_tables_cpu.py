@@ -98,7 +98,7 @@ def test_fused_eligibility():
     assert fused(window_size=4096, window_type=_abi.WIN_HANN) == 1  # C1
     assert fused(window_size=6000) == 1                             # zero-padded to 8192
     assert fused(configuration=_abi.CH_LEFT) == 1
-    assert fused(configuration=_abi.CH_PHASE) == 0
+    assert fused(configuration=_abi.CH_PHASE) == 1
     assert fused(configuration=_abi.CH_COMPLEX) == 1
     assert fused(window_size=2048) == 1                             # k_fused8<2>
     assert fused(window_size=1024) == 1                             # k_fused8<1>
