@@ -61,6 +61,24 @@ def c1():
     return out_lines
 
 
+def c3_variants():
+    """BASELINE config 3's geometry with the two configurations that have their own fused epilogues."""
+    out_lines = []
+    for name, conf in (("Phase", _abi.CH_PHASE), ("Complex", _abi.CH_COMPLEX)):
+        cfg = _abi.default_config(configuration=conf)
+        S, F, hop, W = 1024, 64, 2048, 8192
+        n = signals.frames_length(W, hop, F)
+        d = torch.from_numpy(tile(signals.batch(48, n), S)).cuda()
+        p = TransformPairBatch(cfg, S)
+        p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+        out = torch.empty((S, F, 2, 1024, 2), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: p.process_frames(d, hop, F, out=out), torch.cuda.synchronize)
+        frames = S * F
+        out_lines.append({"config": f"C3 geometry, {name} configuration: 1024 streams x 8192-pt Blackman-Harris, hop 2048, Lanczos, 1024 log bins",
+                          "frames_per_s": frames / ms * 1e3, "ms": ms, "achieved_GBps": frames * 114688 / ms / 1e6, "frac_hbm": frames * 114688 / ms / 1e6 / PEAK})
+    return out_lines
+
+
 def c2():
     cfg = _abi.default_config(algo=_abi.ALGO_RSNT, window_size=8192, window_type=_abi.WIN_HANN)
     out = []
@@ -125,7 +143,7 @@ def c5():
 
 
 if __name__ == "__main__":
-    for fn in (c1, c2, c4, c4_colour, c5):
+    for fn in (c1, c3_variants, c2, c4, c4_colour, c5):
         r = fn()
         for line in (r if isinstance(r, list) else [r]):
             print(json.dumps(line), flush=True)
