@@ -28,7 +28,8 @@
 #endif
 	// K1 = radix of the first pass: 8 -> N = 8192 (M = 8^4, 512 threads); 4 -> N = 4096 (M = 4 x 8^3, 256 threads, whose
 	// first pass is two radix-4 butterflies per thread); 2 -> N = 2048 (128 threads, four radix-2 butterflies); 1 -> N = 1024
-	// (64 threads, no first pass: M = 512 is the sub-transform itself); passes 2-4 and everything after are the same code
+	// (64 threads, no first pass: M = 512 is the sub-transform itself); 16 -> N = 16384 (1024 threads, the radix-16 first
+	// pass split over thread pairs with one extra exchange); passes 2-4 and everything after are the same code
 	template<int K1>
 	struct Fused8GeomT
 	{
@@ -81,7 +82,7 @@
 	template<int K1>
 	__device__ __forceinline__ int phys8(int k1, int d2, int d3, int d4)
 	{
-		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 == 8 ? k1 : K1 == 4 ? (k1 | ((d2 & 1) << 2)) : K1 == 2 ? (k1 | ((d2 & 3) << 1)) : (d2 & 7)));
+		return k1 * 512 + d2 * 64 + d3 * 8 + (d4 ^ (K1 >= 8 ? (k1 & 7) : K1 == 4 ? (k1 | ((d2 & 1) << 2)) : K1 == 2 ? (k1 | ((d2 & 3) << 1)) : (d2 & 7)));
 	}
 
 	// Multiplies output k of a radix-8 butterfly (held in slot perm8(k)) by w1^k, k = 1..7.  The powers are
@@ -115,82 +116,142 @@
 	{
 		constexpr int T = Fused8GeomT<K1>::T;
 
-		if constexpr (K1 == 8)
+		if constexpr (K1 <= 8)
 		{
-			dft8q(re, im);
-#if SGZ8_TW_POWERS
-			applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
-#else
+			if constexpr (K1 == 8)
 			{
-				const int n2 = u >> 6, v = u & 63;
-#pragma unroll
-				for (int k1 = 1; k1 < 8; ++k1)
+				dft8q(re, im);
+	#if SGZ8_TW_POWERS
+				applyTwiddlePowers(cmul(wu, wu), re, im); // W_M^((64 n2 + v) k1) = (W_M^u)^k1 and W_M^u = (W_N^u)^2
+	#else
 				{
-					const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
-					mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
+					const int n2 = u >> 6, v = u & 63;
+	#pragma unroll
+					for (int k1 = 1; k1 < 8; ++k1)
+					{
+						const float2 w = cmul(twA[k1 * 8 + n2], twB[k1 * 64 + v]);
+						mulTwiddleP(re[perm8(k1)], im[perm8(k1)], make_float4(w.x, w.x, w.y, w.y));
+					}
+				}
+	#endif
+			}
+			else if constexpr (K1 > 1)
+			{
+				// G = 8 / K1 radix-K1 butterflies: loaded element e sits at pair index e T + u = n1 (M / K1) + v with
+				// n1 = e / G and v = u + T (e % G); output k1 of group g = e % G lands in slot g + G k1 and takes the twiddle
+				// (W_M^v)^k1, where W_M^v = W_M^u W_8^g because M / T = 8
+				constexpr int G = 8 / K1;
+				constexpr float R = 0.70710678118654752440f;
+				const float2 wa = cmul(wu, wu); // W_M^u
+	#pragma unroll
+				for (int g = 0; g < G; ++g)
+				{
+					float2 w1 = wa;
+					if (g == 1) w1 = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));   // W_8^1 = (1 - i) / sqrt 2
+					if (g == 2) w1 = make_float2(wa.y, -wa.x);                            // W_8^2 = -i
+					if (g == 3) w1 = make_float2(R * (wa.y - wa.x), -R * (wa.x + wa.y));  // W_8^3 = -(1 + i) / sqrt 2
+					if constexpr (K1 == 4)
+					{
+						radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
+						const float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1);
+						mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
+						mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
+						mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
+					}
+					else
+					{
+						const float2 ar = re[g], ai = im[g], br = re[g + 4], bi = im[g + 4];
+						re[g] = add2(ar, br); im[g] = add2(ai, bi);
+						re[g + 4] = sub2(ar, br); im[g + 4] = sub2(ai, bi);
+						mulTwiddleP(re[g + 4], im[g + 4], make_float4(w1.x, w1.x, w1.y, w1.y));
+					}
 				}
 			}
-#endif
-		}
-		else if constexpr (K1 > 1)
-		{
-			// G = 8 / K1 radix-K1 butterflies: loaded element e sits at pair index e T + u = n1 (M / K1) + v with
-			// n1 = e / G and v = u + T (e % G); output k1 of group g = e % G lands in slot g + G k1 and takes the twiddle
-			// (W_M^v)^k1, where W_M^v = W_M^u W_8^g because M / T = 8
-			constexpr int G = 8 / K1;
-			constexpr float R = 0.70710678118654752440f;
-			const float2 wa = cmul(wu, wu); // W_M^u
-#pragma unroll
-			for (int g = 0; g < G; ++g)
+			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+			if constexpr (K1 == 8)
 			{
-				float2 w1 = wa;
-				if (g == 1) w1 = make_float2(R * (wa.x + wa.y), R * (wa.y - wa.x));   // W_8^1 = (1 - i) / sqrt 2
-				if (g == 2) w1 = make_float2(wa.y, -wa.x);                            // W_8^2 = -i
-				if (g == 3) w1 = make_float2(R * (wa.y - wa.x), -R * (wa.x + wa.y));  // W_8^3 = -(1 + i) / sqrt 2
-				if constexpr (K1 == 4)
+				const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
+	#pragma unroll
+				for (int k1 = 0; k1 < 8; ++k1)
 				{
-					radix4p(re[g], im[g], re[g + 2], im[g + 2], re[g + 4], im[g + 4], re[g + 6], im[g + 6]);
-					const float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1);
-					mulTwiddleP(re[g + 2], im[g + 2], make_float4(w1.x, w1.x, w1.y, w1.y));
-					mulTwiddleP(re[g + 4], im[g + 4], make_float4(w2.x, w2.x, w2.y, w2.y));
-					mulTwiddleP(re[g + 6], im[g + 6], make_float4(w3.x, w3.x, w3.y, w3.y));
-				}
-				else
-				{
-					const float2 ar = re[g], ai = im[g], br = re[g + 4], bi = im[g + 4];
-					re[g] = add2(ar, br); im[g] = add2(ai, bi);
-					re[g + 4] = sub2(ar, br); im[g + 4] = sub2(ai, bi);
-					mulTwiddleP(re[g + 4], im[g + 4], make_float4(w1.x, w1.x, w1.y, w1.y));
-				}
-			}
-		}
-		__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
-		if constexpr (K1 == 8)
-		{
-			const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
-#pragma unroll
-			for (int k1 = 0; k1 < 8; ++k1)
-			{
-				const float2 r = re[perm8(k1)], i = im[perm8(k1)];
-				xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
-			}
-		}
-		else
-		{
-			constexpr int G = 8 / K1;
-#pragma unroll
-			for (int g = 0; g < G; ++g)
-			{
-				const int v = u + T * g, n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
-#pragma unroll
-				for (int k1 = 0; k1 < K1; ++k1)
-				{
-					const float2 r = re[g + G * k1], i = im[g + G * k1];
+					const float2 r = re[perm8(k1)], i = im[perm8(k1)];
 					xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 			}
+			else
+			{
+				constexpr int G = 8 / K1;
+	#pragma unroll
+				for (int g = 0; g < G; ++g)
+				{
+					const int v = u + T * g, n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
+	#pragma unroll
+					for (int k1 = 0; k1 < K1; ++k1)
+					{
+						const float2 r = re[g + G * k1], i = im[g + G * k1];
+						xbuf[phys8<K1>(k1, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+					}
+				}
+			}
+			__syncthreads();
 		}
-		__syncthreads();
+		else
+		{
+			// K1 = 16 (N = 16384, 1024 threads): the radix-16 first pass is shared by the thread pair (u, u ^ 512).  Loaded
+			// element e sits at pair index e T + u = (2 e + h) 512 + v with h = u >> 9, v = u & 511, so thread h holds the
+			// n1 of parity h: it takes their DFT8 Y_h[k], the pair swaps them through the exchange buffer, and thread h
+			// forms the outputs k1 = k + 8 h:  X[k] = Y_0[k] + W_16^k Y_1[k],  X[k + 8] = Y_0[k] - W_16^k Y_1[k].
+			const int h = u >> 9, v = u & 511; // h is uniform over a warp
+			dft8q(re, im);
+			if (h)
+			{
+#pragma unroll
+				for (int k = 1; k < 8; ++k)
+				{
+					const float2 w = w32(2 * k);
+					mulTwiddleP(re[perm8(k)], im[perm8(k)], make_float4(w.x, w.x, w.y, w.y));
+				}
+			}
+			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+#pragma unroll
+			for (int k = 0; k < 8; ++k)
+			{
+				const float2 r = re[perm8(k)], i = im[perm8(k)];
+				xbuf[k * T + u] = make_float4(r.x, r.y, i.x, i.y);
+			}
+			__syncthreads();
+#pragma unroll
+			for (int k = 0; k < 8; ++k)
+			{
+				const float4 p = xbuf[k * T + (u ^ 512)];
+				const float2 pr = make_float2(p.x, p.y), pi = make_float2(p.z, p.w);
+				float2& r = re[perm8(k)]; float2& i = im[perm8(k)];
+				if (!h) { r = add2(r, pr); i = add2(i, pi); }
+				else { r = sub2(pr, r); i = sub2(pi, i); }
+			}
+			// pass-1 twiddle (W_M^v)^(k + 8 h), with W_M^v = (W_N^v)^2 and W_N^v = W_N^u W_32^(-h)
+			const float2 c1 = w32(1);
+			const float2 wv = h ? cmul(wu, make_float2(c1.x, -c1.y)) : wu;
+			const float2 w1 = cmul(wv, wv);
+			if (h)
+			{
+				const float2 w2 = cmul(w1, w1), w4 = cmul(w2, w2), w8 = cmul(w4, w4);
+#pragma unroll
+				for (int k = 0; k < 8; ++k) mulTwiddleP(re[k], im[k], make_float4(w8.x, w8.x, w8.y, w8.y));
+			}
+			applyTwiddlePowers(w1, re, im);
+			__syncthreads(); // every partner read is done before the buffer is rewritten
+			{
+				const int n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
+#pragma unroll
+				for (int k = 0; k < 8; ++k)
+				{
+					const float2 r = re[perm8(k)], i = im[perm8(k)];
+					xbuf[phys8<K1>(8 * h + k, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
+				}
+			}
+			__syncthreads();
+		}
 
 		// ---- pass 2 (in place): thread (k1 n3 n4), DFT8 over n2, twiddle W_512^(v k2) ----
 		{
@@ -350,7 +411,7 @@
 	__device__ __forceinline__ float mag2(float2 v) { return sqrtf(v.x * v.x + v.y * v.y); }
 
 	template<int K1, bool STEREO, int BINPOL, int MATRIX>
-	__global__ void __launch_bounds__(64 * K1, K1 == 8 ? 2 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
+	__global__ void __launch_bounds__(64 * K1, K1 == 16 ? 1 : K1 == 8 ? 2 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
 	k_fused8(DeviceTables t, FusedArgs a)
 	{
 		typedef Fused8GeomT<K1> Gm;

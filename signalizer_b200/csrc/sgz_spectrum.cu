@@ -802,6 +802,13 @@ namespace
 
 	int launchFused(sgz_spectrum* h, const FusedArgs& a)
 	{
+		if (h->fusedR3 == 32)
+		{
+			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<16, true, 0>(h, a);
+			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<16, false, 2>(h, a);
+			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<16, true, 3>(h, a);
+			return h->tab.stateChannels == 2 ? launchFused8Binpol<16, true, 1>(h, a) : launchFused8Binpol<16, false, 1>(h, a);
+		}
 		if (h->fusedR3 == 16 && h->fusedVariant8)
 		{
 			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<8, true, 0>(h, a);
@@ -929,7 +936,7 @@ extern "C"
 			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
 			const int rc = buildTables(*cfg, h->tab);
 			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
-			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : h->tab.N == 2048 ? 4 : 2) : 0;
+			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 16384 ? 32 : h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : h->tab.N == 2048 ? 4 : 2) : 0;
 			*out = h;
 			return SGZ_OK;
 		}
@@ -989,8 +996,8 @@ extern "C"
 		if (t.N == 1024 || t.N == 2048 || t.N == 4096 || t.N >= 8192)
 		{
 			// tables of the radix-8 register FFT (k_fused8 and the staged k_fft8): W_n^k for the last radix-2, and
-			// [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2); n = N, or 8192 for the sub-transforms of a larger N
-			const uint32_t subN = std::min<uint32_t>(t.N, 8192), M = subN / 2;
+			// [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2); n = N, or 16384 for the sub-transforms of a larger N
+			const uint32_t subN = std::min<uint32_t>(t.N, 16384), M = subN / 2;
 			std::vector<uint64_t> e3(M);
 			for (uint32_t k = 0; k < M; ++k) e3[k] = k;
 			SGZ_TRY(upload(h, twiddleTable(e3.size(), double(subN), e3), &d.tw3));
@@ -1005,7 +1012,7 @@ extern "C"
 		h->fusedR3 = 0;
 		if (t.fusedOk && t.P <= 2048)
 		{
-			const int R3 = t.N == 8192 ? 16 : t.N == 4096 ? 8 : t.N == 2048 ? 4 : 2; // N = 2048 / 1024 (R3 = 4 / 2) exist as k_fused8<2 / 1> only
+			const int R3 = t.N == 16384 ? 32 : t.N == 8192 ? 16 : t.N == 4096 ? 8 : t.N == 2048 ? 4 : 2; // R3 = 32, 4, 2 (N = 16384, 2048, 1024) exist as k_fused8 only
 			const int T = 16 * R3, M = 16 * T;
 			// tw1 = [A | B]: A[k1][n2] = W_256^(n2 k1) (256 entries), B[k1][n3] = W_M^(n3 k1) (16 R3 entries)
 			std::vector<float2> tw1(256 + size_t(16) * R3);
@@ -1025,7 +1032,7 @@ extern "C"
 				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
 				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
 			}
-			h->fusedR3 = ((R3 <= 4 || cfg->configuration == SGZ_CH_COMPLEX || cfg->configuration == SGZ_CH_PHASE) && !h->fusedVariant8) ? 0 : R3; // k_fused8 only
+			h->fusedR3 = ((R3 <= 4 || R3 == 32 || cfg->configuration == SGZ_CH_COMPLEX || cfg->configuration == SGZ_CH_PHASE) && !h->fusedVariant8) ? 0 : R3; // k_fused8 only
 			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
 		}
 		const size_t workPerStream = std::max<size_t>(t.N, size_t(2) * t.P);
@@ -1177,19 +1184,20 @@ extern "C"
 			SGZ_CUDA(cudaFuncSetAttribute(k_fft8<K1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Fft8Smem<K1>::bytes))); \
 			k_fft8<K1><<<dim3(h->nStreams, SUBS), 64 * K1, Fft8Smem<K1>::bytes, h->stream>>>(h->dev, SRC, SSTRIDE, DST, DSTRIDE, SUBS); \
 		}
-		if (h->dev.tw8 && !generic && (N == 1024 || N == 2048 || N == 4096 || N == 8192))
+		if (h->dev.tw8 && !generic && (N == 1024 || N == 2048 || N == 4096 || N == 8192 || N == 16384))
 		{
-			if (N == 8192) SGZ_FFT8(8, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+			if (N == 16384) SGZ_FFT8(16, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
+			else if (N == 8192) SGZ_FFT8(8, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
 			else if (N == 4096) SGZ_FFT8(4, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
 			else if (N == 2048) SGZ_FFT8(2, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
 			else SGZ_FFT8(1, h->dCsf, csfStride, h->dCsf, csfStride, 1u)
 		}
-		else if (h->dev.tw8 && !generic && N > 8192 && N / 8192 <= 65535)
+		else if (h->dev.tw8 && !generic && N > 16384 && N / 16384 <= 65535)
 		{
-			// N = subs * 8192: log2(subs) Stockham passes through global memory split the transform into `subs` interleaved
-			// 8192-point ones, which the register FFT then finishes straight into audioMemory (out of place when an odd
+			// N = subs * 16384: log2(subs) Stockham passes through global memory split the transform into `subs` interleaved
+			// 16384-point ones, which the register FFT then finishes straight into audioMemory (out of place when an odd
 			// number of passes left the data in the work buffer, in place otherwise): no copy back
-			const uint32_t subs = N / 8192;
+			const uint32_t subs = N / 16384;
 			int passes = 0; for (uint32_t v = subs; v > 1; v >>= 1) ++passes;
 			const float2* src = h->dCsf; float2* dst = h->dWork;
 			uint64_t sStride = csfStride, dStride = workStride;
@@ -1201,7 +1209,7 @@ extern "C"
 				const float2* nsrc = dst; dst = const_cast<float2*>(src); src = nsrc;
 				std::swap(sStride, dStride);
 			}
-			SGZ_FFT8(8, src, sStride, h->dCsf, csfStride, subs)
+			SGZ_FFT8(16, src, sStride, h->dCsf, csfStride, subs)
 		}
 #undef SGZ_FFT8
 		else if (N <= 16384)

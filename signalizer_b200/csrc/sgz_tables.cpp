@@ -267,7 +267,7 @@ namespace sgz
 			const bool cplx = cfg.configuration == SGZ_CH_COMPLEX; // one channel over all N bins, magnitudes throughout
 			bool ok = cfg.algo == SGZ_ALGO_FFT && (isMono(cfg.configuration) || cplx || cfg.configuration == SGZ_CH_SEPARATE || cfg.configuration == SGZ_CH_MIDSIDE
 				|| cfg.configuration == SGZ_CH_PHASE);
-			ok = ok && (N == 1024 || N == 2048 || N == 4096 || N == 8192);
+			ok = ok && (N == 1024 || N == 2048 || N == 4096 || N == 8192 || N == 16384);
 			const bool mono = isMono(cfg.configuration);
 			const bool single = mono || cplx;
 			auto tapL = [&](std::ptrdiff_t i)

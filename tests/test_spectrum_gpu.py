@@ -119,8 +119,9 @@ def compare_frames(got, want, cfg, what, peak_floor=None):
 
 
 FUSED_SIZES = [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (6000, _abi.WIN_HAMMING), (3000, _abi.WIN_BLACKMAN),
-               (2048, _abi.WIN_HANN), (1500, _abi.WIN_HAMMING), (1024, _abi.WIN_BLACKMAN_HARRIS), (700, _abi.WIN_HANN)]
-# N = 8192, 4096, 8192, 4096, 2048, 2048, 1024, 1024
+               (2048, _abi.WIN_HANN), (1500, _abi.WIN_HAMMING), (1024, _abi.WIN_BLACKMAN_HARRIS), (700, _abi.WIN_HANN),
+               (16384, _abi.WIN_BLACKMAN_HARRIS), (10000, _abi.WIN_HANN)]
+# N = 8192, 4096, 8192, 4096, 2048, 2048, 1024, 1024, 16384, 16384
 
 
 @pytest.mark.parametrize("size", FUSED_SIZES)
@@ -179,7 +180,7 @@ def test_fused_complex_configuration_keeps_the_dc_bin_complex(bp, window, view):
 
 
 @pytest.mark.parametrize("bp", INTERPS)
-@pytest.mark.parametrize("size", [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (3000, _abi.WIN_BLACKMAN), (2048, _abi.WIN_HANN), (1024, _abi.WIN_HAMMING)])
+@pytest.mark.parametrize("size", [(8192, _abi.WIN_BLACKMAN_HARRIS), (4096, _abi.WIN_HANN), (3000, _abi.WIN_BLACKMAN), (2048, _abi.WIN_HANN), (1024, _abi.WIN_HAMMING), (16384, _abi.WIN_HANN)])
 @pytest.mark.parametrize("view", [dict(), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.1)])
 def test_fused_phase_configuration(bp, size, view):
     """Phase: magnitude sum (graph .x) against the oracle like every other configuration; the smoothed
@@ -238,7 +239,7 @@ def test_fused_views(view, bp, window):
     compare_frames(got, want, cfg, f"view {view} bp {bp} window {window} fused {g.info.fused_available}", peak_floor=peak_floor)
 
 
-@pytest.mark.parametrize("window", [8192, 4096, 2048, 1024])
+@pytest.mark.parametrize("window", [16384, 8192, 4096, 2048, 1024])
 @pytest.mark.parametrize("points", [300, 777, 2048])
 def test_fused_other_axis_sizes_and_hops_beyond_the_window(window, points):
     # display-point counts that are not a multiple of the CTA size, and frames that do not overlap at all

@@ -103,4 +103,6 @@ def test_fused_eligibility():
     assert fused(window_size=2048) == 1                             # k_fused8<2>
     assert fused(window_size=1024) == 1                             # k_fused8<1>
     assert fused(window_size=512) == 0
+    assert fused(window_size=16384) == 1                            # k_fused8<16>
+    assert fused(window_size=20000) == 0
     assert fused(algo=_abi.ALGO_RSNT) == 0
