@@ -24,6 +24,10 @@
 		const float* audio; uint64_t nSamples; uint64_t streamStride; int layout;
 		uint32_t hop, nFrames;
 		uint32_t firstStream, numStreams; // the launch covers streams [firstStream, firstStream + numStreams)
+		// k_fused8 only, frame-parallel mode: blockIdx.y selects a run of `framesPerChunk` frames (0 = all frames in one
+		// CTA) and its own state slot - `states` is then [S][stateSlots][2][P], slot 0 holding the stream's real state and
+		// the others zero; k_hold_fixup afterwards carries the peak hold from run to run
+		uint32_t framesPerChunk, stateSlots;
 		float2* states;  // [S][2][P]
 		float2* results; // [S][F][2][P]
 	};

@@ -23,6 +23,9 @@
 #endif
 // SGZ8_STATES_GLOBAL: 1 = the peak-hold states stay in global memory (each thread owns fixed display points, so the
 // accesses are coalesced and private) instead of a 16 KB shared-memory copy
+#ifndef SGZ8_FRAME_PARALLEL
+#define SGZ8_FRAME_PARALLEL 1
+#endif
 #ifndef SGZ8_STATES_GLOBAL
 #define SGZ8_STATES_GLOBAL 0
 #endif
@@ -432,7 +435,7 @@
 		float2* twC = twB + 512;                                          // [8][64]  W_512^(v k2)
 #endif
 #if SGZ8_STATES_GLOBAL
-		float2* st = a.states + uint64_t(blockIdx.x + a.firstStream) * 2 * t.P; // [2][P], read and written in place
+		float2* st = a.states + (uint64_t(blockIdx.x + a.firstStream) * (a.stateSlots ? a.stateSlots : 1u) + (a.stateSlots ? blockIdx.y : 0u)) * 2 * t.P; // [2][P], in place
 #else
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
 #endif
@@ -447,7 +450,8 @@
 		int* mapBaseR = reinterpret_cast<int*>(mapSlope + P);
 
 #if !SGZ8_STATES_GLOBAL
-		for (int i = u; i < 2 * P; i += T) st[i] = a.states[uint64_t(stream) * 2 * P + i];
+		float2* stateSlot = a.states + (uint64_t(stream) * (a.stateSlots ? a.stateSlots : 1u) + (a.stateSlots ? blockIdx.y : 0u)) * 2 * P;
+		for (int i = u; i < 2 * P; i += T) st[i] = stateSlot[i];
 #endif
 		for (int i = u; i < P; i += T)
 		{
@@ -469,7 +473,9 @@
 		const int W = int(t.W);
 		bool staged = false;
 
-		for (uint32_t f = 0; f < a.nFrames; ++f)
+		const uint32_t fBegin = (SGZ8_FRAME_PARALLEL && a.framesPerChunk) ? blockIdx.y * a.framesPerChunk : 0u;
+		const uint32_t fEnd = (SGZ8_FRAME_PARALLEL && a.framesPerChunk) ? min(fBegin + a.framesPerChunk, a.nFrames) : a.nFrames;
+		for (uint32_t f = fBegin; f < fEnd; ++f)
 		{
 			float2 re[8], im[8];
 			const uint64_t start = uint64_t(f) * a.hop;
@@ -634,7 +640,7 @@
 
 			// newest half of the next frame -> lower half of the exchange buffer, behind the display points
 			staged = false;
-			if (MATRIX != 3 && vec4 && f + 1 < a.nFrames) // (Phase: the display still reads the whole buffer)
+			if (MATRIX != 3 && vec4 && f + 1 < fEnd) // (Phase: the display still reads the whole buffer)
 			{
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -874,6 +880,67 @@
 		}
 		__syncthreads();
 #if !SGZ8_STATES_GLOBAL
-		for (int i = u; i < 2 * P; i += T) a.states[uint64_t(stream) * 2 * P + i] = st[i];
+		for (int i = u; i < 2 * P; i += T) stateSlot[i] = st[i];
 #endif
+	}
+
+	// Second half of the frame-parallel mode.  Every run of frames went through k_fused8 from a zero state (the first
+	// run from the stream's real one), so its results already hold the peak hold of its OWN frames.  What is missing is
+	// the hold carried in from earlier runs: s_f = max(s_(f-1) pole, m_f) unrolls to max(carry pole^k, local_f), float
+	// multiplication by the pole and the dB scale are both monotone, hence
+	//     result_f = max(local result_f, scale(carry pole^k))        bit for bit what one CTA per stream computes.
+	// One thread per display point walks the runs in order: decays the carried state frame by frame, raises the stored
+	// results where it still dominates, and at the end of a run merges in that run's own final state.
+	__global__ void __launch_bounds__(128) k_hold_fixup(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ slotStates,
+		float2* __restrict__ states, uint32_t nFrames, uint32_t framesPerChunk, uint32_t slots, int stereo)
+	{
+		const int P = int(t.P);
+		const int x = blockIdx.x * blockDim.x + threadIdx.x;
+		if (x >= P) return;
+		const uint64_t s = blockIdx.y;
+		const float sm = t.slope[x] * t.minFracRecip;
+		const float poles[2] = { t.pole0, t.pole1 };
+		const float2* slot = slotStates + (s * slots) * 2 * P + x;
+		float2 carry[2] = { slot[0], slot[P] }; // final state of run 0 = the true state there
+		for (uint32_t c = 1; c < slots; ++c)
+		{
+			const uint32_t f0 = c * framesPerChunk, f1 = min(f0 + framesPerChunk, nFrames);
+			float2* frame = results + ((s * nFrames + f0) * 2) * P + x;
+			// four frames per trip: their stored results are fetched together (the walk is latency-bound, the loads are
+			// independent of the carried state)
+			for (uint32_t f = f0; f < f1; f += 4, frame += 8 * P)
+			{
+				float2 res[4][2];
+#pragma unroll
+				for (int j = 0; j < 4; ++j)
+					if (f + j < f1) { res[j][0] = frame[uint64_t(j) * 2 * P]; res[j][1] = frame[uint64_t(j) * 2 * P + P]; }
+#pragma unroll
+				for (int j = 0; j < 4; ++j)
+				{
+					if (f + j >= f1) break;
+#pragma unroll
+					for (int k = 0; k < 2; ++k)
+					{
+						carry[k].x *= poles[k];
+						res[j][k].x = fmaxf(res[j][k].x, fmaxf(__log2f(sm * carry[k].x) * t.deltaYLn2, t.lowerClip));
+						if (stereo)
+						{
+							carry[k].y *= poles[k];
+							res[j][k].y = fmaxf(res[j][k].y, fmaxf(__log2f(sm * carry[k].y) * t.deltaYLn2, t.lowerClip));
+						}
+						frame[uint64_t(j) * 2 * P + k * P] = res[j][k];
+					}
+				}
+			}
+			const float2* own = slot + uint64_t(c) * 2 * P;
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+			{
+				const float2 l = own[k * P];
+				carry[k].x = fmaxf(carry[k].x, l.x);
+				if (stereo) carry[k].y = fmaxf(carry[k].y, l.y);
+			}
+		}
+		states[(s * 2 + 0) * P + x] = carry[0];
+		states[(s * 2 + 1) * P + x] = carry[1];
 	}

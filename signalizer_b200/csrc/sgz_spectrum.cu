@@ -33,6 +33,8 @@ namespace sgz
 {
 	// which N = 8192 fused kernel runs unless SGZ_FUSED_VARIANT=8|16 overrides it (set from measurement)
 	constexpr bool kDefaultVariant8 = true;
+	constexpr uint32_t kFrameParallelCtas = 592;   // frame-parallel mode aims at four CTAs per SM slot pair (148 SMs x 2 x 2)
+	constexpr uint32_t kFrameParallelMinRun = 4;   // ... but never cuts a stream into runs shorter than this many frames
 
 	// ------------------------------------------------------------------------------------------
 	// error plumbing
@@ -679,6 +681,8 @@ struct sgz_spectrum
 	std::vector<cudaEvent_t> events;
 	bool fusedAttrSet{ false };
 	size_t fusedSmem{ 0 };
+	uint32_t launchGridY{ 1 }; // frame runs per stream of the next k_fused8 launch (frame-parallel mode)
+	float2* dSlotStates{ nullptr }; size_t slotStatesBytes{ 0 }; // [S][runs][2][P] per-run peak-hold states of that mode
 	void* dTrack{ nullptr }; // frequency tracker: [S] bounds in, [S] records out
 	// device-resident audio history (sgz_spectrum_history_*): per stream a ring of `ringCapacity` stereo
 	// samples stored twice back to back ([S][2 C] float2), so that any run of <= C samples ending at the
@@ -778,7 +782,7 @@ namespace
 	int launchFused8Binpol(sgz_spectrum* h, const FusedArgs& a)
 	{
 		const size_t smem = Fused8GeomT<K1>::smemBytes(h->tab.P);
-		const dim3 grid(a.numStreams), block(Fused8GeomT<K1>::T);
+		const dim3 grid(a.numStreams, h->launchGridY), block(Fused8GeomT<K1>::T);
 #define SGZ_LAUNCH8(BP)                                                                                             \
 		{                                                                                                           \
 			auto kern = k_fused8<K1, STEREO, BP, MATRIX>;                                                           \
@@ -913,6 +917,7 @@ extern "C"
 			for (void* p : h->allocations) cudaFree(p);
 			if (h->dRing) cudaFree(h->dRing);
 			if (h->dTrack) cudaFree(h->dTrack);
+			if (h->dSlotStates) cudaFree(h->dSlotStates);
 			if (h->dAudioStage) cudaFree(h->dAudioStage);
 			if (h->dResultStage) cudaFree(h->dResultStage);
 			if (h->dResPartial) cudaFree(h->dResPartial);
@@ -1604,8 +1609,48 @@ extern "C"
 			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
 			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(dRes);
 			a.firstStream = 0; a.numStreams = h->nStreams;
+			// few streams, many frames (a long recording rather than a wall of channels): one CTA per stream would leave the
+			// GPU idle, so the frames of a stream are cut into runs that CTAs process side by side; the only frame-to-frame
+			// dependency, the peak hold, is carried from run to run afterwards by k_hold_fixup
+			uint32_t chunks = 1;
+			if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
+			{
+				const uint32_t wanted = (kFrameParallelCtas + h->nStreams - 1) / h->nStreams;
+				chunks = std::max<uint32_t>(1, std::min<uint32_t>(wanted, n_frames / kFrameParallelMinRun));
+				if (chunks > 65535) chunks = 65535;
+			}
+			uint32_t slots = 1;
+			if (chunks > 1)
+			{
+				a.framesPerChunk = (n_frames + chunks - 1) / chunks;
+				slots = (n_frames + a.framesPerChunk - 1) / a.framesPerChunk;
+			}
+			if (slots > 1)
+			{
+				// per-run state slots: slot 0 of every stream starts from the stream's state, the others from zero
+				const size_t slotBytes = size_t(2) * P * sizeof(float2), need = size_t(h->nStreams) * slots * slotBytes;
+				if (h->slotStatesBytes < need)
+				{
+					if (h->dSlotStates) { SGZ_CUDA(cudaStreamSynchronize(h->stream)); cudaFree(h->dSlotStates); h->dSlotStates = nullptr; h->slotStatesBytes = 0; }
+					SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dSlotStates), need));
+					h->slotStatesBytes = need;
+				}
+				SGZ_CUDA(cudaMemsetAsync(h->dSlotStates, 0, need, h->stream));
+				SGZ_CUDA(cudaMemcpy2DAsync(h->dSlotStates, slots * slotBytes, h->dStates, slotBytes, slotBytes, h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+				a.states = h->dSlotStates; a.stateSlots = slots;
+				h->launchGridY = slots;
+			}
+			else a.framesPerChunk = 0;
 			rc = launchFused(h, a);
+			h->launchGridY = 1;
 			if (rc != SGZ_OK) return rc;
+			if (slots > 1)
+			{
+				const dim3 grid((P + 127) / 128, h->nStreams);
+				k_hold_fixup<<<grid, 128, 0, h->stream>>>(h->dev, reinterpret_cast<float2*>(dRes), h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots,
+					(h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0); // the STEREO argument launchFused picks
+				SGZ_CUDA(cudaGetLastError());
+			}
 			// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
 			SGZ_CUDA(cudaMemcpy2DAsync(h->dResults, size_t(2) * P * sizeof(float2), dRes + size_t(n_frames - 1) * 2 * P * 2,
 				size_t(n_frames) * 2 * P * sizeof(float2), size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));

@@ -215,6 +215,35 @@ def test_fused_phase_configuration(bp, size, view):
         assert np.max(np.abs(g.get_results(k)[:, -2:, 0] - staged.get_results(k)[:, -2:, 0])) < 1e-4
 
 
+@pytest.mark.parametrize("kw", [dict(), dict(window_size=4096, configuration=_abi.CH_LEFT, bin_polation=_abi.BIN_LINEAR),
+                                dict(window_size=2048, configuration=_abi.CH_COMPLEX), dict(window_size=16384, configuration=_abi.CH_MIDSIDE, bin_polation=_abi.BIN_NONE)])
+def test_frame_parallel_mode_gives_the_same_bits(kw, monkeypatch):
+    """few streams x many frames: the frames of a stream are spread over CTAs and the peak hold is applied by a scan
+    afterwards; results, states and the handle's last results must equal the one-CTA-per-stream launch bit for bit,
+    also across two calls (state carried)"""
+    import torch
+    cfg = _abi.default_config(**kw)
+    S, F, hop = 2, 37, cfg.window_size // 8
+    audio = frames_case(cfg, S, 2 * F, hop)
+    first, second = audio[:, :signals.frames_length(cfg.window_size, hop, F)], audio[:, F * hop:]
+    runs = {}
+    for mode in ("parallel", "serial"):
+        if mode == "serial":
+            monkeypatch.setenv("SGZ_NO_FRAME_PARALLEL", "1")
+        g = TransformPairBatch(cfg, S)
+        d1, d2 = torch.from_numpy(np.ascontiguousarray(first)).cuda(), torch.from_numpy(np.ascontiguousarray(second)).cuda()
+        a = g.process_frames(d1, hop, F)   # device buffers: the call returns before the kernels have run, so the inputs stay alive
+        b = g.process_frames(d2, hop, F)
+        g.synchronize()
+        a, b = a.cpu().numpy(), b.cpu().numpy()
+        runs[mode] = (a, b, g.get_states(0), g.get_states(1), g.get_results(0), g.get_results(1))
+    for x, y in zip(runs["parallel"], runs["serial"]):
+        np.testing.assert_array_equal(x, y)
+    want = OracleSpectrum(cfg, S).process_frames(first, hop, F)
+    used = 2 if cfg.configuration in (_abi.CH_SEPARATE, _abi.CH_MIDSIDE) else 1
+    compare_frames(runs["parallel"][0][..., :used], want[..., :used], cfg, "frame-parallel vs oracle")
+
+
 VIEWS = [dict(view_scaling=_abi.VIEW_LINEAR), dict(view_left=0.2, view_right=0.4), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.03),
          dict(view_left=0.6, view_right=1.0, low_dbs=-60.0, high_dbs=6.0), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.9, view_right=1.0, slope_a=0.5, slope_b=0.02)]
 
