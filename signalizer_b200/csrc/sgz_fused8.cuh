@@ -889,58 +889,74 @@
 	// the hold carried in from earlier runs: s_f = max(s_(f-1) pole, m_f) unrolls to max(carry pole^k, local_f), float
 	// multiplication by the pole and the dB scale are both monotone, hence
 	//     result_f = max(local result_f, scale(carry pole^k))        bit for bit what one CTA per stream computes.
-	// One thread per display point walks the runs in order: decays the carried state frame by frame, raises the stored
-	// results where it still dominates, and at the end of a run merges in that run's own final state.
-	__global__ void __launch_bounds__(128) k_hold_fixup(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ slotStates,
-		float2* __restrict__ states, uint32_t nFrames, uint32_t framesPerChunk, uint32_t slots, int stereo)
+	// k_hold_carry: one thread per display point walks the runs in order WITHOUT touching the results - it decays the
+	// carried state once per frame (the same chain of roundings), leaves in each run's slot the state that run starts
+	// from, and merges in the run's own final state.  k_hold_apply: one thread per (run, display point) then raises the
+	// stored results of its run where the decaying carry still dominates - that part is fully parallel.
+	__global__ void __launch_bounds__(128) k_hold_carry(DeviceTables t, float2* __restrict__ slotStates, float2* __restrict__ states, uint32_t nFrames,
+		uint32_t framesPerChunk, uint32_t slots, int stereo)
 	{
 		const int P = int(t.P);
 		const int x = blockIdx.x * blockDim.x + threadIdx.x;
 		if (x >= P) return;
 		const uint64_t s = blockIdx.y;
-		const float sm = t.slope[x] * t.minFracRecip;
 		const float poles[2] = { t.pole0, t.pole1 };
-		const float2* slot = slotStates + (s * slots) * 2 * P + x;
+		float2* slot = slotStates + (s * slots) * 2 * P + x;
 		float2 carry[2] = { slot[0], slot[P] }; // final state of run 0 = the true state there
+		float2 own[2] = { make_float2(0.f, 0.f), make_float2(0.f, 0.f) };
+		if (slots > 1) { own[0] = slot[uint64_t(2) * P]; own[1] = slot[uint64_t(2) * P + P]; }
 		for (uint32_t c = 1; c < slots; ++c)
 		{
-			const uint32_t f0 = c * framesPerChunk, f1 = min(f0 + framesPerChunk, nFrames);
-			float2* frame = results + ((s * nFrames + f0) * 2) * P + x;
-			// four frames per trip: their stored results are fetched together (the walk is latency-bound, the loads are
-			// independent of the carried state)
-			for (uint32_t f = f0; f < f1; f += 4, frame += 8 * P)
+			float2* mine = slot + uint64_t(c) * 2 * P;
+			float2 next[2] = { own[0], own[1] };
+			if (c + 1 < slots) { next[0] = mine[uint64_t(2) * P]; next[1] = mine[uint64_t(2) * P + P]; } // fetched ahead of the decay loop
+			mine[0] = carry[0]; mine[P] = carry[1];          // what run c starts from
+			const uint32_t len = min(framesPerChunk, nFrames - c * framesPerChunk);
+			for (uint32_t f = 0; f < len; ++f)
 			{
-				float2 res[4][2];
 #pragma unroll
-				for (int j = 0; j < 4; ++j)
-					if (f + j < f1) { res[j][0] = frame[uint64_t(j) * 2 * P]; res[j][1] = frame[uint64_t(j) * 2 * P + P]; }
-#pragma unroll
-				for (int j = 0; j < 4; ++j)
-				{
-					if (f + j >= f1) break;
-#pragma unroll
-					for (int k = 0; k < 2; ++k)
-					{
-						carry[k].x *= poles[k];
-						res[j][k].x = fmaxf(res[j][k].x, fmaxf(__log2f(sm * carry[k].x) * t.deltaYLn2, t.lowerClip));
-						if (stereo)
-						{
-							carry[k].y *= poles[k];
-							res[j][k].y = fmaxf(res[j][k].y, fmaxf(__log2f(sm * carry[k].y) * t.deltaYLn2, t.lowerClip));
-						}
-						frame[uint64_t(j) * 2 * P + k * P] = res[j][k];
-					}
-				}
+				for (int k = 0; k < 2; ++k) { carry[k].x *= poles[k]; if (stereo) carry[k].y *= poles[k]; }
 			}
-			const float2* own = slot + uint64_t(c) * 2 * P;
 #pragma unroll
 			for (int k = 0; k < 2; ++k)
 			{
-				const float2 l = own[k * P];
-				carry[k].x = fmaxf(carry[k].x, l.x);
-				if (stereo) carry[k].y = fmaxf(carry[k].y, l.y);
+				carry[k].x = fmaxf(carry[k].x, own[k].x);
+				if (stereo) carry[k].y = fmaxf(carry[k].y, own[k].y);
+				own[k] = next[k];
 			}
 		}
 		states[(s * 2 + 0) * P + x] = carry[0];
 		states[(s * 2 + 1) * P + x] = carry[1];
+	}
+
+	__global__ void __launch_bounds__(128) k_hold_apply(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ slotStates, uint32_t nFrames,
+		uint32_t framesPerChunk, uint32_t slots, int stereo)
+	{
+		const int P = int(t.P);
+		const int x = blockIdx.x * blockDim.x + threadIdx.x;
+		if (x >= P) return;
+		const uint32_t c = blockIdx.y + 1;
+		const uint64_t s = blockIdx.z;
+		const float sm = t.slope[x] * t.minFracRecip;
+		const float poles[2] = { t.pole0, t.pole1 };
+		const float2* mine = slotStates + (s * slots + c) * 2 * P + x;
+		float2 carry[2] = { mine[0], mine[P] };
+		const uint32_t f0 = c * framesPerChunk, f1 = min(f0 + framesPerChunk, nFrames);
+		float2* frame = results + ((s * nFrames + f0) * 2) * P + x;
+		for (uint32_t f = f0; f < f1; ++f, frame += 2 * P)
+		{
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+			{
+				carry[k].x *= poles[k];
+				float2 res = frame[k * P];
+				res.x = fmaxf(res.x, fmaxf(__log2f(sm * carry[k].x) * t.deltaYLn2, t.lowerClip));
+				if (stereo)
+				{
+					carry[k].y *= poles[k];
+					res.y = fmaxf(res.y, fmaxf(__log2f(sm * carry[k].y) * t.deltaYLn2, t.lowerClip));
+				}
+				frame[k * P] = res;
+			}
+		}
 	}

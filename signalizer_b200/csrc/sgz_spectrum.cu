@@ -1611,7 +1611,7 @@ extern "C"
 			a.firstStream = 0; a.numStreams = h->nStreams;
 			// few streams, many frames (a long recording rather than a wall of channels): one CTA per stream would leave the
 			// GPU idle, so the frames of a stream are cut into runs that CTAs process side by side; the only frame-to-frame
-			// dependency, the peak hold, is carried from run to run afterwards by k_hold_fixup
+			// dependency, the peak hold, is carried from run to run afterwards by k_hold_carry / k_hold_apply
 			uint32_t chunks = 1;
 			if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
 			{
@@ -1646,9 +1646,11 @@ extern "C"
 			if (rc != SGZ_OK) return rc;
 			if (slots > 1)
 			{
-				const dim3 grid((P + 127) / 128, h->nStreams);
-				k_hold_fixup<<<grid, 128, 0, h->stream>>>(h->dev, reinterpret_cast<float2*>(dRes), h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots,
-					(h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0); // the STEREO argument launchFused picks
+				const int stereoFlag = (h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
+				k_hold_carry<<<dim3((P + 127) / 128, h->nStreams), 128, 0, h->stream>>>(h->dev, h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots, stereoFlag);
+				if (h->nStreams > 65535) return fail(SGZ_EUNSUPPORTED, "frame-parallel mode with more than 65535 streams");
+				k_hold_apply<<<dim3((P + 127) / 128, slots - 1, h->nStreams), 128, 0, h->stream>>>(h->dev, reinterpret_cast<float2*>(dRes), h->dSlotStates, n_frames,
+					a.framesPerChunk, slots, stereoFlag);
 				SGZ_CUDA(cudaGetLastError());
 			}
 			// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
