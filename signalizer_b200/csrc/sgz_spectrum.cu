@@ -33,6 +33,9 @@ namespace sgz
 {
 	// which N = 8192 fused kernel runs unless SGZ_FUSED_VARIANT=8|16 overrides it (set from measurement)
 	constexpr bool kDefaultVariant8 = true;
+	// the fused kernel keeps 28 bytes per display point next to the N * 8-byte exchange buffer; one CTA must fit the
+	// 227 KB an SM can give (the resident CTAs per SM then follow from the size: 2 at N = 8192 up to 2048 points, 1 beyond)
+	inline bool fusedSharedMemoryFits(uint32_t N, uint32_t P) { return size_t(N) * 8 + 2048 + size_t(P) * 28 <= size_t(227) * 1024; }
 	constexpr uint32_t kFrameParallelCtas = 592;   // frame-parallel mode aims at four CTAs per SM slot pair (148 SMs x 2 x 2)
 	constexpr uint32_t kFrameParallelMinRun = 4;   // ... but never cuts a stream into runs shorter than this many frames
 
@@ -941,7 +944,7 @@ extern "C"
 			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
 			const int rc = buildTables(*cfg, h->tab);
 			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
-			h->fusedR3 = (h->tab.fusedOk && h->tab.P <= 2048) ? (h->tab.N == 16384 ? 32 : h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : h->tab.N == 2048 ? 4 : 2) : 0;
+			h->fusedR3 = (h->tab.fusedOk && fusedSharedMemoryFits(h->tab.N, h->tab.P)) ? (h->tab.N == 16384 ? 32 : h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : h->tab.N == 2048 ? 4 : 2) : 0;
 			*out = h;
 			return SGZ_OK;
 		}
@@ -1015,7 +1018,7 @@ extern "C"
 			SGZ_TRY(upload(h, tw8, &d.tw8));
 		}
 		h->fusedR3 = 0;
-		if (t.fusedOk && t.P <= 2048)
+		if (t.fusedOk && fusedSharedMemoryFits(t.N, t.P))
 		{
 			const int R3 = t.N == 16384 ? 32 : t.N == 8192 ? 16 : t.N == 4096 ? 8 : t.N == 2048 ? 4 : 2; // R3 = 32, 4, 2 (N = 16384, 2048, 1024) exist as k_fused8 only
 			const int T = 16 * R3, M = 16 * T;
