@@ -1616,7 +1616,7 @@ extern "C"
 			// GPU idle, so the frames of a stream are cut into runs that CTAs process side by side; the only frame-to-frame
 			// dependency, the peak hold, is carried from run to run afterwards by k_hold_carry / k_hold_apply
 			uint32_t chunks = 1;
-			if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
+			if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && h->nStreams <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
 			{
 				const uint32_t wanted = (kFrameParallelCtas + h->nStreams - 1) / h->nStreams;
 				chunks = std::max<uint32_t>(1, std::min<uint32_t>(wanted, n_frames / kFrameParallelMinRun));
@@ -1651,7 +1651,6 @@ extern "C"
 			{
 				const int stereoFlag = (h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
 				k_hold_carry<<<dim3((P + 127) / 128, h->nStreams), 128, 0, h->stream>>>(h->dev, h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots, stereoFlag);
-				if (h->nStreams > 65535) return fail(SGZ_EUNSUPPORTED, "frame-parallel mode with more than 65535 streams");
 				k_hold_apply<<<dim3((P + 127) / 128, slots - 1, h->nStreams), 128, 0, h->stream>>>(h->dev, reinterpret_cast<float2*>(dRes), h->dSlotStates, n_frames,
 					a.framesPerChunk, slots, stereoFlag);
 				SGZ_CUDA(cudaGetLastError());
