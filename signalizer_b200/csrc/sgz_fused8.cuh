@@ -894,14 +894,14 @@
 	// from, and merges in the run's own final state.  k_hold_apply: one thread per (run, display point) then raises the
 	// stored results of its run where the decaying carry still dominates - that part is fully parallel.
 	__global__ void __launch_bounds__(128) k_hold_carry(DeviceTables t, float2* __restrict__ slotStates, float2* __restrict__ states, uint32_t nFrames,
-		uint32_t framesPerChunk, uint32_t slots, int stereo)
+		uint32_t framesPerChunk, uint32_t slots, int stereo, uint32_t firstStream, uint32_t slotStride)
 	{
 		const int P = int(t.P);
 		const int x = blockIdx.x * blockDim.x + threadIdx.x;
 		if (x >= P) return;
-		const uint64_t s = blockIdx.y;
+		const uint64_t s = blockIdx.y + firstStream;
 		const float poles[2] = { t.pole0, t.pole1 };
-		float2* slot = slotStates + (s * slots) * 2 * P + x;
+		float2* slot = slotStates + (s * slotStride) * 2 * P + x;
 		float2 carry[2] = { slot[0], slot[P] }; // final state of run 0 = the true state there
 		float2 own[2] = { make_float2(0.f, 0.f), make_float2(0.f, 0.f) };
 		if (slots > 1) { own[0] = slot[uint64_t(2) * P]; own[1] = slot[uint64_t(2) * P + P]; }
@@ -930,16 +930,16 @@
 	}
 
 	__global__ void __launch_bounds__(128) k_hold_apply(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ slotStates, uint32_t nFrames,
-		uint32_t framesPerChunk, uint32_t slots, int stereo)
+		uint32_t framesPerChunk, uint32_t slots, int stereo, uint32_t firstStream, uint32_t slotStride)
 	{
 		const int P = int(t.P);
 		const int x = blockIdx.x * blockDim.x + threadIdx.x;
 		if (x >= P) return;
 		const uint32_t c = blockIdx.y + 1;
-		const uint64_t s = blockIdx.z;
+		const uint64_t s = blockIdx.z + firstStream;
 		const float sm = t.slope[x] * t.minFracRecip;
 		const float poles[2] = { t.pole0, t.pole1 };
-		const float2* mine = slotStates + (s * slots + c) * 2 * P + x;
+		const float2* mine = slotStates + (s * slotStride + c) * 2 * P + x;
 		float2 carry[2] = { mine[0], mine[P] };
 		const uint32_t f0 = c * framesPerChunk, f1 = min(f0 + framesPerChunk, nFrames);
 		float2* frame = results + ((s * nFrames + f0) * 2) * P + x;

@@ -1518,6 +1518,59 @@ extern "C"
 	// Host-resident callers: the streams are cut into chunks so that the upload of chunk c+1, the
 	// kernel of chunk c and the download of chunk c-1 overlap (PCIe is full duplex); results are
 	// identical to the single launch because streams are independent.
+	// Launches the fused kernel for the streams [a.firstStream, a.firstStream + a.numStreams) on the handle's stream.
+	// Few streams, many frames (a long recording rather than a wall of channels, or one chunk of the host-buffer
+	// pipeline): one CTA per stream would leave the GPU idle, so the frames of a stream are cut into runs that CTAs
+	// process side by side; the only frame-to-frame dependency, the peak hold, is carried from run to run afterwards
+	// by k_hold_carry / k_hold_apply (bit-identical results).
+	static int launchFusedFrames(sgz_spectrum* h, FusedArgs a)
+	{
+		const uint32_t P = h->tab.P, n_frames = a.nFrames, nS = a.numStreams;
+		uint32_t chunks = 1;
+		if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && nS <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
+		{
+			const uint32_t wanted = (kFrameParallelCtas + nS - 1) / nS;
+			chunks = std::max<uint32_t>(1, std::min<uint32_t>(wanted, n_frames / kFrameParallelMinRun));
+			if (chunks > 65535) chunks = 65535;
+		}
+		uint32_t slots = 1;
+		if (chunks > 1)
+		{
+			a.framesPerChunk = (n_frames + chunks - 1) / chunks;
+			slots = (n_frames + a.framesPerChunk - 1) / a.framesPerChunk;
+		}
+		if (slots <= 1)
+		{
+			a.framesPerChunk = 0; a.stateSlots = 0;
+			return launchFused(h, a);
+		}
+		// per-run state slots, [all streams][slots][2][P]: slot 0 of every stream starts from the stream's state, the others from zero
+		// (the slot stride is the largest run count this frame count can give, so that concurrent chunk launches of one
+		// call never overlap whatever their own run count)
+		const uint32_t stride = std::max<uint32_t>(1, n_frames / kFrameParallelMinRun);
+		const size_t slotBytes = size_t(2) * P * sizeof(float2), need = size_t(h->nStreams) * stride * slotBytes;
+		if (h->slotStatesBytes < need)
+		{
+			if (h->dSlotStates) { SGZ_CUDA(cudaDeviceSynchronize()); cudaFree(h->dSlotStates); h->dSlotStates = nullptr; h->slotStatesBytes = 0; }
+			SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dSlotStates), need));
+			h->slotStatesBytes = need;
+		}
+		float2* slotBase = h->dSlotStates + size_t(a.firstStream) * stride * 2 * P;
+		SGZ_CUDA(cudaMemsetAsync(slotBase, 0, size_t(nS) * stride * slotBytes, h->stream));
+		SGZ_CUDA(cudaMemcpy2DAsync(slotBase, stride * slotBytes, h->dStates + size_t(a.firstStream) * 2 * P, slotBytes, slotBytes, nS, cudaMemcpyDeviceToDevice, h->stream));
+		float2* const results = a.results;
+		a.states = h->dSlotStates; a.stateSlots = stride;
+		h->launchGridY = slots;
+		const int rc = launchFused(h, a);
+		h->launchGridY = 1;
+		if (rc != SGZ_OK) return rc;
+		const int stereoFlag = (h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
+		k_hold_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots, stereoFlag, a.firstStream, stride);
+		k_hold_apply<<<dim3((P + 127) / 128, slots - 1, nS), 128, 0, h->stream>>>(h->dev, results, h->dSlotStates, n_frames, a.framesPerChunk, slots, stereoFlag, a.firstStream, stride);
+		SGZ_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
 	static int processFramesPipelined(sgz_spectrum* h, const float* audio, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
 		uint32_t n_frames, float* results)
 	{
@@ -1529,7 +1582,11 @@ extern "C"
 		if ((rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, resPerStream * S * sizeof(float))) != SGZ_OK) return rc;
 		if (!h->copyIn) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyIn, cudaStreamNonBlocking));
 		if (!h->copyOut) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyOut, cudaStreamNonBlocking));
-		const uint32_t chunks = std::min<uint32_t>(8, S);
+		// chunks of streams flow through copy-in -> kernels -> copy-out; the first copy-in and the last copy-out are not
+		// overlapped, so smaller chunks shorten that fill / drain.  A chunk of a few dozen streams would not fill the GPU
+		// with one CTA per stream, which is what launchFusedFrames' frame-parallel mode is for
+		uint32_t chunks = std::max<uint32_t>(1, std::min<uint32_t>(16, S / 8)); // measured on BASELINE config 3: 8 -> 2.59 M, 16 -> 2.68 M, 32 -> 2.66 M, 64 -> 2.53 M frames/s
+		if (const char* e = std::getenv("SGZ_PIPE_CHUNKS")) chunks = std::max<uint32_t>(1, std::min<uint32_t>(std::min<uint32_t>(uint32_t(std::atoi(e)), S), 256u));
 		while (h->events.size() < 2 * chunks + 1)
 		{
 			cudaEvent_t e;
@@ -1552,7 +1609,7 @@ extern "C"
 			a.audio = h->dAudioStage; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
 			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(h->dResultStage);
 			a.firstStream = s0; a.numStreams = s1 - s0;
-			if ((rc = launchFused(h, a)) != SGZ_OK) return rc;
+			if ((rc = launchFusedFrames(h, a)) != SGZ_OK) return rc;
 			SGZ_CUDA(cudaEventRecord(h->events[2 * c + 1], h->stream));
 			SGZ_CUDA(cudaStreamWaitEvent(h->copyOut, h->events[2 * c + 1], 0));
 			SGZ_CUDA(cudaMemcpyAsync(results + resPerStream * s0, h->dResultStage + resPerStream * s0, resPerStream * (s1 - s0) * sizeof(float),
@@ -1612,49 +1669,7 @@ extern "C"
 			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
 			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(dRes);
 			a.firstStream = 0; a.numStreams = h->nStreams;
-			// few streams, many frames (a long recording rather than a wall of channels): one CTA per stream would leave the
-			// GPU idle, so the frames of a stream are cut into runs that CTAs process side by side; the only frame-to-frame
-			// dependency, the peak hold, is carried from run to run afterwards by k_hold_carry / k_hold_apply
-			uint32_t chunks = 1;
-			if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && h->nStreams <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
-			{
-				const uint32_t wanted = (kFrameParallelCtas + h->nStreams - 1) / h->nStreams;
-				chunks = std::max<uint32_t>(1, std::min<uint32_t>(wanted, n_frames / kFrameParallelMinRun));
-				if (chunks > 65535) chunks = 65535;
-			}
-			uint32_t slots = 1;
-			if (chunks > 1)
-			{
-				a.framesPerChunk = (n_frames + chunks - 1) / chunks;
-				slots = (n_frames + a.framesPerChunk - 1) / a.framesPerChunk;
-			}
-			if (slots > 1)
-			{
-				// per-run state slots: slot 0 of every stream starts from the stream's state, the others from zero
-				const size_t slotBytes = size_t(2) * P * sizeof(float2), need = size_t(h->nStreams) * slots * slotBytes;
-				if (h->slotStatesBytes < need)
-				{
-					if (h->dSlotStates) { SGZ_CUDA(cudaStreamSynchronize(h->stream)); cudaFree(h->dSlotStates); h->dSlotStates = nullptr; h->slotStatesBytes = 0; }
-					SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dSlotStates), need));
-					h->slotStatesBytes = need;
-				}
-				SGZ_CUDA(cudaMemsetAsync(h->dSlotStates, 0, need, h->stream));
-				SGZ_CUDA(cudaMemcpy2DAsync(h->dSlotStates, slots * slotBytes, h->dStates, slotBytes, slotBytes, h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
-				a.states = h->dSlotStates; a.stateSlots = slots;
-				h->launchGridY = slots;
-			}
-			else a.framesPerChunk = 0;
-			rc = launchFused(h, a);
-			h->launchGridY = 1;
-			if (rc != SGZ_OK) return rc;
-			if (slots > 1)
-			{
-				const int stereoFlag = (h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
-				k_hold_carry<<<dim3((P + 127) / 128, h->nStreams), 128, 0, h->stream>>>(h->dev, h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots, stereoFlag);
-				k_hold_apply<<<dim3((P + 127) / 128, slots - 1, h->nStreams), 128, 0, h->stream>>>(h->dev, reinterpret_cast<float2*>(dRes), h->dSlotStates, n_frames,
-					a.framesPerChunk, slots, stereoFlag);
-				SGZ_CUDA(cudaGetLastError());
-			}
+			if ((rc = launchFusedFrames(h, a)) != SGZ_OK) return rc;
 			// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
 			SGZ_CUDA(cudaMemcpy2DAsync(h->dResults, size_t(2) * P * sizeof(float2), dRes + size_t(n_frames - 1) * 2 * P * 2,
 				size_t(n_frames) * 2 * P * sizeof(float2), size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
