@@ -744,6 +744,9 @@
 						float2 res;
 						res.x = fmaxf(__log2f(sm * sv.x) * t.deltaYLn2, t.lowerClip);
 						res.y = fmaxf(__log2f(sm * sv.y) * t.deltaYLn2, t.lowerClip);
+						// frame-parallel mode: the smoothing runs over ALL frames afterwards (k_phase_smooth), which needs this
+						// frame's filter input rather than the output of a filter that started from nothing
+						if (a.stateSlots) res.y = ph;
 						stg_stream_f2(resOut + k * P + x, res);
 					}
 					continue;
@@ -925,8 +928,13 @@
 				own[k] = next[k];
 			}
 		}
-		states[(s * 2 + 0) * P + x] = carry[0];
-		states[(s * 2 + 1) * P + x] = carry[1];
+		// (.y is only a peak hold in the stereo forms; otherwise it is left as it was - unused, or the Phase smoother's)
+#pragma unroll
+		for (int k = 0; k < 2; ++k)
+		{
+			float2* st = states + (s * 2 + k) * P + x;
+			if (stereo) *st = carry[k]; else st->x = carry[k].x;
+		}
 	}
 
 	__global__ void __launch_bounds__(128) k_hold_apply(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ slotStates, uint32_t nFrames,
@@ -959,4 +967,44 @@
 				frame[k * P] = res;
 			}
 		}
+	}
+
+	// Frame-parallel mode, Phase configuration: the second state of a display point is a one-pole smoother of
+	// ph = cancellation x magnitude (TransformDSP.inl:1417-1419), not a maximum, so it cannot be patched up run by run.
+	// The runs leave ph in the .y slot of both graphs and this kernel, one thread per display point, filters it over all
+	// frames in order with the reference's expression and writes the dB-scaled value - the same roundings as one CTA per
+	// stream.  Four frames are fetched per trip: the walk is latency-bound and the loads do not depend on the filter.
+	__global__ void __launch_bounds__(128) k_phase_smooth(DeviceTables t, float2* __restrict__ results, float2* __restrict__ states, uint32_t nFrames,
+		uint32_t firstStream)
+	{
+		const int P = int(t.P);
+		const int x = blockIdx.x * blockDim.x + threadIdx.x;
+		if (x >= P) return;
+		const uint64_t s = blockIdx.y + firstStream;
+		const float sm = t.slope[x] * t.minFracRecip;
+		const float phasePoles[2] = { t.phasePole0, t.phasePole1 };
+		float y[2] = { states[(s * 2 + 0) * P + x].y, states[(s * 2 + 1) * P + x].y };
+		float2* frame = results + (s * nFrames * 2) * P + x;
+		for (uint32_t f = 0; f < nFrames; f += 4, frame += 8 * P)
+		{
+			float2 res[4][2];
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
+				if (f + j < nFrames) { res[j][0] = frame[uint64_t(j) * 2 * P]; res[j][1] = frame[uint64_t(j) * 2 * P + P]; }
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
+			{
+				if (f + j >= nFrames) break;
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+				{
+					const float ph = res[j][k].y;
+					y[k] = ph + phasePoles[k] * (y[k] - ph);
+					res[j][k].y = fmaxf(__log2f(sm * y[k]) * t.deltaYLn2, t.lowerClip);
+					frame[uint64_t(j) * 2 * P + k * P] = res[j][k];
+				}
+			}
+		}
+		states[(s * 2 + 0) * P + x].y = y[0];
+		states[(s * 2 + 1) * P + x].y = y[1];
 	}

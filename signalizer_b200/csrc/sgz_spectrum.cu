@@ -1527,7 +1527,7 @@ extern "C"
 	{
 		const uint32_t P = h->tab.P, n_frames = a.nFrames, nS = a.numStreams;
 		uint32_t chunks = 1;
-		if (h->fusedVariant8 && h->cfg.configuration != SGZ_CH_PHASE && nS <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
+		if (h->fusedVariant8 && nS <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
 		{
 			const uint32_t wanted = (kFrameParallelCtas + nS - 1) / nS;
 			chunks = std::max<uint32_t>(1, std::min<uint32_t>(wanted, n_frames / kFrameParallelMinRun));
@@ -1564,9 +1564,11 @@ extern "C"
 		const int rc = launchFused(h, a);
 		h->launchGridY = 1;
 		if (rc != SGZ_OK) return rc;
-		const int stereoFlag = (h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
+		const bool phase = h->cfg.configuration == SGZ_CH_PHASE; // .x is a peak hold like the others, .y a smoother (k_phase_smooth below)
+		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
 		k_hold_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots, stereoFlag, a.firstStream, stride);
 		k_hold_apply<<<dim3((P + 127) / 128, slots - 1, nS), 128, 0, h->stream>>>(h->dev, results, h->dSlotStates, n_frames, a.framesPerChunk, slots, stereoFlag, a.firstStream, stride);
+		if (phase) k_phase_smooth<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, results, h->dStates, n_frames, a.firstStream);
 		SGZ_CUDA(cudaGetLastError());
 		return SGZ_OK;
 	}
