@@ -25,6 +25,9 @@ CASES = {
     "bh8192_left_linear": dict(configuration=_abi.CH_LEFT, bin_polation=_abi.BIN_LINEAR),
     "hamming6000_midside_none": dict(window_size=6000, window_type=_abi.WIN_HAMMING, configuration=_abi.CH_MIDSIDE, bin_polation=_abi.BIN_NONE),
     "phase2048_lanczos_p256": dict(window_size=2048, configuration=_abi.CH_PHASE, axis_points=256),
+    "complex2048_lanczos": dict(window_size=2048, configuration=_abi.CH_COMPLEX),
+    "hann1024_separate_linear_p512": dict(window_size=1024, window_type=_abi.WIN_HANN, bin_polation=_abi.BIN_LINEAR, axis_points=512),
+    "bh16384_side_lanczos_p700": dict(window_size=16384, configuration=_abi.CH_SIDE, axis_points=700),
 }
 S, F = 3, 3
 
