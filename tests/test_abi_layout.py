@@ -52,3 +52,23 @@ def test_field_counts_match_the_header():
             if decl:
                 members += len(decl.split(","))
         assert members == len(cls._fields_), (cname, members, len(cls._fields_))
+
+
+def test_argument_counts_match_the_header():
+    """every prototype in the header against the argtypes the ctypes loader declares for it"""
+    import re
+    from signalizer_b200 import _lib
+    lib = _lib.load()
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "sgz.h")).read(), flags=re.S)
+    protos = re.findall(r"\b(sgz_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", text, re.S)
+    assert len(protos) >= len(_lib.EXPORTS)
+    checked = 0
+    for name, params in protos:
+        fn = getattr(lib, name)
+        if fn.argtypes is None:
+            continue
+        params = params.strip()
+        n = 0 if params in ("", "void") else len(params.split(","))
+        assert n == len(fn.argtypes), (name, n, len(fn.argtypes))
+        checked += 1
+    assert checked >= 40
