@@ -25,6 +25,8 @@ except Exception:
 
 
 def timed(fn, sync, steps=10, warmup=3):
+    if os.environ.get("SGZ_BENCH_ONCE"):   # one launch per kernel: what an ncu --set full capture of this script wants
+        steps, warmup = 1, 0
     for _ in range(warmup):
         fn()
     sync()
