@@ -88,6 +88,56 @@
 		else partial[(uint64_t(s) * a.chunks + chunk) * total + g] = st;
 	}
 
+	// Two-channel form: the pole of a filter is the same for both channels, so one thread carries both states as
+	// register pairs (re_1, re_2), (im_1, im_2) and every step is four packed FP32 instructions (fma.rn.f32x2 / mul)
+	// for the two channels instead of eight scalar ones; the kernel is bound by instruction issue, not by memory.
+	// Thread g owns (z, i) = filter g of P * V; its states sit at g (channel 1) and g + P * V (channel 2).
+	__global__ void __launch_bounds__(256) k_resonate_pair(DeviceTables t, ResArgs a, float2* __restrict__ state, float2* __restrict__ partial)
+	{
+		__shared__ float2 xs[kResTile];
+		const uint32_t P = t.P, V = t.resVectors;
+		const uint32_t half = P * V, total = 2 * half;
+		const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+		const uint32_t chunk = blockIdx.y, s = blockIdx.z;
+		const bool active = g < half;
+		const uint32_t gi = active ? g : 0;
+		const float2 p = t.resCoeff[gi];   // [z][i] = gi
+		const float* base = a.audio + uint64_t(s) * a.streamStride;
+		const uint64_t begin = a.first + uint64_t(chunk) * a.chunkLen;
+		const uint64_t end = min(a.first + uint64_t(a.count), begin + uint64_t(a.chunkLen));
+		float2 re = make_float2(0.f, 0.f), im = make_float2(0.f, 0.f);
+		if (a.chunks == 1 && active)
+		{
+			const float2 s1 = state[uint64_t(s) * total + g], s2 = state[uint64_t(s) * total + half + g];
+			re = make_float2(s1.x, s2.x); im = make_float2(s1.y, s2.y);
+		}
+		const float2 PX = bc2(p.x), PY = bc2(p.y), NPY = bc2(-p.y);
+		for (uint64_t n0 = begin; n0 < end; n0 += kResTile)
+		{
+			const uint32_t len = uint32_t(min(uint64_t(kResTile), end - n0));
+			__syncthreads();
+			if (threadIdx.x < len)
+			{
+				float l, r;
+				fetchLR(base, a.layout, a.nSamples, n0 + threadIdx.x, l, r);
+				xs[threadIdx.x] = resonatorMatrix(t.conf, l, r);
+			}
+			__syncthreads();
+#pragma unroll 4
+			for (uint32_t j = 0; j < len; ++j)
+			{
+				// s <- p s + x for both channels: re' = re px - im py + x, im' = re py + im px
+				const float2 nre = fma2(im, NPY, fma2(re, PX, xs[j]));
+				im = fma2(re, PY, mul2(im, PX));
+				re = nre;
+			}
+		}
+		if (!active) return;
+		float2* dst = a.chunks == 1 ? state + uint64_t(s) * total : partial + (uint64_t(s) * a.chunks + chunk) * total;
+		dst[g] = make_float2(re.x, im.x);
+		dst[half + g] = make_float2(re.y, im.y);
+	}
+
 	__device__ __forceinline__ float2 cpowu(float2 p, uint32_t e)
 	{
 		float2 r = make_float2(1.f, 0.f);

@@ -1375,7 +1375,10 @@ extern "C"
 				h->resPartialBytes = need;
 			}
 		}
-		k_resonate<<<dim3(blocksX, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+		if (h->tab.stateChannels == 2 && !std::getenv("SGZ_RESONATE_SCALAR"))
+			k_resonate_pair<<<dim3((total / 2 + 255) / 256, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+		else
+			k_resonate<<<dim3(blocksX, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
 		if (a.chunks > 1) k_resonate_combine<<<dim3(blocksX, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
 		SGZ_CUDA(cudaGetLastError());
 		return SGZ_OK;
