@@ -1530,8 +1530,9 @@ extern "C"
 	{
 		const uint32_t P = h->tab.P, n_frames = a.nFrames, nS = a.numStreams;
 		uint32_t chunks = 1;
-		// (carrying the hold across runs relies on x -> x * pole being monotone, i.e. on non-negative poles)
-		const bool polesOk = h->cfg.pole[0] >= 0.f && h->cfg.pole[1] >= 0.f;
+		// (carrying the hold across runs relies on x -> x * pole and on the dB scale being monotone non-decreasing:
+		// non-negative poles and slope, an upright dB range)
+		const bool polesOk = h->cfg.pole[0] >= 0.f && h->cfg.pole[1] >= 0.f && h->cfg.slope_b >= 0.0 && h->dev.deltaYLn2 > 0.f;
 		if (h->fusedVariant8 && polesOk && nS <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
 		{
 			const uint32_t wanted = (kFrameParallelCtas + nS - 1) / nS;
