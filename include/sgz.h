@@ -210,7 +210,13 @@ int  sgz_spectrum_clear_audio_state(sgz_spectrum* h);
  * audioEntryPoint :1172-1204 when hop == sample_buffer_size).
  * `results`: [stream][frame][graph(2)][P][2] floats.  Peak-hold state is
  * carried frame to frame and call to call.  n_samples must be >=
- * (n_frames-1)*hop + window_size. */
+ * (n_frames-1)*hop + window_size.
+ * One fused kernel launch covers all frames of all streams when the
+ * configuration has a fused kernel (sgz_spectrum_info.fused_available:
+ * FFT algorithm, transform size 1024 ... 16384, display points that fit one
+ * CTA's shared memory); with few streams the frames of a stream are spread
+ * over CTAs as well, with bit-identical results.  Everything else runs the
+ * four staged kernels per frame. */
 int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout,
                                  uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
                                  uint32_t n_frames, float* results, int results_mem);
