@@ -144,8 +144,10 @@ def run_reference(args):
     from oracle import binding
     binding.build()
     cores = binding.hardware_concurrency() or os.cpu_count() or 1
-    streams = max(cores * 2, 16)
-    frames = 8
+    # a step large enough that thread start-up does not count against the reference (about 0.1 s of work on 16 cores),
+    # small enough that the default --steps 50 ends within seconds
+    streams = max(cores * 16, 64)
+    frames = 16
     vals = []
     for i in range(args.warmup + args.steps):
         v, dt = cpu_sample(args, cores, streams, frames)
