@@ -15,10 +15,18 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _libs = {}
 
 
+REF_LIB = os.path.join(_HERE, "_ref", "libsgz_oracle_ref.so")
+
+
 def build(force: bool = False) -> None:
-    need = force or not all(os.path.exists(os.path.join(_HERE, n)) for n in ("libsgz_oracle.so", "libsgz_oracle_fast.so"))
-    if need:
-        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    # oracle/_ref: the reference's own TransformDSP.inl behind the same entry points; needs the reference checkout
+    # (this container), a no-op elsewhere (the GPU box uses the prebuilt file that travels with the snapshot)
+    subprocess.check_call(["bash", os.path.join(_HERE, "build_ref.sh")])
+
+
+def ref_available() -> bool:
+    return os.path.exists(REF_LIB)
 
 
 def _cpu_has_avx2() -> bool:
@@ -30,13 +38,17 @@ def _cpu_has_avx2() -> bool:
         return False
 
 
-def load(fast: bool = False):
-    name = "libsgz_oracle_fast.so" if fast and _cpu_has_avx2() else "libsgz_oracle.so"
+def load(fast: bool = False, ref: bool = False):
+    """fast: the -O3 -mavx2 build of the restatement (timing only); ref: oracle/_ref, the reference's own
+    TransformDSP.inl compiled against the cpl stand-ins (same entry points, Spectrum path only)."""
+    name = "_ref/libsgz_oracle_ref.so" if ref else "libsgz_oracle_fast.so" if fast and _cpu_has_avx2() else "libsgz_oracle.so"
     if name in _libs:
         return _libs[name]
     path = os.path.join(_HERE, name)
     if not os.path.exists(path):
         build()
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path}: oracle/_ref can only be built where the reference checkout is (oracle/build_ref.sh)")
     lib = C.CDLL(path)
     vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
     fp, dp, ip = C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_int32)
@@ -73,8 +85,8 @@ class OracleSpectrum:
     """`n_streams` TransformPair objects sharing one TransformConstant (float32 like the
     reference, Spectrum.h:71; `double=True` instantiates the same restatement in float64)."""
 
-    def __init__(self, cfg: _abi.SpectrumConfig, n_streams: int = 1, double: bool = False, fast: bool = False):
-        self.lib = load(fast)
+    def __init__(self, cfg: _abi.SpectrumConfig, n_streams: int = 1, double: bool = False, fast: bool = False, ref: bool = False):
+        self.lib = load(fast, ref)
         self.cfg = _abi.copy_config(cfg)
         self.n_streams = n_streams
         self.h = self.lib.sgzo_create(C.byref(self.cfg), n_streams, int(double))

@@ -7,7 +7,15 @@
 // The handle mirrors the product's batched C ABI (include/sgz.h) so one test
 // harness drives both: `n_streams` TransformPair objects sharing one
 // TransformConstant, as in SpectrumDSP.cpp:83-102.
+//
+// Built twice: libsgz_oracle.so over the restatement (sgz_oracle.hpp), and - with -DSGZ_ORACLE_REF, by
+// oracle/build_ref.sh - oracle/_ref/libsgz_oracle_ref.so over the REFERENCE's own TransformDSP.inl / TransformPair.h /
+// TransformConstant.h (ref_adapter.hpp); tests/test_oracle_ref.py holds the two to the same bits.
+#ifdef SGZ_ORACLE_REF
+#include "ref_adapter.hpp"
+#else
 #include "sgz_oracle.hpp"
+#endif
 #include "../include/sgz.h"
 
 #include <atomic>
@@ -15,7 +23,19 @@
 #include <memory>
 #include <thread>
 
+#ifdef SGZ_ORACLE_REF
+using namespace sgzref;
+#else
 using namespace sgzo;
+namespace
+{
+	// first / second scalar of a result or state entry
+	template<typename S> inline S first(const UComplexFilter<S>& v) { return v.a; }
+	template<typename S> inline S second(const UComplexFilter<S>& v) { return v.b; }
+	template<typename S> inline void assign(UComplexFilter<S>& v, S a, S b) { v.a = a; v.b = b; }
+	template<typename T> inline ComplexResonator<T>& resonatorOf(TransformPair<T>& p) { return p.cresonator; }
+}
+#endif
 
 namespace
 {
@@ -265,7 +285,7 @@ namespace
 			for (std::size_t s = 0; s < pairs.size(); ++s)
 			{
 				const auto& r = pairs[s].lineGraphs[graph].getResults(P);
-				for (std::size_t i = 0; i < P; ++i) { out[2 * (s * P + i)] = r[i].a; out[2 * (s * P + i) + 1] = r[i].b; }
+				for (std::size_t i = 0; i < P; ++i) { out[2 * (s * P + i)] = first(r[i]); out[2 * (s * P + i) + 1] = second(r[i]); }
 			}
 		}
 		void states(int graph, float* out) override
@@ -274,7 +294,7 @@ namespace
 			for (std::size_t s = 0; s < pairs.size(); ++s)
 			{
 				auto& g = pairs[s].lineGraphs[graph]; g.resize(P);
-				for (std::size_t i = 0; i < P; ++i) { out[2 * (s * P + i)] = g.states[i].a; out[2 * (s * P + i) + 1] = g.states[i].b; }
+				for (std::size_t i = 0; i < P; ++i) { out[2 * (s * P + i)] = first(g.states[i]); out[2 * (s * P + i) + 1] = second(g.states[i]); }
 			}
 		}
 		void setStates(int graph, const float* in) override
@@ -283,7 +303,7 @@ namespace
 			for (std::size_t s = 0; s < pairs.size(); ++s)
 			{
 				auto& g = pairs[s].lineGraphs[graph]; g.resize(P);
-				for (std::size_t i = 0; i < P; ++i) { g.states[i].a = in[2 * (s * P + i)]; g.states[i].b = in[2 * (s * P + i) + 1]; }
+				for (std::size_t i = 0; i < P; ++i) { assign(g.states[i], in[2 * (s * P + i)], in[2 * (s * P + i) + 1]); }
 			}
 		}
 		void clearLineGraphs() override { for (auto& p : pairs) p.clearLineGraphStates(); }
@@ -332,7 +352,7 @@ namespace
 							{
 								const auto& r = p.lineGraphs[g].getResults(P);
 								float* o = results + (((s * nFrames + f) * 2 + g) * P) * 2;
-								for (std::size_t i = 0; i < P; ++i) { o[2 * i] = r[i].a; o[2 * i + 1] = r[i].b; }
+								for (std::size_t i = 0; i < P; ++i) { o[2 * i] = first(r[i]); o[2 * i + 1] = second(r[i]); }
 							}
 						}
 					}
@@ -365,7 +385,7 @@ namespace
 			const std::size_t ch = constant.getStateConfigurationChannels(), V = constant.resonator.numVectors, P = constant.axisPoints;
 			for (std::size_t s = 0; s < pairs.size(); ++s)
 			{
-				auto& r = pairs[s].cresonator;
+				auto& r = resonatorOf(pairs[s]);
 				r.ensure(constant.resonator);
 				for (std::size_t k = 0; k < ch * V * P; ++k)
 				{
@@ -398,7 +418,7 @@ namespace
 				for (uint32_t f = 0; f < emitted && f < maxFrames; ++f)
 				{
 					float* o = frames + ((s * maxFrames + f) * P) * 2;
-					for (std::size_t i = 0; i < P; ++i) { o[2 * i] = pairs[s].sfbuf[f][i].a; o[2 * i + 1] = pairs[s].sfbuf[f][i].b; }
+					for (std::size_t i = 0; i < P; ++i) { o[2 * i] = first(pairs[s].sfbuf[f][i]); o[2 * i + 1] = second(pairs[s].sfbuf[f][i]); }
 				}
 				pairs[s].sfbuf.clear();
 			}
@@ -450,6 +470,7 @@ extern "C"
 	unsigned sgzo_hardware_concurrency(void) { return std::thread::hardware_concurrency(); }
 }
 
+#ifndef SGZ_ORACLE_REF // (the reference build covers the Spectrum path only)
 // ---------------------------------------------------------------------------------------------
 // secondary paths (sgz_oracle_scope.hpp)
 // ---------------------------------------------------------------------------------------------
@@ -693,3 +714,4 @@ extern "C" void sgzo_scope_crossover(double sampleRate, const float* x, uint64_t
 		bands[3 * i] = b[0]; bands[3 * i + 1] = b[1]; bands[3 * i + 2] = b[2];
 	}
 }
+#endif // SGZ_ORACLE_REF

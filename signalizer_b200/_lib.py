@@ -9,7 +9,8 @@ import subprocess
 from . import _abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsgz_cuda.so")
+# SGZ_CUDA_LIB: development hook, loads an A/B build of the same sources (csrc/Makefile VARIANT=...) instead
+LIB_PATH = os.environ.get("SGZ_CUDA_LIB") or os.path.join(_HERE, "libsgz_cuda.so")
 _lib = None
 
 # every symbol include/sgz.h declares
@@ -40,7 +41,7 @@ class SgzError(RuntimeError):
 def build(force: bool = False) -> str:
     """Compile the library for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
     csrc = os.path.join(_HERE, "csrc")
-    cmd = ["make", "-C", csrc, "-s"] + (["-B"] if force else [])
+    cmd = ["make", "-C", csrc, "-s", "-j4"] + (["-B"] if force else [])
     subprocess.check_call(cmd)
     return LIB_PATH
 

@@ -21,13 +21,22 @@
 #ifndef SGZ8_TW_POWERS
 #define SGZ8_TW_POWERS 1
 #endif
-// SGZ8_STATES_GLOBAL: 1 = the peak-hold states stay in global memory (each thread owns fixed display points, so the
-// accesses are coalesced and private) instead of a 16 KB shared-memory copy
-#ifndef SGZ8_FRAME_PARALLEL
-#define SGZ8_FRAME_PARALLEL 1
+// SGZ8_WINDOW: 0 = window taps from the table, fetched ahead of the audio; 1 = fetched after it; 2 = evaluated from
+// the thread's twiddle when the window is a cosine sum spanning the whole transform (table otherwise)
+#ifndef SGZ8_WINDOW
+#define SGZ8_WINDOW 0
 #endif
-#ifndef SGZ8_STATES_GLOBAL
-#define SGZ8_STATES_GLOBAL 0
+// A/B switches (tools/ab_libs.sh): SGZ8_SPLIT_SMEM 1 = the two-for-one split fetches its partner bins through shared
+// memory instead of warp shuffles; SGZ8_STAGE_LATE 1 = the next frame's audio is staged after the split instead of
+// before it; SGZ8_AOS_WEIGHTS 1 = Lanczos weights read point-major
+#ifndef SGZ8_SPLIT_SMEM
+#define SGZ8_SPLIT_SMEM 0
+#endif
+#ifndef SGZ8_STAGE_LATE
+#define SGZ8_STAGE_LATE 0
+#endif
+#ifndef SGZ8_AOS_WEIGHTS
+#define SGZ8_AOS_WEIGHTS 0
 #endif
 	// K1 = radix of the first pass: 8 -> N = 8192 (M = 8^4, 512 threads); 4 -> N = 4096 (M = 4 x 8^3, 256 threads, whose
 	// first pass is two radix-4 butterflies per thread); 2 -> N = 2048 (128 threads, four radix-2 butterflies); 1 -> N = 1024
@@ -48,11 +57,7 @@
 #endif
 		static constexpr size_t twBytes = size_t(twEntries) * sizeof(float2);
 		static constexpr size_t stateOffset = twOffset + twBytes;
-#if SGZ8_STATES_GLOBAL
-		__host__ __device__ static size_t mapOffset(uint32_t) { return stateOffset; }
-#else
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
-#endif
 		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12; }
 	};
 	typedef Fused8GeomT<8> Fused8Geom;
@@ -109,13 +114,29 @@
 		mulTwiddleP(re[perm8(7)], im[perm8(7)], make_float4(w7.x, w7.x, w7.y, w7.y));
 	}
 
+	// Which bins a thread owns after the last pass: t + T k4.  The two-for-one split pairs bin j with bin N - j, i.e. thread
+	// t with thread T - t (slot k4 with slot 7 - k4); this map puts the two partners in lanes l and l ^ 16 of one warp, so
+	// that the split can swap them with warp shuffles instead of a shared-memory round trip: lanes 0-15 of warp w hold
+	// i = 16 w .. 16 w + 15, lanes 16-31 hold T - i.  The two self-paired threads (t = 0 and t = T / 2) share lane pair 0 / 16
+	// of warp 0.  Quarter warps still hold 8 consecutive values of t, which is all the exchange swizzle needs in pass 4.
+	template<int T>
+	__device__ __forceinline__ int pairedBin(int u)
+	{
+#if SGZ8_SPLIT_SMEM
+		return u;
+#endif
+		const int i = 16 * (u >> 5) + (u & 15);
+		return (u & 16) ? (i == 0 ? T / 2 : T - i) : i;
+	}
+
 	// The FFT of one frame once its 8 windowed (E, O) pairs per thread sit in registers: first pass in registers,
 	// three in-place radix-8 passes through the exchange buffer, the last radix-2 that joins the even and odd halves.
-	// On return re[perm8(k4)] = (Z[k].re, Z[k + M].re), im[...] likewise, for the bins k = u + T k4.  Contains the
+	// On return re[perm8(k4)] = (Z[k].re, Z[k + M].re), im[...] likewise, for the bins k = t + T k4 (t = pairedBin(u); `wt`
+	// points at the W_N^k table, from which W_N^t is fetched just in time for the last radix-2).  Contains the
 	// block-wide barriers of the exchanges; the first one also orders whatever the caller still had in xbuf before it.
 	template<int K1>
 	__device__ __forceinline__ void fusedFftCore(float2 (&re)[8], float2 (&im)[8], float4* xbuf, const float2* twA, const float2* twB, const float2* twC,
-		float2 wu, int u)
+		float2 wu, int u, int t, const float2* __restrict__ twN)
 	{
 		constexpr int T = Fused8GeomT<K1>::T;
 
@@ -324,9 +345,14 @@
 		}
 		__syncthreads();
 
-		// ---- pass 4: thread t = k1 + 8 k2 + 64 k3, DFT8 over n4; owns bins k = t + 512 k4 ----
+		// ---- pass 4: thread t = k1 + K1 k2 + 8 K1 k3, DFT8 over n4; owns bins k = t + T k4 ----
+#if SGZ8_SPLIT_SMEM
+		const float2 wt = wu;
+#else
+		const float2 wt = ldg_f2(twN + t); // W_N^t, in flight behind the exchange reads
+#endif
 		{
-			const int k1 = u & (K1 - 1), k2 = (u / K1) & 7, k3 = u / (8 * K1);
+			const int k1 = t & (K1 - 1), k2 = (t / K1) & 7, k3 = t / (8 * K1);
 #pragma unroll
 			for (int n4 = 0; n4 < 8; ++n4)
 			{
@@ -335,13 +361,13 @@
 			}
 		}
 		dft8q(re, im);
-		// last radix-2: re[slot] = (Zp.re, Zm.re), im[slot] = (Zp.im, Zm.im); W_N^(t + 512 k4) = W_N^t W_16^k4
+		// last radix-2: re[slot] = (Zp.re, Zm.re), im[slot] = (Zp.im, Zm.im); W_N^(t + T k4) = W_N^t W_16^k4
 #pragma unroll
 		for (int k4 = 0; k4 < 8; ++k4)
 		{
 			const int slot = perm8(k4);
 			const float2 o = make_float2(re[slot].y, im[slot].y), e = make_float2(re[slot].x, im[slot].x);
-			const float2 wo = cmul(cmul(o, w32(2 * k4)), wu);
+			const float2 wo = cmul(cmul(o, w32(2 * k4)), wt);
 			re[slot] = make_float2(e.x + wo.x, e.x - wo.x);
 			im[slot] = make_float2(e.y + wo.y, e.y - wo.y);
 		}
@@ -392,12 +418,13 @@
 			re[e] = make_float2(ev.x, od.x); im[e] = make_float2(ev.y, od.y);
 		}
 		__syncthreads(); // the twiddle tables are in place
-		fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u);
+		const int tb = pairedBin<T>(u);
+		fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u, tb, t.tw3);
 #pragma unroll
 		for (int k4 = 0; k4 < 8; ++k4)
 		{
 			const int slot = perm8(k4);
-			const uint64_t k = uint64_t(u + T * k4);
+			const uint64_t k = uint64_t(tb + T * k4);
 			y[k * subs] = make_float2(re[slot].x, im[slot].x);
 			y[(k + M) * subs] = make_float2(re[slot].y, im[slot].y);
 		}
@@ -421,7 +448,6 @@
 		constexpr int T = Gm::T, M = Gm::M, N = Gm::N;
 		extern __shared__ __align__(16) unsigned char smemRaw[];
 		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
-		float2* zm = reinterpret_cast<float2*>(smemRaw);                 // [M], lower half of xbuf
 		float4* stage = reinterpret_cast<float4*>(smemRaw);               // [4][T] next frame's newest half
 		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
 		float2* csfC = reinterpret_cast<float2*>(smemRaw);                 // Phase configuration: [N+1] complex csf = the whole xbuf (+8 B of the pad)
@@ -434,14 +460,10 @@
 		float2* twB = twA + 64;                                           // [8][64]  W_M^(v k1)
 		float2* twC = twB + 512;                                          // [8][64]  W_512^(v k2)
 #endif
-#if SGZ8_STATES_GLOBAL
-		float2* st = a.states + (uint64_t(blockIdx.x + a.firstStream) * (a.stateSlots ? a.stateSlots : 1u) + (a.stateSlots ? blockIdx.y : 0u)) * 2 * t.P; // [2][P], in place
-#else
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
-#endif
 
 		const int u = threadIdx.x;
-		const int stream = blockIdx.x + a.firstStream;
+		const int tb = pairedBin<T>(u); // this thread owns bins tb + T k4 after the FFT
 		const int P = int(t.P);
 		const int conf = t.conf;
 		const int linLimit = int(t.linLimit);
@@ -449,10 +471,6 @@
 		float* mapSlope = reinterpret_cast<float*>(mapPacked + P);
 		int* mapBaseR = reinterpret_cast<int*>(mapSlope + P);
 
-#if !SGZ8_STATES_GLOBAL
-		float2* stateSlot = a.states + (uint64_t(stream) * (a.stateSlots ? a.stateSlots : 1u) + (a.stateSlots ? blockIdx.y : 0u)) * 2 * P;
-		for (int i = u; i < 2 * P; i += T) st[i] = stateSlot[i];
-#endif
 		for (int i = u; i < P; i += T)
 		{
 			const int4 bm = t.binmap[i];
@@ -465,16 +483,72 @@
 #else
 		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i];
 #endif
-		const float2 wu = t.tw3[u]; // W_N^t, the thread-constant part of the last radix-2 twiddle
+		const float2 wu = t.tw3[u]; // W_N^u: pass 1 uses its square W_M^u
 		__syncthreads();
 
-		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
-		const bool vec4 = a.layout == SGZ_LAYOUT_INTERLEAVED && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0) && int(t.W) == N;
+#ifdef SGZ8_STAGGER
+		// A/B switch: the two CTAs of an SM start half a frame apart instead of in lock step
+		if (((blockIdx.x & 1u) ^ (blockIdx.x >= gridDim.x / 2 ? 1u : 0u)) != 0u)
+		{
+			const long long t0 = clock64();
+			while (clock64() - t0 < SGZ8_STAGGER) { }
+		}
+#endif
+		// ---- this CTA's share of the launch: items [i0, i1) of the stream-major frame list, cut into per-stream parts ----
+		const uint32_t F = a.nFrames, G = gridDim.x, cta = blockIdx.x;
+		const uint64_t items = uint64_t(a.numStreams) * F;
+		const uint64_t i0 = items * cta / G, i1 = items * (cta + 1) / G;
+		if (i1 == i0) return; // (the host never launches more CTAs than items)
+		const uint32_t sA = uint32_t(i0 / F), fA = uint32_t(i0 - uint64_t(sA) * F);
+		const uint32_t sZ = uint32_t((i1 - 1) / F), fZ = uint32_t(i1 - uint64_t(sZ) * F);
+		const uint32_t nParts = sZ - sA + 1;
+		const uint32_t headFirst = (a.chained && fZ < F && sZ > sA) ? 1u : 0u; // the head of stream sZ runs first and is published
+		const uint32_t tailLast = (a.chained && fA != 0) ? 1u : 0u;            // the tail of stream sA runs last, from the published state
 		const int W = int(t.W);
+
+		for (uint32_t q = 0; q < nParts; ++q)
+		{
+		uint32_t sLocal = sA + q;
+		if (a.chained)
+		{
+			if (headFirst && q == 0) sLocal = sZ;
+			else
+			{
+				const uint32_t r = q - headFirst, nMid = nParts - headFirst - tailLast;
+				sLocal = r < nMid ? sA + tailLast + r : sA;
+			}
+		}
+		const uint32_t fBegin = sLocal == sA ? fA : 0u, fEnd = sLocal == sZ ? fZ : F;
+		const int stream = int(sLocal + a.firstStream);
+		// where the part's peak-hold state comes from and goes to
+		const float2* stateSrc = nullptr; float2* stateDst; bool publish = false;
+		if (fBegin == 0) stateSrc = a.states + uint64_t(stream) * 2 * P;
+		else if (a.chained)
+		{
+			if (u == 0)
+			{
+				// (published at the very start of the neighbour's work, so this hardly ever spins; the bound turns a lost
+				// neighbour - a launch that was not co-resident - into a launch error instead of a hang)
+				uint32_t spins = 0;
+				while (ldAcquire(a.flags + (cta - 1)) != a.epoch) { __nanosleep(128); if (++spins > (1u << 24)) __trap(); }
+			}
+			__syncthreads();
+			stateSrc = a.seam + uint64_t(cta - 1) * 2 * P;
+		}
+		if (a.chained)
+		{
+			if (fEnd == F) stateDst = a.states + uint64_t(stream) * 2 * P;
+			else { stateDst = a.seam + uint64_t(cta) * 2 * P; publish = true; }
+		}
+		else stateDst = a.seam + uint64_t(fBegin ? cta : G + cta) * 2 * P;
+		if (stateSrc) { for (int i = u; i < 2 * P; i += T) st[i] = __ldcg(stateSrc + i); }
+		else { for (int i = u; i < 2 * P; i += T) st[i] = make_float2(0.f, 0.f); }
+		// (the first block-wide barrier of the frame orders these writes before any display point reads them)
+
+		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
+		const bool vec4 = a.layout == SGZ_LAYOUT_INTERLEAVED && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0) && W == N;
 		bool staged = false;
 
-		const uint32_t fBegin = (SGZ8_FRAME_PARALLEL && a.framesPerChunk) ? blockIdx.y * a.framesPerChunk : 0u;
-		const uint32_t fEnd = (SGZ8_FRAME_PARALLEL && a.framesPerChunk) ? min(fBegin + a.framesPerChunk, a.nFrames) : a.nFrames;
 		for (uint32_t f = fBegin; f < fEnd; ++f)
 		{
 			float2 re[8], im[8];
@@ -483,8 +557,10 @@
 			// ---- pass 1: load (all loads first), window + channel matrix, DFT8 over n1 ----
 			{
 				float2 wv[8];
+#if SGZ8_WINDOW == 0
 #pragma unroll
 				for (int n1 = 0; n1 < 8; ++n1) wv[n1] = ldg_f2(reinterpret_cast<const float2*>(t.window) + n1 * T + u);
+#endif
 				float4 rv[8];
 				if (vec4)
 				{
@@ -515,6 +591,34 @@
 						rv[n1] = v;
 					}
 				}
+#if SGZ8_WINDOW == 2
+				if (t.winPolyOk)
+				{
+					// cosine-sum window over the whole transform: w = sum_k (-1)^k a_k cos(k theta) is a polynomial p in
+					// c = cos(theta), and theta of sample 2 (n1 T + u) + parity is 2 arg(conj W_N^u) + n1 pi / 4 (+ 2 pi / N):
+					// nothing is read, eight multiples of 45 degrees share the even / odd halves of p
+					constexpr float R = 0.70710678118654752440f;
+					const float zx = wu.x * wu.x - wu.y * wu.y, zy = -2.f * wu.x * wu.y;            // e^(i theta) of the even sample, n1 = 0
+					const float ox = zx * t.winStep.x - zy * t.winStep.y, oy = zx * t.winStep.y + zy * t.winStep.x; // ... of the odd one
+					const float2 c = make_float2(zx, ox), sn = make_float2(zy, oy);
+					const float2 arg[4] = { c, mul2(sub2(c, sn), bc2(R)), sub2(bc2(0.f), sn), mul2(add2(c, sn), bc2(-R)) }; // cos at n1 = 0..3
+#pragma unroll
+					for (int q4 = 0; q4 < 4; ++q4)
+					{
+						const float2 x = arg[q4], x2 = mul2(x, x);
+						const float2 ev = fma2(x2, fma2(x2, bc2(t.winPoly[4]), bc2(t.winPoly[2])), bc2(t.winPoly[0]));
+						const float2 od = mul2(x, fma2(x2, bc2(t.winPoly[3]), bc2(t.winPoly[1])));
+						wv[q4] = add2(ev, od); wv[q4 + 4] = sub2(ev, od); // cos(theta + pi) = -cos(theta)
+					}
+				}
+				else
+#endif
+#if SGZ8_WINDOW >= 1
+				{
+#pragma unroll
+					for (int n1 = 0; n1 < 8; ++n1) wv[n1] = ldg_f2(reinterpret_cast<const float2*>(t.window) + n1 * T + u);
+				}
+#endif
 #pragma unroll
 				for (int n1 = 0; n1 < 8; ++n1)
 				{
@@ -532,8 +636,22 @@
 					}
 				}
 			}
-			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u);
-			__syncthreads(); // every pass-4 read of xbuf is done before zm / csfmag overwrite it
+			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u, tb, t.tw3);
+			__syncthreads(); // every pass-4 read of xbuf is done before csfmag and the staged audio overwrite it
+
+#if !SGZ8_STAGE_LATE && !SGZ8_SPLIT_SMEM
+			// newest half of the next frame -> lower half of the exchange buffer, in flight behind the split and the display
+			// (Phase keeps the whole buffer for its complex spectra)
+			staged = false;
+			if (MATRIX != 3 && vec4 && f + 1 < fEnd)
+			{
+				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
+#pragma unroll
+				for (int n1 = 4; n1 < 8; ++n1) cpAsync16(stage + (n1 - 4) * T + u, src + n1 * T);
+				cpAsyncCommit();
+				staged = true;
+			}
+#endif
 
 			if constexpr (MATRIX == 3)
 			{
@@ -542,13 +660,13 @@
 				// the partner Z[N - j] of bin j then sits at slot N - j, which is also where B_j goes - every upper slot is
 				// read and rewritten by one thread only, and the lower half (the A's) holds nothing that is still needed.
 #pragma unroll
-				for (int k4 = 0; k4 < 8; ++k4) csfC[M + u + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
+				for (int k4 = 0; k4 < 8; ++k4) csfC[M + tb + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
 				__syncthreads();
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
 					const int slot = perm8(k4);
-					const int j = u + T * k4;
+					const int j = tb + T * k4;
 					const float2 zj = make_float2(re[slot].x, im[slot].x);
 					if (k4 == 0 && j == 0)
 					{
@@ -568,12 +686,11 @@
 			}
 			else 			if constexpr (STEREO)
 			{
+#if SGZ8_SPLIT_SMEM
+				float2* zm = reinterpret_cast<float2*>(smemRaw);
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4) zm[u + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
 				__syncthreads();
-				// A = (Z[j] + conj Z[N-j]) / 2, B = (Z[j] - conj Z[N-j]) / 2i.  With S = Z[j] + Z[N-j] and
-				// D = Z[j] - Z[N-j]: 2A = (S.x, D.y), 2|B| components = (D.x, S.y).  The halving is folded into the
-				// display scale (magScale = invSize / 2), so entries hold 2|.| (or 4|.|^2 beyond linLimit).
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
@@ -582,7 +699,6 @@
 					const float2 zj = make_float2(re[slot].x, im[slot].x);
 					if (k4 == 0 && j == 0)
 					{
-						// :861-864: csf[N] = Im Z[0] / 2, csf[0] = Re Z[0] / 2, csf[N/2] = packed Nyquists / 2
 						const float2 ny = make_float2(re[slot].y, im[slot].y); // Z[M] = Zm[0]
 						const float h2 = cnorm(ny);
 						csfmag[0] = zj.x;
@@ -599,6 +715,50 @@
 					csfmag[j] = a2;
 					csfmag[N - j] = b2;
 				}
+#else
+				// Z[N - j] = Zm[M - j] is held by thread T - t in slot 7 - k4: the lane pair (l, l ^ 16) swaps them by shuffle
+				// (pairedBin); lane 16 of warp 0 (t = T / 2) is its own partner, and t = 0 is redone below.
+				// A = (Z[j] + conj Z[N-j]) / 2, B = (Z[j] - conj Z[N-j]) / 2i.  With S = Z[j] + Z[N-j] and
+				// D = Z[j] - Z[N-j]: 2A = (S.x, D.y), 2|B| components = (D.x, S.y).  The halving is folded into the
+				// display scale (magScale = invSize / 2), so entries hold 2|.| (or 4|.|^2 beyond linLimit).
+				const int partnerLane = (tb == T / 2 || tb == 0) ? (u & 31) : ((u & 31) ^ 16);
+				if (tb == 0)
+				{
+					// thread 0 pairs with itself one slot further (bin T k4 with Zm[M - T k4] = slot 8 - k4): shift its upper halves
+					// down one slot so that the loop below is the same for everybody; Z[0] and Z[M] (DC / Nyquist) are redone after it
+					const float2 dc = make_float2(re[perm8(0)].y, im[perm8(0)].y);
+#pragma unroll
+					for (int m = 0; m < 7; ++m) { re[perm8(m)].y = re[perm8(m + 1)].y; im[perm8(m)].y = im[perm8(m + 1)].y; }
+					re[perm8(7)].y = dc.x; im[perm8(7)].y = dc.y; // Z[M], read back below
+				}
+#pragma unroll
+				for (int k4 = 0; k4 < 8; ++k4)
+				{
+					const int slot = perm8(k4), pslot = perm8(7 - k4);
+					const int j = tb + T * k4;
+					const float2 zj = make_float2(re[slot].x, im[slot].x);
+					float2 zn; // Z[N - j]
+					zn.x = __shfl_sync(0xffffffffu, re[pslot].y, partnerLane);
+					zn.y = __shfl_sync(0xffffffffu, im[pslot].y, partnerLane);
+					const float2 S = add2(zj, zn), D = sub2(zj, zn);
+					const float2 SS = mul2(S, S), DD = mul2(D, D);
+					float a2 = SS.x + DD.y, b2 = DD.x + SS.y;
+					if (k4 == 7 && j == M - 1) a2 *= 0.25f; // csf[(N >> 1) - 1] *= 0.5, channel 1 only
+					if ((k4 == 0 || linLimit > T) && j < linLimit) { a2 = approxSqrt(a2); b2 = approxSqrt(b2); }
+					csfmag[j] = a2;
+					csfmag[N - j] = b2;
+				}
+				if (tb == 0)
+				{
+					// :861-864: csf[N] = Im Z[0] / 2, csf[0] = Re Z[0] / 2, csf[N/2] = packed Nyquists / 2
+					const float2 zj = make_float2(re[perm8(0)].x, im[perm8(0)].x);
+					const float2 ny = make_float2(re[perm8(7)].y, im[perm8(7)].y); // Z[M] = Zm[0], parked above
+					const float h2 = cnorm(ny);
+					csfmag[0] = zj.x;
+					csfmag[N] = zj.y;
+					csfmag[M] = (M < linLimit) ? approxSqrt(h2) : h2;
+				}
+			#endif
 			}
 			else if constexpr (MATRIX == 2)
 			{
@@ -609,7 +769,7 @@
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
 					const int slot = perm8(k4);
-					const int j = u + T * k4;
+					const int j = tb + T * k4;
 					float2 zp = make_float2(re[slot].x, im[slot].x);
 					const float2 zq = make_float2(re[slot].y, im[slot].y);
 					if (j == 0) { zp.x *= 0.5f; zp.y *= 0.5f; *z0c = zp; csfmag[N] = 0.f; }
@@ -623,7 +783,7 @@
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
 					const int slot = perm8(k4);
-					const int j = u + T * k4;
+					const int j = tb + T * k4;
 					float2 zj = make_float2(re[slot].x, im[slot].x);
 					if (j == 0)
 					{
@@ -638,9 +798,11 @@
 			}
 			__syncthreads();
 
-			// newest half of the next frame -> lower half of the exchange buffer, behind the display points
+#if SGZ8_STAGE_LATE || SGZ8_SPLIT_SMEM
+			// newest half of the next frame -> lower half of the exchange buffer, in flight behind the split and the display
+			// (Phase keeps the whole buffer for its complex spectra)
 			staged = false;
-			if (MATRIX != 3 && vec4 && f + 1 < fEnd) // (Phase: the display still reads the whole buffer)
+			if (MATRIX != 3 && vec4 && f + 1 < fEnd)
 			{
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -648,7 +810,7 @@
 				cpAsyncCommit();
 				staged = true;
 			}
-
+#endif
 			// ---- display points: one per thread per step ----
 			float2* resOut = a.results + ((uint64_t(stream) * a.nFrames + f) * 2) * P;
 			const float poles[2] = { t.pole0, t.pole1 };
@@ -693,10 +855,10 @@
 						{
 							const int np = __ldg(t.phaseNormPos + x);
 							const int bl = first - (kLanczosSize - 1), br = mapBaseR[x];
-							const float4* wl4 = reinterpret_cast<const float4*>(t.wL + size_t(x) * kLanczosStride);
-							const float4* wr4 = reinterpret_cast<const float4*>(t.wR + size_t(x) * kLanczosStride);
-							const float4 w0 = __ldg(wl4), w1 = __ldg(wl4 + 1), w2 = __ldg(wl4 + 2);
-							const float4 r0 = __ldg(wr4), r1 = __ldg(wr4 + 1), r2 = __ldg(wr4 + 2);
+							const float4* wl4 = t.wL4 + x; // [3][P]: consecutive lanes read consecutive 16-byte words
+							const float4* wr4 = t.wR4 + x;
+							const float4 w0 = __ldg(wl4), w1 = __ldg(wl4 + P), w2 = __ldg(wl4 + 2 * P);
+							const float4 r0 = __ldg(wr4), r1 = __ldg(wr4 + P), r2 = __ldg(wr4 + 2 * P);
 							const float w[10] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y };
 							const float v[10] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y };
 							iL = iR = mL = mR = make_float2(0.f, 0.f);
@@ -742,11 +904,11 @@
 						sv.y = ph + phasePoles[k] * (sv.y - ph);
 						st[k * P + x] = sv;
 						float2 res;
-						res.x = fmaxf(__log2f(sm * sv.x) * t.deltaYLn2, t.lowerClip);
-						res.y = fmaxf(__log2f(sm * sv.y) * t.deltaYLn2, t.lowerClip);
+						res.x = fastLogScale(sm, sv.x, 1.f, t.deltaYLn2, t.lowerClip);
+						res.y = fastLogScale(sm, sv.y, 1.f, t.deltaYLn2, t.lowerClip);
 						// frame-parallel mode: the smoothing runs over ALL frames afterwards (k_phase_smooth), which needs this
 						// frame's filter input rather than the output of a filter that started from nothing
-						if (a.stateSlots) res.y = ph;
+						if (!a.chained) res.y = ph;
 						stg_stream_f2(resOut + k * P + x, res);
 					}
 					continue;
@@ -783,13 +945,23 @@
 					else
 					{
 						const int bl = first - (kLanczosSize - 1);
+#if SGZ8_AOS_WEIGHTS
 						const float4* wl4 = reinterpret_cast<const float4*>(t.wL + size_t(x) * kLanczosStride);
 						const float4 w0 = __ldg(wl4), w1 = __ldg(wl4 + 1), w2 = __ldg(wl4 + 2);
+#else
+						const float4* wl4 = t.wL4 + x; // [3][P]: consecutive lanes read consecutive 16-byte words
+						const float4 w0 = __ldg(wl4), w1 = __ldg(wl4 + P), w2 = __ldg(wl4 + 2 * P);
+#endif
 						float4 r0, r1, r2; int br = 0;
 						if constexpr (STEREO)
 						{
+#if SGZ8_AOS_WEIGHTS
 							const float4* wr4 = reinterpret_cast<const float4*>(t.wR + size_t(x) * kLanczosStride);
 							r0 = __ldg(wr4); r1 = __ldg(wr4 + 1); r2 = __ldg(wr4 + 2);
+#else
+							const float4* wr4 = t.wR4 + x;
+							r0 = __ldg(wr4); r1 = __ldg(wr4 + P); r2 = __ldg(wr4 + 2 * P);
+#endif
 							br = mapBaseR[x];
 						}
 						const float w[10] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y };
@@ -869,11 +1041,11 @@
 					// (log2(0) = -inf and NaN both fall to clip, exactly like the reference's `d > 0 ?`)
 					sv.x = fmaxf(sv.x * poles[k], lmag);
 					float2 res;
-					res.x = fmaxf(__log2f(sm * sv.x) * t.deltaYLn2, t.lowerClip);
+					res.x = fastLogScale(sm, sv.x, 1.f, t.deltaYLn2, t.lowerClip);
 					if constexpr (STEREO)
 					{
 						sv.y = fmaxf(sv.y * poles[k], rmag);
-						res.y = fmaxf(__log2f(sm * sv.y) * t.deltaYLn2, t.lowerClip);
+						res.y = fastLogScale(sm, sv.y, 1.f, t.deltaYLn2, t.lowerClip);
 					}
 					else res.y = 0.f;
 					st[k * P + x] = sv;
@@ -881,40 +1053,52 @@
 				}
 			}
 		}
-		__syncthreads();
-#if !SGZ8_STATES_GLOBAL
-		for (int i = u; i < 2 * P; i += T) stateSlot[i] = st[i];
-#endif
+		__syncthreads(); // every display point of the part's last frame has updated its state
+		for (int i = u; i < 2 * P; i += T) stateDst[i] = st[i];
+		if (publish)
+		{
+			__syncthreads();
+			if (u == 0) { __threadfence(); stRelease(a.flags + cta, a.epoch); }
+		}
+		} // parts
 	}
 
-	// Second half of the frame-parallel mode.  Every run of frames went through k_fused8 from a zero state (the first
-	// run from the stream's real one), so its results already hold the peak hold of its OWN frames.  What is missing is
-	// the hold carried in from earlier runs: s_f = max(s_(f-1) pole, m_f) unrolls to max(carry pole^k, local_f), float
-	// multiplication by the pole and the dB scale are both monotone, hence
+	// Second half of the unchained launch mode (fewer streams than CTAs).  Every part of a stream went through k_fused8
+	// from a zero state (the part that begins the stream from the stream's real one), so its results already hold the
+	// peak hold of its OWN frames.  What is missing is the hold carried in from earlier parts:
+	// s_f = max(s_(f-1) pole, m_f) unrolls to max(carry pole^k, local_f), float multiplication by the pole and the dB
+	// scale are both monotone, hence
 	//     result_f = max(local result_f, scale(carry pole^k))        bit for bit what one CTA per stream computes.
-	// k_hold_carry: one thread per display point walks the runs in order WITHOUT touching the results - it decays the
-	// carried state once per frame (the same chain of roundings), leaves in each run's slot the state that run starts
-	// from, and merges in the run's own final state.  k_hold_apply: one thread per (run, display point) then raises the
-	// stored results of its run where the decaying carry still dominates - that part is fully parallel.
-	__global__ void __launch_bounds__(128) k_hold_carry(DeviceTables t, float2* __restrict__ slotStates, float2* __restrict__ states, uint32_t nFrames,
-		uint32_t framesPerChunk, uint32_t slots, int stereo, uint32_t firstStream, uint32_t slotStride)
+	// k_seam_carry: one thread per display point walks the parts of a stream in order WITHOUT touching the results - it
+	// decays the carried state once per frame (the same chain of roundings), leaves in each part's slot the state that
+	// part starts from, and merges in the part's own final state.  k_seam_apply: one thread per (part, display point)
+	// then raises the stored results of its part where the decaying carry still dominates - fully parallel.
+	// Parts are the CTA ranges of k_fused8: cut(c) = floor(c I / G); the part of CTA c that began mid-stream keeps its
+	// state in seam[c], the part that began a stream in seam[G + c].
+	__device__ __forceinline__ uint64_t seamCut(uint64_t items, uint32_t G, uint32_t c) { return items * c / G; }
+
+	__global__ void __launch_bounds__(128) k_seam_carry(DeviceTables t, float2* __restrict__ seam, float2* __restrict__ states, uint32_t nFrames,
+		uint32_t nStreams, uint32_t G, int stereo, uint32_t firstStream)
 	{
 		const int P = int(t.P);
 		const int x = blockIdx.x * blockDim.x + threadIdx.x;
 		if (x >= P) return;
-		const uint64_t s = blockIdx.y + firstStream;
+		const uint32_t sLocal = blockIdx.y;
+		const uint64_t items = uint64_t(nStreams) * nFrames, begin = uint64_t(sLocal) * nFrames, end = begin + nFrames;
+		// the CTA whose range holds the stream's first frame
+		uint32_t c = uint32_t(begin * G / items);
+		while (c + 1 < G && seamCut(items, G, c + 1) <= begin) ++c;
+		while (c > 0 && seamCut(items, G, c) > begin) --c;
 		const float poles[2] = { t.pole0, t.pole1 };
-		float2* slot = slotStates + (s * slotStride) * 2 * P + x;
-		float2 carry[2] = { slot[0], slot[P] }; // final state of run 0 = the true state there
-		float2 own[2] = { make_float2(0.f, 0.f), make_float2(0.f, 0.f) };
-		if (slots > 1) { own[0] = slot[uint64_t(2) * P]; own[1] = slot[uint64_t(2) * P + P]; }
-		for (uint32_t c = 1; c < slots; ++c)
+		const float2* firstSlot = seam + uint64_t(G + c) * 2 * P + x;
+		float2 carry[2] = { firstSlot[0], firstSlot[P] }; // final state of the stream's first part = the true state there
+		for (++c; c < G && seamCut(items, G, c) < end; ++c)
 		{
-			float2* mine = slot + uint64_t(c) * 2 * P;
-			float2 next[2] = { own[0], own[1] };
-			if (c + 1 < slots) { next[0] = mine[uint64_t(2) * P]; next[1] = mine[uint64_t(2) * P + P]; } // fetched ahead of the decay loop
-			mine[0] = carry[0]; mine[P] = carry[1];          // what run c starts from
-			const uint32_t len = min(framesPerChunk, nFrames - c * framesPerChunk);
+			float2* mine = seam + uint64_t(c) * 2 * P + x;
+			const float2 own[2] = { mine[0], mine[P] };
+			mine[0] = carry[0]; mine[P] = carry[1]; // what this part starts from
+			const uint64_t stop = seamCut(items, G, c + 1);
+			const uint32_t len = uint32_t((stop < end ? stop : end) - seamCut(items, G, c));
 			for (uint32_t f = 0; f < len; ++f)
 			{
 #pragma unroll
@@ -925,32 +1109,34 @@
 			{
 				carry[k].x = fmaxf(carry[k].x, own[k].x);
 				if (stereo) carry[k].y = fmaxf(carry[k].y, own[k].y);
-				own[k] = next[k];
 			}
 		}
 		// (.y is only a peak hold in the stereo forms; otherwise it is left as it was - unused, or the Phase smoother's)
 #pragma unroll
 		for (int k = 0; k < 2; ++k)
 		{
-			float2* st = states + (s * 2 + k) * P + x;
+			float2* st = states + ((uint64_t(sLocal) + firstStream) * 2 + k) * P + x;
 			if (stereo) *st = carry[k]; else st->x = carry[k].x;
 		}
 	}
 
-	__global__ void __launch_bounds__(128) k_hold_apply(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ slotStates, uint32_t nFrames,
-		uint32_t framesPerChunk, uint32_t slots, int stereo, uint32_t firstStream, uint32_t slotStride)
+	__global__ void __launch_bounds__(128) k_seam_apply(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ seam, uint32_t nFrames,
+		uint32_t nStreams, uint32_t G, int stereo, uint32_t firstStream)
 	{
 		const int P = int(t.P);
 		const int x = blockIdx.x * blockDim.x + threadIdx.x;
 		if (x >= P) return;
-		const uint32_t c = blockIdx.y + 1;
-		const uint64_t s = blockIdx.z + firstStream;
+		const uint32_t c = blockIdx.y;
+		const uint64_t items = uint64_t(nStreams) * nFrames, i0 = seamCut(items, G, c), i1 = seamCut(items, G, c + 1);
+		if (i1 == i0) return;
+		const uint32_t sLocal = uint32_t(i0 / nFrames), f0 = uint32_t(i0 - uint64_t(sLocal) * nFrames);
+		if (f0 == 0) return; // the range begins a stream: nothing is carried in
+		const uint32_t f1 = uint32_t(min(uint64_t(nFrames), i1 - uint64_t(sLocal) * nFrames));
 		const float sm = t.slope[x] * t.minFracRecip;
 		const float poles[2] = { t.pole0, t.pole1 };
-		const float2* mine = slotStates + (s * slotStride + c) * 2 * P + x;
+		const float2* mine = seam + uint64_t(c) * 2 * P + x;
 		float2 carry[2] = { mine[0], mine[P] };
-		const uint32_t f0 = c * framesPerChunk, f1 = min(f0 + framesPerChunk, nFrames);
-		float2* frame = results + ((s * nFrames + f0) * 2) * P + x;
+		float2* frame = results + (((uint64_t(sLocal) + firstStream) * nFrames + f0) * 2) * P + x;
 		for (uint32_t f = f0; f < f1; ++f, frame += 2 * P)
 		{
 #pragma unroll
@@ -958,11 +1144,11 @@
 			{
 				carry[k].x *= poles[k];
 				float2 res = frame[k * P];
-				res.x = fmaxf(res.x, fmaxf(__log2f(sm * carry[k].x) * t.deltaYLn2, t.lowerClip));
+				res.x = fmaxf(res.x, fastLogScale(sm, carry[k].x, 1.f, t.deltaYLn2, t.lowerClip));
 				if (stereo)
 				{
 					carry[k].y *= poles[k];
-					res.y = fmaxf(res.y, fmaxf(__log2f(sm * carry[k].y) * t.deltaYLn2, t.lowerClip));
+					res.y = fmaxf(res.y, fastLogScale(sm, carry[k].y, 1.f, t.deltaYLn2, t.lowerClip));
 				}
 				frame[k * P] = res;
 			}
@@ -1000,7 +1186,7 @@
 				{
 					const float ph = res[j][k].y;
 					y[k] = ph + phasePoles[k] * (y[k] - ph);
-					res[j][k].y = fmaxf(__log2f(sm * y[k]) * t.deltaYLn2, t.lowerClip);
+					res[j][k].y = fastLogScale(sm, y[k], 1.f, t.deltaYLn2, t.lowerClip);
 					frame[uint64_t(j) * 2 * P + k * P] = res[j][k];
 				}
 			}

@@ -22,6 +22,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <atomic>
 #include <complex>
 #include <vector>
 
@@ -31,13 +32,12 @@
 
 namespace sgz
 {
-	// which N = 8192 fused kernel runs unless SGZ_FUSED_VARIANT=8|16 overrides it (set from measurement)
-	constexpr bool kDefaultVariant8 = true;
+	// first-pass radix of the fused kernel k_fused8<K1> for transform size N (0 = no fused kernel at this size)
+	inline int fusedK1For(uint32_t N) { return N == 16384 ? 16 : N == 8192 ? 8 : N == 4096 ? 4 : N == 2048 ? 2 : N == 1024 ? 1 : 0; }
 	// the fused kernel keeps 28 bytes per display point next to the N * 8-byte exchange buffer; one CTA must fit the
 	// 227 KB an SM can give (the resident CTAs per SM then follow from the size: 2 at N = 8192 up to 2048 points, 1 beyond)
 	inline bool fusedSharedMemoryFits(uint32_t N, uint32_t P) { return size_t(N) * 8 + 2048 + size_t(P) * 28 <= size_t(227) * 1024; }
-	constexpr uint32_t kFrameParallelCtas = 592;   // frame-parallel mode aims at four CTAs per SM slot pair (148 SMs x 2 x 2)
-	constexpr uint32_t kFrameParallelMinRun = 4;   // ... but never cuts a stream into runs shorter than this many frames
+	constexpr uint32_t kFrameParallelMinRun = 4;   // with fewer streams than resident CTAs a stream is cut into parts of at least this many frames
 
 	// ------------------------------------------------------------------------------------------
 	// error plumbing
@@ -77,10 +77,10 @@ namespace sgz
 		const int* baseR;        // [P]
 		const float* wL;         // [P][10]
 		const float* wR;         // [P][10]
+		const float4* wL4;       // [3][P] the same weights, four taps per word, point-major within a word row (fused kernel)
+		const float4* wR4;
 		const int* phaseNormPos; // [P]
 		const float2* twN;       // [N/2] W_N^k (generic FFT)
-		const float2* tw1;       // [256 + 16 R3] W_256^(n2 k1) | W_M^(n3 k1)   (fused FFT)
-		const float2* tw2;       // [16][R3] W_(16 R3)^(n3 k2)
 		const float2* tw3;       // [M]      W_N^k
 		const float2* tw8;       // k_fused8: [8][8] W_64^(ab) | [8][64] W_M^(v k1) | [8][64] W_512^(v k2)
 		const float2* resCoeff;  // [V][P] pole per vector and filter
@@ -95,6 +95,11 @@ namespace sgz
 		float invSize, deltaYRecip, minFracRecip, lowerClip;
 		float deltaYLn2; // deltaYRecip * ln 2, for the log2-based display scale of the fused kernel
 		float pole0, pole1, phasePole0, phasePole1;
+		// cosine-sum window spanning the whole transform (W == N, periodic): w(n) = winPoly(cos(2 pi n / N)), powers 0..4;
+		// winStep = (cos, sin)(2 pi / N)
+		float winPoly[5];
+		float2 winStep;
+		int winPolyOk;
 	};
 
 	__device__ __forceinline__ bool isMonoConf(int conf) { return conf <= SGZ_CH_SIDE; }
@@ -678,14 +683,14 @@ struct sgz_spectrum
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
 	int stage{ 0 }; // 0 idle, 1 prepared, 2 transformed, 3 mapped
 	uint64_t processedSamplesSinceLastFrame{ 0 }; // TransformPair.h:189 (one authority counter for all pairs, SpectrumDSP.cpp:81,93)
-	int fusedR3{ 0 };
-	bool fusedVariant8{ false }; // use k_fused8<K1> (64 K1 threads, 8 pairs per thread, radix-K1 x 8 x 8 x 8) instead of k_fused<R3> (16 R3 threads, 16 pairs per thread)
+	int fusedK1{ 0 }; // first-pass radix of the fused kernel k_fused8<K1> this handle uses (0: staged kernels only)
 	cudaStream_t copyIn{ nullptr }, copyOut{ nullptr }; // host-buffer pipeline of process_frames
 	std::vector<cudaEvent_t> events;
-	bool fusedAttrSet{ false };
-	size_t fusedSmem{ 0 };
-	uint32_t launchGridY{ 1 }; // frame runs per stream of the next k_fused8 launch (frame-parallel mode)
-	float2* dSlotStates{ nullptr }; size_t slotStatesBytes{ 0 }; // [S][runs][2][P] per-run peak-hold states of that mode
+	bool seamsOk{ false };        // the unchained launch mode is exact for this configuration (monotone hold and display scale)
+	uint32_t fusedCapacity{ 0 };  // CTAs of this handle's fused kernel the device holds at once (the launch size of k_fused8)
+	uint32_t fusedEpoch{ 0 };     // launch counter: the value a seam flag must show (no clearing between launches)
+	float2* dSeam{ nullptr };     // [2 capacity][2][P] peak-hold states at the seams between CTA ranges
+	uint32_t* dSeamFlags{ nullptr }; // [capacity]
 	void* dTrack{ nullptr }; // frequency tracker: [S] bounds in, [S] records out
 	// device-resident audio history (sgz_spectrum_history_*): per stream a ring of `ringCapacity` stereo
 	// samples stored twice back to back ([S][2 C] float2), so that any run of <= C samples ending at the
@@ -755,108 +760,87 @@ namespace
 		return SGZ_OK;
 	}
 
-	template<int R3, bool STEREO, int MATRIX>
-	int launchFusedBinpol(sgz_spectrum* h, const FusedArgs& a)
+	// FusedLaunch: what one k_fused8 launch of `a` should look like.  query = true only fills h->fusedCapacity (the
+	// number of CTAs of this handle's kernel the device holds at once), launching nothing.
+	struct FusedPlan { uint32_t ctas; bool chained; bool cooperative; };
+
+	template<void (*kern)(DeviceTables, FusedArgs)>
+	int launchFusedKernel(sgz_spectrum* h, int threads, size_t smem, FusedArgs& a, const FusedPlan* plan)
 	{
-		const size_t smem = FusedGeom<R3>::smemBytes(h->tab.P);
-		const dim3 grid(a.numStreams), block(16 * R3);
-#define SGZ_LAUNCH(BP)                                                                                              \
-		{                                                                                                           \
-			auto kern = k_fused<R3, STEREO, BP, MATRIX>;                                                            \
-			if (!h->fusedAttrSet)                                                                                   \
-			{                                                                                                       \
-				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
-				h->fusedAttrSet = true;                                                                             \
-			}                                                                                                       \
-			kern<<<grid, block, smem, h->stream>>>(h->dev, a);                                                      \
-		}
-		switch (h->cfg.bin_polation)
+		// the opt-in shared-memory limit belongs to the kernel function on a device, not to a handle: raise it once
+		// per (kernel, device) to the most any handle can ask for
+		static std::atomic<uint64_t> attrDone{ 0 };
+		const uint64_t bit = uint64_t(1) << (h->device & 63);
+		if (!(attrDone.load(std::memory_order_acquire) & bit))
 		{
-		case SGZ_BIN_NONE: SGZ_LAUNCH(SGZ_BIN_NONE); break;
-		case SGZ_BIN_LINEAR: SGZ_LAUNCH(SGZ_BIN_LINEAR); break;
-		default: SGZ_LAUNCH(SGZ_BIN_LANCZOS); break;
+			int optin = 0;
+			SGZ_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+			SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+			attrDone.fetch_or(bit, std::memory_order_release);
 		}
-#undef SGZ_LAUNCH
+		if (!plan)
+		{
+			int perSm = 0, sms = 0;
+			SGZ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, threads, smem));
+			SGZ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+			h->fusedCapacity = uint32_t(std::max(1, perSm) * std::max(1, sms));
+			return SGZ_OK;
+		}
+		a.chained = plan->chained ? 1u : 0u;
+		a.epoch = ++h->fusedEpoch;
+		a.seam = h->dSeam; a.flags = h->dSeamFlags;
+		if (plan->cooperative)
+		{
+			// CTAs wait on one another's seam flags: the launch must be co-resident
+			void* params[] = { &h->dev, &a };
+			SGZ_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kern), dim3(plan->ctas), dim3(threads), params, smem, h->stream));
+		}
+		else kern<<<plan->ctas, threads, smem, h->stream>>>(h->dev, a);
 		SGZ_CUDA(cudaGetLastError());
 		return SGZ_OK;
 	}
 
 	template<int K1, bool STEREO, int MATRIX>
-	int launchFused8Binpol(sgz_spectrum* h, const FusedArgs& a)
+	int launchFused8Binpol(sgz_spectrum* h, FusedArgs& a, const FusedPlan* plan)
 	{
 		const size_t smem = Fused8GeomT<K1>::smemBytes(h->tab.P);
-		const dim3 grid(a.numStreams, h->launchGridY), block(Fused8GeomT<K1>::T);
-#define SGZ_LAUNCH8(BP)                                                                                             \
-		{                                                                                                           \
-			auto kern = k_fused8<K1, STEREO, BP, MATRIX>;                                                           \
-			if (!h->fusedAttrSet)                                                                                   \
-			{                                                                                                       \
-				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));       \
-				h->fusedAttrSet = true;                                                                             \
-			}                                                                                                       \
-			kern<<<grid, block, smem, h->stream>>>(h->dev, a);                                                      \
-		}
+		constexpr int T = Fused8GeomT<K1>::T;
 		switch (h->cfg.bin_polation)
 		{
-		case SGZ_BIN_NONE: SGZ_LAUNCH8(SGZ_BIN_NONE); break;
-		case SGZ_BIN_LINEAR: SGZ_LAUNCH8(SGZ_BIN_LINEAR); break;
-		default: SGZ_LAUNCH8(SGZ_BIN_LANCZOS); break;
+#ifndef SGZ_HEADLINE_ONLY
+		case SGZ_BIN_NONE: return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_NONE, MATRIX>>(h, T, smem, a, plan);
+		case SGZ_BIN_LINEAR: return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_LINEAR, MATRIX>>(h, T, smem, a, plan);
+#endif
+		default: return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_LANCZOS, MATRIX>>(h, T, smem, a, plan);
 		}
-#undef SGZ_LAUNCH8
-		SGZ_CUDA(cudaGetLastError());
-		return SGZ_OK;
 	}
 
-	int launchFused(sgz_spectrum* h, const FusedArgs& a)
+	template<int K1>
+	int launchFusedK1(sgz_spectrum* h, FusedArgs& a, const FusedPlan* plan)
 	{
-		if (h->fusedR3 == 32)
+		if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<K1, true, 0>(h, a, plan);
+#ifdef SGZ_HEADLINE_ONLY // (A/B builds of the bench configuration: nothing else is instantiated)
+		return fail(SGZ_EUNSUPPORTED, "headline-only build");
+#endif
+		if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<K1, false, 2>(h, a, plan);
+		if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<K1, true, 3>(h, a, plan);
+		return h->tab.stateChannels == 2 ? launchFused8Binpol<K1, true, 1>(h, a, plan) : launchFused8Binpol<K1, false, 1>(h, a, plan);
+	}
+
+	// plan = nullptr: capacity query only (sgz_spectrum_create)
+	int launchFused(sgz_spectrum* h, FusedArgs& a, const FusedPlan* plan)
+	{
+		switch (h->fusedK1)
 		{
-			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<16, true, 0>(h, a);
-			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<16, false, 2>(h, a);
-			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<16, true, 3>(h, a);
-			return h->tab.stateChannels == 2 ? launchFused8Binpol<16, true, 1>(h, a) : launchFused8Binpol<16, false, 1>(h, a);
+#ifndef SGZ_HEADLINE_ONLY
+		case 16: return launchFusedK1<16>(h, a, plan);
+		case 4: return launchFusedK1<4>(h, a, plan);
+		case 2: return launchFusedK1<2>(h, a, plan);
+		case 1: return launchFusedK1<1>(h, a, plan);
+#endif
+		case 8: return launchFusedK1<8>(h, a, plan);
+		default: return fail(SGZ_EUNSUPPORTED, "no fused kernel for this configuration");
 		}
-		if (h->fusedR3 == 16 && h->fusedVariant8)
-		{
-			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<8, true, 0>(h, a);
-			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<8, false, 2>(h, a);
-			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<8, true, 3>(h, a);
-			return h->tab.stateChannels == 2 ? launchFused8Binpol<8, true, 1>(h, a) : launchFused8Binpol<8, false, 1>(h, a);
-		}
-		if (h->fusedR3 == 2)
-		{
-			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<1, true, 0>(h, a);
-			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<1, false, 2>(h, a);
-			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<1, true, 3>(h, a);
-			return h->tab.stateChannels == 2 ? launchFused8Binpol<1, true, 1>(h, a) : launchFused8Binpol<1, false, 1>(h, a);
-		}
-		if (h->fusedR3 == 4)
-		{
-			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<2, true, 0>(h, a);
-			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<2, false, 2>(h, a);
-			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<2, true, 3>(h, a);
-			return h->tab.stateChannels == 2 ? launchFused8Binpol<2, true, 1>(h, a) : launchFused8Binpol<2, false, 1>(h, a);
-		}
-		if (h->fusedR3 == 8 && h->fusedVariant8)
-		{
-			if (h->cfg.configuration == SGZ_CH_SEPARATE) return launchFused8Binpol<4, true, 0>(h, a);
-			if (h->cfg.configuration == SGZ_CH_COMPLEX) return launchFused8Binpol<4, false, 2>(h, a);
-			if (h->cfg.configuration == SGZ_CH_PHASE) return launchFused8Binpol<4, true, 3>(h, a);
-			return h->tab.stateChannels == 2 ? launchFused8Binpol<4, true, 1>(h, a) : launchFused8Binpol<4, false, 1>(h, a);
-		}
-		const bool stereo = h->tab.stateChannels == 2;
-		const bool passthru = h->cfg.configuration == SGZ_CH_SEPARATE;
-		if (h->fusedR3 == 16)
-		{
-			if (passthru) return launchFusedBinpol<16, true, 0>(h, a);
-			return stereo ? launchFusedBinpol<16, true, 1>(h, a) : launchFusedBinpol<16, false, 1>(h, a);
-		}
-		if (h->fusedR3 == 8)
-		{
-			if (passthru) return launchFusedBinpol<8, true, 0>(h, a);
-			return stereo ? launchFusedBinpol<8, true, 1>(h, a) : launchFusedBinpol<8, false, 1>(h, a);
-		}
-		return fail(SGZ_EUNSUPPORTED, "no fused kernel for this configuration");
 	}
 
 	size_t audioFloatsPerStream(uint64_t nSamples) { return size_t(nSamples) * 2; }
@@ -920,7 +904,6 @@ extern "C"
 			for (void* p : h->allocations) cudaFree(p);
 			if (h->dRing) cudaFree(h->dRing);
 			if (h->dTrack) cudaFree(h->dTrack);
-			if (h->dSlotStates) cudaFree(h->dSlotStates);
 			if (h->dAudioStage) cudaFree(h->dAudioStage);
 			if (h->dResultStage) cudaFree(h->dResultStage);
 			if (h->dResPartial) cudaFree(h->dResPartial);
@@ -944,7 +927,7 @@ extern "C"
 			h->cfg = *cfg; h->nStreams = n_streams; h->device = SGZ_DEVICE_NONE;
 			const int rc = buildTables(*cfg, h->tab);
 			if (rc != SGZ_OK) { delete h; return fail(rc, "invalid spectrum configuration"); }
-			h->fusedR3 = (h->tab.fusedOk && fusedSharedMemoryFits(h->tab.N, h->tab.P)) ? (h->tab.N == 16384 ? 32 : h->tab.N == 8192 ? 16 : h->tab.N == 4096 ? 8 : h->tab.N == 2048 ? 4 : 2) : 0;
+			h->fusedK1 = (h->tab.fusedOk && fusedSharedMemoryFits(h->tab.N, h->tab.P)) ? fusedK1For(h->tab.N) : 0;
 			*out = h;
 			return SGZ_OK;
 		}
@@ -974,6 +957,9 @@ extern "C"
 		d.phaseNormFinal = t.phaseNormFinal;
 		d.safeFrom = t.safeFrom;
 		d.workStride = uint32_t(std::max<size_t>(t.N, size_t(2) * t.P));
+		d.winPolyOk = t.winPolyOk ? 1 : 0;
+		for (int k = 0; k < 5; ++k) d.winPoly[k] = t.winPoly[k];
+		d.winStep = make_float2(float(std::cos(6.283185307179586476925286766559 / double(t.N))), float(std::sin(6.283185307179586476925286766559 / double(t.N))));
 
 		std::vector<int4> binmap(t.P);
 		for (uint32_t x = 0; x < t.P; ++x) binmap[x] = make_int4(t.mode[x], t.first[x], t.count[x], t.fallback[x]);
@@ -987,6 +973,24 @@ extern "C"
 		SGZ_TRY(upload(h, t.baseR, &d.baseR));
 		SGZ_TRY(upload(h, t.wL, &d.wL));
 		SGZ_TRY(upload(h, t.wR, &d.wR));
+		{
+			// fused kernel: word r of point x at [r][x], so a warp's 32 points are 512 contiguous bytes per load
+			std::vector<float4> l4(size_t(3) * t.P, make_float4(0.f, 0.f, 0.f, 0.f)), r4(l4);
+			if (t.wL.size() >= size_t(t.P) * kLanczosStride)
+				for (uint32_t x = 0; x < t.P; ++x)
+					for (int r = 0; r < 3; ++r)
+					{
+						const float* wl = &t.wL[size_t(x) * kLanczosStride + 4 * r];
+						l4[size_t(r) * t.P + x] = make_float4(wl[0], wl[1], wl[2], wl[3]);
+						if (t.wR.size() >= size_t(t.P) * kLanczosStride)
+						{
+							const float* wr = &t.wR[size_t(x) * kLanczosStride + 4 * r];
+							r4[size_t(r) * t.P + x] = make_float4(wr[0], wr[1], wr[2], wr[3]);
+						}
+					}
+			SGZ_TRY(upload(h, l4, &d.wL4));
+			SGZ_TRY(upload(h, r4, &d.wR4));
+		}
 		SGZ_TRY(upload(h, t.phaseNormPos, &d.phaseNormPos));
 		{
 			std::vector<float2> coeff(t.resCoeffReal.size());
@@ -1017,38 +1021,26 @@ extern "C"
 			tw8.insert(tw8.end(), A.begin(), A.end()); tw8.insert(tw8.end(), B.begin(), B.end()); tw8.insert(tw8.end(), C.begin(), C.end());
 			SGZ_TRY(upload(h, tw8, &d.tw8));
 		}
-		h->fusedR3 = 0;
-		if (t.fusedOk && fusedSharedMemoryFits(t.N, t.P))
-		{
-			const int R3 = t.N == 16384 ? 32 : t.N == 8192 ? 16 : t.N == 4096 ? 8 : t.N == 2048 ? 4 : 2; // R3 = 32, 4, 2 (N = 16384, 2048, 1024) exist as k_fused8 only
-			const int T = 16 * R3, M = 16 * T;
-			// tw1 = [A | B]: A[k1][n2] = W_256^(n2 k1) (256 entries), B[k1][n3] = W_M^(n3 k1) (16 R3 entries)
-			std::vector<float2> tw1(256 + size_t(16) * R3);
-			{
-				std::vector<uint64_t> eA(256), eB(size_t(16) * R3);
-				for (int k1 = 0; k1 < 16; ++k1) for (int n2 = 0; n2 < 16; ++n2) eA[k1 * 16 + n2] = uint64_t(n2) * k1;
-				for (int k1 = 0; k1 < 16; ++k1) for (int n3 = 0; n3 < R3; ++n3) eB[size_t(k1) * R3 + n3] = uint64_t(n3) * k1;
-				const auto A = twiddleTable(eA.size(), 256.0, eA), B = twiddleTable(eB.size(), double(M), eB);
-				std::copy(A.begin(), A.end(), tw1.begin());
-				std::copy(B.begin(), B.end(), tw1.begin() + 256);
-			}
-			std::vector<uint64_t> e2(size_t(16) * R3);
-			for (int k2 = 0; k2 < 16; ++k2) for (int n3 = 0; n3 < R3; ++n3) e2[size_t(k2) * R3 + n3] = uint64_t(n3) * k2;
-			SGZ_TRY(upload(h, tw1, &d.tw1));
-			SGZ_TRY(upload(h, twiddleTable(e2.size(), double(16 * R3), e2), &d.tw2));
-			{
-				const char* variant = std::getenv("SGZ_FUSED_VARIANT");
-				h->fusedVariant8 = variant ? (std::strcmp(variant, "8") == 0) : kDefaultVariant8;
-			}
-			h->fusedR3 = ((R3 <= 4 || R3 == 32 || cfg->configuration == SGZ_CH_COMPLEX || cfg->configuration == SGZ_CH_PHASE) && !h->fusedVariant8) ? 0 : R3; // k_fused8 only
-			h->fusedSmem = R3 == 16 ? FusedGeom<16>::smemBytes(t.P) : FusedGeom<8>::smemBytes(t.P);
-		}
+		h->fusedK1 = (t.fusedOk && fusedSharedMemoryFits(t.N, t.P)) ? fusedK1For(t.N) : 0;
 		const size_t workPerStream = std::max<size_t>(t.N, size_t(2) * t.P);
 		SGZ_TRY(allocZero(h, size_t(n_streams) * (t.N + 1), &h->dCsf));
 		SGZ_TRY(allocZero(h, size_t(n_streams) * workPerStream, &h->dWork));
 		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dStates));
 		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dResults));
 		if (cfg->algo == SGZ_ALGO_RSNT) SGZ_TRY(allocZero(h, size_t(n_streams) * t.stateChannels * t.resonatorVectors * t.P, &h->dResState));
+		if (h->fusedK1 != 0)
+		{
+			FusedArgs none{};
+			SGZ_TRY(launchFused(h, none, nullptr)); // capacity query only
+			SGZ_TRY(allocZero(h, size_t(2) * h->fusedCapacity * 2 * t.P, &h->dSeam));
+			SGZ_TRY(allocZero(h, size_t(h->fusedCapacity), &h->dSeamFlags));
+			// carrying the hold across zero-started parts relies on x -> x * pole and on the dB scale being monotone
+			// non-decreasing: non-negative poles and slope, an upright dB range, and a clip value below every reachable one
+			h->seamsOk = cfg->pole[0] >= 0.f && cfg->pole[1] >= 0.f && cfg->slope_b >= 0.0 && d.deltaYLn2 > 0.f
+				&& d.lowerClip <= -104.f * d.deltaYRecip;
+		}
+		// the tables and cleared buffers above went through the legacy stream; the handle's own stream is non-blocking
+		if (cudaDeviceSynchronize() != cudaSuccess) return bail(fail(SGZ_ECUDA, "cudaDeviceSynchronize failed in create"));
 #undef SGZ_TRY
 		*out = h;
 		return SGZ_OK;
@@ -1063,7 +1055,7 @@ extern "C"
 		out->break_point = h->tab.P;
 		for (uint32_t x = 0; x < h->tab.P; ++x) if (h->tab.mode[x] == 1) { out->break_point = x; break; }
 		out->window_kernel_scale = h->tab.windowKernelScale; out->inv_size = h->tab.invSize; out->freq_to_bin = h->tab.freqToBin;
-		out->resonator_vectors = h->tab.resonatorVectors; out->device = h->device; out->fused_available = h->fusedR3 != 0;
+		out->resonator_vectors = h->tab.resonatorVectors; out->device = h->device; out->fused_available = h->fusedK1 != 0;
 		return SGZ_OK;
 	}
 
@@ -1522,59 +1514,37 @@ extern "C"
 	// kernel of chunk c and the download of chunk c-1 overlap (PCIe is full duplex); results are
 	// identical to the single launch because streams are independent.
 	// Launches the fused kernel for the streams [a.firstStream, a.firstStream + a.numStreams) on the handle's stream.
-	// Few streams, many frames (a long recording rather than a wall of channels, or one chunk of the host-buffer
-	// pipeline): one CTA per stream would leave the GPU idle, so the frames of a stream are cut into runs that CTAs
-	// process side by side; the only frame-to-frame dependency, the peak hold, is carried from run to run afterwards
-	// by k_hold_carry / k_hold_apply (bit-identical results).
+	// One k_fused8 launch over streams [a.firstStream, + a.numStreams) x a.nFrames frames.  The grid is the number of CTAs
+	// the device holds at once (sgz_fused.cuh, FusedArgs): with at least that many streams the seams between CTA ranges
+	// are chained inside the kernel; with fewer (a long recording rather than a wall of channels, or one chunk of the
+	// host-buffer pipeline) parts start from zero and k_seam_carry / k_seam_apply carry the peak hold across afterwards.
 	static int launchFusedFrames(sgz_spectrum* h, FusedArgs a)
 	{
-		const uint32_t P = h->tab.P, n_frames = a.nFrames, nS = a.numStreams;
-		uint32_t chunks = 1;
-		// (carrying the hold across runs relies on x -> x * pole and on the dB scale being monotone non-decreasing:
-		// non-negative poles and slope, an upright dB range)
-		const bool polesOk = h->cfg.pole[0] >= 0.f && h->cfg.pole[1] >= 0.f && h->cfg.slope_b >= 0.0 && h->dev.deltaYLn2 > 0.f;
-		if (h->fusedVariant8 && polesOk && nS <= 65535 && !std::getenv("SGZ_NO_FRAME_PARALLEL"))
+		const uint32_t P = h->tab.P, F = a.nFrames, nS = a.numStreams;
+		const uint64_t items = uint64_t(nS) * F;
+		const uint32_t capacity = std::max<uint32_t>(1, h->fusedCapacity);
+		FusedPlan plan{ nS, true, false };
+#ifdef SGZ8_PER_STREAM_GRID
+		if (false)
+#else
+		if (nS >= capacity)
+#endif
 		{
-			const uint32_t wanted = (kFrameParallelCtas + nS - 1) / nS;
-			chunks = std::max<uint32_t>(1, std::min<uint32_t>(wanted, n_frames / kFrameParallelMinRun));
-			if (chunks > 65535) chunks = 65535;
+			plan.ctas = capacity;                 // balanced ranges of >= one stream's worth of frames each
+			plan.cooperative = nS > capacity;     // some range ends mid-stream: CTAs wait on their neighbour's flag
 		}
-		uint32_t slots = 1;
-		if (chunks > 1)
+		else if (h->seamsOk && items / kFrameParallelMinRun > nS)
 		{
-			a.framesPerChunk = (n_frames + chunks - 1) / chunks;
-			slots = (n_frames + a.framesPerChunk - 1) / a.framesPerChunk;
+			plan.ctas = uint32_t(std::min<uint64_t>(capacity, items / kFrameParallelMinRun));
+			plan.chained = false;
 		}
-		if (slots <= 1)
-		{
-			a.framesPerChunk = 0; a.stateSlots = 0;
-			return launchFused(h, a);
-		}
-		// per-run state slots, [all streams][slots][2][P]: slot 0 of every stream starts from the stream's state, the others from zero
-		// (the slot stride is the largest run count this frame count can give, so that concurrent chunk launches of one
-		// call never overlap whatever their own run count)
-		const uint32_t stride = std::max<uint32_t>(1, n_frames / kFrameParallelMinRun);
-		const size_t slotBytes = size_t(2) * P * sizeof(float2), need = size_t(h->nStreams) * stride * slotBytes;
-		if (h->slotStatesBytes < need)
-		{
-			if (h->dSlotStates) { SGZ_CUDA(cudaDeviceSynchronize()); cudaFree(h->dSlotStates); h->dSlotStates = nullptr; h->slotStatesBytes = 0; }
-			SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dSlotStates), need));
-			h->slotStatesBytes = need;
-		}
-		float2* slotBase = h->dSlotStates + size_t(a.firstStream) * stride * 2 * P;
-		SGZ_CUDA(cudaMemsetAsync(slotBase, 0, size_t(nS) * stride * slotBytes, h->stream));
-		SGZ_CUDA(cudaMemcpy2DAsync(slotBase, stride * slotBytes, h->dStates + size_t(a.firstStream) * 2 * P, slotBytes, slotBytes, nS, cudaMemcpyDeviceToDevice, h->stream));
-		float2* const results = a.results;
-		a.states = h->dSlotStates; a.stateSlots = stride;
-		h->launchGridY = slots;
-		const int rc = launchFused(h, a);
-		h->launchGridY = 1;
-		if (rc != SGZ_OK) return rc;
+		int rc = launchFused(h, a, &plan);
+		if (rc != SGZ_OK || plan.chained) return rc;
 		const bool phase = h->cfg.configuration == SGZ_CH_PHASE; // .x is a peak hold like the others, .y a smoother (k_phase_smooth below)
-		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO argument launchFused picks
-		k_hold_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSlotStates, h->dStates, n_frames, a.framesPerChunk, slots, stereoFlag, a.firstStream, stride);
-		k_hold_apply<<<dim3((P + 127) / 128, slots - 1, nS), 128, 0, h->stream>>>(h->dev, results, h->dSlotStates, n_frames, a.framesPerChunk, slots, stereoFlag, a.firstStream, stride);
-		if (phase) k_phase_smooth<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, results, h->dStates, n_frames, a.firstStream);
+		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO form of the hold
+		k_seam_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSeam, h->dStates, F, nS, plan.ctas, stereoFlag, a.firstStream);
+		k_seam_apply<<<dim3((P + 127) / 128, plan.ctas), 128, 0, h->stream>>>(h->dev, a.results, h->dSeam, F, nS, plan.ctas, stereoFlag, a.firstStream);
+		if (phase) k_phase_smooth<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, a.results, h->dStates, F, a.firstStream);
 		SGZ_CUDA(cudaGetLastError());
 		return SGZ_OK;
 	}
@@ -1645,7 +1615,7 @@ extern "C"
 		if (layout == SGZ_LAYOUT_INTERLEAVED && ((stream_stride & 1) || (reinterpret_cast<uintptr_t>(audio) & 7)))
 			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
 		SGZ_GUARD(h);
-		if (!rsnt && h->fusedR3 != 0 && mem == SGZ_MEM_HOST && results_mem == SGZ_MEM_HOST && h->nStreams >= 8)
+		if (!rsnt && h->fusedK1 != 0 && mem == SGZ_MEM_HOST && results_mem == SGZ_MEM_HOST && h->nStreams >= 8)
 			return processFramesPipelined(h, audio, layout, n_samples, stream_stride, hop, n_frames, results);
 		const float* dAudio = nullptr;
 		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);
@@ -1671,7 +1641,7 @@ extern "C"
 					size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
 			}
 		}
-		else if (h->fusedR3 != 0)
+		else if (h->fusedK1 != 0)
 		{
 			FusedArgs a{};
 			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;

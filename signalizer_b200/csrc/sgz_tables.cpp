@@ -130,6 +130,17 @@ namespace sgz
 				sum += static_cast<double>(t.window[n]);
 			}
 			t.windowKernelScale = static_cast<float>(sum > 0 ? double(W) / sum : 1.0);
+			// the same window as a polynomial in cos(2 pi n / N) (Chebyshev T_k -> powers), for kernels that would rather
+			// evaluate it than read it: only when the window spans the transform in its periodic shape
+			t.winPolyOk = W == N && cfg.window_shape == SGZ_WINSHAPE_PERIODIC && terms.size() <= 5;
+			if (t.winPolyOk)
+			{
+				static const double cheb[5][5] = { { 1, 0, 0, 0, 0 }, { 0, 1, 0, 0, 0 }, { -1, 0, 2, 0, 0 }, { 0, -3, 0, 4, 0 }, { 1, 0, -8, 0, 8 } };
+				double p[5] = { 0, 0, 0, 0, 0 }, sg = 1;
+				for (std::size_t k = 0; k < terms.size(); ++k, sg = -sg)
+					for (int j = 0; j < 5; ++j) p[j] += sg * terms[k] * cheb[k][j];
+				for (int j = 0; j < 5; ++j) t.winPoly[j] = static_cast<float>(p[j]);
+			}
 		}
 
 		// scalars of mapToLinearSpace, TransformDSP.inl:522-540

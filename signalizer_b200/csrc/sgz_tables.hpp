@@ -55,6 +55,9 @@ namespace sgz
 		uint32_t safeFrom{ 0 };
 		// true when the fused kernel reproduces the staged result for this configuration
 		bool fusedOk{ false };
+		// cosine-sum window spanning the whole transform in its periodic shape: window[n] = sum_k winPoly[k] cos^k(2 pi n / N)
+		bool winPolyOk{ false };
+		float winPoly[5]{ 0, 0, 0, 0, 0 };
 
 		uint32_t resonatorVectors{ 1 };
 		std::vector<float> resCoeffReal, resCoeffImag; // [V][P]

@@ -218,10 +218,10 @@ def test_fused_phase_configuration(bp, size, view):
 @pytest.mark.parametrize("kw", [dict(), dict(window_size=4096, configuration=_abi.CH_LEFT, bin_polation=_abi.BIN_LINEAR),
                                 dict(window_size=2048, configuration=_abi.CH_COMPLEX), dict(window_size=16384, configuration=_abi.CH_MIDSIDE, bin_polation=_abi.BIN_NONE),
                                 dict(configuration=_abi.CH_PHASE), dict(window_size=4096, configuration=_abi.CH_PHASE, bin_polation=_abi.BIN_LINEAR)])
-def test_frame_parallel_mode_gives_the_same_bits(kw, monkeypatch):
-    """few streams x many frames: the frames of a stream are spread over CTAs and the peak hold is applied by a scan
-    afterwards; results, states and the handle's last results must equal the one-CTA-per-stream launch bit for bit,
-    also across two calls (state carried)"""
+def test_frame_parallel_mode_gives_the_same_bits(kw):
+    """few streams x many frames: the frames of a stream are spread over CTAs (parts that start from a zero state) and the
+    peak hold is carried across the seams afterwards; results, states and the handle's last results must equal frame-by-
+    frame calls (one frame per stream per launch: no seams) bit for bit, also across two calls (state carried)"""
     import torch
     cfg = _abi.default_config(**kw)
     S, F, hop = 2, 37, cfg.window_size // 8
@@ -229,12 +229,20 @@ def test_frame_parallel_mode_gives_the_same_bits(kw, monkeypatch):
     first, second = audio[:, :signals.frames_length(cfg.window_size, hop, F)], audio[:, F * hop:]
     runs = {}
     for mode in ("parallel", "serial"):
-        if mode == "serial":
-            monkeypatch.setenv("SGZ_NO_FRAME_PARALLEL", "1")
         g = TransformPairBatch(cfg, S)
         d1, d2 = torch.from_numpy(np.ascontiguousarray(first)).cuda(), torch.from_numpy(np.ascontiguousarray(second)).cuda()
-        a = g.process_frames(d1, hop, F)   # device buffers: the call returns before the kernels have run, so the inputs stay alive
-        b = g.process_frames(d2, hop, F)
+        if mode == "parallel":
+            a = g.process_frames(d1, hop, F)   # device buffers: the call returns before the kernels have run, so the inputs stay alive
+            b = g.process_frames(d2, hop, F)
+        else:
+            W = cfg.window_size   # (the slices stay alive until the handle's stream has been drained)
+            s1 = [d1[:, f * hop:f * hop + W].contiguous() for f in range(F)]
+            s2 = [d2[:, f * hop:f * hop + W].contiguous() for f in range(F)]
+            torch.cuda.synchronize()
+            a = [g.process_frames(x, hop, 1) for x in s1]
+            b = [g.process_frames(x, hop, 1) for x in s2]
+            g.synchronize()
+            a, b = torch.cat(a, dim=1), torch.cat(b, dim=1)
         g.synchronize()
         a, b = a.cpu().numpy(), b.cpu().numpy()
         runs[mode] = (a, b, g.get_states(0), g.get_states(1), g.get_results(0), g.get_results(1))
@@ -244,6 +252,37 @@ def test_frame_parallel_mode_gives_the_same_bits(kw, monkeypatch):
     used = 2 if cfg.configuration in (_abi.CH_SEPARATE, _abi.CH_MIDSIDE) else 1
     last = -2 if cfg.configuration == _abi.CH_PHASE else None   # (Phase next to Nyquist: see test_fused_phase_configuration)
     compare_frames(runs["parallel"][0][..., :last, :used], want[..., :last, :used], cfg, "frame-parallel vs oracle")
+
+
+@pytest.mark.parametrize("kw,S", [(dict(), 301), (dict(window_size=1024, bin_polation=_abi.BIN_LINEAR), 811),
+                                  (dict(window_size=4096, configuration=_abi.CH_PHASE), 471), (dict(window_size=2048, configuration=_abi.CH_LEFT), 700)])
+def test_balanced_ranges_chain_the_seams(kw, S):
+    """more streams than resident CTAs: the launch gives every CTA the same number of frames, so most ranges end
+    mid-stream; the head of such a stream runs first on one CTA, its state is handed to the next CTA, which runs the tail.
+    Must equal frame-by-frame calls (whole streams per CTA, nothing to hand over) bit for bit, and the oracle."""
+    import torch
+    cfg = _abi.default_config(**kw)
+    F, hop, W = 5, cfg.window_size // 4, cfg.window_size
+    audio = frames_case(cfg, S, F, hop)
+    d = torch.from_numpy(np.ascontiguousarray(audio)).cuda()
+    g = TransformPairBatch(cfg, S)
+    whole = g.process_frames(d, hop, F)
+    g.synchronize()
+    st = (g.get_states(0), g.get_states(1), g.get_results(0), g.get_results(1))
+    g2 = TransformPairBatch(cfg, S)
+    slices = [d[:, f * hop:f * hop + W].contiguous() for f in range(F)]
+    torch.cuda.synchronize()
+    steps = [g2.process_frames(x, hop, 1) for x in slices]
+    g2.synchronize()
+    steps = torch.cat(steps, dim=1)
+    np.testing.assert_array_equal(whole.cpu().numpy(), steps.cpu().numpy())
+    for x, y in zip(st, (g2.get_states(0), g2.get_states(1), g2.get_results(0), g2.get_results(1))):
+        np.testing.assert_array_equal(x, y)
+    sample = np.r_[0:3, S // 2:S // 2 + 3, S - 3:S]
+    want = OracleSpectrum(cfg, len(sample)).process_frames(audio[sample], hop, F)
+    used = 2 if cfg.configuration in (_abi.CH_SEPARATE, _abi.CH_MIDSIDE) else 1
+    last = -2 if cfg.configuration == _abi.CH_PHASE else None
+    compare_frames(whole.cpu().numpy()[sample][..., :last, :used], want[..., :last, :used], cfg, "chained seams vs oracle")
 
 
 VIEWS = [dict(view_scaling=_abi.VIEW_LINEAR), dict(view_left=0.2, view_right=0.4), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.03),
