@@ -386,6 +386,20 @@ int  sgz_vscope_meters(sgz_context* ctx, const float* audio, int mem, int layout
                        uint64_t n_samples, uint64_t stream_stride, float envelope_coeff,
                        float stereo_coeff, float second_stereo_filter_speed, sgz_vscope_filters* filters);
 
+/* Replaces `VectorScope::runPeakFilter` (VectorscopeRendering.cpp:826-889): the
+ * auto-gain envelope of the vectorscope.  Per stream: the largest |L| and |R|
+ * of the window - whole groups of 8 samples only, like the reference's AVX
+ * loop (:857-868, its remainder is a TODO at :870) - squared and folded into
+ * filters[s].envelope[0 / 1] with coeff = envelope_coeff^(n_samples *
+ * delta_time) (:840-842; delta_time = openGLDeltaTime(), seconds per rendered
+ * frame), then envelope_gain[s] = 1 / max(sqrt(e0), sqrt(e1)), written only
+ * when it is a normal number (:882-888; otherwise the previous gain stays).
+ * The result is what sgz_vscope_config.gain takes in the peak envelope mode
+ * (gain = envelopeGain * userGain, VectorscopeRendering.cpp:451,512).  filters, envelope_gain: HOST, in/out. */
+int  sgz_vscope_peak_envelope(sgz_context* ctx, const float* audio, int mem, int layout, uint32_t n_streams,
+                              uint64_t n_samples, uint64_t stream_stride, float envelope_coeff, double delta_time,
+                              sgz_vscope_filters* filters, double* envelope_gain);
+
 /* ---- Oscilloscope ---------------------------------------------------------
  * Replaces the Lanczos branch of `Oscilloscope::drawWavePlot`
  * (Source/Oscilloscope/OscilloscopeRendering.cpp:790-891): windowed-sinc
@@ -415,6 +429,40 @@ int  sgz_scope_trigger(sgz_context* ctx, int mode, int channel, const float* aud
                        uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride, double threshold,
                        double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* states,
                        uint64_t* peaks, uint32_t* counts, uint32_t max_peaks);
+
+/* Replaces `TriggeringProcessor::update` and `::processMutating`
+ * (Source/Oscilloscope/StreamPreprocessing.h:54-75, :78-206): the consumer of
+ * the trigger positions above.  Per stream and callback block it decides how
+ * many samples go into the back buffer before each window, and which window
+ * (first sample, length) is swapped to the front buffer once the samples
+ * around a trigger position are complete.  Integer bookkeeping on the host,
+ * bit-exact; the reference's `audioProcessing(..., channelData.back)` (:91) and
+ * `channelData.swapBuffers(cappedSize, -bufferedSamples)` (:194) are reported
+ * as events for the caller to act on, in order:
+ *   SGZ_WINDOW_PROCESS  `size` samples starting at steady clock `origin` are
+ *                       appended to the back buffer (`buffered` = samples the
+ *                       back buffer held before them);
+ *   SGZ_WINDOW_SWAP     the `size` samples starting at clock `origin`
+ *                       (= frontOrigin) become the displayed window; `buffered`
+ *                       = bufferedSamples, i.e. swapBuffers' offset is -buffered.
+ * states: HOST [stream] in/out (zero-initialise; set window_size /
+ * window_changed as `setSettings` does, :45-52).  peaks: HOST
+ * [stream][max_peaks], the queue front first; peak_counts: in = queued
+ * positions (append what sgz_scope_trigger found), out = positions left, which
+ * are moved to the front of the stream's row.  events: HOST
+ * [stream][max_events]; event_counts: the number produced (a stream that
+ * needs more than max_events returns SGZ_EINVAL with its state untouched).
+ * steady_clock: the block's first sample (ctx.getPlayhead().getSteadyClock()). */
+enum { SGZ_WINDOW_PROCESS = 0, SGZ_WINDOW_SWAP = 1 };
+typedef struct sgz_scope_window_state {
+    double   window_size;                 /* windowSize */
+    uint64_t old_peak, current_peak, buffered_samples, front_origin, steady_clock;
+    int32_t  is_working_on_peak, window_changed;
+} sgz_scope_window_state;
+typedef struct sgz_scope_window_event { uint64_t origin, size, buffered; uint32_t kind, reserved; } sgz_scope_window_event;
+int  sgz_scope_trigger_windows(uint32_t n_streams, sgz_scope_window_state* states, uint64_t* peaks, uint32_t* peak_counts,
+                               uint32_t max_peaks, uint64_t steady_clock, uint64_t n_samples,
+                               sgz_scope_window_event* events, uint32_t* event_counts, uint32_t max_events);
 /* Replaces `calculateFundamentalPeriod` + `calculateTriggeringOffset`
  * (Source/Oscilloscope/OscilloscopeDSP.inl:61-308, Spectral trigger mode):
  * 8192-point float64 FFT of the newest samples, fundamental pick with

@@ -276,6 +276,16 @@ class OracleScope:
         self.lib.sgzo_vscope_meters(p, layout, S, n, stride, envelope_coeff, stereo_coeff, second_speed, filters)
         return filters
 
+    def vscope_peak_envelope(self, audio, filters, gains, envelope_coeff, delta_time, layout=_abi.LAYOUT_INTERLEAVED):
+        a, p = _f32(audio)
+        S, n, stride = _geom(a, layout)
+        g = np.ascontiguousarray(gains, dtype=np.float64)
+        self.lib.sgzo_vscope_peak_envelope.restype = None
+        self.lib.sgzo_vscope_peak_envelope.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_uint64, C.c_float, C.c_double,
+                                                       C.c_void_p, C.POINTER(C.c_double)]
+        self.lib.sgzo_vscope_peak_envelope(p, layout, S, n, stride, envelope_coeff, delta_time, C.addressof(filters), g.ctypes.data_as(C.POINTER(C.c_double)))
+        return filters, g
+
     def scope_resample_count(self, cfg):
         return int(self.lib.sgzo_scope_resample_count(C.byref(cfg)))
 

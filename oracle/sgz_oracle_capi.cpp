@@ -567,6 +567,36 @@ extern "C"
 			for (uint32_t k = 0; k < found.size() && k < maxPeaks; ++k) peaks[uint64_t(s) * maxPeaks + k] = found[k];
 		}
 	}
+	// TriggeringProcessor::update + processMutating per stream; same argument meaning as sgz_scope_trigger_windows
+	int sgzo_scope_trigger_windows(uint32_t S, sgz_scope_window_state* states, uint64_t* peaks, uint32_t* peakCounts, uint32_t maxPeaks, uint64_t steadyClock,
+		uint64_t n, sgz_scope_window_event* events, uint32_t* eventCounts, uint32_t maxEvents)
+	{
+		for (uint32_t s = 0; s < S; ++s)
+		{
+			TriggeringProcessor tp;
+			const sgz_scope_window_state& in = states[s];
+			tp.windowSize = in.window_size; tp.windowChanged = in.window_changed != 0;
+			tp.oldPeak = in.old_peak; tp.currentPeak = in.current_peak; tp.bufferedSamples = in.buffered_samples;
+			tp.frontOrigin = in.front_origin; tp.steadyClock = in.steady_clock; tp.isWorkingOnPeak = in.is_working_on_peak != 0;
+			uint64_t* row = peaks + size_t(s) * maxPeaks;
+			tp.peaks.assign(row, row + peakCounts[s]);
+			std::vector<WindowEvent> found;
+			tp.update(steadyClock);
+			tp.processMutating(static_cast<std::size_t>(n), found);
+			if (found.size() > maxEvents) return SGZ_EINVAL;
+			for (size_t k = 0; k < found.size(); ++k)
+				events[size_t(s) * maxEvents + k] = sgz_scope_window_event{ found[k].origin, found[k].size, found[k].buffered, uint32_t(found[k].kind), 0u };
+			eventCounts[s] = uint32_t(found.size());
+			sgz_scope_window_state out{};
+			out.window_size = tp.windowSize; out.window_changed = tp.windowChanged ? 1 : 0;
+			out.old_peak = tp.oldPeak; out.current_peak = tp.currentPeak; out.buffered_samples = tp.bufferedSamples;
+			out.front_origin = tp.frontOrigin; out.steady_clock = tp.steadyClock; out.is_working_on_peak = tp.isWorkingOnPeak ? 1 : 0;
+			states[s] = out;
+			peakCounts[s] = uint32_t(tp.peaks.size());
+			std::copy(tp.peaks.begin(), tp.peaks.end(), row);
+		}
+		return SGZ_OK;
+	}
 	void sgzo_scope_period(const sgz_scope_period_params* prm, const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride,
 		sgz_scope_period_state* states, sgz_scope_period_result* results)
 	{
@@ -700,6 +730,21 @@ extern "C" void sgzo_scope_peak_envelope(int channelMode, const float* audio, in
 			else { l[i] = base[i]; r[i] = base[n + i]; }
 		}
 		gain[s] = sgz_oracle::runPeakFilter(channelMode, l.data(), r.data(), n, coeff, env + 2 * size_t(s));
+	}
+}
+extern "C" void sgzo_vscope_peak_envelope(const float* audio, int layout, uint32_t S, uint64_t n, uint64_t stride, float envelopeCoeff, double deltaTime,
+	sgz_vscope_filters* filters, double* gain)
+{
+	std::vector<float> l(n), r(n);
+	for (uint32_t s = 0; s < S; ++s)
+	{
+		const float* base = audio + size_t(s) * stride;
+		for (uint64_t i = 0; i < n; ++i)
+		{
+			if (layout == SGZ_LAYOUT_INTERLEAVED) { l[i] = base[2 * i]; r[i] = base[2 * i + 1]; }
+			else { l[i] = base[i]; r[i] = base[n + i]; }
+		}
+		sgz_oracle::runVectorscopePeakFilter(l.data(), r.data(), n, envelopeCoeff, deltaTime, filters[s].envelope, gain + s);
 	}
 }
 // the crossover alone, for the tests that pin it against scipy: bands [n][3]

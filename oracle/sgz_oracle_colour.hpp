@@ -188,4 +188,35 @@ namespace sgz_oracle
 		for (int c = 0; c < 2; ++c) start = std::max(start, std::sqrt(env[c]));
 		return 1.0 / start;
 	}
+	// VectorScope::runPeakFilter (Source/Vectorscope/VectorscopeRendering.cpp:826-889) for one stereo pair.
+	// env[2] = processor->filters.envelope (relaxed_atomic<float>), gain = processor->envelopeGain (in/out).
+	inline void runVectorscopePeakFilter(const float* left, const float* right, std::size_t numSamples, float envelopeCoeff, double openGLDeltaTime,
+		float* env, double* gain)
+	{
+		double currentEnvelope = 1;
+		{
+			// :840-842
+			double power = numSamples * openGLDeltaTime;
+			double coeff = std::pow(envelopeCoeff, power);
+			// :845-868: vLMax / vRMax over whole vectors of 8 floats, |x| through the sign mask
+			float lmax[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }, rmax[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+			const std::size_t loopIncrement = 8;
+			std::size_t stop = numSamples - (numSamples & (loopIncrement - 1));
+			for (std::size_t i = 0; i < stop; i += loopIncrement)
+				for (std::size_t k = 0; k < loopIncrement; ++k)
+				{
+					lmax[k] = std::max(std::fabs(left[i + k]), lmax[k]);
+					rmax[k] = std::max(std::fabs(right[i + k]), rmax[k]);
+				}
+			// :874-880
+			double highestLeft = *std::max_element(lmax, lmax + 8);
+			double highestRight = *std::max_element(rmax, rmax + 8);
+			env[0] = static_cast<float>(std::max(env[0] * coeff, highestLeft * highestLeft));
+			env[1] = static_cast<float>(std::max(env[1] * coeff, highestRight * highestRight));
+			// :882: std::sqrt of the float states
+			currentEnvelope = 1.0 / std::max(std::sqrt(env[0]), std::sqrt(env[1]));
+		}
+		// :885-888
+		if (std::isnormal(currentEnvelope)) *gain = currentEnvelope;
+	}
 }

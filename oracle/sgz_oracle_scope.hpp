@@ -9,6 +9,7 @@
 #include <cmath>
 #include <complex>
 #include <cstdint>
+#include <deque>
 #include <vector>
 
 #include "sgz_oracle.hpp"
@@ -236,6 +237,145 @@ namespace sgzo
 			}
 		}
 	}
+
+	// TriggeringProcessor — Oscilloscope/StreamPreprocessing.h:40-226: turns the queue of trigger positions into display
+	// windows.  `processIntoBackBuffer(samples)` (audio appended to the back buffer) and
+	// `channelData.swapBuffers(cappedSize, -bufferedSamples)` (a window copied from the back to the front buffer) are
+	// recorded as events instead of being executed; everything else is the reference's bookkeeping, with its types
+	// (std::ceil / halfSize in double, the clocks in std::uint64_t, the mixed conversions of :146-191 as written).
+	struct WindowEvent
+	{
+		enum Kind { Process = 0, Swap = 1 };
+		int kind;
+		uint64_t origin;   // Process: steadyClock before the samples; Swap: frontOrigin, the clock of the window's first sample
+		uint64_t size;     // Process: samples; Swap: cappedSize
+		uint64_t buffered; // bufferedSamples at the event (Swap: the offset handed to swapBuffers is -buffered)
+	};
+
+	struct TriggeringProcessor
+	{
+		double windowSize{ 0 };
+		bool windowChanged{ false };
+		uint64_t oldPeak{ 0 }, currentPeak{ 0 }, bufferedSamples{ 0 }, frontOrigin{ 0 }, steadyClock{ 0 };
+		std::deque<uint64_t> peaks;
+		bool isWorkingOnPeak{ false };
+
+		// :45-52 (the part that concerns the window)
+		void setWindowSize(double newWindowSize)
+		{
+			windowChanged = std::ceil(newWindowSize) != std::ceil(windowSize);
+			windowSize = newWindowSize;
+		}
+
+		// :54-75
+		void update(uint64_t currentSteadyClock)
+		{
+			steadyClock = currentSteadyClock;
+			if (windowChanged)
+			{
+				windowChanged = false;
+				if (isWorkingOnPeak && peaks.size()) peaks.pop_front(); // (the reference pops unconditionally)
+				while (peaks.size() && peaks.front() < currentSteadyClock) peaks.pop_front();
+				bufferedSamples = currentPeak = oldPeak = 0;
+				frontOrigin = currentSteadyClock;
+				isWorkingOnPeak = false;
+			}
+		}
+
+		// :78-206
+		void processMutating(std::size_t numSamples, std::vector<WindowEvent>& events)
+		{
+			if (frontOrigin + bufferedSamples < steadyClock)
+			{
+				frontOrigin = steadyClock;
+				bufferedSamples = 0;
+			}
+			auto ceilingSize = std::ceil(windowSize);
+			auto halfSize = ceilingSize / 2;
+			auto processIntoBackBuffer = [&](auto samples)
+			{
+				events.push_back({ WindowEvent::Process, steadyClock, static_cast<uint64_t>(samples), bufferedSamples });
+				numSamples -= samples;
+				auto oldSamples = bufferedSamples;
+				steadyClock += samples;
+				bufferedSamples += samples;
+				bufferedSamples = std::min<std::uint64_t>(bufferedSamples, ceilingSize + 1);
+				frontOrigin += (oldSamples + samples) - bufferedSamples;
+			};
+			if (ceilingSize == 0 && peaks.size()) peaks.clear();
+			while (numSamples != 0)
+			{
+				if (!peaks.size())
+				{
+					processIntoBackBuffer(numSamples);
+					break;
+				}
+				else if (!isWorkingOnPeak)
+				{
+					isWorkingOnPeak = true;
+					auto nextPeak = peaks.front();
+					if (nextPeak >= steadyClock)
+					{
+						auto deltaToPeak = nextPeak - steadyClock;
+						auto numSamplesToProcess = std::min<std::uint64_t>(numSamples, deltaToPeak + halfSize);
+						processIntoBackBuffer(numSamplesToProcess);
+						currentPeak = nextPeak;
+					}
+					else
+					{
+						currentPeak = nextPeak;
+					}
+				}
+				std::uint64_t windowEnd;
+				bool isPeakOutsideOfWindow = false;
+				bool readyForBufferSwap = false;
+				if (currentPeak - oldPeak < halfSize)
+				{
+					windowEnd = oldPeak + halfSize;
+				}
+				else
+				{
+					isPeakOutsideOfWindow = true;
+					windowEnd = frontOrigin + bufferedSamples;
+				}
+				std::uint64_t peakWindowEnd = (isPeakOutsideOfWindow ? 1 : 0) + currentPeak + halfSize;
+				std::uint64_t numSamplesToProcess = 0;
+				auto missingBufferSamples = peakWindowEnd - std::min(peakWindowEnd, windowEnd);
+				auto neededPreSamples = std::min<std::uint64_t>(halfSize, std::max<double>((currentPeak - oldPeak), halfSize) - halfSize);
+				if (isPeakOutsideOfWindow)
+				{
+					numSamplesToProcess = std::min<std::uint64_t>(numSamples, missingBufferSamples);
+					if (numSamplesToProcess > 0) processIntoBackBuffer(numSamplesToProcess);
+					readyForBufferSwap = missingBufferSamples == numSamplesToProcess;
+				}
+				else
+				{
+					if (bufferedSamples >= missingBufferSamples)
+					{
+						readyForBufferSwap = true;
+					}
+					else
+					{
+						auto numRemaining = missingBufferSamples - bufferedSamples;
+						numSamplesToProcess = std::min<std::uint64_t>(numSamples, numRemaining);
+						if (numSamplesToProcess > 0) processIntoBackBuffer(numSamplesToProcess);
+						readyForBufferSwap = numRemaining == numSamplesToProcess;
+					}
+				}
+				if (readyForBufferSwap)
+				{
+					auto amount = (isPeakOutsideOfWindow ? halfSize : missingBufferSamples) + neededPreSamples;
+					auto cappedSize = std::min<std::size_t>(bufferedSamples, std::ceil(amount + 1));
+					events.push_back({ WindowEvent::Swap, frontOrigin, static_cast<uint64_t>(cappedSize), bufferedSamples });
+					bufferedSamples -= std::min<std::uint64_t>(bufferedSamples, cappedSize);
+					frontOrigin += cappedSize;
+					oldPeak = currentPeak;
+					isWorkingOnPeak = false;
+					peaks.pop_front();
+				}
+			}
+		}
+	};
 
 	// calculateFundamentalPeriod + calculateTriggeringOffset — Oscilloscope/OscilloscopeDSP.inl:61-308
 	struct BinRecord

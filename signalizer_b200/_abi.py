@@ -133,6 +133,18 @@ class ScopeTriggerState(C.Structure):
     _fields_ = [("state", C.c_double), ("cross_origin", C.c_uint64), ("is_peak_holding", C.c_int32), ("reserved", C.c_int32)]
 
 
+class ScopeWindowState(C.Structure):
+    _fields_ = [("window_size", C.c_double), ("old_peak", C.c_uint64), ("current_peak", C.c_uint64), ("buffered_samples", C.c_uint64),
+                ("front_origin", C.c_uint64), ("steady_clock", C.c_uint64), ("is_working_on_peak", C.c_int32), ("window_changed", C.c_int32)]
+
+
+class ScopeWindowEvent(C.Structure):
+    _fields_ = [("origin", C.c_uint64), ("size", C.c_uint64), ("buffered", C.c_uint64), ("kind", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+WINDOW_PROCESS, WINDOW_SWAP = 0, 1
+
+
 class ScopeBinRecord(C.Structure):
     _fields_ = [("index", C.c_uint64), ("value", C.c_double), ("offset", C.c_double)]
 

@@ -29,6 +29,7 @@ EXPORTS = [
     "sgz_context_create", "sgz_context_destroy", "sgz_context_set_cuda_stream", "sgz_context_synchronize",
     "sgz_vscope_vertices", "sgz_vscope_histogram", "sgz_vscope_meters",
     "sgz_scope_resample_count", "sgz_scope_resample", "sgz_scope_trigger", "sgz_scope_period", "sgz_scope_colour", "sgz_scope_peak_envelope",
+    "sgz_vscope_peak_envelope", "sgz_scope_trigger_windows",
 ]
 
 
@@ -92,6 +93,9 @@ def load():
     lib.sgz_scope_resample_count.argtypes = [rc_]
     lib.sgz_scope_resample_count.restype = C.c_uint64
     lib.sgz_scope_resample.argtypes = [vp, rc_, C.POINTER(C.c_double), fp, i32, i32, u32, u64, u64, fp, i32]
+    lib.sgz_vscope_peak_envelope.argtypes = [vp, fp, i32, i32, u32, u64, u64, C.c_float, C.c_double, C.POINTER(_abi.VScopeFilters), C.POINTER(C.c_double)]
+    lib.sgz_scope_trigger_windows.argtypes = [u32, C.POINTER(_abi.ScopeWindowState), C.POINTER(u64), C.POINTER(u32), u32, u64, u64,
+                                              C.POINTER(_abi.ScopeWindowEvent), C.POINTER(u32), u32]
     lib.sgz_scope_trigger.argtypes = [vp, i32, i32, fp, i32, i32, u32, u64, u64, C.c_double, C.c_double, u64,
                                       C.POINTER(_abi.ScopeTriggerState), C.POINTER(C.c_uint64), C.POINTER(u32), u32]
     lib.sgz_scope_period.argtypes = [vp, C.POINTER(_abi.ScopePeriodParams), fp, i32, i32, u32, u64, u64,

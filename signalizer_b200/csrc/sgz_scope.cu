@@ -1272,4 +1272,170 @@ extern "C"
 		}
 		return SGZ_OK;
 	}
+	// VectorScope::runPeakFilter (VectorscopeRendering.cpp:826-889): largest |L| and |R| of the window (whole groups of 8
+	// samples only, the AVX loop of :857-868), squared and folded into processor->filters.envelope[0 / 1] with
+	// coeff = envelopeCoeff^(numSamples * openGLDeltaTime) (:840-842), then envelopeGain = 1 / max(sqrt, sqrt), kept only
+	// when it is a normal number (:882-888).  The window maximum runs on the GPU (k_scope_peak_max in its two-channel
+	// form); the fold is a handful of scalar operations per stream on the host, in the reference's types (float envelope
+	// states, double arithmetic, float square roots).
+	int sgz_vscope_peak_envelope(sgz_context* c, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+		float envelope_coeff, double delta_time, sgz_vscope_filters* filters, double* envelope_gain)
+	{
+		int rc;
+		if (!filters || !envelope_gain) return fail(SGZ_EINVAL, "null argument");
+		if ((rc = validateAudio(audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		const float* d = nullptr;
+		if ((rc = stageIn(c, audio, mem, n_streams, n_samples, stream_stride, &d)) != SGZ_OK) return rc;
+		void* dMax = nullptr; if ((rc = ensure(c, 2, size_t(n_streams) * sizeof(float2), &dMax)) != SGZ_OK) return rc;
+		const uint64_t stop = n_samples - (n_samples & 7); // whole 8-float vectors only (:860); "TODO: remainder?" (:870)
+		k_scope_peak_max<<<n_streams, 256, 0, c->stream>>>(d, layout, n_samples, stream_stride, stop, SGZ_OSC_SEPARATE, static_cast<float2*>(dMax));
+		SGZS_CUDA(cudaGetLastError());
+		std::vector<float2> hi(n_streams);
+		SGZS_CUDA(cudaMemcpyAsync(hi.data(), dMax, size_t(n_streams) * sizeof(float2), cudaMemcpyDeviceToHost, c->stream));
+		SGZS_CUDA(cudaStreamSynchronize(c->stream));
+		const double power = double(n_samples) * delta_time;
+		const double coeff = std::pow(envelope_coeff, power); // std::pow(float, double) -> double
+		for (uint32_t s = 0; s < n_streams; ++s)
+		{
+			float* env = filters[s].envelope;
+			const double highestLeft = hi[s].x, highestRight = hi[s].y;
+			env[0] = static_cast<float>(std::max(env[0] * coeff, highestLeft * highestLeft));
+			env[1] = static_cast<float>(std::max(env[1] * coeff, highestRight * highestRight));
+			const double currentEnvelope = 1.0 / std::max(std::sqrt(env[0]), std::sqrt(env[1]));
+			if (std::isnormal(currentEnvelope)) envelope_gain[s] = currentEnvelope;
+		}
+		return SGZ_OK;
+	}
+	// TriggeringProcessor::update + ::processMutating (StreamPreprocessing.h:54-75, :78-206) for every stream of a batch.
+	// The peak queue is the caller's row [head, count); events stand in for the two side effects (back-buffer append,
+	// front-buffer swap).  The decisions mix std::uint64_t clocks with the double halfSize exactly as the reference
+	// writes them (comparisons and sums in double, truncation where it assigns to an integer).
+	namespace
+	{
+		struct WindowRun
+		{
+			sgz_scope_window_state st;
+			const uint64_t* queue; uint32_t head, count; // peaks.front() == queue[head]
+			uint64_t numSamples;
+			sgz_scope_window_event* events; uint32_t nEvents, maxEvents;
+			bool overflow;
+			double ceilingSize;
+
+			bool hasPeaks() const { return head < count; }
+			void emit(uint32_t kind, uint64_t origin, uint64_t size)
+			{
+				if (nEvents < maxEvents) events[nEvents] = sgz_scope_window_event{ origin, size, st.buffered_samples, kind, 0u };
+				else overflow = true;
+				++nEvents;
+			}
+			void processIntoBackBuffer(uint64_t samples) // the lambda at :89-103
+			{
+				emit(SGZ_WINDOW_PROCESS, st.steady_clock, samples);
+				numSamples -= samples;
+				const uint64_t oldSamples = st.buffered_samples;
+				st.steady_clock += samples;
+				st.buffered_samples += samples;
+				st.buffered_samples = std::min<uint64_t>(st.buffered_samples, static_cast<uint64_t>(ceilingSize + 1));
+				st.front_origin += (oldSamples + samples) - st.buffered_samples;
+			}
+		};
+	}
+
+	int sgz_scope_trigger_windows(uint32_t n_streams, sgz_scope_window_state* states, uint64_t* peaks, uint32_t* peak_counts, uint32_t max_peaks,
+		uint64_t steady_clock, uint64_t n_samples, sgz_scope_window_event* events, uint32_t* event_counts, uint32_t max_events)
+	{
+		if (!states || !peak_counts || !event_counts || (!peaks && max_peaks) || (!events && max_events)) return fail(SGZ_EINVAL, "null argument");
+		for (uint32_t s = 0; s < n_streams; ++s) if (peak_counts[s] > max_peaks) return fail(SGZ_EINVAL, "stream %u: peak count %u exceeds max_peaks %u", s, peak_counts[s], max_peaks);
+		for (uint32_t s = 0; s < n_streams; ++s)
+		{
+			WindowRun r{};
+			r.st = states[s];
+			r.queue = peaks + size_t(s) * max_peaks; r.head = 0; r.count = peak_counts[s];
+			r.numSamples = n_samples;
+			r.events = events + size_t(s) * max_events; r.maxEvents = max_events;
+			sgz_scope_window_state& st = r.st;
+
+			// update(currentSteadyClock), :54-75
+			st.steady_clock = steady_clock;
+			if (st.window_changed)
+			{
+				st.window_changed = 0;
+				if (st.is_working_on_peak && r.hasPeaks()) ++r.head;
+				while (r.hasPeaks() && r.queue[r.head] < steady_clock) ++r.head;
+				st.buffered_samples = st.current_peak = st.old_peak = 0;
+				st.front_origin = steady_clock;
+				st.is_working_on_peak = 0;
+			}
+
+			// processMutating, :78-206
+			if (st.front_origin + st.buffered_samples < st.steady_clock)
+			{
+				st.front_origin = st.steady_clock;
+				st.buffered_samples = 0;
+			}
+			r.ceilingSize = std::ceil(st.window_size);
+			const double halfSize = r.ceilingSize / 2;
+			if (r.ceilingSize == 0 && r.hasPeaks()) r.head = r.count;
+			while (r.numSamples != 0)
+			{
+				if (!r.hasPeaks())
+				{
+					r.processIntoBackBuffer(r.numSamples);
+					break;
+				}
+				else if (!st.is_working_on_peak)
+				{
+					st.is_working_on_peak = 1;
+					const uint64_t nextPeak = r.queue[r.head];
+					if (nextPeak >= st.steady_clock)
+					{
+						// select closest peak that has a full buffer
+						const uint64_t deltaToPeak = nextPeak - st.steady_clock;
+						r.processIntoBackBuffer(std::min<uint64_t>(r.numSamples, static_cast<uint64_t>(double(deltaToPeak) + halfSize)));
+					}
+					st.current_peak = nextPeak;
+				}
+				const uint64_t sincePeak = st.current_peak - st.old_peak;
+				const bool isPeakOutsideOfWindow = !(double(sincePeak) < halfSize);
+				const uint64_t windowEnd = isPeakOutsideOfWindow ? st.front_origin + st.buffered_samples : static_cast<uint64_t>(double(st.old_peak) + halfSize);
+				const uint64_t peakWindowEnd = static_cast<uint64_t>(double((isPeakOutsideOfWindow ? 1 : 0) + st.current_peak) + halfSize);
+				const uint64_t missingBufferSamples = peakWindowEnd - std::min(peakWindowEnd, windowEnd);
+				const uint64_t neededPreSamples = std::min<uint64_t>(static_cast<uint64_t>(halfSize), static_cast<uint64_t>(std::max<double>(double(sincePeak), halfSize) - halfSize));
+				bool readyForBufferSwap;
+				if (isPeakOutsideOfWindow)
+				{
+					const uint64_t n = std::min<uint64_t>(r.numSamples, missingBufferSamples);
+					if (n > 0) r.processIntoBackBuffer(n);
+					readyForBufferSwap = missingBufferSamples == n;
+				}
+				else if (st.buffered_samples >= missingBufferSamples) readyForBufferSwap = true;
+				else
+				{
+					const uint64_t numRemaining = missingBufferSamples - st.buffered_samples;
+					const uint64_t n = std::min<uint64_t>(r.numSamples, numRemaining);
+					if (n > 0) r.processIntoBackBuffer(n);
+					readyForBufferSwap = numRemaining == n;
+				}
+				if (readyForBufferSwap)
+				{
+					const double amount = (isPeakOutsideOfWindow ? halfSize : double(missingBufferSamples)) + double(neededPreSamples);
+					const uint64_t cappedSize = std::min<size_t>(st.buffered_samples, static_cast<size_t>(std::ceil(amount + 1)));
+					r.emit(SGZ_WINDOW_SWAP, st.front_origin, cappedSize);
+					st.buffered_samples -= std::min<uint64_t>(st.buffered_samples, cappedSize);
+					st.front_origin += cappedSize;
+					st.old_peak = st.current_peak;
+					st.is_working_on_peak = 0;
+					++r.head;
+				}
+			}
+			if (r.overflow) return fail(SGZ_EINVAL, "stream %u needs %u window events, max_events is %u (nothing was written back for it)", s, r.nEvents, max_events);
+			states[s] = st;
+			event_counts[s] = r.nEvents;
+			uint64_t* row = peaks + size_t(s) * max_peaks;
+			for (uint32_t k = r.head; k < r.count; ++k) row[k - r.head] = row[k];
+			peak_counts[s] = r.count - r.head;
+		}
+		return SGZ_OK;
+	}
 }

@@ -23,6 +23,7 @@
 #include <new>
 #include <string>
 #include <atomic>
+#include <mutex>
 #include <complex>
 #include <vector>
 
@@ -767,16 +768,24 @@ namespace
 	template<void (*kern)(DeviceTables, FusedArgs)>
 	int launchFusedKernel(sgz_spectrum* h, int threads, size_t smem, FusedArgs& a, const FusedPlan* plan)
 	{
-		// the opt-in shared-memory limit belongs to the kernel function on a device, not to a handle: raise it once
-		// per (kernel, device) to the most any handle can ask for
-		static std::atomic<uint64_t> attrDone{ 0 };
-		const uint64_t bit = uint64_t(1) << (h->device & 63);
-		if (!(attrDone.load(std::memory_order_acquire) & bit))
+		// the opt-in shared-memory limit belongs to the kernel function on a device, not to a handle: keep a running
+		// maximum per (kernel, device) and only ever raise it, so handles with different display-point counts coexist
+		// (the limit is kept no larger than needed: the driver sizes the shared-memory carve-out, and with it what is
+		// left for L1, from it)
+		static std::atomic<size_t> attrBytes[64];
+		std::atomic<size_t>& limit = attrBytes[h->device & 63];
+		if (limit.load(std::memory_order_acquire) < smem)
 		{
-			int optin = 0;
-			SGZ_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-			SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-			attrDone.fetch_or(bit, std::memory_order_release);
+			static std::mutex attrMutex;
+			std::lock_guard<std::mutex> lock(attrMutex);
+			if (limit.load(std::memory_order_relaxed) < smem)
+			{
+				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+#ifdef SGZ8_CARVEOUT
+				SGZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, SGZ8_CARVEOUT));
+#endif
+				limit.store(smem, std::memory_order_release);
+			}
 		}
 		if (!plan)
 		{

@@ -70,6 +70,18 @@ class Context:
         check(self.lib.sgz_vscope_meters(self._h, ptr, mem, layout, S, n, stride, envelope_coeff, stereo_coeff, second_speed, filters))
         return filters
 
+    def vscope_peak_envelope(self, audio, filters, gains, envelope_coeff, delta_time, layout=_abi.LAYOUT_INTERLEAVED):
+        """VectorScope::runPeakFilter (VectorscopeRendering.cpp:826-889): folds the window's largest |L|, |R| into
+        filters[s].envelope and returns the envelopeGain per stream (`gains` in, kept where the new value is not normal)."""
+        keep, ptr, mem = _buf(audio)
+        S, n, stride = _geometry(keep, layout)
+        assert len(filters) == S
+        g = np.ascontiguousarray(gains, dtype=np.float64).copy()
+        assert g.shape == (S,)
+        check(self.lib.sgz_vscope_peak_envelope(self._h, ptr, mem, layout, S, n, stride, envelope_coeff, delta_time, filters,
+                                                g.ctypes.data_as(C.POINTER(C.c_double))))
+        return filters, g
+
     # ---- Oscilloscope ---------------------------------------------------------------------
     def scope_resample_count(self, cfg) -> int:
         return int(self.lib.sgz_scope_resample_count(C.byref(cfg)))
@@ -134,3 +146,20 @@ class Context:
         check(self.lib.sgz_scope_peak_envelope(self._h, channel_mode, ptr, mem, layout, S, n, stride, coeff,
                                                envelopes.ctypes.data_as(C.POINTER(C.c_float)), gain.ctypes.data_as(C.POINTER(C.c_double))))
         return gain
+
+
+def scope_trigger_windows(lib, states, peaks, peak_counts, steady_clock, n_samples, max_events=256):
+    """TriggeringProcessor::update + processMutating (StreamPreprocessing.h:54-206) for every stream: consumes the queued
+    trigger positions (`peaks` [S, max_peaks] uint64 with `peak_counts` valid entries per row, both updated in place) and
+    returns the per-stream lists of (kind, origin, size, buffered) events.  Host-only bookkeeping: `lib` is the loaded
+    library (signalizer_b200._lib.load() or the oracle's, which exports the same function under its own prefix)."""
+    S = len(states)
+    assert peaks.dtype == np.uint64 and peaks.shape[0] == S and peak_counts.dtype == np.uint32
+    events = (_abi.ScopeWindowEvent * (S * max_events))()
+    counts = np.zeros(S, dtype=np.uint32)
+    fn = getattr(lib, "sgz_scope_trigger_windows", None) or lib.sgzo_scope_trigger_windows
+    rc = fn(S, states, peaks.ctypes.data_as(C.POINTER(C.c_uint64)), peak_counts.ctypes.data_as(C.POINTER(C.c_uint32)), peaks.shape[1],
+            steady_clock, n_samples, events, counts.ctypes.data_as(C.POINTER(C.c_uint32)), max_events)
+    if rc != 0:
+        raise ValueError(f"trigger_windows rc={rc}")
+    return [[(e.kind, e.origin, e.size, e.buffered) for e in events[s * max_events:s * max_events + counts[s]]] for s in range(S)]

@@ -84,3 +84,24 @@ def test_spectral_period_finds_the_fundamental():
         assert abs(r[s].fundamental - f0[s]) < 0.01 * f0[s]
         assert abs(r[s].cycle_samples - 48000.0 / r[s].fundamental) < 1e-9
         assert -1.0 <= r[s].sample_offset < r[s].cycle_samples
+
+
+def test_vectorscope_peak_filter_known_answers():
+    """VectorScope::runPeakFilter (VectorscopeRendering.cpp:826-889) on constructed inputs"""
+    o = OracleScope()
+    n = 64
+    a = np.zeros((2, n, 2), np.float32)
+    a[0, 5, 0], a[0, 9, 1] = -0.5, 0.25          # |L| max 0.5, |R| max 0.25
+    a[1, 63, 0] = 0.8                             # stream 1: n = 64 is whole vectors, so the last sample counts
+    f = (_abi.VScopeFilters * 2)()
+    f, g = o.vscope_peak_envelope(a, f, np.array([1.0, 1.0]), 0.5, 0.25)
+    assert tuple(f[0].envelope) == (0.25, 0.0625) and g[0] == 2.0
+    assert abs(f[1].envelope[0] - 0.64) < 1e-7 and abs(g[1] - 1.25) < 1e-6
+    # second frame, silence: the envelopes decay by coeff = 0.5^(64 * 0.25) = 2^-16, the gain follows
+    f, g = o.vscope_peak_envelope(np.zeros_like(a), f, g, 0.5, 0.25)
+    assert tuple(f[0].envelope) == (0.25 * 2.0 ** -16, 0.0625 * 2.0 ** -16) and g[0] == 2.0 * 256
+    # remainder rule: 65 samples, the loud one is the 65th
+    b = np.zeros((1, 65, 2), np.float32)
+    b[0, 64, 0] = 1.0
+    f1, g1 = o.vscope_peak_envelope(b, (_abi.VScopeFilters * 1)(), np.array([3.0]), 0.5, 0.0)
+    assert tuple(f1[0].envelope) == (0.0, 0.0) and g1[0] == 3.0   # 1 / 0 = inf is not normal: the old gain stays

@@ -217,3 +217,29 @@ def test_scope_spectral_period():
             assert sg[s].median_pos == so[s].median_pos
     for s in range(S):
         assert abs(rg[s].fundamental - f0[s]) < 0.02 * f0[s]
+
+
+@pytest.mark.parametrize("layout", [_abi.LAYOUT_INTERLEAVED, _abi.LAYOUT_PLANAR])
+def test_vectorscope_peak_envelope_matches_oracle(layout):
+    """VectorScope::runPeakFilter (VectorscopeRendering.cpp:826-889): envelope states and envelopeGain bit for bit, over
+    several frames, incl. the whole-groups-of-8 rule (the loud sample in the remainder is not seen) and the isnormal guard
+    (a silent stream keeps its previous gain)"""
+    S, n = 7, 4099
+    audio = signals.batch(S, n, first_stream=2)
+    audio[3] = 0.0                      # silence: 1 / 0 is not normal, the gain stays
+    audio[4, :, :] *= 0.01
+    audio[4, n - 2, 0] = 0.9            # in the remainder (n & 7 = 3): ignored
+    if layout == _abi.LAYOUT_PLANAR:
+        audio = np.ascontiguousarray(audio.transpose(0, 2, 1))
+    ctx, orc = Context(), OracleScope()
+    fg, fo = (_abi.VScopeFilters * S)(), (_abi.VScopeFilters * S)()
+    gg, go = np.full(S, 0.75), np.full(S, 0.75)
+    for frame in range(3):
+        scale = np.float32(1.0 / (1 + frame))
+        fg, gg = ctx.vscope_peak_envelope(audio * scale, fg, gg, 0.97, 1.0 / 60.0, layout=layout)
+        fo, go = orc.vscope_peak_envelope(audio * scale, fo, go, 0.97, 1.0 / 60.0, layout=layout)
+        np.testing.assert_array_equal(gg, go)
+        for s in range(S):
+            assert tuple(fg[s].envelope) == tuple(fo[s].envelope)
+    assert gg[3] == 0.75
+    assert fg[4].envelope[0] < 0.01     # 0.9 was not seen
