@@ -95,14 +95,18 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic():
-    """dram bytes per launch of the fused kernel from the committed ncu summary, if any."""
+def ncu_traffic(kernel_name):
+    """dram bytes per launch of the fused kernel from the committed ncu summary - only when that capture is of the
+    kernel this run launches (the summary records the name), otherwise None: a stale profile must not be quoted."""
     path = os.path.join(ROOT, "profiles", "fused_kernel_summary.json")
     try:
         with open(path) as f:
-            return json.load(f).get("dram_bytes_per_launch")
+            d = json.load(f)
+        captured = d.get("metrics", {}).get("Kernel Name", {}).get("value", "")
+        same = kernel_name.replace("sgz::", "").replace(" ", "") in captured.replace("void ", "").replace(" ", "")
+        return (d.get("dram_bytes_per_launch"), d.get("capture")) if same and d.get("round") == 2 else (None, None)
     except Exception:
-        return None
+        return None, None
 
 
 def bench_cfg():
@@ -120,14 +124,27 @@ def make_audio(args, rank):
     return np.ascontiguousarray(np.tile(base, (reps, 1, 1))[:args.streams]), n
 
 
-def cpu_sample(args, threads, streams, frames, fast=True):
-    """Time the oracle (the reference's CPU algorithm restated) on a bounded sample."""
+def cpu_arm():
+    """Which CPU implementation is timed: oracle/_ref (the reference's own TransformDSP.inl / TransformPair.h /
+    TransformConstant.h compiled against stand-ins for its absent cpl library) when it was built, else the restated port."""
+    from oracle import binding
+    binding.build()
+    ref = binding.ref_available()
+    note = ("the reference's own Source/Spectrum transform code (oracle/_ref), -O3 -mavx2; its cpl primitives (FFT, Lanczos / linear filters, "
+            "window) are this repo's stand-ins - a scalar-complex Stockham FFT, not the shipped binary's pffft") if ref else \
+           "restated reference algorithm (oracle port, scalar Stockham FFT), not the shipped binary (pffft)"
+    return ref, ("reference" if ref else "port"), note
+
+
+def cpu_sample(args, threads, streams, frames, ref):
+    """Time the CPU implementation on a bounded sample of the same workload (threads over streams, like the reference's
+    parallel_for over pairs, SpectrumDSP.cpp:83)."""
     from oracle.binding import OracleSpectrum
     from signalizer_b200 import signals
     cfg = bench_cfg()
     n = signals.frames_length(8192, args.hop, frames)
     audio = signals.batch(streams, n)
-    o = OracleSpectrum(cfg, streams, fast=fast)
+    o = OracleSpectrum(cfg, streams, fast=True, ref=ref)
     o.process_frames(audio[:, :8192], args.hop, 1, threads=threads, want_results=False)  # touch
     t0 = time.perf_counter()
     o.process_frames(audio, args.hop, frames, threads=threads, want_results=False)
@@ -135,14 +152,48 @@ def cpu_sample(args, threads, streams, frames, fast=True):
     return streams * frames / dt, dt
 
 
+def cpu_stage_split(ref, frames=48):
+    """microseconds per frame of the four stages on one core (prepareTransform / doTransform / mapToLinearSpace /
+    postProcessStdTransform called one after the other over `frames` single-frame streams)"""
+    from oracle.binding import OracleSpectrum
+    from signalizer_b200 import signals
+    cfg = bench_cfg()
+    audio = signals.batch(frames, 8192)
+    o = OracleSpectrum(cfg, frames, fast=True, ref=ref)
+    best = None
+    for _ in range(3):
+        t = [time.perf_counter()]
+        o.prepare(audio); t.append(time.perf_counter())
+        o.transform(); t.append(time.perf_counter())
+        o.map(); t.append(time.perf_counter())
+        o.postprocess(); t.append(time.perf_counter())
+        cur = [(t[i + 1] - t[i]) / frames * 1e6 for i in range(4)]
+        best = cur if best is None or sum(cur) < sum(best) else best
+    return dict(zip(("prepare_us", "fft_us", "map_us", "post_us"), (round(x, 1) for x in best)))
+
+
+def cpu_baseline(args):
+    from oracle import binding
+    ref, kind, note = cpu_arm()
+    cores = binding.hardware_concurrency() or os.cpu_count() or 1
+    cs, cf = min(max(16 * cores, 64), 1024), args.frames   # ~10-30 s of single-core work
+    v, dt = cpu_sample(args, cores, cs, cf, ref)
+    v1, dt1 = cpu_sample(args, 1, 16, 16, ref)
+    return {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{cs} streams x {cf} frames of the same C3 workload in {dt:.2f} s, {cores} threads over streams",
+            "one_core": {"value": v1, "unit": UNIT, "sample": f"16 streams x 16 frames in {dt1:.2f} s on one thread"},
+            "stage_split_one_core": cpu_stage_split(ref), "note": note}
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path cannot be built
-    (External/cpl is absent), so this times the oracle port with every host thread."""
+    """--impl reference: the reference's CPU implementation of the path with every host thread.  Its own build system
+    cannot run here (External/cpl is absent, JUCE needs X11), so this is oracle/_ref - the reference's Source/Spectrum
+    transform sources compiled against cpl stand-ins - or, where that was not built, the restated port."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import binding
-    binding.build()
+    ref, kind, note = cpu_arm()
     cores = binding.hardware_concurrency() or os.cpu_count() or 1
     # a step large enough that thread start-up does not count against the reference (about 0.1 s of work on 16 cores),
     # small enough that the default --steps 50 ends within seconds
@@ -150,7 +201,7 @@ def run_reference(args):
     frames = 16
     vals = []
     for i in range(args.warmup + args.steps):
-        v, dt = cpu_sample(args, cores, streams, frames)
+        v, dt = cpu_sample(args, cores, streams, frames, ref)
         if i >= args.warmup:
             vals.append((v, dt))
     value = statistics.median(v for v, _ in vals)
@@ -160,8 +211,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                         "note": "restated reference algorithm (scalar Stockham FFT), not the shipped binary (pffft); parity unpinned"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample, "note": note},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -171,7 +221,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from signalizer_b200 import _abi
+    from signalizer_b200 import _abi, sharding
     from signalizer_b200.spectrum import TransformPairBatch
 
     rank = int(os.environ.get("RANK", "0"))
@@ -191,15 +241,27 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed(fn, steps):
+        """device time of `steps` calls of fn on the launch stream, barrier + synchronize on both sides; per-step list"""
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        barrier()
+        ev[0].record(stream)
+        for i in range(steps):
+            fn()
+            ev[i + 1].record(stream)
+        barrier()
+        return ev[0].elapsed_time(ev[-1]), [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
+
     cfg = bench_cfg()
     audio_np, n = make_audio(args, rank)
     S, F, hop, P = args.streams, args.frames, args.hop, cfg.axis_points
     pairs = TransformPairBatch(cfg, S, device=local)
     assert pairs.info.fused_available == 1
+    kernel_name = pairs.kernel_name()
     stream = torch.cuda.current_stream()
     pairs.set_cuda_stream(stream.cuda_stream)
 
-    # ---- device-resident throughput ("value") ----
+    # ---- device-resident throughput ("value"): every rank its own 1024 streams ----
     d_audio = torch.from_numpy(audio_np).to(dev)
     d_out = torch.empty((S, F, 2, P, 2), dtype=torch.float32, device=dev)
     sampler = ClockSampler(local)
@@ -207,38 +269,54 @@ def run_ours(args):
         sampler.start()   # nvidia-smi needs ~100 ms to start: launched before the warm-up, read after the timed region
     for _ in range(max(args.warmup, 3)):
         pairs.process_frames(d_audio, hop, F, out=d_out)
-    barrier()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    barrier()
-    ev[0].record(stream)
-    for i in range(args.steps):
-        pairs.process_frames(d_audio, hop, F, out=d_out)
-        ev[i + 1].record(stream)
-    barrier()
-    total_ms = ev[0].elapsed_time(ev[-1])
-    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    total_ms, step_ms = timed(lambda: pairs.process_frames(d_audio, hop, F, out=d_out), args.steps)
     checksum = float(d_out[:, -1, 0, :, 0].float().mean().item())
 
-    # ---- end to end through the C ABI with HOST buffers ("e2e") ----
-    h_audio = torch.from_numpy(audio_np).pin_memory()
-    h_out = torch.empty((S, F, 2, P, 2), dtype=torch.float32).pin_memory()
-    e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 3))
-    if e2e_steps:
-        pairs.process_frames(h_audio.numpy(), hop, F, out=h_out.numpy())  # warm (allocates staging once)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(e2e_steps):
-        pairs.process_frames(h_audio.numpy(), hop, F, out=h_out.numpy())
-    e1.record(stream)
-    barrier()
-    clocks = sampler.stop() if rank == 0 else None   # sampled across the device-resident and the host-buffer timed regions
-    e2e_ms = e0.elapsed_time(e1) / max(e2e_steps, 1)
+    # ---- the configuration BASELINE.json names at N > 1: 1024 streams in TOTAL, sharded over the ranks ("strong_1024") ----
+    lo, hi = sharding.stream_range(rank, world, S)
+    strong_ms, gather = total_ms, None
+    if world > 1:
+        shard = TransformPairBatch(cfg, hi - lo, device=local)
+        shard.set_cuda_stream(stream.cuda_stream)
+        sh_audio, sh_out = d_audio[lo:hi], d_out[lo:hi]
+        for _ in range(max(args.warmup, 3)):
+            shard.process_frames(sh_audio, hop, F, out=sh_out)
+        strong_ms, _ = timed(lambda: shard.process_frames(sh_audio, hop, F, out=sh_out), args.steps)
+        # the optional final gather: one frame-step of results of all 1024 streams to rank 0 over NCCL,
+        # outside the metric, reported separately
+        last = sh_out[:, -1].contiguous()
+        for _ in range(3):
+            sharding.gather_results(last, S)
+        g_steps = 10
+        g_ms, _ = timed(lambda: sharding.gather_results(last, S), g_steps)
+        gather = {"bytes": int(S * 2 * P * 2 * 4), "ms": g_ms / g_steps, "what": "last frame of all 1024 streams -> rank 0, torch.distributed gather on NCCL"}
 
-    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    # ---- end to end through the C ABI with HOST buffers ("e2e" = pinned, full results; the other legs next to it) ----
+    e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 3))
+    legs = {}
+    if e2e_steps:
+        h_audio = torch.from_numpy(audio_np).pin_memory()
+        shapes = {"full": ((S, F, 2, P, 2), _abi.OUT_FULL), "line_main": ((S, F, P, 2), _abi.OUT_LINE_MAIN), "last_frame": ((S, 2, P, 2), _abi.OUT_LAST_FRAME)}
+        for name, (shape, mode) in shapes.items():
+            h_out = torch.empty(shape, dtype=torch.float32).pin_memory()
+            call = lambda: pairs.process_frames(h_audio.numpy(), hop, F, out=h_out.numpy(), output=mode)  # noqa: E731
+            call()   # warm (sizes the staging buffers once)
+            ms, _ = timed(call, e2e_steps)
+            legs[name] = (ms / e2e_steps, int(h_audio.numel() * 4), int(h_out.numel() * 4))
+        # what the reference's callers hand over: pageable memory (the driver stages it through its own pinned buffers)
+        p_out = np.empty((S, F, 2, P, 2), dtype=np.float32)
+        call = lambda: pairs.process_frames(audio_np, hop, F, out=p_out)  # noqa: E731
+        call()
+        ms, _ = timed(call, e2e_steps)
+        legs["pageable_full"] = (ms / e2e_steps, int(audio_np.size * 4), int(p_out.size * 4))
+    clocks = sampler.stop() if rank == 0 else None   # sampled across the device-resident and the host-buffer timed regions
+
+    keys = sorted(legs)
+    t = torch.tensor([total_ms, strong_ms] + [legs[k][0] for k in keys], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(t[0].item()), float(t[1].item())
+    total_ms, strong_ms = float(t[0].item()), float(t[1].item())
+    leg_ms = {k: float(t[2 + i].item()) for i, k in enumerate(keys)}
 
     if rank == 0:
         frames_per_step = S * F * world
@@ -247,31 +325,33 @@ def run_ours(args):
         peak, peak_src = measured_peak()
         kernel_ms = statistics.mean(step_ms)           # rank 0's own launches
         achieved = S * F * ALGO_BYTES_PER_FRAME / (kernel_ms * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(kernel_name)
+        strong_value = S * F / (strong_ms / args.steps * 1e-3)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(), "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_frame": ALGO_BYTES_PER_FRAME,
                          "unique_bytes_per_frame": UNIQUE_BYTES_PER_FRAME,
                          "unique_bytes_frac": S * F * UNIQUE_BYTES_PER_FRAME / (kernel_ms * 1e-3) / 1e9 / peak,
-                         "kernel": "sgz::k_fused8<8,true,2,0>", "kernel_ms": kernel_ms},
-            "e2e": {"value": frames_per_step / (e2e_ms * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": int(h_audio.numel() * 4), "d2h_bytes_per_step": int(h_out.numel() * 4),
-                    "ms_per_step": e2e_ms, "steps": e2e_steps},
-            "gpu_launches": args.steps,  # one k_fused8 launch per device-resident step (plus one D2D memcpy node)
+                         "kernel": kernel_name, "kernel_ms": kernel_ms},
+            # BASELINE.json config 3 as written: 1024 streams in total over the N GPUs (strong scaling; = value at N = 1)
+            "strong_1024": {"value": strong_value, "unit": UNIT, "streams_total": S, "streams_per_gpu": hi - lo,
+                            "ms_per_step": strong_ms / args.steps,
+                            "per_gpu_rate_vs_1024_per_gpu": (strong_value / world) / (value / world), "gather": gather},
+            "gpu_launches": args.steps,  # one k_fused8 launch per device-resident step
             "clocks": clocks, "checksum": checksum,
         }
+        if legs:
+            def leg(k):
+                return {"value": frames_per_step / (leg_ms[k] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": legs[k][1],
+                        "d2h_bytes_per_step": legs[k][2], "ms_per_step": leg_ms[k], "steps": e2e_steps}
+            line["e2e"] = dict(leg("full"), host_memory="pinned", output="full results [S][F][2][P][2]")
+            line["e2e_outputs"] = {"line_main": leg("line_main"), "last_frame": leg("last_frame"), "pageable_full": leg("pageable_full")}
         if world == 1 and not args.no_cpu_baseline:
-            from oracle import binding
-            binding.build()
-            cores = binding.hardware_concurrency() or os.cpu_count() or 1
-            cs, cf = min(max(16 * cores, 64), 1024), args.frames   # ~10-30 s of single-core work
-            v, dt = cpu_sample(args, cores, cs, cf)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": f"{cs} streams x {cf} frames of the same C3 workload in {dt:.2f} s, {cores} threads over streams",
-                                    "note": "restated reference algorithm (scalar Stockham FFT), not the shipped binary (pffft); parity unpinned"}
+            line["cpu_baseline"] = cpu_baseline(args)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -141,6 +141,10 @@ void sgz_spectrum_destroy(sgz_spectrum* h);
 int  sgz_spectrum_get_info(const sgz_spectrum* h, sgz_spectrum_info* out);
 const char* sgz_last_error(void);
 
+/* The fused kernel sgz_spectrum_process_frames launches for this handle, as a
+ * profiler prints it ("sgz::k_fused8<8, 1, 2, 0>"; "" when the configuration
+ * runs the staged kernels).  No reference counterpart: measurement only. */
+const char* sgz_spectrum_kernel_name(const sgz_spectrum* h);
 /* All work of a handle is enqueued on one CUDA stream (default: a stream the
  * handle creates).  `cuda_stream` is a cudaStream_t. */
 int  sgz_spectrum_set_cuda_stream(sgz_spectrum* h, void* cuda_stream);
@@ -220,6 +224,19 @@ int  sgz_spectrum_clear_audio_state(sgz_spectrum* h);
 int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout,
                                  uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
                                  uint32_t n_frames, float* results, int results_mem);
+/* The same call with a choice of what is written to `results` (the transfer
+ * back to a host caller is most of the cost of the call above):
+ *   SGZ_OUT_FULL        [stream][frame][graph(2)][P][2]      (= sgz_spectrum_process_frames)
+ *   SGZ_OUT_LINE_MAIN   [stream][frame][P][2]: graph LineMain of every frame, what
+ *                       `addAudioFrame` appends to `sfbuf` (TransformDSP.inl:1139-1148) and the
+ *                       spectrogram consumes (SpectrumDSP.cpp:119-199)
+ *   SGZ_OUT_LAST_FRAME  [stream][graph(2)][P][2]: the last frame only, what the line graph shows
+ *                       (`lineGraphs[k].getResults`, TransformPair.h:72-76)
+ * Every frame is computed in all three; states and sgz_spectrum_get_results are the same after the call. */
+enum { SGZ_OUT_FULL = 0, SGZ_OUT_LINE_MAIN = 1, SGZ_OUT_LAST_FRAME = 2 };
+int  sgz_spectrum_process_frames_select(sgz_spectrum* h, const float* audio, int mem, int layout,
+                                        uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
+                                        uint32_t n_frames, float* results, int results_mem, int output);
 
 /* ---- audioEntryPoint ------------------------------------------------------
  * Replaces `template<ISA> void audioEntryPoint(const Constant&, const
@@ -429,6 +446,14 @@ int  sgz_scope_trigger(sgz_context* ctx, int mode, int channel, const float* aud
                        uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride, double threshold,
                        double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* states,
                        uint64_t* peaks, uint32_t* counts, uint32_t max_peaks);
+/* The same with states / peaks / counts (and the audio) in DEVICE memory: the
+ * call only enqueues the kernel on the context's stream - no copy, no wait -
+ * so a device-resident pipeline keeps the kernel's rate (the host-array form
+ * above spends most of its time copying the peak lists back). */
+int  sgz_scope_trigger_device(sgz_context* ctx, int mode, int channel, const float* d_audio, int layout,
+                              uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride, double threshold,
+                              double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* d_states,
+                              uint64_t* d_peaks, uint32_t* d_counts, uint32_t max_peaks);
 
 /* Replaces `TriggeringProcessor::update` and `::processMutating`
  * (Source/Oscilloscope/StreamPreprocessing.h:54-75, :78-206): the consumer of
@@ -533,7 +558,8 @@ int  sgz_scope_peak_envelope(sgz_context* ctx, int channel_mode, const float* au
  * the caller.  The call never invokes cudaMalloc/cudaFree or any allocating
  * routine: its working buffer is a fixed 8 MiB array inside the library
  * (resident on every GPU that loads the library, until the process exits), so
- * n * batch must not exceed SGZ_NOALLOC_MAX_POINTS (SGZ_EINVAL otherwise).
+ * n * batch must not exceed SGZ_NOALLOC_MAX_POINTS and batch must not exceed
+ * 65535 (SGZ_EINVAL otherwise); d_in and d_out must not overlap anywhere.
  * The first call on each device looks up that array's address (with that
  * device current); make it before starting any stream capture.  All calls
  * share the one working buffer: calls that overlap on the GPU (different

@@ -41,7 +41,8 @@ def _cpu_has_avx2() -> bool:
 def load(fast: bool = False, ref: bool = False):
     """fast: the -O3 -mavx2 build of the restatement (timing only); ref: oracle/_ref, the reference's own
     TransformDSP.inl compiled against the cpl stand-ins (same entry points, Spectrum path only)."""
-    name = "_ref/libsgz_oracle_ref.so" if ref else "libsgz_oracle_fast.so" if fast and _cpu_has_avx2() else "libsgz_oracle.so"
+    quick = fast and _cpu_has_avx2()
+    name = ("_ref/libsgz_oracle_ref_fast.so" if quick else "_ref/libsgz_oracle_ref.so") if ref else "libsgz_oracle_fast.so" if quick else "libsgz_oracle.so"
     if name in _libs:
         return _libs[name]
     path = os.path.join(_HERE, name)

@@ -31,6 +31,8 @@ cp -r "$here/ref_stubs/cpl" "$src/"
 cp "$here/ref_stubs/Signalizer.h" "$src/"
 cp "$here/ref_stubs/Spectrum/SpectrumParameters.h" "$src/Spectrum/"
 for f in TransformDSP.inl TransformPair.h TransformConstant.h; do cp "$ref/$f" "$src/Spectrum/$f"; done
-${CXX:-g++} -std=c++17 -shared -fPIC -pthread -O2 -ffp-contract=off -Wall -Wno-unused-variable -Wno-unused-but-set-variable -Wno-sign-compare \
-	-Wno-unused-local-typedefs -Wno-switch -Wno-class-memaccess -DSGZ_ORACLE_REF -I"$src" -I"$here" -o "$stamp" "$here/sgz_oracle_capi.cpp"
-echo "build_ref: built $stamp"
+flags="-std=c++17 -shared -fPIC -pthread -ffp-contract=off -Wall -Wno-unused-variable -Wno-unused-but-set-variable -Wno-sign-compare -Wno-unused-local-typedefs -Wno-switch -Wno-class-memaccess -DSGZ_ORACLE_REF"
+# parity build (same flags as libsgz_oracle.so) and the timed build (same flags as libsgz_oracle_fast.so)
+${CXX:-g++} $flags -O2 -I"$src" -I"$here" -o "$stamp" "$here/sgz_oracle_capi.cpp"
+${CXX:-g++} $flags -O3 -mavx2 -mfma -I"$src" -I"$here" -o "$out/libsgz_oracle_ref_fast.so" "$here/sgz_oracle_capi.cpp"
+echo "build_ref: built $stamp and its -O3 twin"

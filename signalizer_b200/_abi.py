@@ -143,6 +143,7 @@ class ScopeWindowEvent(C.Structure):
 
 
 WINDOW_PROCESS, WINDOW_SWAP = 0, 1
+OUT_FULL, OUT_LINE_MAIN, OUT_LAST_FRAME = 0, 1, 2   # sgz_spectrum_process_frames_select
 
 
 class ScopeBinRecord(C.Structure):

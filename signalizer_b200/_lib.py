@@ -22,14 +22,14 @@ EXPORTS = [
     "sgz_spectrum_transform", "sgz_spectrum_map", "sgz_spectrum_postprocess", "sgz_spectrum_get_raw_fft",
     "sgz_spectrum_get_transform_result", "sgz_spectrum_get_results", "sgz_spectrum_get_states",
     "sgz_spectrum_set_states", "sgz_spectrum_clear_line_graph_states", "sgz_spectrum_clear_audio_state",
-    "sgz_spectrum_process_frames", "sgz_fft_forward_noalloc",
+    "sgz_spectrum_process_frames", "sgz_spectrum_process_frames_select", "sgz_fft_forward_noalloc",
     "sgz_spectrum_history_reserve", "sgz_spectrum_history_append", "sgz_spectrum_history_info", "sgz_spectrum_history_view",
     "sgz_spectrum_history_read", "sgz_spectrum_history_process", "sgz_spectrum_track_peaks",
     "sgz_resonator_process", "sgz_resonator_get_state", "sgz_spectrum_colour_columns", "sgz_spectrum_audio_entry_point",
     "sgz_context_create", "sgz_context_destroy", "sgz_context_set_cuda_stream", "sgz_context_synchronize",
     "sgz_vscope_vertices", "sgz_vscope_histogram", "sgz_vscope_meters",
     "sgz_scope_resample_count", "sgz_scope_resample", "sgz_scope_trigger", "sgz_scope_period", "sgz_scope_colour", "sgz_scope_peak_envelope",
-    "sgz_vscope_peak_envelope", "sgz_scope_trigger_windows",
+    "sgz_vscope_peak_envelope", "sgz_scope_trigger_windows", "sgz_spectrum_kernel_name", "sgz_scope_trigger_device",
 ]
 
 
@@ -65,6 +65,8 @@ def load():
     lib.sgz_spectrum_destroy.restype = None
     lib.sgz_spectrum_get_info.argtypes = [vp, C.POINTER(_abi.SpectrumInfo)]
     lib.sgz_spectrum_set_cuda_stream.argtypes = [vp, vp]
+    lib.sgz_spectrum_kernel_name.argtypes = [vp]
+    lib.sgz_spectrum_kernel_name.restype = C.c_char_p
     lib.sgz_spectrum_synchronize.argtypes = [vp]
     for n in ("sgz_spectrum_get_window_kernel", "sgz_spectrum_get_mapped_frequencies", "sgz_spectrum_get_slope_map"):
         getattr(lib, n).argtypes = [vp, fp, sz]
@@ -80,6 +82,7 @@ def load():
     lib.sgz_spectrum_get_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_set_states.argtypes = [vp, i32, fp, i32]
     lib.sgz_spectrum_process_frames.argtypes = [vp, fp, i32, i32, u64, u64, u32, u32, fp, i32]
+    lib.sgz_spectrum_process_frames_select.argtypes = [vp, fp, i32, i32, u64, u64, u32, u32, fp, i32, i32]
     lib.sgz_context_create.argtypes = [i32, C.POINTER(vp)]
     lib.sgz_context_destroy.argtypes = [vp]
     lib.sgz_context_destroy.restype = None
@@ -98,6 +101,7 @@ def load():
                                               C.POINTER(_abi.ScopeWindowEvent), C.POINTER(u32), u32]
     lib.sgz_scope_trigger.argtypes = [vp, i32, i32, fp, i32, i32, u32, u64, u64, C.c_double, C.c_double, u64,
                                       C.POINTER(_abi.ScopeTriggerState), C.POINTER(C.c_uint64), C.POINTER(u32), u32]
+    lib.sgz_scope_trigger_device.argtypes = [vp, i32, i32, fp, i32, u32, u64, u64, C.c_double, C.c_double, u64, vp, vp, vp, u32]
     lib.sgz_scope_period.argtypes = [vp, C.POINTER(_abi.ScopePeriodParams), fp, i32, i32, u32, u64, u64,
                                      C.POINTER(_abi.ScopePeriodState), C.POINTER(_abi.ScopePeriodResult)]
     lib.sgz_scope_colour.argtypes = [vp, C.POINTER(_abi.ScopeColourConfig), fp, i32, i32, u32, u64, u64, C.POINTER(_abi.ScopeColourState), fp, i32, C.POINTER(C.c_double)]
@@ -116,7 +120,8 @@ def load():
     lib.sgz_spectrum_history_process.argtypes = [vp, u32, u32, fp, i32, C.POINTER(u32)]
     for n in EXPORTS:
         f = getattr(lib, n)  # raises AttributeError if the symbol is not exported
-        if n not in ("sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_destroy", "sgz_context_destroy", "sgz_scope_resample_count"):
+        if n not in ("sgz_last_error", "sgz_spectrum_default_config", "sgz_spectrum_destroy", "sgz_context_destroy", "sgz_scope_resample_count",
+                     "sgz_spectrum_kernel_name"):
             f.restype = C.c_int
     _lib = lib
     return lib

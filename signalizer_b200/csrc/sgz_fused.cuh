@@ -21,9 +21,29 @@
 		float2* states;  // [S][2][P]
 		float2* seam;    // [2 G][2][P]
 		uint32_t* flags; // [G]
-		float2* results; // [S][F][2][P]
+		float2* results; // outMode 0: [S][F][2][P]; 1 (LineMain of every frame): [S][F][P]; 2 (last frame only): [S][2][P]
+		float2* lastResults; // [S][2][P] lineGraphs[k].results of the handle (see resultRow)
+		float2* spare;       // [P] where results that the output mode does not keep are written
+		uint32_t outMode;
 	};
 
+	// Where graph k of frame f of stream s is written.  Every frame writes both graphs somewhere, so that the store in the
+	// display loop is unconditional: what the output mode does not keep goes to `spare` (one row of P points that nobody
+	// reads), except that the LAST frame's unkept graphs go straight to the handle's lineGraphs results (`last`, [S][2][P]).
+	// The host copies the kept rows of the last frame into `last` afterwards, so `last` is complete in every mode.
+	__device__ __forceinline__ float2* resultRow(const FusedArgs& a, uint64_t s, uint32_t f, int k, uint32_t P)
+	{
+		const uint32_t F = a.nFrames;
+		if (a.outMode == SGZ_OUT_FULL) return a.results + ((s * F + f) * 2 + k) * P;
+		if (a.outMode == SGZ_OUT_LINE_MAIN) return k == 0 ? a.results + (s * F + f) * P : (f + 1 == F ? a.lastResults + (s * 2 + 1) * P : a.spare);
+		return f + 1 == F ? a.results + (s * 2 + k) * P : a.spare;
+	}
+	// the same for code that revisits results after the kernel (k_seam_apply): nullptr where nothing was kept
+	__device__ __forceinline__ float2* keptRow(const FusedArgs& a, uint64_t s, uint32_t f, int k, uint32_t P)
+	{
+		float2* r = resultRow(a, s, f, k, P);
+		return r == a.spare ? nullptr : r;
+	}
 
 	// display scale with the hardware log2 (MUFU.LG2): |error| of lg2.approx is ~2^-22 absolute,
 	// i.e. < 1e-7 on the [0, 1] display scale after the multiply by deltaYRecip * ln 2
@@ -71,6 +91,66 @@
 		return v;
 	}
 	__device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory"); }
+
+	// One part of a CTA's range: frames [fBegin, fEnd) of one stream, where its peak-hold state comes from (nullptr: zero)
+	// and goes to.  Lives in shared memory, written by thread 0 (planFusedPart) once per part.
+	struct FusedPart
+	{
+		const float2* src; float2* dst;
+		const float* audio;   // the stream's first sample
+		uint32_t nParts, fBegin, fEnd, publish;
+		int stream;
+		uint32_t vec4;        // the frame loop may fetch the stream's audio as 16-byte words
+	};
+
+	// Part q of CTA blockIdx.x (FusedArgs explains the two launch modes).  Also waits for the neighbour's flag when the
+	// part continues a stream the previous CTA began.  One thread runs it once per part; everything it computes is dead afterwards.
+	__device__ __forceinline__ void planFusedPart(const FusedArgs& a, uint32_t q, uint32_t P, bool wholeWindow, FusedPart* out)
+	{
+		const uint32_t F = a.nFrames, G = gridDim.x, cta = blockIdx.x;
+		const uint64_t items = uint64_t(a.numStreams) * F;
+		const uint64_t i0 = items * cta / G, i1 = items * (cta + 1) / G;
+		if (i1 == i0) { out->nParts = 0; return; } // (the host never launches more CTAs than items)
+		const uint32_t sA = uint32_t(i0 / F), fA = uint32_t(i0 - uint64_t(sA) * F);
+		const uint32_t sZ = uint32_t((i1 - 1) / F), fZ = uint32_t(i1 - uint64_t(sZ) * F);
+		const uint32_t nParts = sZ - sA + 1;
+		out->nParts = nParts;
+		if (q >= nParts) return;
+		const uint32_t headFirst = (a.chained && fZ < F && sZ > sA) ? 1u : 0u; // the head of stream sZ runs first and is published
+		const uint32_t tailLast = (a.chained && fA != 0) ? 1u : 0u;            // the tail of stream sA runs last, from the published state
+		uint32_t sLocal = sA + q;
+		if (a.chained)
+		{
+			if (headFirst && q == 0) sLocal = sZ;
+			else
+			{
+				const uint32_t r = q - headFirst, nMid = nParts - headFirst - tailLast;
+				sLocal = r < nMid ? sA + tailLast + r : sA;
+			}
+		}
+		const uint32_t fBegin = sLocal == sA ? fA : 0u, fEnd = sLocal == sZ ? fZ : F;
+		const int stream = int(sLocal + a.firstStream);
+		out->fBegin = fBegin; out->fEnd = fEnd; out->stream = stream; out->publish = 0;
+		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
+		out->audio = sbase;
+		out->vec4 = (a.layout == SGZ_LAYOUT_INTERLEAVED && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0) && wholeWindow) ? 1u : 0u;
+		out->src = nullptr;
+		if (fBegin == 0) out->src = a.states + uint64_t(stream) * 2 * P;
+		else if (a.chained)
+		{
+			// (published at the very start of the neighbour's work, so this hardly ever spins; the bound turns a lost
+			// neighbour - a launch that was not co-resident - into a launch error instead of a hang)
+			uint32_t spins = 0;
+			while (ldAcquire(a.flags + (cta - 1)) != a.epoch) { __nanosleep(128); if (++spins > (1u << 24)) __trap(); }
+			out->src = a.seam + uint64_t(cta - 1) * 2 * P;
+		}
+		if (a.chained)
+		{
+			if (fEnd == F) out->dst = a.states + uint64_t(stream) * 2 * P;
+			else { out->dst = a.seam + uint64_t(cta) * 2 * P; out->publish = 1; }
+		}
+		else out->dst = a.seam + uint64_t(fBegin ? cta : G + cta) * 2 * P;
+	}
 
 	// packed bin map entry: bit 31 = max-of-bins, bits 30..16 = count, bits 15..0 = first
 	__host__ __device__ __forceinline__ uint32_t packBinMap(int mode, int first, int count) { return (uint32_t(mode) << 31) | (uint32_t(count) << 16) | uint32_t(first); }

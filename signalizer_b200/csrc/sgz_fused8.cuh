@@ -24,13 +24,17 @@
 // SGZ8_WINDOW: 0 = window taps from the table, fetched ahead of the audio; 1 = fetched after it; 2 = evaluated from
 // the thread's twiddle when the window is a cosine sum spanning the whole transform (table otherwise)
 #ifndef SGZ8_WINDOW
-#define SGZ8_WINDOW 0
+#define SGZ8_WINDOW 1
 #endif
 // A/B switches (tools/ab_libs.sh): SGZ8_SPLIT_SMEM 1 = the two-for-one split fetches its partner bins through shared
 // memory instead of warp shuffles; SGZ8_STAGE_LATE 1 = the next frame's audio is staged after the split instead of
 // before it; SGZ8_AOS_WEIGHTS 1 = Lanczos weights read point-major
 #ifndef SGZ8_SPLIT_SMEM
-#define SGZ8_SPLIT_SMEM 0
+#define SGZ8_SPLIT_SMEM 1
+#endif
+// SGZ8_PAIR_BARRIER 1 = the barrier between passes 2 and 3 covers only the two warps that share a sub-transform
+#ifndef SGZ8_PAIR_BARRIER
+#define SGZ8_PAIR_BARRIER 0
 #endif
 #ifndef SGZ8_STAGE_LATE
 #define SGZ8_STAGE_LATE 0
@@ -58,7 +62,7 @@
 		static constexpr size_t twBytes = size_t(twEntries) * sizeof(float2);
 		static constexpr size_t stateOffset = twOffset + twBytes;
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
-		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12; }
+		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12 + 48; } // ... + the part plan (FusedPart)
 	};
 	typedef Fused8GeomT<8> Fused8Geom;
 
@@ -309,7 +313,13 @@
 			}
 #endif
 		}
+#if SGZ8_PAIR_BARRIER
+		// passes 2 and 3 stay inside the 512-point sub-transform k1 = u >> 6, i.e. inside one pair of warps: only they wait
+		if constexpr (K1 <= 8) asm volatile("bar.sync %0, 64;" :: "r"(1 + (u >> 6)) : "memory");
+		else __syncthreads();
+#else
 		__syncthreads();
+#endif
 
 		// ---- pass 3 (in place): thread (k1 k2 n4), DFT8 over n3, twiddle W_64^(n4 k3) ----
 		{
@@ -495,64 +505,44 @@
 		}
 #endif
 		// ---- this CTA's share of the launch: items [i0, i1) of the stream-major frame list, cut into per-stream parts ----
-		const uint32_t F = a.nFrames, G = gridDim.x, cta = blockIdx.x;
-		const uint64_t items = uint64_t(a.numStreams) * F;
-		const uint64_t i0 = items * cta / G, i1 = items * (cta + 1) / G;
-		if (i1 == i0) return; // (the host never launches more CTAs than items)
-		const uint32_t sA = uint32_t(i0 / F), fA = uint32_t(i0 - uint64_t(sA) * F);
-		const uint32_t sZ = uint32_t((i1 - 1) / F), fZ = uint32_t(i1 - uint64_t(sZ) * F);
-		const uint32_t nParts = sZ - sA + 1;
-		const uint32_t headFirst = (a.chained && fZ < F && sZ > sA) ? 1u : 0u; // the head of stream sZ runs first and is published
-		const uint32_t tailLast = (a.chained && fA != 0) ? 1u : 0u;            // the tail of stream sA runs last, from the published state
+		// (planned one part at a time into shared memory by planFusedPart, so that nothing of the bookkeeping stays in
+		// registers across the frame loop, which has none to spare)
+		FusedPart* part = reinterpret_cast<FusedPart*>(smemRaw + Gm::mapOffset(t.P) + size_t(P) * 12);
 		const int W = int(t.W);
 
-		for (uint32_t q = 0; q < nParts; ++q)
+		for (uint32_t q = 0;; ++q)
 		{
-		uint32_t sLocal = sA + q;
-		if (a.chained)
+		__syncthreads(); // the previous part's plan is no longer read (and its state has been written out)
+#ifdef SGZ8_NO_PARTS // A/B: one CTA per stream, nothing planned
+		if (u == 0)
 		{
-			if (headFirst && q == 0) sLocal = sZ;
-			else
-			{
-				const uint32_t r = q - headFirst, nMid = nParts - headFirst - tailLast;
-				sLocal = r < nMid ? sA + tailLast + r : sA;
-			}
+			part->nParts = 1; part->fBegin = 0; part->fEnd = a.nFrames; part->stream = int(blockIdx.x + a.firstStream); part->publish = 0;
+			part->src = a.states + uint64_t(part->stream) * 2 * P; part->dst = a.states + uint64_t(part->stream) * 2 * P;
+			part->audio = a.audio + uint64_t(part->stream) * a.streamStride; part->vec4 = 1;
 		}
-		const uint32_t fBegin = sLocal == sA ? fA : 0u, fEnd = sLocal == sZ ? fZ : F;
-		const int stream = int(sLocal + a.firstStream);
-		// where the part's peak-hold state comes from and goes to
-		const float2* stateSrc = nullptr; float2* stateDst; bool publish = false;
-		if (fBegin == 0) stateSrc = a.states + uint64_t(stream) * 2 * P;
-		else if (a.chained)
+#else
+		if (u == 0) planFusedPart(a, q, t.P, W == N, part);
+#endif
+		__syncthreads();
+		if (q >= part->nParts) break;
+		// (the frame loop reads the plan from shared memory where it needs it, like the kernel arguments from constant memory:
+		// its registers are all spoken for)
+		const volatile FusedPart* const plan = part;
 		{
-			if (u == 0)
-			{
-				// (published at the very start of the neighbour's work, so this hardly ever spins; the bound turns a lost
-				// neighbour - a launch that was not co-resident - into a launch error instead of a hang)
-				uint32_t spins = 0;
-				while (ldAcquire(a.flags + (cta - 1)) != a.epoch) { __nanosleep(128); if (++spins > (1u << 24)) __trap(); }
-			}
-			__syncthreads();
-			stateSrc = a.seam + uint64_t(cta - 1) * 2 * P;
+			const float2* stateSrc = part->src;
+			if (stateSrc) { for (int i = u; i < 2 * P; i += T) st[i] = __ldcg(stateSrc + i); }
+			else { for (int i = u; i < 2 * P; i += T) st[i] = make_float2(0.f, 0.f); }
 		}
-		if (a.chained)
-		{
-			if (fEnd == F) stateDst = a.states + uint64_t(stream) * 2 * P;
-			else { stateDst = a.seam + uint64_t(cta) * 2 * P; publish = true; }
-		}
-		else stateDst = a.seam + uint64_t(fBegin ? cta : G + cta) * 2 * P;
-		if (stateSrc) { for (int i = u; i < 2 * P; i += T) st[i] = __ldcg(stateSrc + i); }
-		else { for (int i = u; i < 2 * P; i += T) st[i] = make_float2(0.f, 0.f); }
 		// (the first block-wide barrier of the frame orders these writes before any display point reads them)
 
-		const float* sbase = a.audio + uint64_t(stream) * a.streamStride;
-		const bool vec4 = a.layout == SGZ_LAYOUT_INTERLEAVED && ((reinterpret_cast<uintptr_t>(sbase) & 15) == 0) && ((a.hop & 1) == 0) && W == N;
 		bool staged = false;
 
-		for (uint32_t f = fBegin; f < fEnd; ++f)
+		for (uint32_t f = plan->fBegin; f < plan->fEnd; ++f)
 		{
 			float2 re[8], im[8];
 			const uint64_t start = uint64_t(f) * a.hop;
+			const float* const sbase = plan->audio;
+			const bool vec4 = plan->vec4 != 0;
 
 			// ---- pass 1: load (all loads first), window + channel matrix, DFT8 over n1 ----
 			{
@@ -643,7 +633,7 @@
 			// newest half of the next frame -> lower half of the exchange buffer, in flight behind the split and the display
 			// (Phase keeps the whole buffer for its complex spectra)
 			staged = false;
-			if (MATRIX != 3 && vec4 && f + 1 < fEnd)
+			if (MATRIX != 3 && vec4 && f + 1 < plan->fEnd)
 			{
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -802,7 +792,7 @@
 			// newest half of the next frame -> lower half of the exchange buffer, in flight behind the split and the display
 			// (Phase keeps the whole buffer for its complex spectra)
 			staged = false;
-			if (MATRIX != 3 && vec4 && f + 1 < fEnd)
+			if (MATRIX != 3 && vec4 && f + 1 < plan->fEnd)
 			{
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -812,7 +802,8 @@
 			}
 #endif
 			// ---- display points: one per thread per step ----
-			float2* resOut = a.results + ((uint64_t(stream) * a.nFrames + f) * 2) * P;
+			// where this frame's two graphs go (resultRow: always somewhere, so the stores below are unconditional)
+			float2* const resRow[2] = { resultRow(a, uint64_t(plan->stream), f, 0, uint32_t(P)), resultRow(a, uint64_t(plan->stream), f, 1, uint32_t(P)) };
 			const float poles[2] = { t.pole0, t.pole1 };
 			const int safeFrom = int(t.safeFrom);
 			const float magScale = STEREO ? 0.5f * t.invSize : t.invSize; // the stereo split stores 2 |.|
@@ -909,7 +900,7 @@
 						// frame-parallel mode: the smoothing runs over ALL frames afterwards (k_phase_smooth), which needs this
 						// frame's filter input rather than the output of a filter that started from nothing
 						if (!a.chained) res.y = ph;
-						stg_stream_f2(resOut + k * P + x, res);
+						stg_stream_f2(resRow[k] + x, res);
 					}
 					continue;
 				}
@@ -1049,16 +1040,19 @@
 					}
 					else res.y = 0.f;
 					st[k * P + x] = sv;
-					stg_stream_f2(resOut + k * P + x, res);
+					stg_stream_f2(resRow[k] + x, res);
 				}
 			}
 		}
 		__syncthreads(); // every display point of the part's last frame has updated its state
-		for (int i = u; i < 2 * P; i += T) stateDst[i] = st[i];
-		if (publish)
 		{
-			__syncthreads();
-			if (u == 0) { __threadfence(); stRelease(a.flags + cta, a.epoch); }
+			float2* stateDst = part->dst;
+			for (int i = u; i < 2 * P; i += T) stateDst[i] = st[i];
+			if (part->publish)
+			{
+				__syncthreads();
+				if (u == 0) { __threadfence(); stRelease(a.flags + blockIdx.x, a.epoch); }
+			}
 		}
 		} // parts
 	}
@@ -1120,37 +1114,35 @@
 		}
 	}
 
-	__global__ void __launch_bounds__(128) k_seam_apply(DeviceTables t, float2* __restrict__ results, const float2* __restrict__ seam, uint32_t nFrames,
-		uint32_t nStreams, uint32_t G, int stereo, uint32_t firstStream)
+	__global__ void __launch_bounds__(128) k_seam_apply(DeviceTables t, FusedArgs a, uint32_t G, int stereo)
 	{
 		const int P = int(t.P);
 		const int x = blockIdx.x * blockDim.x + threadIdx.x;
 		if (x >= P) return;
-		const uint32_t c = blockIdx.y;
-		const uint64_t items = uint64_t(nStreams) * nFrames, i0 = seamCut(items, G, c), i1 = seamCut(items, G, c + 1);
+		const uint32_t c = blockIdx.y, nFrames = a.nFrames;
+		const uint64_t items = uint64_t(a.numStreams) * nFrames, i0 = seamCut(items, G, c), i1 = seamCut(items, G, c + 1);
 		if (i1 == i0) return;
 		const uint32_t sLocal = uint32_t(i0 / nFrames), f0 = uint32_t(i0 - uint64_t(sLocal) * nFrames);
 		if (f0 == 0) return; // the range begins a stream: nothing is carried in
 		const uint32_t f1 = uint32_t(min(uint64_t(nFrames), i1 - uint64_t(sLocal) * nFrames));
 		const float sm = t.slope[x] * t.minFracRecip;
 		const float poles[2] = { t.pole0, t.pole1 };
-		const float2* mine = seam + uint64_t(c) * 2 * P + x;
+		const float2* mine = a.seam + uint64_t(c) * 2 * P + x;
 		float2 carry[2] = { mine[0], mine[P] };
-		float2* frame = results + (((uint64_t(sLocal) + firstStream) * nFrames + f0) * 2) * P + x;
-		for (uint32_t f = f0; f < f1; ++f, frame += 2 * P)
+		const uint64_t stream = uint64_t(sLocal) + a.firstStream;
+		for (uint32_t f = f0; f < f1; ++f)
 		{
 #pragma unroll
 			for (int k = 0; k < 2; ++k)
 			{
 				carry[k].x *= poles[k];
-				float2 res = frame[k * P];
+				if (stereo) carry[k].y *= poles[k];
+				float2* row = keptRow(a, stream, f, k, uint32_t(P));
+				if (!row) continue;
+				float2 res = row[x];
 				res.x = fmaxf(res.x, fastLogScale(sm, carry[k].x, 1.f, t.deltaYLn2, t.lowerClip));
-				if (stereo)
-				{
-					carry[k].y *= poles[k];
-					res.y = fmaxf(res.y, fastLogScale(sm, carry[k].y, 1.f, t.deltaYLn2, t.lowerClip));
-				}
-				frame[k * P] = res;
+				if (stereo) res.y = fmaxf(res.y, fastLogScale(sm, carry[k].y, 1.f, t.deltaYLn2, t.lowerClip));
+				row[x] = res;
 			}
 		}
 	}

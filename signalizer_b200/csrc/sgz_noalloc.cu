@@ -12,6 +12,7 @@
 // through global memory).  There is no counterpart in the reference.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 
 #include "../../include/sgz.h"
@@ -43,8 +44,9 @@ namespace sgz
 		y[q + s * (2 * p + 1)] = cmul(csub(u, v), make_float2(cs, sn));
 	}
 
-	// per-device address of g_noallocScratch, looked up once per device
-	static float2* g_scratchAddress[64] = {};
+	// per-device address of g_noallocScratch, looked up once per device (host threads may race to the first call on
+	// a device: they all store the same value)
+	static std::atomic<float2*> g_scratchAddress[64];
 }
 
 extern "C" int sgz_fft_forward_noalloc(const float* d_in, float* d_out, uint32_t n, uint32_t batch, void* cuda_stream)
@@ -58,19 +60,25 @@ extern "C" int sgz_fft_forward_noalloc(const float* d_in, float* d_out, uint32_t
 		return fail(SGZ_EINVAL, "sgz_fft_forward_noalloc: n * batch = %llu exceeds the built-in scratch of %u complex points; "
 			"split the batch or use the handle API", (unsigned long long)(uint64_t(n) * batch), unsigned(SGZ_NOALLOC_MAX_POINTS));
 	if (batch > 65535) return fail(SGZ_EINVAL, "sgz_fft_forward_noalloc: batch %u exceeds 65535", batch);
+	{
+		// the first pass may write d_out while other threads still read d_in: the two ranges must not overlap at all
+		const uintptr_t a = reinterpret_cast<uintptr_t>(d_in), b = reinterpret_cast<uintptr_t>(d_out);
+		const uintptr_t bytes = uintptr_t(n) * batch * sizeof(float2);
+		if (a < b + bytes && b < a + bytes) return fail(SGZ_EINVAL, "sgz_fft_forward_noalloc: d_in and d_out overlap");
+	}
 
 	int dev = -1;
 	if (cudaGetDevice(&dev) != cudaSuccess) return fail(SGZ_ECUDA, "sgz_fft_forward_noalloc: no current CUDA device");
 	if (dev < 0 || dev >= 64) return fail(SGZ_EUNSUPPORTED, "sgz_fft_forward_noalloc: device ordinal %d out of range", dev);
-	if (!g_scratchAddress[dev])
+	if (!g_scratchAddress[dev].load(std::memory_order_acquire))
 	{
 		// set-up, once per device, with that device current: translate the symbol to its address
 		float2* p = nullptr;
 		const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noallocScratch);
 		if (e != cudaSuccess || !p) return fail(SGZ_ECUDA, "sgz_fft_forward_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
-		g_scratchAddress[dev] = p;
+		g_scratchAddress[dev].store(p, std::memory_order_release);
 	}
-	float2* scratch = g_scratchAddress[dev];
+	float2* scratch = g_scratchAddress[dev].load(std::memory_order_acquire);
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
 
 	uint32_t passes = 0;

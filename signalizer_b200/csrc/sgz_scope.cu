@@ -1049,6 +1049,35 @@ extern "C"
 		return SGZ_OK;
 	}
 
+	// the two trigger kernels on device-resident arrays (shared by the host-array and the device-array entry points)
+	static int launchTrigger(sgz_context* c, int mode, int channel, const float* d, int layout, uint32_t n_streams, uint64_t n_samples, uint64_t stream_stride,
+		double threshold, double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* dStates, uint64_t* dPeaks, uint32_t* dCounts, uint32_t max_peaks)
+	{
+		TriggerArgs a{};
+		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = channel; a.nStreams = n_streams;
+		a.threshold = threshold; a.hysteresis = hysteresis; a.steadyClock = steady_clock; a.states = dStates; a.peaks = dPeaks; a.counts = dCounts; a.maxPeaks = max_peaks;
+		const unsigned warpsPerBlock = 4, blocks = (n_streams + warpsPerBlock - 1) / warpsPerBlock;
+		if (mode == 0) k_scope_trigger_zero<<<n_streams, 32 * kTrigWarps, 0, c->stream>>>(a);
+		else k_scope_trigger_peak<<<blocks, warpsPerBlock * 32, 0, c->stream>>>(a);
+		SGZS_CUDA(cudaGetLastError());
+		return SGZ_OK;
+	}
+
+	// sgz_scope_trigger with every array on the device: nothing is copied and nothing waits - the call only enqueues the
+	// kernel on the context's stream, so a device-resident pipeline keeps the kernel's rate
+	int sgz_scope_trigger_device(sgz_context* c, int mode, int channel, const float* d_audio, int layout, uint32_t n_streams, uint64_t n_samples,
+		uint64_t stream_stride, double threshold, double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* d_states, uint64_t* d_peaks,
+		uint32_t* d_counts, uint32_t max_peaks)
+	{
+		int rc;
+		if (!d_states || !d_counts || (max_peaks && !d_peaks)) return fail(SGZ_EINVAL, "null argument");
+		if (mode != 0 && mode != 1) return fail(SGZ_EINVAL, "mode must be 0 (zero crossing) or 1 (envelope hold)");
+		if (channel < SGZ_OSC_LEFT || channel > SGZ_OSC_SIDE) return fail(SGZ_EINVAL, "bad channel");
+		if ((rc = validateAudio(d_audio, layout, n_streams, n_samples, stream_stride)) != SGZ_OK) return rc;
+		SGZS_GUARD(c);
+		return launchTrigger(c, mode, channel, d_audio, layout, n_streams, n_samples, stream_stride, threshold, hysteresis, steady_clock, d_states, d_peaks, d_counts, max_peaks);
+	}
+
 	int sgz_scope_trigger(sgz_context* c, int mode, int channel, const float* audio, int mem, int layout, uint32_t n_streams, uint64_t n_samples,
 		uint64_t stream_stride, double threshold, double hysteresis, uint64_t steady_clock, sgz_scope_trigger_state* states, uint64_t* peaks,
 		uint32_t* counts, uint32_t max_peaks)
@@ -1068,13 +1097,7 @@ extern "C"
 		auto* dPeaks = reinterpret_cast<uint64_t*>(static_cast<char*>(p) + ((stBytes + 15) & ~size_t(15)));
 		auto* dCounts = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(dPeaks) + pkBytes);
 		SGZS_CUDA(cudaMemcpyAsync(dStates, states, stBytes, cudaMemcpyHostToDevice, c->stream));
-		TriggerArgs a{};
-		a.audio = d; a.layout = layout; a.n = n_samples; a.stride = stream_stride; a.channel = channel; a.nStreams = n_streams;
-		a.threshold = threshold; a.hysteresis = hysteresis; a.steadyClock = steady_clock; a.states = dStates; a.peaks = dPeaks; a.counts = dCounts; a.maxPeaks = max_peaks;
-		const unsigned warpsPerBlock = 4, blocks = (n_streams + warpsPerBlock - 1) / warpsPerBlock;
-		if (mode == 0) k_scope_trigger_zero<<<n_streams, 32 * kTrigWarps, 0, c->stream>>>(a);
-		else k_scope_trigger_peak<<<blocks, warpsPerBlock * 32, 0, c->stream>>>(a);
-		SGZS_CUDA(cudaGetLastError());
+		if ((rc = launchTrigger(c, mode, channel, d, layout, n_streams, n_samples, stream_stride, threshold, hysteresis, steady_clock, dStates, dPeaks, dCounts, max_peaks)) != SGZ_OK) return rc;
 		SGZS_CUDA(cudaMemcpyAsync(states, dStates, stBytes, cudaMemcpyDeviceToHost, c->stream));
 		if (max_peaks) SGZS_CUDA(cudaMemcpyAsync(peaks, dPeaks, size_t(n_streams) * max_peaks * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
 		SGZS_CUDA(cudaMemcpyAsync(counts, dCounts, cnBytes, cudaMemcpyDeviceToHost, c->stream));

@@ -37,7 +37,7 @@ namespace sgz
 	inline int fusedK1For(uint32_t N) { return N == 16384 ? 16 : N == 8192 ? 8 : N == 4096 ? 4 : N == 2048 ? 2 : N == 1024 ? 1 : 0; }
 	// the fused kernel keeps 28 bytes per display point next to the N * 8-byte exchange buffer; one CTA must fit the
 	// 227 KB an SM can give (the resident CTAs per SM then follow from the size: 2 at N = 8192 up to 2048 points, 1 beyond)
-	inline bool fusedSharedMemoryFits(uint32_t N, uint32_t P) { return size_t(N) * 8 + 2048 + size_t(P) * 28 <= size_t(227) * 1024; }
+	inline bool fusedSharedMemoryFits(uint32_t N, uint32_t P) { return size_t(N) * 8 + 2048 + 48 + size_t(P) * 28 <= size_t(227) * 1024; }
 	constexpr uint32_t kFrameParallelMinRun = 4;   // with fewer streams than resident CTAs a stream is cut into parts of at least this many frames
 
 	// ------------------------------------------------------------------------------------------
@@ -687,11 +687,13 @@ struct sgz_spectrum
 	int fusedK1{ 0 }; // first-pass radix of the fused kernel k_fused8<K1> this handle uses (0: staged kernels only)
 	cudaStream_t copyIn{ nullptr }, copyOut{ nullptr }; // host-buffer pipeline of process_frames
 	std::vector<cudaEvent_t> events;
+	uint32_t pipeChunks{ 16 };    // stream chunks of the host-buffer pipeline (measured on BASELINE config 3: 8 -> 2.59 M, 16 -> 2.68 M, 32 -> 2.66 M, 64 -> 2.53 M frames/s)
 	bool seamsOk{ false };        // the unchained launch mode is exact for this configuration (monotone hold and display scale)
 	uint32_t fusedCapacity{ 0 };  // CTAs of this handle's fused kernel the device holds at once (the launch size of k_fused8)
 	uint32_t fusedEpoch{ 0 };     // launch counter: the value a seam flag must show (no clearing between launches)
 	float2* dSeam{ nullptr };     // [2 capacity][2][P] peak-hold states at the seams between CTA ranges
 	uint32_t* dSeamFlags{ nullptr }; // [capacity]
+	float2* dSpare{ nullptr };    // [P] sink for results an output mode does not keep (FusedArgs::spare)
 	void* dTrack{ nullptr }; // frequency tracker: [S] bounds in, [S] records out
 	// device-resident audio history (sgz_spectrum_history_*): per stream a ring of `ringCapacity` stereo
 	// samples stored twice back to back ([S][2 C] float2), so that any run of <= C samples ending at the
@@ -1043,6 +1045,7 @@ extern "C"
 			SGZ_TRY(launchFused(h, none, nullptr)); // capacity query only
 			SGZ_TRY(allocZero(h, size_t(2) * h->fusedCapacity * 2 * t.P, &h->dSeam));
 			SGZ_TRY(allocZero(h, size_t(h->fusedCapacity), &h->dSeamFlags));
+			SGZ_TRY(allocZero(h, size_t(t.P), &h->dSpare));
 			// carrying the hold across zero-started parts relies on x -> x * pole and on the dB scale being monotone
 			// non-decreasing: non-negative poles and slope, an upright dB range, and a clip value below every reachable one
 			h->seamsOk = cfg->pole[0] >= 0.f && cfg->pole[1] >= 0.f && cfg->slope_b >= 0.0 && d.deltaYLn2 > 0.f
@@ -1066,6 +1069,18 @@ extern "C"
 		out->window_kernel_scale = h->tab.windowKernelScale; out->inv_size = h->tab.invSize; out->freq_to_bin = h->tab.freqToBin;
 		out->resonator_vectors = h->tab.resonatorVectors; out->device = h->device; out->fused_available = h->fusedK1 != 0;
 		return SGZ_OK;
+	}
+
+	const char* sgz_spectrum_kernel_name(const sgz_spectrum* h)
+	{
+		// the instantiation launchFused picks for this handle, spelled like the profiler spells it
+		static thread_local char name[96];
+		if (!h || h->fusedK1 == 0) return "";
+		const int conf = h->cfg.configuration;
+		const bool stereo = conf == SGZ_CH_SEPARATE || conf == SGZ_CH_PHASE || (conf != SGZ_CH_COMPLEX && h->tab.stateChannels == 2);
+		const int matrix = conf == SGZ_CH_SEPARATE ? 0 : conf == SGZ_CH_COMPLEX ? 2 : conf == SGZ_CH_PHASE ? 3 : 1;
+		std::snprintf(name, sizeof(name), "sgz::k_fused8<%d, %d, %d, %d>", h->fusedK1, stereo ? 1 : 0, int(h->cfg.bin_polation), matrix);
+		return name;
 	}
 
 	int sgz_spectrum_set_cuda_stream(sgz_spectrum* h, void* cuda_stream)
@@ -1115,9 +1130,12 @@ extern "C"
 		return SGZ_OK;
 	}
 
+	// nPrelim: samples of the preliminary buffer that count as the newest audio; prelimLength: samples per channel the
+	// buffer actually holds (>= nPrelim) - the planar channel stride and what a host buffer needs staged
 	static int prepareCommon(sgz_spectrum* h, const float* hist, uint64_t nHist, uint64_t histStride, const float* prelim, uint64_t nPrelim,
-		uint64_t prelimStride, int mem, int layout, bool withPrelim)
+		uint64_t prelimStride, int mem, int layout, bool withPrelim, uint64_t prelimLength = 0)
 	{
+		if (prelimLength < nPrelim) prelimLength = nPrelim;
 		if (!h || !hist) return fail(SGZ_EINVAL, "null argument");
 		if (h->cfg.algo != SGZ_ALGO_FFT) return nHist < h->tab.W ? SGZ_SKIPPED : SGZ_OK; // the switch at TransformDSP.inl:51-53 only has an FFT case
 		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
@@ -1153,13 +1171,13 @@ extern "C"
 			if (mem == SGZ_MEM_DEVICE) a.prelim = prelim;
 			else
 			{
-				const size_t floats = size_t(prelimStride) * (h->nStreams - 1) + audioFloatsPerStream(nPrelim);
+				const size_t floats = size_t(prelimStride) * (h->nStreams - 1) + audioFloatsPerStream(prelimLength);
 				rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, floats * sizeof(float));
 				if (rc != SGZ_OK) return rc;
 				SGZ_CUDA(cudaMemcpyAsync(h->dResultStage, prelim, floats * sizeof(float), cudaMemcpyHostToDevice, h->stream));
 				a.prelim = h->dResultStage;
 			}
-			a.nPrelim = nPrelim; a.prelimStride = prelimStride;
+			a.nPrelim = prelimLength; a.prelimStride = prelimStride;
 		}
 		const dim3 block(256), grid((h->tab.N + 1 + 255) / 256, h->nStreams);
 		k_prepare<<<grid, block, 0, h->stream>>>(h->dev, a, h->dCsf);
@@ -1186,7 +1204,11 @@ extern "C"
 		if (h->stage < 1) return fail(SGZ_ESTATE, "call prepareTransform() first (TransformPair.h:123-124)");
 		SGZ_GUARD(h);
 		const uint32_t N = h->tab.N;
-		const bool generic = std::getenv("SGZ_STAGED_FFT_GENERIC") != nullptr;
+#ifdef SGZ_STAGED_FFT_GENERIC // (development switch: every size through the shared-memory / global-pass kernels)
+		const bool generic = true;
+#else
+		const bool generic = false;
+#endif
 		const uint64_t csfStride = uint64_t(N) + 1, workStride = std::max<size_t>(N, size_t(2) * h->tab.P);
 #define SGZ_FFT8(K1, SRC, SSTRIDE, DST, DSTRIDE, SUBS)                                                                        \
 		{                                                                                                                     \
@@ -1376,7 +1398,7 @@ extern "C"
 				h->resPartialBytes = need;
 			}
 		}
-		if (h->tab.stateChannels == 2 && !std::getenv("SGZ_RESONATE_SCALAR"))
+		if (h->tab.stateChannels == 2)
 			k_resonate_pair<<<dim3((total / 2 + 255) / 256, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
 		else
 			k_resonate<<<dim3(blocksX, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
@@ -1420,7 +1442,8 @@ extern "C"
 					if (fft)
 					{
 						// NOTE: `buffer`, not buffer + offset, exactly like the reference (:1192)
-						rc = sgz_spectrum_prepare_preliminary(h, history, n_history, history_stride, block, uint64_t(availableSamples), block_stride, mem, layout);
+						// (the block keeps its own length as planar channel stride; only availableSamples of it count)
+						rc = prepareCommon(h, history, n_history, history_stride, block, uint64_t(availableSamples), block_stride, mem, layout, true, n_block);
 						if (rc < 0) return rc;
 						transformReady = rc == SGZ_OK;
 						if (transformReady && (rc = sgz_spectrum_transform(h)) != SGZ_OK) return rc;
@@ -1523,6 +1546,22 @@ extern "C"
 	// kernel of chunk c and the download of chunk c-1 overlap (PCIe is full duplex); results are
 	// identical to the single launch because streams are independent.
 	// Launches the fused kernel for the streams [a.firstStream, a.firstStream + a.numStreams) on the handle's stream.
+	// lineGraphs[k].results of the handle = the last frame (TransformPair.h:72-76): the rows of it that the output mode
+	// kept in the caller's buffer are copied over; the others the kernel wrote there itself (resultRow)
+	static int keepLastFrame(sgz_spectrum* h, const FusedArgs& a)
+	{
+		const size_t graph = size_t(h->tab.P) * sizeof(float2);
+		const uint32_t F = a.nFrames, nS = a.numStreams;
+		float2* dst = h->dResults + size_t(a.firstStream) * 2 * h->tab.P;
+		if (a.outMode == SGZ_OUT_FULL)
+			SGZ_CUDA(cudaMemcpy2DAsync(dst, 2 * graph, a.results + (size_t(a.firstStream) * F + (F - 1)) * 2 * h->tab.P, size_t(F) * 2 * graph, 2 * graph, nS, cudaMemcpyDeviceToDevice, h->stream));
+		else if (a.outMode == SGZ_OUT_LINE_MAIN)
+			SGZ_CUDA(cudaMemcpy2DAsync(dst, 2 * graph, a.results + (size_t(a.firstStream) * F + (F - 1)) * h->tab.P, size_t(F) * graph, graph, nS, cudaMemcpyDeviceToDevice, h->stream));
+		else
+			SGZ_CUDA(cudaMemcpyAsync(dst, a.results + size_t(a.firstStream) * 2 * h->tab.P, size_t(nS) * 2 * graph, cudaMemcpyDeviceToDevice, h->stream));
+		return SGZ_OK;
+	}
+
 	// One k_fused8 launch over streams [a.firstStream, + a.numStreams) x a.nFrames frames.  The grid is the number of CTAs
 	// the device holds at once (sgz_fused.cuh, FusedArgs): with at least that many streams the seams between CTA ranges
 	// are chained inside the kernel; with fewer (a long recording rather than a wall of channels, or one chunk of the
@@ -1532,6 +1571,9 @@ extern "C"
 		const uint32_t P = h->tab.P, F = a.nFrames, nS = a.numStreams;
 		const uint64_t items = uint64_t(nS) * F;
 		const uint32_t capacity = std::max<uint32_t>(1, h->fusedCapacity);
+		// Phase: .x is a peak hold like the others, .y a smoother (k_phase_smooth below, which needs every frame's filter input,
+		// i.e. the full output)
+		const bool phase = h->cfg.configuration == SGZ_CH_PHASE;
 		FusedPlan plan{ nS, true, false };
 #ifdef SGZ8_PER_STREAM_GRID
 		if (false)
@@ -1542,38 +1584,58 @@ extern "C"
 			plan.ctas = capacity;                 // balanced ranges of >= one stream's worth of frames each
 			plan.cooperative = nS > capacity;     // some range ends mid-stream: CTAs wait on their neighbour's flag
 		}
-		else if (h->seamsOk && items / kFrameParallelMinRun > nS)
+		else if (h->seamsOk && items / kFrameParallelMinRun > nS && !(phase && a.outMode != SGZ_OUT_FULL))
 		{
 			plan.ctas = uint32_t(std::min<uint64_t>(capacity, items / kFrameParallelMinRun));
 			plan.chained = false;
 		}
+		a.lastResults = h->dResults; a.spare = h->dSpare;
 		int rc = launchFused(h, a, &plan);
-		if (rc != SGZ_OK || plan.chained) return rc;
-		const bool phase = h->cfg.configuration == SGZ_CH_PHASE; // .x is a peak hold like the others, .y a smoother (k_phase_smooth below)
+		if (rc != SGZ_OK) return rc;
+		if (plan.chained) return keepLastFrame(h, a);
 		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO form of the hold
 		k_seam_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSeam, h->dStates, F, nS, plan.ctas, stereoFlag, a.firstStream);
-		k_seam_apply<<<dim3((P + 127) / 128, plan.ctas), 128, 0, h->stream>>>(h->dev, a.results, h->dSeam, F, nS, plan.ctas, stereoFlag, a.firstStream);
+		k_seam_apply<<<dim3((P + 127) / 128, plan.ctas), 128, 0, h->stream>>>(h->dev, a, plan.ctas, stereoFlag);
 		if (phase) k_phase_smooth<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, a.results, h->dStates, F, a.firstStream);
 		SGZ_CUDA(cudaGetLastError());
-		return SGZ_OK;
+		return keepLastFrame(h, a);
+	}
+
+	// floats of `results` per stream in each output mode (include/sgz.h, SGZ_OUT_*)
+	static size_t resultFloatsPerStream(int output, uint32_t n_frames, uint32_t P)
+	{
+		switch (output)
+		{
+		case SGZ_OUT_LINE_MAIN: return size_t(n_frames) * P * 2;
+		case SGZ_OUT_LAST_FRAME: return size_t(2) * P * 2;
+		default: return size_t(n_frames) * 2 * P * 2;
+		}
+	}
+
+	// waits for whatever a failed call left in flight on the handle's streams (copies into or out of caller memory)
+	static int drained(sgz_spectrum* h, int rc)
+	{
+		if (h->copyIn) cudaStreamSynchronize(h->copyIn);
+		if (h->stream) cudaStreamSynchronize(h->stream);
+		if (h->copyOut) cudaStreamSynchronize(h->copyOut);
+		return rc;
 	}
 
 	static int processFramesPipelined(sgz_spectrum* h, const float* audio, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
-		uint32_t n_frames, float* results)
+		uint32_t n_frames, float* results, int output)
 	{
 		const uint32_t P = h->tab.P, S = h->nStreams;
 		const size_t audioFloats = size_t(stream_stride) * (S - 1) + size_t(n_samples) * 2;
-		const size_t resPerStream = size_t(n_frames) * 2 * P * 2;
+		const size_t resPerStream = resultFloatsPerStream(output, n_frames, P);
 		int rc = ensureStage(h, &h->dAudioStage, &h->audioStageBytes, audioFloats * sizeof(float));
 		if (rc != SGZ_OK) return rc;
 		if ((rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, resPerStream * S * sizeof(float))) != SGZ_OK) return rc;
 		if (!h->copyIn) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyIn, cudaStreamNonBlocking));
 		if (!h->copyOut) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyOut, cudaStreamNonBlocking));
 		// chunks of streams flow through copy-in -> kernels -> copy-out; the first copy-in and the last copy-out are not
-		// overlapped, so smaller chunks shorten that fill / drain.  A chunk of a few dozen streams would not fill the GPU
-		// with one CTA per stream, which is what launchFusedFrames' frame-parallel mode is for
-		uint32_t chunks = std::max<uint32_t>(1, std::min<uint32_t>(16, S / 8)); // measured on BASELINE config 3: 8 -> 2.59 M, 16 -> 2.68 M, 32 -> 2.66 M, 64 -> 2.53 M frames/s
-		if (const char* e = std::getenv("SGZ_PIPE_CHUNKS")) chunks = std::max<uint32_t>(1, std::min<uint32_t>(std::min<uint32_t>(uint32_t(std::atoi(e)), S), 256u));
+		// overlapped, so smaller chunks shorten that fill / drain.  A chunk of a few dozen streams has fewer streams than
+		// the GPU holds CTAs, which is what launchFusedFrames' unchained mode is for
+		const uint32_t chunks = std::max<uint32_t>(1, std::min<uint32_t>(h->pipeChunks, S / 8));
 		while (h->events.size() < 2 * chunks + 1)
 		{
 			cudaEvent_t e;
@@ -1583,38 +1645,53 @@ extern "C"
 		// the copy streams start after whatever the caller queued on the handle's stream
 		SGZ_CUDA(cudaEventRecord(h->events[2 * chunks], h->stream));
 		SGZ_CUDA(cudaStreamWaitEvent(h->copyIn, h->events[2 * chunks], 0));
+		auto fail2 = [&](cudaError_t e, const char* what) { return drained(h, fail(SGZ_ECUDA, "%s failed: %s", what, cudaGetErrorString(e))); };
 		for (uint32_t c = 0; c < chunks; ++c)
 		{
 			const uint32_t s0 = uint32_t(uint64_t(S) * c / chunks), s1 = uint32_t(uint64_t(S) * (c + 1) / chunks);
 			if (s1 == s0) continue;
 			const size_t off = size_t(s0) * stream_stride;
 			const size_t floats = size_t(stream_stride) * (s1 - s0 - 1) + size_t(n_samples) * 2;
-			SGZ_CUDA(cudaMemcpyAsync(h->dAudioStage + off, audio + off, floats * sizeof(float), cudaMemcpyHostToDevice, h->copyIn));
-			SGZ_CUDA(cudaEventRecord(h->events[2 * c], h->copyIn));
-			SGZ_CUDA(cudaStreamWaitEvent(h->stream, h->events[2 * c], 0));
+			cudaError_t e;
+			if ((e = cudaMemcpyAsync(h->dAudioStage + off, audio + off, floats * sizeof(float), cudaMemcpyHostToDevice, h->copyIn)) != cudaSuccess) return fail2(e, "copy-in");
+			if ((e = cudaEventRecord(h->events[2 * c], h->copyIn)) != cudaSuccess) return fail2(e, "event record");
+			if ((e = cudaStreamWaitEvent(h->stream, h->events[2 * c], 0)) != cudaSuccess) return fail2(e, "stream wait");
 			FusedArgs a{};
 			a.audio = h->dAudioStage; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
 			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(h->dResultStage);
+			a.outMode = uint32_t(output);
 			a.firstStream = s0; a.numStreams = s1 - s0;
-			if ((rc = launchFusedFrames(h, a)) != SGZ_OK) return rc;
-			SGZ_CUDA(cudaEventRecord(h->events[2 * c + 1], h->stream));
-			SGZ_CUDA(cudaStreamWaitEvent(h->copyOut, h->events[2 * c + 1], 0));
-			SGZ_CUDA(cudaMemcpyAsync(results + resPerStream * s0, h->dResultStage + resPerStream * s0, resPerStream * (s1 - s0) * sizeof(float),
-				cudaMemcpyDeviceToHost, h->copyOut));
+			if ((rc = launchFusedFrames(h, a)) != SGZ_OK) return drained(h, rc);
+			if ((e = cudaEventRecord(h->events[2 * c + 1], h->stream)) != cudaSuccess) return fail2(e, "event record");
+			if ((e = cudaStreamWaitEvent(h->copyOut, h->events[2 * c + 1], 0)) != cudaSuccess) return fail2(e, "stream wait");
+			if ((e = cudaMemcpyAsync(results + resPerStream * s0, h->dResultStage + resPerStream * s0, resPerStream * (s1 - s0) * sizeof(float),
+				cudaMemcpyDeviceToHost, h->copyOut)) != cudaSuccess) return fail2(e, "copy-out");
 		}
-		// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
-		SGZ_CUDA(cudaMemcpy2DAsync(h->dResults, size_t(2) * P * sizeof(float2), h->dResultStage + size_t(n_frames - 1) * 2 * P * 2,
-			size_t(n_frames) * 2 * P * sizeof(float2), size_t(2) * P * sizeof(float2), S, cudaMemcpyDeviceToDevice, h->stream));
 		SGZ_CUDA(cudaStreamSynchronize(h->copyOut));
 		SGZ_CUDA(cudaStreamSynchronize(h->stream));
 		return SGZ_OK;
 	}
 
-	int sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
-		uint32_t n_frames, float* results, int results_mem)
+	// one frame's lineGraphs results (h->dResults, [S][2][P]) -> its place in `dRes` for the staged / resonator paths
+	static int storeStagedFrame(sgz_spectrum* h, float* dRes, int output, uint32_t f, uint32_t n_frames)
+	{
+		const uint32_t P = h->tab.P;
+		const size_t graph = size_t(P) * sizeof(float2);
+		if (output == SGZ_OUT_FULL)
+			SGZ_CUDA(cudaMemcpy2DAsync(dRes + size_t(f) * 2 * P * 2, size_t(n_frames) * 2 * graph, h->dResults, 2 * graph, 2 * graph, h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+		else if (output == SGZ_OUT_LINE_MAIN)
+			SGZ_CUDA(cudaMemcpy2DAsync(dRes + size_t(f) * P * 2, size_t(n_frames) * graph, h->dResults, 2 * graph, graph, h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+		else if (f + 1 == n_frames)
+			SGZ_CUDA(cudaMemcpyAsync(dRes, h->dResults, size_t(h->nStreams) * 2 * graph, cudaMemcpyDeviceToDevice, h->stream));
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_process_frames_select(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
+		uint32_t n_frames, float* results, int results_mem, int output)
 	{
 		if (!h || !audio || !results) return fail(SGZ_EINVAL, "null argument");
 		if (layout != SGZ_LAYOUT_PLANAR && layout != SGZ_LAYOUT_INTERLEAVED) return fail(SGZ_EINVAL, "bad layout");
+		if (output != SGZ_OUT_FULL && output != SGZ_OUT_LINE_MAIN && output != SGZ_OUT_LAST_FRAME) return fail(SGZ_EINVAL, "bad output selector %d", output);
 		if (n_frames == 0) return SGZ_OK;
 		const uint32_t W = h->tab.W, P = h->tab.P;
 		const bool rsnt = h->cfg.algo == SGZ_ALGO_RSNT;
@@ -1625,16 +1702,16 @@ extern "C"
 			return fail(SGZ_EINVAL, "interleaved audio must be 8-byte aligned with an even stream_stride");
 		SGZ_GUARD(h);
 		if (!rsnt && h->fusedK1 != 0 && mem == SGZ_MEM_HOST && results_mem == SGZ_MEM_HOST && h->nStreams >= 8)
-			return processFramesPipelined(h, audio, layout, n_samples, stream_stride, hop, n_frames, results);
+			return processFramesPipelined(h, audio, layout, n_samples, stream_stride, hop, n_frames, results, output);
 		const float* dAudio = nullptr;
 		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);
 		if (rc != SGZ_OK) return rc;
-		const size_t resFloats = size_t(h->nStreams) * n_frames * 2 * P * 2;
+		const size_t resFloats = size_t(h->nStreams) * resultFloatsPerStream(output, n_frames, P);
 		float* dRes = results;
 		if (results_mem == SGZ_MEM_HOST)
 		{
 			rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, resFloats * sizeof(float));
-			if (rc != SGZ_OK) return rc;
+			if (rc != SGZ_OK) return drained(h, rc);
 			dRes = h->dResultStage;
 		}
 		if (rsnt)
@@ -1643,11 +1720,10 @@ extern "C"
 			// addAudioFrame = snapshot + post-process
 			for (uint32_t f = 0; f < n_frames; ++f)
 			{
-				if ((rc = resonateBlock(h, dAudio, layout, n_samples, stream_stride, uint64_t(f) * hop, hop)) != SGZ_OK) return rc;
-				if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return rc;
-				if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return rc;
-				SGZ_CUDA(cudaMemcpy2DAsync(dRes + size_t(f) * 2 * P * 2, size_t(n_frames) * 2 * P * sizeof(float2), h->dResults, size_t(2) * P * sizeof(float2),
-					size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+				if ((rc = resonateBlock(h, dAudio, layout, n_samples, stream_stride, uint64_t(f) * hop, hop)) != SGZ_OK) return drained(h, rc);
+				if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return drained(h, rc);
+				if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return drained(h, rc);
+				if ((rc = storeStagedFrame(h, dRes, output, f, n_frames)) != SGZ_OK) return drained(h, rc);
 			}
 		}
 		else if (h->fusedK1 != 0)
@@ -1655,11 +1731,9 @@ extern "C"
 			FusedArgs a{};
 			a.audio = dAudio; a.nSamples = n_samples; a.streamStride = stream_stride; a.layout = layout;
 			a.hop = hop; a.nFrames = n_frames; a.states = h->dStates; a.results = reinterpret_cast<float2*>(dRes);
+			a.outMode = uint32_t(output);
 			a.firstStream = 0; a.numStreams = h->nStreams;
-			if ((rc = launchFusedFrames(h, a)) != SGZ_OK) return rc;
-			// keep lineGraphs[k].results coherent with the last frame (TransformPair.h:72-76)
-			SGZ_CUDA(cudaMemcpy2DAsync(h->dResults, size_t(2) * P * sizeof(float2), dRes + size_t(n_frames - 1) * 2 * P * 2,
-				size_t(n_frames) * 2 * P * sizeof(float2), size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+			if ((rc = launchFusedFrames(h, a)) != SGZ_OK) return drained(h, rc);
 		}
 		else
 		{
@@ -1669,15 +1743,14 @@ extern "C"
 				PrepareArgs a{};
 				a.layout = layout; a.hist = dAudio; a.nHist = n_samples; a.histStride = stream_stride;
 				a.histSkip = uint32_t(uint64_t(f) * hop); a.histCount = W; a.prelimCount = 0;
-				if (uint64_t(f) * hop > 0xFFFFFFFFull) return fail(SGZ_EUNSUPPORTED, "frame offset exceeds 32 bits");
+				if (uint64_t(f) * hop > 0xFFFFFFFFull) return drained(h, fail(SGZ_EUNSUPPORTED, "frame offset exceeds 32 bits"));
 				const dim3 block(256), grid((h->tab.N + 1 + 255) / 256, h->nStreams);
 				k_prepare<<<grid, block, 0, h->stream>>>(h->dev, a, h->dCsf);
 				h->stage = 1;
-				if ((rc = sgz_spectrum_transform(h)) != SGZ_OK) return rc;
-				if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return rc;
-				if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return rc;
-				SGZ_CUDA(cudaMemcpy2DAsync(dRes + size_t(f) * 2 * P * 2, size_t(n_frames) * 2 * P * sizeof(float2), h->dResults, size_t(2) * P * sizeof(float2),
-					size_t(2) * P * sizeof(float2), h->nStreams, cudaMemcpyDeviceToDevice, h->stream));
+				if ((rc = sgz_spectrum_transform(h)) != SGZ_OK) return drained(h, rc);
+				if ((rc = sgz_spectrum_map(h)) != SGZ_OK) return drained(h, rc);
+				if ((rc = sgz_spectrum_postprocess(h)) != SGZ_OK) return drained(h, rc);
+				if ((rc = storeStagedFrame(h, dRes, output, f, n_frames)) != SGZ_OK) return drained(h, rc);
 			}
 		}
 		SGZ_CUDA(cudaGetLastError());
@@ -1687,6 +1760,12 @@ extern "C"
 			SGZ_CUDA(cudaStreamSynchronize(h->stream));
 		}
 		return SGZ_OK;
+	}
+
+	int sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout, uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
+		uint32_t n_frames, float* results, int results_mem)
+	{
+		return sgz_spectrum_process_frames_select(h, audio, mem, layout, n_samples, stream_stride, hop, n_frames, results, results_mem, SGZ_OUT_FULL);
 	}
 
 	// ---- device-resident audio history ---------------------------------------------------------

@@ -110,6 +110,15 @@ class Context:
                                          peaks.ctypes.data_as(C.POINTER(C.c_uint64)), counts.ctypes.data_as(C.POINTER(C.c_uint32)), max_peaks))
         return [peaks[s, :min(int(counts[s]), max_peaks)].copy() for s in range(S)], counts
 
+    def scope_trigger_device(self, mode, channel, d_audio, d_states, d_peaks, d_counts, threshold, hysteresis=0.0, steady_clock=0, layout=_abi.LAYOUT_INTERLEAVED):
+        """sgz_scope_trigger with every array a CUDA tensor (d_states: uint8 [S, 24] holding sgz_scope_trigger_state records,
+        d_peaks: int64 [S, max_peaks], d_counts: int32 [S]); asynchronous on the context's stream."""
+        keep, ptr, mem = _buf(d_audio)
+        assert mem == _abi.MEM_DEVICE
+        S, n, stride = _geometry(keep, layout)
+        check(self.lib.sgz_scope_trigger_device(self._h, mode, channel, ptr, layout, S, n, stride, threshold, hysteresis, steady_clock,
+                                                d_states.data_ptr(), d_peaks.data_ptr(), d_counts.data_ptr(), d_peaks.shape[1]))
+
     def scope_period(self, params, audio, states, layout=_abi.LAYOUT_INTERLEAVED):
         keep, ptr, mem = _buf(audio)
         S, n, stride = _geometry(keep, layout)

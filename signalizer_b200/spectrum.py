@@ -206,14 +206,19 @@ class TransformPairBatch:
         return out
 
     # -- fused batched path ---------------------------------------------------------------
-    def process_frames(self, audio, hop: int, n_frames: int, layout=_abi.LAYOUT_INTERLEAVED, out=None):
+    def kernel_name(self) -> str:
+        return self.lib.sgz_spectrum_kernel_name(self._h).decode()
+
+    def process_frames(self, audio, hop: int, n_frames: int, layout=_abi.LAYOUT_INTERLEAVED, out=None, output=_abi.OUT_FULL):
         """For every stream, `n_frames` frames at `hop`: the loop body of
         SpectrumRendering.cpp:622-634 / addAudioFrame (TransformDSP.inl:1139-1148).
-        Returns results [streams, frames, 2 graphs, P, 2]."""
+        Returns results [streams, frames, 2 graphs, P, 2]; with output=OUT_LINE_MAIN only graph LineMain of every frame
+        ([streams, frames, P, 2], what addAudioFrame keeps), with OUT_LAST_FRAME only the last frame ([streams, 2, P, 2])."""
         keep, ptr, mem = _buf(audio)
         s, n, stride = self._geometry(keep, layout)
         assert s == self.n_streams
-        shape = (self.n_streams, n_frames, 2, self.P, 2)
+        shape = {_abi.OUT_FULL: (self.n_streams, n_frames, 2, self.P, 2), _abi.OUT_LINE_MAIN: (self.n_streams, n_frames, self.P, 2),
+                 _abi.OUT_LAST_FRAME: (self.n_streams, 2, self.P, 2)}[output]
         if out is None:
             if mem == _abi.MEM_DEVICE:
                 import torch
@@ -222,7 +227,7 @@ class TransformPairBatch:
                 out = np.empty(shape, dtype=np.float32)
         okeep, optr, omem = _buf(out, writable=True)
         assert tuple(okeep.shape) == shape
-        check(self.lib.sgz_spectrum_process_frames(self._h, ptr, mem, layout, n, stride, hop, n_frames, optr, omem))
+        check(self.lib.sgz_spectrum_process_frames_select(self._h, ptr, mem, layout, n, stride, hop, n_frames, optr, omem, output))
         return out
 
     # -- device-resident audio history -------------------------------------

@@ -243,3 +243,31 @@ def test_vectorscope_peak_envelope_matches_oracle(layout):
             assert tuple(fg[s].envelope) == tuple(fo[s].envelope)
     assert gg[3] == 0.75
     assert fg[4].envelope[0] < 0.01     # 0.9 was not seen
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_trigger_with_device_arrays_equals_host_arrays(mode):
+    """sgz_scope_trigger_device: states, peak lists and counts stay on the GPU; same bits as the host-array call"""
+    import ctypes as C
+    import torch
+    S, n, max_peaks = 9, 20000, 512
+    audio = signals.batch(S, n, first_stream=1)
+    ctx = Context()
+    host_states = (_abi.ScopeTriggerState * S)()
+    host_peaks, host_counts = ctx.scope_trigger(mode, _abi.OSC_MID, audio, host_states, 0.02, 0.1, steady_clock=777, max_peaks=max_peaks)
+    d_audio = torch.from_numpy(audio).cuda()
+    d_states = torch.zeros((S, C.sizeof(_abi.ScopeTriggerState)), dtype=torch.uint8, device="cuda")
+    d_peaks = torch.zeros((S, max_peaks), dtype=torch.int64, device="cuda")
+    d_counts = torch.zeros(S, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.scope_trigger_device(mode, _abi.OSC_MID, d_audio, d_states, d_peaks, d_counts, 0.02, 0.1, steady_clock=777)
+    ctx.synchronize()
+    counts = d_counts.cpu().numpy().astype(np.uint32)
+    np.testing.assert_array_equal(counts, host_counts)
+    peaks = d_peaks.cpu().numpy().astype(np.uint64)
+    for s in range(S):
+        np.testing.assert_array_equal(peaks[s, :min(int(counts[s]), max_peaks)], host_peaks[s])
+    got_states = (_abi.ScopeTriggerState * S).from_buffer_copy(d_states.cpu().numpy().tobytes())
+    for s in range(S):
+        want = (host_states[s].state, host_states[s].cross_origin, host_states[s].is_peak_holding)
+        assert (got_states[s].state, got_states[s].cross_origin, got_states[s].is_peak_holding) == want

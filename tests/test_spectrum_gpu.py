@@ -557,9 +557,10 @@ def test_spectrogram_colour_columns_bit_exact():
     assert np.all(got[..., 3] == 255) and got[..., :3].max() > 0
 
 
+@pytest.mark.parametrize("layout", [_abi.LAYOUT_INTERLEAVED, _abi.LAYOUT_PLANAR])
 @pytest.mark.parametrize("algo", [_abi.ALGO_FFT, _abi.ALGO_RSNT])
 @pytest.mark.parametrize("conf", [_abi.CH_LEFT, _abi.CH_SEPARATE, _abi.CH_MIDSIDE])
-def test_audio_entry_point_frame_scheduler(algo, conf):
+def test_audio_entry_point_frame_scheduler(algo, conf, layout):
     # audioEntryPoint (TransformDSP.inl:1165-1211): blocks cut at sampleBufferSize boundaries, frames into sfbuf
     cfg = _abi.default_config(algo=algo, window_size=2048, window_type=_abi.WIN_HANN, configuration=conf,
                               display_mode=_abi.DISPLAY_COLOURSPECTRUM, sample_buffer_size=300, axis_points=256)
@@ -568,12 +569,17 @@ def test_audio_entry_point_frame_scheduler(algo, conf):
     g = TransformPairBatch(cfg, S)
     hist = signals.batch(S, 2048, first_stream=1)
     total = signals.batch(S, 5000, first_stream=4)
+    planar = layout == _abi.LAYOUT_PLANAR   # (planar: the right channel of a block starts at the block's own length)
+    if planar:
+        hist = np.ascontiguousarray(hist.transpose(0, 2, 1))
     pos = 0
     emitted = 0
     for block in (100, 250, 1024, 299, 301, 1500):   # boundaries fall inside, at the end of, and across blocks
         chunk = np.ascontiguousarray(total[:, pos:pos + block]); pos += block
-        want = o.audio_entry_point(hist, chunk)
-        got = g.audio_entry_point(hist if algo == _abi.ALGO_FFT else None, chunk)
+        if planar:
+            chunk = np.ascontiguousarray(chunk.transpose(0, 2, 1))
+        want = o.audio_entry_point(hist, chunk, layout)
+        got = g.audio_entry_point(hist if algo == _abi.ALGO_FFT else None, chunk, layout)
         assert got.shape == want.shape, (block, got.shape, want.shape)
         emitted += got.shape[1]
         if got.shape[1]:
@@ -588,6 +594,39 @@ def test_audio_entry_point_frame_scheduler(algo, conf):
     # LineGraph mode: FFT does nothing here, RSNT resonates the whole block
     cfg2 = _abi.copy_config(cfg, display_mode=_abi.DISPLAY_LINEGRAPH)
     g2 = TransformPairBatch(cfg2, S)
-    assert g2.audio_entry_point(hist if algo == _abi.ALGO_FFT else None, total[:, :700].copy()).shape[1] == 0
+    tail = total[:, :700].copy()
+    assert g2.audio_entry_point(hist if algo == _abi.ALGO_FFT else None, np.ascontiguousarray(tail.transpose(0, 2, 1)) if planar else tail, layout).shape[1] == 0
     if algo == _abi.ALGO_RSNT:
         assert np.abs(g2.get_resonator_state()).max() > 0
+
+
+@pytest.mark.parametrize("kw,S,host", [(dict(), 5, False), (dict(), 24, True), (dict(window_size=4096, configuration=_abi.CH_PHASE), 3, False),
+                                        (dict(window_size=2048, configuration=_abi.CH_LEFT, bin_polation=_abi.BIN_NONE), 310, False),
+                                        (dict(window_size=700, window_type=_abi.WIN_BLACKMAN, axis_points=300), 4, True),
+                                        (dict(algo=_abi.ALGO_RSNT, window_size=2048, axis_points=128, window_type=_abi.WIN_HANN), 2, False)])
+def test_output_selector_is_a_view_of_the_full_results(kw, S, host):
+    """sgz_spectrum_process_frames_select: LineMain-of-every-frame and last-frame-only outputs are bit for bit the
+    corresponding parts of the full output, states and lineGraphs results are the same afterwards - on the fused kernel
+    (few streams: parts and seam fix-up; many streams: chained ranges; host buffers: the chunked pipeline) and on the
+    staged / resonator paths"""
+    import torch
+    cfg = _abi.default_config(**kw)
+    F, hop = 9, max(cfg.window_size // 4, 64)
+    n = signals.frames_length(cfg.window_size, hop, F) if cfg.algo == _abi.ALGO_FFT else F * hop
+    audio = signals.batch(S, n, first_stream=2)
+    data = audio if host else torch.from_numpy(np.ascontiguousarray(audio)).cuda()
+    runs = {}
+    for mode in (_abi.OUT_FULL, _abi.OUT_LINE_MAIN, _abi.OUT_LAST_FRAME):
+        g = TransformPairBatch(cfg, S)
+        r = g.process_frames(data, hop, F, output=mode)
+        g.synchronize()
+        r = r if host else r.cpu().numpy()
+        runs[mode] = (r, g.get_states(0), g.get_states(1), g.get_results(0), g.get_results(1))
+    full = runs[_abi.OUT_FULL][0]
+    np.testing.assert_array_equal(runs[_abi.OUT_LINE_MAIN][0], full[:, :, 0])
+    np.testing.assert_array_equal(runs[_abi.OUT_LAST_FRAME][0], full[:, -1])
+    np.testing.assert_array_equal(runs[_abi.OUT_FULL][3], full[:, -1, 0])     # lineGraphs[k].results = the last frame
+    np.testing.assert_array_equal(runs[_abi.OUT_FULL][4], full[:, -1, 1])
+    for mode in (_abi.OUT_LINE_MAIN, _abi.OUT_LAST_FRAME):
+        for x, y in zip(runs[mode][1:], runs[_abi.OUT_FULL][1:]):
+            np.testing.assert_array_equal(x, y)

@@ -55,10 +55,12 @@ def test_noalloc_fft_matches_handle_fft_twice_in_a_row(n, batch):
         fft_forward_noalloc(d_in, d_out, n, batch, stream)
         torch.cuda.synchronize()
         got = d_out.cpu().numpy()
-        if want is None:  # below the handle API's minimum transform size: check against numpy
-            z = np.fft.fft(x[..., 0].astype(np.float64) + 1j * x[..., 1], axis=1)
-            want = np.stack([z.real, z.imag], axis=-1)
-        close_enough(got, want)
+        # an independent answer at every size (numpy, float64) ...
+        z = np.fft.fft(x[..., 0].astype(np.float64) + 1j * x[..., 1], axis=1)
+        close_enough(got, np.stack([z.real, z.imag], axis=-1))
+        # ... and the existing entry point's (the handle API, which starts at 32 points)
+        if want is not None:
+            close_enough(got, want)
 
 
 def test_noalloc_fft_rejects_what_the_fixed_buffer_cannot_hold():
@@ -76,3 +78,6 @@ def test_noalloc_fft_rejects_what_the_fixed_buffer_cannot_hold():
         assert err.value.code == _abi.EINVAL
     with pytest.raises(_lib.SgzError):
         _lib.check(lib.sgz_fft_forward_noalloc(d.data_ptr(), d.data_ptr(), 8, 1, None))  # in place
+    with pytest.raises(_lib.SgzError) as err:
+        _lib.check(lib.sgz_fft_forward_noalloc(d.data_ptr(), d.data_ptr() + 32, 8, 1, None))  # 8 points = 64 bytes: the ranges share 32 bytes
+    assert "overlap" in str(err.value)

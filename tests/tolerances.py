@@ -27,8 +27,8 @@ def assert_linear_close(a, b, rel=REL, floor=FLOOR, frame_axes=None, what=""):
 
 
 def assert_log_close(a, b, lin=None, peak=None, dy=1.0 / np.log(1e6), rel=REL, floor=FLOOR, what=""):
-    """Results on the display scale y = ln(v / low) * dy.  The linear bound
-    |dv| <= rel |v| + floor * peak maps to |dy| <= dy * (rel + floor * peak / v) (first order);
+    """Results on the display scale y = ln(v / low) * dy.  The linear bound |dv| <= x v with x = rel + floor * peak / v
+    maps to |dy| <= -dy ln(1 - x), exactly (no bound where x >= 1: the value may be anything down to silence);
     2e-6 is added for the float32 rounding of y itself.  Without `lin` a flat LOG_ABS is used."""
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
     assert a.shape == b.shape, (a.shape, b.shape)
@@ -40,7 +40,9 @@ def assert_log_close(a, b, lin=None, peak=None, dy=1.0 / np.log(1e6), rel=REL, f
         pk = np.max(lin) if peak is None else peak
         with np.errstate(divide="ignore"):
             ratio = np.where(lin > 0, floor * pk / np.where(lin > 0, lin, 1.0), np.inf)
-        bound = dy * (rel + ratio) * 1.5 + 2e-6
+        x = rel + ratio
+        with np.errstate(divide="ignore", invalid="ignore"):
+            bound = np.where(x < 1.0, -dy * np.log1p(-np.minimum(x, 0.999999)), np.inf) + 2e-6
     bad = err > bound
     if np.any(bad):
         i = np.unravel_index(np.argmax(err - np.where(np.isfinite(bound), bound, 0)), err.shape)
