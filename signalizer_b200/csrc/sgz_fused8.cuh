@@ -62,7 +62,8 @@
 		static constexpr size_t twBytes = size_t(twEntries) * sizeof(float2);
 		static constexpr size_t stateOffset = twOffset + twBytes;
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
-		static size_t smemBytes(uint32_t P) { return mapOffset(P) + size_t(P) * 12 + 48; } // ... + the part plan (FusedPart)
+		__host__ __device__ static size_t partOffset(uint32_t P) { return (mapOffset(P) + size_t(P) * 12 + 15) & ~size_t(15); }
+		static size_t smemBytes(uint32_t P) { return partOffset(P) + 64; } // ... + the part plan (FusedPart)
 	};
 	typedef Fused8GeomT<8> Fused8Geom;
 
@@ -507,7 +508,7 @@
 		// ---- this CTA's share of the launch: items [i0, i1) of the stream-major frame list, cut into per-stream parts ----
 		// (planned one part at a time into shared memory by planFusedPart, so that nothing of the bookkeeping stays in
 		// registers across the frame loop, which has none to spare)
-		FusedPart* part = reinterpret_cast<FusedPart*>(smemRaw + Gm::mapOffset(t.P) + size_t(P) * 12);
+		FusedPart* part = reinterpret_cast<FusedPart*>(smemRaw + Gm::partOffset(t.P));
 		const int W = int(t.W);
 
 		for (uint32_t q = 0;; ++q)

@@ -23,6 +23,7 @@
 		uint32_t count;       // samples in the block
 		uint32_t chunks;      // time slices
 		uint32_t chunkLen;    // samples per slice (last one may be shorter)
+		uint32_t chunk0;      // first slice this launch computes (blockIdx.y counts from it): the tensor-core kernel takes the ones before
 	};
 
 	// channel matrix of resonatingDispatch (:1249-1294); note Mid = L + R (no 0.5) and MidSide =
@@ -48,7 +49,7 @@
 		const uint32_t P = t.P, V = t.resVectors, ch = t.resChannels;
 		const uint32_t total = P * V * ch;
 		const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-		const uint32_t chunk = blockIdx.y, s = blockIdx.z;
+		const uint32_t chunk = blockIdx.y + a.chunk0, s = blockIdx.z;
 		const bool active = g < total;
 		const uint32_t gi = active ? g : 0;
 		const uint32_t i = gi % P, z = (gi / P) % V, c = gi / (P * V);
@@ -98,7 +99,7 @@
 		const uint32_t P = t.P, V = t.resVectors;
 		const uint32_t half = P * V, total = 2 * half;
 		const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-		const uint32_t chunk = blockIdx.y, s = blockIdx.z;
+		const uint32_t chunk = blockIdx.y + a.chunk0, s = blockIdx.z;
 		const bool active = g < half;
 		const uint32_t gi = active ? g : 0;
 		const float2 p = t.resCoeff[gi];   // [z][i] = gi

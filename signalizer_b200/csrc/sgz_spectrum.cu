@@ -37,7 +37,7 @@ namespace sgz
 	inline int fusedK1For(uint32_t N) { return N == 16384 ? 16 : N == 8192 ? 8 : N == 4096 ? 4 : N == 2048 ? 2 : N == 1024 ? 1 : 0; }
 	// the fused kernel keeps 28 bytes per display point next to the N * 8-byte exchange buffer; one CTA must fit the
 	// 227 KB an SM can give (the resident CTAs per SM then follow from the size: 2 at N = 8192 up to 2048 points, 1 beyond)
-	inline bool fusedSharedMemoryFits(uint32_t N, uint32_t P) { return size_t(N) * 8 + 2048 + 48 + size_t(P) * 28 <= size_t(227) * 1024; }
+	inline bool fusedSharedMemoryFits(uint32_t N, uint32_t P) { return size_t(N) * 8 + 2048 + 80 + size_t(P) * 28 <= size_t(227) * 1024; }
 	constexpr uint32_t kFrameParallelMinRun = 4;   // with fewer streams than resident CTAs a stream is cut into parts of at least this many frames
 
 	// ------------------------------------------------------------------------------------------
@@ -654,6 +654,7 @@ namespace sgz
 #include "sgz_fused.cuh"
 #include "sgz_fused8.cuh"
 #include "sgz_resonator.cuh"
+#include "sgz_resonator_tc.cuh"
 
 } // namespace sgz
 
@@ -679,6 +680,8 @@ struct sgz_spectrum
 	float2* dResults{ nullptr }; // [S][2][P]
 	float2* dResState{ nullptr };   // [S][ch][V][P] resonator state (cresonator)
 	float2* dResPartial{ nullptr }; size_t resPartialBytes{ 0 }; // time-slice scratch of k_resonate
+	float* dResTcA{ nullptr };      // tensor-core resonator: pole-power operand tiles (sgz_resonator_tc.cuh)
+	float2* dResTcPowL{ nullptr };  // ... and p^L per filter row
 	// staging for host-resident callers
 	float* dAudioStage{ nullptr }; size_t audioStageBytes{ 0 };
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
@@ -1039,6 +1042,39 @@ extern "C"
 		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dStates));
 		SGZ_TRY(allocZero(h, size_t(n_streams) * 2 * t.P, &h->dResults));
 		if (cfg->algo == SGZ_ALGO_RSNT) SGZ_TRY(allocZero(h, size_t(n_streams) * t.stateChannels * t.resonatorVectors * t.P, &h->dResState));
+		if (cfg->algo == SGZ_ALGO_RSNT)
+		{
+			// operands of k_resonate_tc: for every filter row g = z P + i the powers p^(L-1-k), k = 0 .. L-1, in double,
+			// split into a TF32 head and tail, stored per 128-row tile in the kernel's shared-memory order
+			const uint32_t half = t.P * t.resonatorVectors, rowTiles = (half + kTcRows - 1) / kTcRows;
+			std::vector<float> aTiles(size_t(rowTiles) * 4 * kTcMatFloats, 0.f);
+			std::vector<float2> powL(size_t(rowTiles) * kTcRows, make_float2(0.f, 0.f));
+			auto tf32 = [](double v) { // round to 11 significant bits (ties away), like cvt.rna.tf32.f32
+				float f = float(v); uint32_t u; std::memcpy(&u, &f, 4);
+				u = (u + 0x1000u) & 0xFFFFE000u; std::memcpy(&f, &u, 4); return f; };
+			for (uint32_t g = 0; g < half; ++g)
+			{
+				const std::complex<double> p(t.resCoeffReal[g], t.resCoeffImag[g]);
+				std::complex<double> pw(1.0, 0.0);
+				float* tile = aTiles.data() + size_t(g / kTcRows) * 4 * kTcMatFloats;
+				const uint32_t row = g % kTcRows, rg = row / 8, r = row % 8;
+				for (int e = 0; e < kTcL; ++e, pw *= p)
+				{
+					const int k = kTcL - 1 - e;   // x[k] is multiplied by p^(L-1-k) = p^e
+					const size_t off = ((size_t(k / 4) * (kTcRows / 8) + rg) * 8 + r) * 4 + (k % 4);
+					const float reH = tf32(pw.real()), imH = tf32(pw.imag());
+					tile[0 * kTcMatFloats + off] = reH; tile[1 * kTcMatFloats + off] = tf32(pw.real() - reH);
+					tile[2 * kTcMatFloats + off] = imH; tile[3 * kTcMatFloats + off] = tf32(pw.imag() - imH);
+				}
+				powL[g] = make_float2(float(pw.real()), float(pw.imag())); // p^L
+			}
+			const float* da = nullptr; const float2* dp = nullptr;
+			SGZ_TRY(upload(h, aTiles, &da));
+			SGZ_TRY(upload(h, powL, &dp));
+			h->dResTcA = const_cast<float*>(da); h->dResTcPowL = const_cast<float2*>(dp);
+			if (cudaFuncSetAttribute(k_resonate_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kTcSmemBytes)) != cudaSuccess)
+				return bail(fail(SGZ_ECUDA, "cudaFuncSetAttribute(k_resonate_tc) failed"));
+		}
 		if (h->fusedK1 != 0)
 		{
 			FusedArgs none{};
@@ -1376,33 +1412,59 @@ extern "C"
 	static int resonateBlock(sgz_spectrum* h, const float* dAudio, int layout, uint64_t nSamples, uint64_t streamStride, uint64_t first, uint32_t count)
 	{
 		if (count == 0) return SGZ_OK; // TransformDSP.inl:1246-1247
-		const uint32_t total = h->tab.P * h->tab.resonatorVectors * h->tab.stateChannels;
+		const uint32_t half = h->tab.P * h->tab.resonatorVectors;
+		const uint32_t total = half * h->tab.stateChannels;
 		const uint32_t blocksX = (total + 255) / 256;
-		// enough time slices for ~2 waves of CTAs over the SMs, each at least 256 samples long
 		int sms = 148;
 		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
-		uint64_t want = (uint64_t(sms) * 8 + uint64_t(blocksX) * h->nStreams - 1) / (uint64_t(blocksX) * h->nStreams);
-		uint32_t chunks = uint32_t(std::max<uint64_t>(1, std::min<uint64_t>(want, count / 256)));
-		if (chunks > 65535) chunks = 65535;
 		ResArgs a{};
 		a.audio = dAudio; a.nSamples = nSamples; a.streamStride = streamStride; a.layout = layout;
-		a.first = first; a.count = count; a.chunks = chunks; a.chunkLen = (count + chunks - 1) / chunks;
-		a.chunks = (count + a.chunkLen - 1) / a.chunkLen;
-		if (a.chunks > 1)
+		a.first = first; a.count = count;
+		// Blocks of at least one tile go to the tensor cores (k_resonate_tc): whole tiles of kTcSpan samples become the
+		// first time slices, whatever is left over is one more slice for the FP32 kernel, k_resonate_combine chains them
+		const uint32_t tcTiles = h->dResTcA ? count / kTcSpan : 0;
+		if (tcTiles > 0)
+		{
+			a.chunkLen = kTcSpan; a.chunks = tcTiles + (count % kTcSpan ? 1u : 0u); a.chunk0 = tcTiles;
+		}
+		else
+		{
+			// enough time slices for ~2 waves of CTAs over the SMs, each at least 256 samples long
+			uint64_t want = (uint64_t(sms) * 8 + uint64_t(blocksX) * h->nStreams - 1) / (uint64_t(blocksX) * h->nStreams);
+			uint32_t chunks = uint32_t(std::max<uint64_t>(1, std::min<uint64_t>(want, count / 256)));
+			if (chunks > 65535) chunks = 65535;
+			a.chunks = chunks; a.chunkLen = (count + chunks - 1) / chunks;
+			a.chunks = (count + a.chunkLen - 1) / a.chunkLen;
+			a.chunk0 = 0;
+		}
+		if (a.chunks > 1 || tcTiles > 0)
 		{
 			const size_t need = size_t(h->nStreams) * a.chunks * total * sizeof(float2);
 			if (h->resPartialBytes < need)
 			{
-				if (h->dResPartial) { cudaFree(h->dResPartial); h->dResPartial = nullptr; h->resPartialBytes = 0; }
+				if (h->dResPartial) { SGZ_CUDA(cudaStreamSynchronize(h->stream)); cudaFree(h->dResPartial); h->dResPartial = nullptr; h->resPartialBytes = 0; }
 				SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dResPartial), need));
 				h->resPartialBytes = need;
 			}
 		}
-		if (h->tab.stateChannels == 2)
-			k_resonate_pair<<<dim3((total / 2 + 255) / 256, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
-		else
-			k_resonate<<<dim3(blocksX, a.chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
-		if (a.chunks > 1) k_resonate_combine<<<dim3(blocksX, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+		if (tcTiles > 0)
+		{
+			ResTcArgs ta{};
+			ta.audio = dAudio; ta.nSamples = nSamples; ta.streamStride = streamStride; ta.layout = layout; ta.first = first;
+			ta.tiles = tcTiles; ta.chunks = a.chunks; ta.nStreams = h->nStreams; ta.aTiles = h->dResTcA; ta.powL = h->dResTcPowL;
+			const uint64_t items = uint64_t((half + kTcRows - 1) / kTcRows) * h->nStreams * h->tab.stateChannels * tcTiles;
+			const uint32_t ctas = uint32_t(std::min<uint64_t>(items, uint64_t(sms)));
+			k_resonate_tc<<<ctas, 128, kTcSmemBytes, h->stream>>>(h->dev, ta, h->dResPartial);
+		}
+		const uint32_t fp32Chunks = a.chunks - a.chunk0; // slices the FP32 kernel computes
+		if (fp32Chunks > 0)
+		{
+			if (h->tab.stateChannels == 2)
+				k_resonate_pair<<<dim3((total / 2 + 255) / 256, fp32Chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+			else
+				k_resonate<<<dim3(blocksX, fp32Chunks, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
+		}
+		if (a.chunks > 1 || tcTiles > 0) k_resonate_combine<<<dim3(blocksX, h->nStreams), 256, 0, h->stream>>>(h->dev, a, h->dResState, h->dResPartial);
 		SGZ_CUDA(cudaGetLastError());
 		return SGZ_OK;
 	}
