@@ -88,11 +88,14 @@ def c2():
         d = torch.from_numpy(tile(signals.batch(min(S, 16), n), S)).cuda()
         p = TransformPairBatch(cfg, S)
         p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
-        ms = timed(lambda: p.resonating_dispatch(d), torch.cuda.synchronize, steps=5)
         V = p.info.resonator_vectors
         flops = 8.0 * 1024 * V * 2 * n * S   # 8 flop per complex one-pole update, filters x vectors x channels
-        out.append({"config": f"C2 resonator bank: {S} stereo stream(s), 1024 log bins, Hann (V={V}), {n} samples", "ms": ms,
-                    "samples_per_s_per_stream": n / ms * 1e3, "realtime_factor_48k": n / ms * 1e3 / 48000.0, "fp32_TFLOPs": flops / ms / 1e9})
+        for path, name in ((0, "tensor cores (k_resonate_tc, TF32 x3 split)"), (1, "FP32 recurrence (k_resonate_pair)")):
+            p.set_resonator_path(path)
+            ms = timed(lambda: p.resonating_dispatch(d), torch.cuda.synchronize, steps=5)
+            out.append({"config": f"C2 resonator bank, {name}: {S} stereo stream(s), 1024 log bins, Hann (V={V}), {n} samples", "ms": ms,
+                        "samples_per_s_per_stream": n / ms * 1e3, "realtime_factor_48k": n / ms * 1e3 / 48000.0,
+                        "recurrence_equivalent_TFLOPs": flops / ms / 1e9})
     return out
 
 
@@ -110,9 +113,21 @@ def c4():
     algo = S * (W * 4 + count * 8)   # read W samples of one channel, write 16 W vertices (x, y)
     st = (_abi.ScopeTriggerState * S)()
     ms_t = timed(lambda: ctx.scope_trigger(0, _abi.OSC_LEFT, d, st, 0.05, max_peaks=4096), torch.cuda.synchronize, steps=5)
+    # the same trigger with states / peaks / counts resident on the device (sgz_scope_trigger_device): no copies, no wait
+    import ctypes as C
+    d_states = torch.zeros((S, C.sizeof(_abi.ScopeTriggerState)), dtype=torch.uint8, device="cuda")
+    d_peaks = torch.zeros((S, 4096), dtype=torch.int64, device="cuda")
+    d_counts = torch.zeros(S, dtype=torch.int32, device="cuda")
+    ms_td = timed(lambda: ctx.scope_trigger_device(0, _abi.OSC_LEFT, d, d_states, d_peaks, d_counts, 0.05), torch.cuda.synchronize, steps=10)
+    # calculateFundamentalPeriod + calculateTriggeringOffset (a19): fp64 8192-point FFT, peak pick, Goertzel, per stream
+    prm = _abi.ScopePeriodParams(_abi.ABI_VERSION, _abi.OSC_LEFT, 2048.0, 48000.0, 0.01, 0.05, 0.0)
+    pst = (_abi.ScopePeriodState * S)()
+    ms_p = timed(lambda: ctx.scope_period(prm, d, pst), torch.cuda.synchronize, steps=5)
     return {"config": f"C4 oscilloscope: 256 streams, Lanczos-10 16x resampling of a {W}-sample window ({count} vertices) + zero-crossing trigger over {n} samples",
             "resample_ms": ms, "vertices_per_s": S * count / ms * 1e3, "resample_achieved_GBps": algo / ms / 1e6, "resample_frac_hbm": algo / ms / 1e6 / PEAK,
-            "trigger_ms_incl_host_copies": ms_t, "trigger_samples_per_s": S * n / ms_t * 1e3}
+            "trigger_ms_incl_host_copies": ms_t, "trigger_samples_per_s": S * n / ms_t * 1e3,
+            "trigger_device_arrays_ms": ms_td, "trigger_device_arrays_samples_per_s": S * n / ms_td * 1e3,
+            "period_search_ms_256_streams_incl_host_tail": ms_p, "period_searches_per_s": S / ms_p * 1e3}
 
 
 def c4_colour():
@@ -144,8 +159,26 @@ def c5():
             "points_per_s": S * n / ms * 1e3, "achieved_GBps": algo / ms / 1e6, "frac_hbm": algo / ms / 1e6 / PEAK}
 
 
+def c3_few_streams():
+    """BASELINE config 3 cut for N GPUs: 1024 / N streams per GPU (the strong-scaling shape) and long recordings; fewer
+    streams than the GPU holds CTAs, so parts start from zero and the seam kernels carry the hold across"""
+    out_lines = []
+    cfg = _abi.default_config()
+    for S, F in ((512, 64), (256, 64), (128, 64), (8, 1024), (1, 4096)):
+        hop, W = 2048, 8192
+        n = signals.frames_length(W, hop, F)
+        d = torch.from_numpy(tile(signals.batch(min(S, 16), n), S)).cuda()
+        p = TransformPairBatch(cfg, S)
+        p.set_cuda_stream(torch.cuda.current_stream().cuda_stream)
+        out = torch.empty((S, F, 2, 1024, 2), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: p.process_frames(d, hop, F, out=out), torch.cuda.synchronize)
+        out_lines.append({"config": f"C3 with {S} streams x {F} frames on one GPU", "frames_per_s": S * F / ms * 1e3, "ms": ms,
+                          "frac_hbm": S * F * 114688 / ms / 1e6 / PEAK})
+    return out_lines
+
+
 if __name__ == "__main__":
-    for fn in (c1, c3_variants, c2, c4, c4_colour, c5):
+    for fn in (c1, c3_variants, c3_few_streams, c2, c4, c4_colour, c5):
         r = fn()
         for line in (r if isinstance(r, list) else [r]):
             print(json.dumps(line), flush=True)

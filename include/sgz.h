@@ -355,6 +355,12 @@ int  sgz_spectrum_colour_columns(sgz_spectrum* h, const float* results, int mem,
 int  sgz_resonator_process(sgz_spectrum* h, const float* audio, int mem, int layout,
                            uint64_t n_samples, uint64_t stream_stride);
 /* Raw resonator state (cresonator), [stream][channel][vector][filter] complex. */
+/* Which kernels advance the resonator bank.  SGZ_RESONATOR_AUTO (default): blocks of at least 8192 samples run on the
+ * tensor cores - the block's whole 8192-sample tiles as a TF32 GEMM with a three-term operand split and FP32
+ * accumulation - and shorter blocks / remainders on the FP32 recurrence; SGZ_RESONATOR_FP32: the FP32 recurrence
+ * always (the two agree to about 1e-6 of the state's magnitude, not bit for bit).  No reference counterpart. */
+enum { SGZ_RESONATOR_AUTO = 0, SGZ_RESONATOR_FP32 = 1 };
+int  sgz_resonator_set_path(sgz_spectrum* h, int path);
 int  sgz_resonator_get_state(sgz_spectrum* h, float* out, int mem);
 
 /* ==== secondary paths: Vectorscope and Oscilloscope =========================

@@ -36,8 +36,9 @@
 	{
 		const float* audio; uint64_t nSamples; uint64_t streamStride; int layout;
 		uint64_t first;      // first sample of the block inside the buffer
-		uint32_t tiles;      // whole tiles of kTcSpan samples in the block
-		uint32_t chunks;     // time slices per stream in `partial` (the tiles, plus the remainder the FP32 kernel takes)
+		uint32_t count;      // samples in the block
+		uint32_t tiles;      // ceil(count / kTcSpan) = time slices per stream in `partial`; the LAST tile ends at the block's end and
+		                     // reads zeros where it reaches back into the previous tile's samples (leading zeros leave its sum unchanged)
 		uint32_t nStreams;
 		const float* aTiles; // [rowTiles][4][kTcMatFloats]: re head, re tail, im head, im tail
 		const float2* powL;  // [rowTiles * 128] p^L
@@ -107,22 +108,37 @@
 				for (int i = tid; i < 4 * kTcMatFloats / 4; i += 128) dst[i] = __ldg(src + i);
 				loadedRowTile = rt;
 			}
-			// ---- fill B: slice n = 8 rg + r (row of the operand), samples k = 4 kg + e; a warp task is one rg x four kg ----
+			// ---- fill B: slice n = 8 rg + r (row of the operand), samples k = 4 kg + e; a warp task is one rg x four kg.  All
+			// of a thread's 64 samples are requested before the first is used: one memory latency per tile, not sixteen ----
 			{
 				const float* base = a.audio + uint64_t(s) * a.streamStride;
-				const uint64_t tile0 = a.first + uint64_t(tt) * kTcSpan;
+				// samples [lo, hi) of the block belong to this tile; its 8192 slots end at hi
+				const uint64_t lo = uint64_t(tt) * kTcSpan, hi = min(lo + uint64_t(kTcSpan), uint64_t(a.count));
+				const long long tile0 = (long long)hi - kTcSpan; // block-relative; below lo (even negative) for the block's last, short tile
+				const bool whole = tile0 >= (long long)lo;
 				const uint32_t r = lane & 7, kq = lane >> 3;
-				for (uint32_t task = warp; task < 64; task += 4)
+				float2 raw[16][4];
+#pragma unroll
+				for (int i = 0; i < 16; ++i)
 				{
-					const uint32_t rg = task & 15, kg = (task >> 4) * 4 + kq;
-					const uint64_t n0 = tile0 + uint64_t(rg * 8 + r) * kTcL + kg * 4;
+					const uint32_t task = warp + 4u * i, rg = task & 15, kg = (task >> 4) * 4 + kq;
+					const long long n0 = tile0 + (long long)((rg * 8 + r) * kTcL + kg * 4);
+#pragma unroll
+					for (int e = 0; e < 4; ++e)
+					{
+						raw[i][e] = make_float2(0.f, 0.f);
+						if (whole || n0 + e >= (long long)lo) fetchLR(base, a.layout, a.nSamples, a.first + uint64_t(n0 + e), raw[i][e].x, raw[i][e].y);
+					}
+				}
+#pragma unroll
+				for (int i = 0; i < 16; ++i)
+				{
+					const uint32_t task = warp + 4u * i, rg = task & 15, kg = (task >> 4) * 4 + kq;
 					float x[4];
 #pragma unroll
 					for (int e = 0; e < 4; ++e)
 					{
-						float l, rr;
-						fetchLR(base, a.layout, a.nSamples, n0 + e, l, rr);
-						const float2 m = resonatorMatrix(t.conf, l, rr);
+						const float2 m = resonatorMatrix(t.conf, raw[i][e].x, raw[i][e].y);
 						x[e] = c ? m.y : m.x;
 					}
 					float4 hd, tl;
@@ -199,7 +215,7 @@
 						st = make_float2(nr, ni);
 					}
 				}
-				if (g < half) partial[(uint64_t(s) * a.chunks + tt) * total + uint64_t(c) * half + g] = st;
+				if (g < half) partial[(uint64_t(s) * a.tiles + tt) * total + uint64_t(c) * half + g] = st;
 			}
 			asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 			__syncthreads(); // the accumulators and the B operand are free again

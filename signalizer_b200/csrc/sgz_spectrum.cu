@@ -682,6 +682,7 @@ struct sgz_spectrum
 	float2* dResPartial{ nullptr }; size_t resPartialBytes{ 0 }; // time-slice scratch of k_resonate
 	float* dResTcA{ nullptr };      // tensor-core resonator: pole-power operand tiles (sgz_resonator_tc.cuh)
 	float2* dResTcPowL{ nullptr };  // ... and p^L per filter row
+	int resonatorPath{ SGZ_RESONATOR_AUTO };
 	// staging for host-resident callers
 	float* dAudioStage{ nullptr }; size_t audioStageBytes{ 0 };
 	float* dResultStage{ nullptr }; size_t resultStageBytes{ 0 };
@@ -1420,12 +1421,12 @@ extern "C"
 		ResArgs a{};
 		a.audio = dAudio; a.nSamples = nSamples; a.streamStride = streamStride; a.layout = layout;
 		a.first = first; a.count = count;
-		// Blocks of at least one tile go to the tensor cores (k_resonate_tc): whole tiles of kTcSpan samples become the
-		// first time slices, whatever is left over is one more slice for the FP32 kernel, k_resonate_combine chains them
-		const uint32_t tcTiles = h->dResTcA ? count / kTcSpan : 0;
+		// Blocks of at least half a tile go to the tensor cores (k_resonate_tc): every time slice is a tile of kTcSpan samples
+		// (the last one reaches back and reads zeros), k_resonate_combine chains them
+		const uint32_t tcTiles = (h->dResTcA && h->resonatorPath != SGZ_RESONATOR_FP32 && count >= kTcSpan / 2) ? (count + kTcSpan - 1) / kTcSpan : 0;
 		if (tcTiles > 0)
 		{
-			a.chunkLen = kTcSpan; a.chunks = tcTiles + (count % kTcSpan ? 1u : 0u); a.chunk0 = tcTiles;
+			a.chunkLen = kTcSpan; a.chunks = tcTiles; a.chunk0 = tcTiles;
 		}
 		else
 		{
@@ -1451,7 +1452,7 @@ extern "C"
 		{
 			ResTcArgs ta{};
 			ta.audio = dAudio; ta.nSamples = nSamples; ta.streamStride = streamStride; ta.layout = layout; ta.first = first;
-			ta.tiles = tcTiles; ta.chunks = a.chunks; ta.nStreams = h->nStreams; ta.aTiles = h->dResTcA; ta.powL = h->dResTcPowL;
+			ta.tiles = tcTiles; ta.count = count; ta.nStreams = h->nStreams; ta.aTiles = h->dResTcA; ta.powL = h->dResTcPowL;
 			const uint64_t items = uint64_t((half + kTcRows - 1) / kTcRows) * h->nStreams * h->tab.stateChannels * tcTiles;
 			const uint32_t ctas = uint32_t(std::min<uint64_t>(items, uint64_t(sms)));
 			k_resonate_tc<<<ctas, 128, kTcSmemBytes, h->stream>>>(h->dev, ta, h->dResPartial);
@@ -1591,6 +1592,14 @@ extern "C"
 		int rc = stageAudio(h, audio, mem, n_samples, stream_stride, &dAudio, &h->dAudioStage, &h->audioStageBytes);
 		if (rc != SGZ_OK) return rc;
 		return resonateBlock(h, dAudio, layout, n_samples, stream_stride, 0, uint32_t(n_samples));
+	}
+
+	int sgz_resonator_set_path(sgz_spectrum* h, int path)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (path != SGZ_RESONATOR_AUTO && path != SGZ_RESONATOR_FP32) return fail(SGZ_EINVAL, "bad resonator path %d", path);
+		h->resonatorPath = path;
+		return SGZ_OK;
 	}
 
 	int sgz_resonator_get_state(sgz_spectrum* h, float* out, int mem)

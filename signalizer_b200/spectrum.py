@@ -191,6 +191,10 @@ class TransformPairBatch:
         return out
 
     # -- resonator bank (algo = RSNT) ------------------------------------------------------
+    def set_resonator_path(self, path: int) -> None:
+        """0 = tensor cores for blocks of at least 8192 samples (default), 1 = the FP32 recurrence always"""
+        check(self.lib.sgz_resonator_set_path(self._h, path))
+
     def resonating_dispatch(self, audio, layout=_abi.LAYOUT_INTERLEAVED):
         """template<ISA> void resonatingDispatch(const Constant&, array<AFloat*, 2> buffer, size_t n)
         (TransformDSP.inl:1215-1295) for every stream."""

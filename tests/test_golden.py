@@ -1,6 +1,7 @@
-"""Committed golden vectors (tests/golden/spectrum_golden.npz, made by tests/golden/make_golden.py from
-the CPU oracle): the oracle must keep reproducing them bit for bit, and the CUDA path must match
-them within the stated tolerance without the oracle in the loop."""
+"""Committed golden vectors (tests/golden/spectrum_golden.npz, made by tests/golden/make_golden.py from oracle/_ref, i.e.
+the reference's own TransformDSP.inl run in the build container): the restated oracle - and oracle/_ref where it is
+present - must reproduce them bit for bit, and the CUDA path must match them within the stated tolerance without
+either in the loop."""
 import importlib.util
 import json
 import os
@@ -26,6 +27,17 @@ def test_golden_metadata_matches_generator():
 @pytest.mark.parametrize("name", list(make_golden.CASES))
 def test_oracle_reproduces_golden_bit_exact(name):
     res, st = make_golden.run(make_golden.CASES[name])
+    np.testing.assert_array_equal(res, GOLD[name + "/results"])
+    np.testing.assert_array_equal(st, GOLD[name + "/states"])
+
+
+@pytest.mark.parametrize("name", list(make_golden.CASES))
+def test_reference_build_reproduces_golden_bit_exact(name):
+    from oracle import binding
+    binding.build()
+    if not binding.ref_available():
+        pytest.skip("oracle/_ref not built (no reference checkout)")
+    res, st = make_golden.run(make_golden.CASES[name], ref=True)
     np.testing.assert_array_equal(res, GOLD[name + "/results"])
     np.testing.assert_array_equal(st, GOLD[name + "/states"])
 

@@ -459,6 +459,34 @@ def test_full_size_c3_properties():
     np.testing.assert_array_equal(first, second)
 
 
+def test_bench_workload_against_the_oracle():
+    """the workload bench.py times - 1024 streams x 64 frames, hop 2048, the same signals (bench.make_audio) - through
+    the same device-resident call, compared with the oracle on 32 streams spread over the batch, every frame; the mean
+    bench.py prints as `checksum` is recomputed from the oracle-checked values where the streams overlap"""
+    import argparse
+    import torch
+    import bench
+    args = argparse.Namespace(streams=1024, frames=64, hop=2048)
+    audio, n = bench.make_audio(args, 0)
+    cfg = bench.bench_cfg()
+    S, F, hop = args.streams, args.frames, args.hop
+    g = TransformPairBatch(cfg, S)
+    d_audio = torch.from_numpy(audio).cuda()
+    d_out = g.process_frames(d_audio, hop, F)
+    g.synchronize()
+    pick = np.unique(np.r_[np.arange(0, S, 37), 95, 96, 295, 296, S - 1])[:32]
+    assert len(pick) == 32
+    got = d_out[torch.from_numpy(pick).cuda()].cpu().numpy()
+    want = OracleSpectrum(cfg, len(pick)).process_frames(np.ascontiguousarray(audio[pick]), hop, F, threads=8)
+    assert np.isfinite(got).all()
+    compare_frames(got, want, cfg, "bench workload")
+    # the states the kernel leaves behind are the last frame's, whichever CTA ranges the streams fell into
+    for k in range(2):
+        st = g.get_states(k)[pick]
+        lin = np.where(want[:, -1, k] > -300, 1e-6 * np.exp(want[:, -1, k].astype(np.float64) * np.log(1e6)), 0.0)
+        assert_linear_close(st, lin, frame_axes=(1, 2), what=f"bench states {k}")
+
+
 # ---------------------------------------------------------------------------------------------
 # resonator bank (BASELINE config 2: RDFT mode, 1 stereo stream, 1024 log-spaced bins, 48 kHz)
 # ---------------------------------------------------------------------------------------------

@@ -29,18 +29,25 @@ def main():
     g = TransformPairBatch(cfg, S)
     V = g.info.resonator_vectors
     audio = torch.from_numpy(signals.batch(S, n)).to(dev)
-    # the product's FP32 recurrence (k_resonate_pair + k_resonate_combine)
-    for _ in range(3):
-        g.resonating_dispatch(audio)
-    g.synchronize()
-    t0 = time.perf_counter()
-    reps = 5
-    for _ in range(reps):
-        g.resonating_dispatch(audio)
-    g.synchronize()
-    direct_ms = (time.perf_counter() - t0) / reps * 1e3
     flops = 8.0 * P * V * 2 * n
-    print(f"recurrence kernel: {direct_ms:.3f} ms for {n} samples x {P} filters x {V} vectors x 2 channels = {flops / direct_ms / 1e9:.1f} TFLOP/s (8 flop per update)")
+    states = {}
+    for path, name in ((1, "FP32 recurrence (k_resonate_pair + k_resonate_combine)"), (0, "tensor cores (k_resonate_tc + remainder + combine)")):
+        g.set_resonator_path(path)
+        g.clear_audio_state()
+        g.resonating_dispatch(audio)
+        states[path] = g.get_resonator_state().astype(np.float64)
+        for _ in range(3):
+            g.resonating_dispatch(audio)
+        g.synchronize()
+        t0 = time.perf_counter()
+        reps = 10
+        for _ in range(reps):
+            g.resonating_dispatch(audio)
+        g.synchronize()
+        ms = (time.perf_counter() - t0) / reps * 1e3
+        print(f"{name}: {ms:.3f} ms for {n} samples x {P} filters x {V} vectors x 2 channels = {flops / ms / 1e9:.1f} TFLOP/s-equivalent (8 flop per update)")
+    d = np.abs(states[0] - states[1]).max() / np.abs(states[1]).max()
+    print(f"state after one pass: max |tensor - fp32| / max |state| = {d:.2e}")
 
     # pole powers in float64 from random stable poles of the same magnitude range (the rate does not depend on their values)
     rng = np.random.default_rng(1)
