@@ -204,6 +204,15 @@ int  sgz_spectrum_set_states(sgz_spectrum* h, int graph, const float* in, int me
 int  sgz_spectrum_clear_line_graph_states(sgz_spectrum* h);
 int  sgz_spectrum_clear_audio_state(sgz_spectrum* h);
 
+/* Sizes, once, every buffer the process calls below would otherwise grow on first use: the device staging of
+ * host-resident audio (`n_samples` per channel and stream at `stream_stride`) and results (`n_frames` frames, full
+ * output), the copy streams and events of the host-buffer pipeline, the resonator's time-slice scratch.  After it,
+ * sgz_spectrum_process_frames* / sgz_resonator_process / sgz_spectrum_audio_entry_point with sizes up to these call
+ * neither cudaMalloc nor cudaFree (the reference's TransformPair likewise grows its vectors lazily,
+ * TransformPair.h:213-233; a caller with a deadline reserves up front).  Optional: without it the first call, and
+ * any call with larger sizes, allocates and may wait for the handle's stream. */
+int  sgz_spectrum_reserve(sgz_spectrum* h, uint64_t n_samples, uint64_t stream_stride, uint32_t n_frames);
+
 /* ---- fused batched path --------------------------------------------------
  * One call = for every stream, `n_frames` successive frames: frame f uses
  * samples [f*hop, f*hop + window_size) of the stream and runs

@@ -29,7 +29,7 @@ EXPORTS = [
     "sgz_context_create", "sgz_context_destroy", "sgz_context_set_cuda_stream", "sgz_context_synchronize",
     "sgz_vscope_vertices", "sgz_vscope_histogram", "sgz_vscope_meters",
     "sgz_scope_resample_count", "sgz_scope_resample", "sgz_scope_trigger", "sgz_scope_period", "sgz_scope_colour", "sgz_scope_peak_envelope",
-    "sgz_vscope_peak_envelope", "sgz_scope_trigger_windows", "sgz_spectrum_kernel_name", "sgz_scope_trigger_device", "sgz_resonator_set_path",
+    "sgz_vscope_peak_envelope", "sgz_scope_trigger_windows", "sgz_spectrum_kernel_name", "sgz_scope_trigger_device", "sgz_resonator_set_path", "sgz_spectrum_reserve",
 ]
 
 
@@ -111,6 +111,7 @@ def load():
     lib.sgz_resonator_process.argtypes = [vp, fp, i32, i32, u64, u64]
     lib.sgz_resonator_get_state.argtypes = [vp, fp, i32]
     lib.sgz_resonator_set_path.argtypes = [vp, i32]
+    lib.sgz_spectrum_reserve.argtypes = [vp, u64, u64, u32]
     lib.sgz_fft_forward_noalloc.argtypes = [fp, fp, u32, u32, vp]
     lib.sgz_spectrum_track_peaks.argtypes = [vp, i32, C.POINTER(C.c_double), C.c_double, C.c_double, C.POINTER(_abi.TrackerState), C.POINTER(_abi.TrackerResult)]
     lib.sgz_spectrum_history_reserve.argtypes = [vp, u64]

@@ -441,6 +441,98 @@
 		}
 	}
 
+	// Unchained launches, fixup = 1 (FusedArgs): what k_seam_carry + k_seam_apply do, done by the CTA for its own first part
+	// right after its frames, while its results are still in L2.  The part went through the frame loop from a zero state;
+	// with the true state `carry` its predecessor ended on, s_f = max(s_(f-1) pole, m_f) unrolls to
+	// max(carry pole^k, local_f), and multiplication by the pole and the dB scale are monotone, so
+	//     result_f = max(local result_f, scale(carry pole^k))        bit for bit what one CTA per stream computes.
+	// The chain along a stream is as long as the stream has parts (two or three); every CTA of the launch is resident
+	// (cooperative launch), so the wait is short and cannot deadlock.
+	template<int T, bool HOLD2>
+	__device__ __forceinline__ void seamFixup(const DeviceTables& t, const FusedArgs& a, int u)
+	{
+		const int P = int(t.P);
+		const uint32_t F = a.nFrames, G = gridDim.x, cta = blockIdx.x;
+		const uint64_t items = uint64_t(a.numStreams) * F;
+		const uint64_t i0 = items * cta / G, i1 = items * (cta + 1) / G;
+		if (i1 == i0) return;
+		const uint32_t sA = uint32_t(i0 / F), fA = uint32_t(i0 - uint64_t(sA) * F);
+		if (fA == 0) return; // the range begins a stream: nothing is carried in
+		const uint32_t f1 = uint32_t(min(uint64_t(F), i1 - uint64_t(sA) * F));
+		if (u == 0)
+		{
+			uint32_t spins = 0;
+			while (ldAcquire(a.flags + (cta - 1)) != a.epoch) { __nanosleep(64); if (++spins > (1u << 24)) __trap(); }
+		}
+		__syncthreads(); // (also: this CTA's own state and result stores are visible to all its threads)
+		const float2* carryIn = a.seam + uint64_t(2 * G + cta - 1) * 2 * P; // true final state of the part before this one
+		const float2* local = a.seam + uint64_t(cta) * 2 * P;               // this part's final state from zero
+		const uint64_t stream = uint64_t(sA) + a.firstStream;
+		const bool ends = f1 == F;
+		float2* out = ends ? a.states + stream * 2 * P : a.seam + uint64_t(2 * G + cta) * 2 * P;
+		const float poles[2] = { t.pole0, t.pole1 };
+		// 1. this part's own true final state first - the next part of the stream is waiting for it: the carried state decayed
+		//    once per frame (the same chain of roundings as the frame loop), merged with the part's final state from zero
+		for (int x = u; x < P; x += T)
+		{
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+			{
+				float2 carry = __ldcg(carryIn + k * P + x);
+				for (uint32_t f = fA; f < f1; ++f) { carry.x *= poles[k]; if (HOLD2) carry.y *= poles[k]; }
+				const float2 own = __ldcg(local + k * P + x);
+				// (.y is only a peak hold in the two-channel forms; otherwise it stays what it was)
+				if (HOLD2) out[k * P + x] = make_float2(fmaxf(carry.x, own.x), fmaxf(carry.y, own.y));
+				else if (ends) out[k * P + x].x = fmaxf(carry.x, own.x);
+				else out[k * P + x] = make_float2(fmaxf(carry.x, own.x), own.y);
+			}
+		}
+		if (!ends)
+		{
+			__syncthreads();
+			if (u == 0) { __threadfence(); stRelease(a.flags + cta, a.epoch); }
+		}
+		// 2. raise the part's stored results where the decaying carry still dominates.  The walk is latency-bound (the rows
+		//    were written with streaming stores and come back from DRAM) and the loads do not depend on the carry, so both
+		//    graphs of four frames are requested per trip (eight loads in flight per thread; sixteen spilled and were no faster)
+#ifndef SGZ8_FIXUP_BATCH
+#define SGZ8_FIXUP_BATCH 4
+#endif
+		constexpr int kBatch = SGZ8_FIXUP_BATCH;
+		for (int x = u; x < P; x += T)
+		{
+			const float sm = t.slope[x] * t.minFracRecip;
+			float2 carry[2] = { __ldcg(carryIn + x), __ldcg(carryIn + P + x) };
+			for (uint32_t f = fA; f < f1; f += kBatch)
+			{
+				float2* row[kBatch][2]; float2 res[kBatch][2];
+#pragma unroll
+				for (int j = 0; j < kBatch; ++j)
+#pragma unroll
+					for (int k = 0; k < 2; ++k)
+					{
+						row[j][k] = f + j < f1 ? keptRow(a, stream, f + j, k, uint32_t(P)) : nullptr;
+						if (row[j][k]) res[j][k] = __ldcg(row[j][k] + x);
+					}
+#pragma unroll
+				for (int j = 0; j < kBatch; ++j)
+				{
+					if (f + j >= f1) break;
+#pragma unroll
+					for (int k = 0; k < 2; ++k)
+					{
+						carry[k].x *= poles[k];
+						if (HOLD2) carry[k].y *= poles[k];
+						if (!row[j][k]) continue;
+						res[j][k].x = fmaxf(res[j][k].x, fastLogScale(sm, carry[k].x, 1.f, t.deltaYLn2, t.lowerClip));
+						if (HOLD2) res[j][k].y = fmaxf(res[j][k].y, fastLogScale(sm, carry[k].y, 1.f, t.deltaYLn2, t.lowerClip));
+						row[j][k][x] = res[j][k];
+					}
+				}
+			}
+		}
+	}
+
 	// ---- Phase configuration (MATRIX == 3): the display works on the complex split spectra themselves ----
 	// csf as the reference's magnitude pass sees it once the `np` lowest indices and their mirrors have been replaced by
 	// their magnitudes (the lazy in-place normalisation of TransformDSP.inl:709-727)
@@ -1056,6 +1148,7 @@
 			}
 		}
 		} // parts
+		if (!a.chained && a.fixup) seamFixup<T, (STEREO && MATRIX != 3)>(t, a, u);
 	}
 
 	// Second half of the unchained launch mode (fewer streams than CTAs).  Every part of a stream went through k_fused8

@@ -695,7 +695,7 @@ struct sgz_spectrum
 	bool seamsOk{ false };        // the unchained launch mode is exact for this configuration (monotone hold and display scale)
 	uint32_t fusedCapacity{ 0 };  // CTAs of this handle's fused kernel the device holds at once (the launch size of k_fused8)
 	uint32_t fusedEpoch{ 0 };     // launch counter: the value a seam flag must show (no clearing between launches)
-	float2* dSeam{ nullptr };     // [2 capacity][2][P] peak-hold states at the seams between CTA ranges
+	float2* dSeam{ nullptr };     // [3 capacity][2][P] peak-hold states at the seams between CTA ranges
 	uint32_t* dSeamFlags{ nullptr }; // [capacity]
 	float2* dSpare{ nullptr };    // [P] sink for results an output mode does not keep (FusedArgs::spare)
 	void* dTrack{ nullptr }; // frequency tracker: [S] bounds in, [S] records out
@@ -1080,7 +1080,7 @@ extern "C"
 		{
 			FusedArgs none{};
 			SGZ_TRY(launchFused(h, none, nullptr)); // capacity query only
-			SGZ_TRY(allocZero(h, size_t(2) * h->fusedCapacity * 2 * t.P, &h->dSeam));
+			SGZ_TRY(allocZero(h, size_t(3) * h->fusedCapacity * 2 * t.P, &h->dSeam));
 			SGZ_TRY(allocZero(h, size_t(h->fusedCapacity), &h->dSeamFlags));
 			SGZ_TRY(allocZero(h, size_t(t.P), &h->dSpare));
 			// carrying the hold across zero-started parts relies on x -> x * pole and on the dB scale being monotone
@@ -1659,11 +1659,15 @@ extern "C"
 		{
 			plan.ctas = uint32_t(std::min<uint64_t>(capacity, items / kFrameParallelMinRun));
 			plan.chained = false;
+			// a stream in two to four parts: the CTAs carry the hold across the seams themselves (they wait on one another: a
+			// chain of that many short hops); longer chains - a few long recordings - and Phase go to the seam kernels
+			a.fixup = (!phase && uint64_t(plan.ctas) <= uint64_t(4) * nS) ? 1u : 0u;
+			plan.cooperative = a.fixup != 0;
 		}
 		a.lastResults = h->dResults; a.spare = h->dSpare;
 		int rc = launchFused(h, a, &plan);
 		if (rc != SGZ_OK) return rc;
-		if (plan.chained) return keepLastFrame(h, a);
+		if (plan.chained || a.fixup) return keepLastFrame(h, a);
 		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO form of the hold
 		k_seam_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSeam, h->dStates, F, nS, plan.ctas, stereoFlag, a.firstStream);
 		k_seam_apply<<<dim3((P + 127) / 128, plan.ctas), 128, 0, h->stream>>>(h->dev, a, plan.ctas, stereoFlag);
@@ -1829,6 +1833,41 @@ extern "C"
 		{
 			SGZ_CUDA(cudaMemcpyAsync(results, dRes, resFloats * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
 			SGZ_CUDA(cudaStreamSynchronize(h->stream));
+		}
+		return SGZ_OK;
+	}
+
+	int sgz_spectrum_reserve(sgz_spectrum* h, uint64_t n_samples, uint64_t stream_stride, uint32_t n_frames)
+	{
+		if (!h) return fail(SGZ_EINVAL, "null handle");
+		if (h->nStreams > 1 && stream_stride < 2 * n_samples) return fail(SGZ_EINVAL, "stream_stride smaller than one stream");
+		SGZ_GUARD(h);
+		const uint32_t P = h->tab.P;
+		const size_t audioFloats = size_t(stream_stride) * (h->nStreams - 1) + size_t(n_samples) * 2;
+		int rc = ensureStage(h, &h->dAudioStage, &h->audioStageBytes, audioFloats * sizeof(float));
+		if (rc != SGZ_OK) return rc;
+		if ((rc = ensureStage(h, &h->dResultStage, &h->resultStageBytes, size_t(h->nStreams) * resultFloatsPerStream(SGZ_OUT_FULL, n_frames, P) * sizeof(float))) != SGZ_OK) return rc;
+		if (!h->copyIn) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyIn, cudaStreamNonBlocking));
+		if (!h->copyOut) SGZ_CUDA(cudaStreamCreateWithFlags(&h->copyOut, cudaStreamNonBlocking));
+		while (h->events.size() < 2 * h->pipeChunks + 1)
+		{
+			cudaEvent_t e;
+			SGZ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+			h->events.push_back(e);
+		}
+		if (h->cfg.algo == SGZ_ALGO_RSNT)
+		{
+			// time-slice scratch of the resonator for blocks of up to n_samples: tiles of the tensor-core kernel, or the
+			// FP32 kernels' slices of at least 256 samples
+			const size_t total = size_t(P) * h->tab.resonatorVectors * h->tab.stateChannels;
+			const size_t slices = std::max<size_t>((n_samples + kTcSpan - 1) / kTcSpan, std::min<size_t>(65535, n_samples / 256 + 1));
+			const size_t need = size_t(h->nStreams) * slices * total * sizeof(float2);
+			if (h->resPartialBytes < need)
+			{
+				if (h->dResPartial) { SGZ_CUDA(cudaStreamSynchronize(h->stream)); cudaFree(h->dResPartial); h->dResPartial = nullptr; h->resPartialBytes = 0; }
+				SGZ_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->dResPartial), need));
+				h->resPartialBytes = need;
+			}
 		}
 		return SGZ_OK;
 	}

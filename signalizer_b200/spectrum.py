@@ -210,6 +210,10 @@ class TransformPairBatch:
         return out
 
     # -- fused batched path ---------------------------------------------------------------
+    def reserve(self, n_samples: int, stream_stride: int, n_frames: int) -> None:
+        """size every lazily grown buffer once (staging, pipeline streams / events, resonator scratch)"""
+        check(self.lib.sgz_spectrum_reserve(self._h, n_samples, stream_stride, n_frames))
+
     def kernel_name(self) -> str:
         return self.lib.sgz_spectrum_kernel_name(self._h).decode()
 

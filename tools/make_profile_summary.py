@@ -21,5 +21,5 @@ def num(k):
     return x * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(unit, 1)
 rd, wr = num("dram__bytes_read.sum"), num("dram__bytes_write.sum")
 frames = 65536
-print(json.dumps({"round": 1, "capture": what, "frames_per_launch": frames, "algorithmic_bytes_per_launch": frames * 114688,
+print(json.dumps({"round": 2, "capture": what, "frames_per_launch": frames, "algorithmic_bytes_per_launch": frames * 114688,
                   "dram_bytes_per_launch": rd + wr, "dram_bytes_read": rd, "dram_bytes_write": wr, "metrics": m}, indent=1))
