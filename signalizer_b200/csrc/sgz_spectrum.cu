@@ -1048,7 +1048,7 @@ extern "C"
 			// operands of k_resonate_tc: for every filter row g = z P + i the powers p^(L-1-k), k = 0 .. L-1, in double,
 			// split into a TF32 head and tail, stored per 128-row tile in the kernel's shared-memory order
 			const uint32_t half = t.P * t.resonatorVectors, rowTiles = (half + kTcRows - 1) / kTcRows;
-			std::vector<float> aTiles(size_t(rowTiles) * 4 * kTcMatFloats, 0.f);
+			std::vector<float> aTiles(size_t(rowTiles) * 4 * kTcAFloats, 0.f);
 			std::vector<float2> powL(size_t(rowTiles) * kTcRows, make_float2(0.f, 0.f));
 			auto tf32 = [](double v) { // round to 11 significant bits (ties away), like cvt.rna.tf32.f32
 				float f = float(v); uint32_t u; std::memcpy(&u, &f, 4);
@@ -1057,15 +1057,15 @@ extern "C"
 			{
 				const std::complex<double> p(t.resCoeffReal[g], t.resCoeffImag[g]);
 				std::complex<double> pw(1.0, 0.0);
-				float* tile = aTiles.data() + size_t(g / kTcRows) * 4 * kTcMatFloats;
+				float* tile = aTiles.data() + size_t(g / kTcRows) * 4 * kTcAFloats;
 				const uint32_t row = g % kTcRows, rg = row / 8, r = row % 8;
 				for (int e = 0; e < kTcL; ++e, pw *= p)
 				{
 					const int k = kTcL - 1 - e;   // x[k] is multiplied by p^(L-1-k) = p^e
 					const size_t off = ((size_t(k / 4) * (kTcRows / 8) + rg) * 8 + r) * 4 + (k % 4);
 					const float reH = tf32(pw.real()), imH = tf32(pw.imag());
-					tile[0 * kTcMatFloats + off] = reH; tile[1 * kTcMatFloats + off] = tf32(pw.real() - reH);
-					tile[2 * kTcMatFloats + off] = imH; tile[3 * kTcMatFloats + off] = tf32(pw.imag() - imH);
+					tile[0 * kTcAFloats + off] = reH; tile[1 * kTcAFloats + off] = tf32(pw.real() - reH);
+					tile[2 * kTcAFloats + off] = imH; tile[3 * kTcAFloats + off] = tf32(pw.imag() - imH);
 				}
 				powL[g] = make_float2(float(pw.real()), float(pw.imag())); // p^L
 			}
@@ -1455,7 +1455,7 @@ extern "C"
 			ta.tiles = tcTiles; ta.count = count; ta.nStreams = h->nStreams; ta.aTiles = h->dResTcA; ta.powL = h->dResTcPowL;
 			const uint64_t items = uint64_t((half + kTcRows - 1) / kTcRows) * h->nStreams * h->tab.stateChannels * tcTiles;
 			const uint32_t ctas = uint32_t(std::min<uint64_t>(items, uint64_t(sms)));
-			k_resonate_tc<<<ctas, 128, kTcSmemBytes, h->stream>>>(h->dev, ta, h->dResPartial);
+			k_resonate_tc<<<ctas, kTcThreads, kTcSmemBytes, h->stream>>>(h->dev, ta, h->dResPartial);
 		}
 		const uint32_t fp32Chunks = a.chunks - a.chunk0; // slices the FP32 kernel computes
 		if (fp32Chunks > 0)
