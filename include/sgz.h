@@ -227,9 +227,11 @@ int  sgz_spectrum_reserve(sgz_spectrum* h, uint64_t n_samples, uint64_t stream_s
  * One fused kernel launch covers all frames of all streams when the
  * configuration has a fused kernel (sgz_spectrum_info.fused_available:
  * FFT algorithm, transform size 1024 ... 16384, display points that fit one
- * CTA's shared memory); with few streams the frames of a stream are spread
- * over CTAs as well, with bit-identical results.  Everything else runs the
- * four staged kernels per frame. */
+ * CTA's shared memory): the launch is as many CTAs as the GPU holds at once,
+ * each taking an equal share of the (stream, frame) list, whatever the stream
+ * count, with bit-identical results (the peak-hold state is handed across
+ * where a stream is cut between CTAs).  Everything else runs the four staged
+ * kernels per frame. */
 int  sgz_spectrum_process_frames(sgz_spectrum* h, const float* audio, int mem, int layout,
                                  uint64_t n_samples, uint64_t stream_stride, uint32_t hop,
                                  uint32_t n_frames, float* results, int results_mem);
@@ -363,13 +365,14 @@ int  sgz_spectrum_colour_columns(sgz_spectrum* h, const float* results, int mem,
  * audioEntryPoint (:1172-1204). */
 int  sgz_resonator_process(sgz_spectrum* h, const float* audio, int mem, int layout,
                            uint64_t n_samples, uint64_t stream_stride);
-/* Raw resonator state (cresonator), [stream][channel][vector][filter] complex. */
-/* Which kernels advance the resonator bank.  SGZ_RESONATOR_AUTO (default): blocks of at least 8192 samples run on the
- * tensor cores - the block's whole 8192-sample tiles as a TF32 GEMM with a three-term operand split and FP32
- * accumulation - and shorter blocks / remainders on the FP32 recurrence; SGZ_RESONATOR_FP32: the FP32 recurrence
- * always (the two agree to about 1e-6 of the state's magnitude, not bit for bit).  No reference counterpart. */
+/* Which kernels advance the resonator bank.  SGZ_RESONATOR_AUTO (default): blocks of at least 2048 samples run on the
+ * tensor cores - tiles of 4096 samples as a TF32 GEMM with a three-term operand split and FP32 accumulation - and
+ * shorter blocks on the FP32 recurrence; SGZ_RESONATOR_FP32: the FP32 recurrence
+ * always (after 480 000 samples the two differ by about 2e-5 of the state's peak - both inside the tolerance held
+ * against the CPU oracle - not bit for bit).  No reference counterpart. */
 enum { SGZ_RESONATOR_AUTO = 0, SGZ_RESONATOR_FP32 = 1 };
 int  sgz_resonator_set_path(sgz_spectrum* h, int path);
+/* Raw resonator state (cresonator), [stream][channel][vector][filter] complex. */
 int  sgz_resonator_get_state(sgz_spectrum* h, float* out, int mem);
 
 /* ==== secondary paths: Vectorscope and Oscilloscope =========================

@@ -2,7 +2,8 @@
 
 TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
 cpu_baseline / --impl reference legs.  Never import this from signalizer_b200/.
-PARITY UNPINNED — see oracle/sgz_oracle.hpp."""
+Pinned by the reference's own transform source (oracle/_ref, tests/test_oracle_ref.py); cpl primitives are
+decisions — see oracle/sgz_oracle.hpp."""
 import ctypes as C
 import os
 import subprocess

@@ -4,15 +4,19 @@
 // or call this; only tests/, __graft_entry__.smoke() and bench.py's
 // cpu_baseline / --impl reference legs use it, as the checker / CPU baseline.
 //
-// PARITY UNPINNED: the reference (jthorborg/signalizer @ 8286702) ships no
-// tests, fixtures or golden vectors, and cannot be compiled here because its
-// numeric library `cpl` (bitbucket.org/Mayae/cpl @ fa8e21e1, a git submodule,
-// which itself bundles pffft and DustFFT) is absent from the checkout.  What
-// is in-tree (Source/Spectrum/TransformDSP.inl, TransformConstant.h,
-// TransformPair.h) is restated statement by statement below, with the same
-// integer/float types at every conversion.  The cpl primitives it calls are
-// restated from their published/textbook definitions as constrained by the
-// call sites; each such decision is marked "cpl decision".
+// PINNED BY THE REFERENCE'S SOURCE, cpl excepted: what is in-tree
+// (Source/Spectrum/TransformDSP.inl, TransformConstant.h, TransformPair.h) is
+// restated statement by statement below, with the same integer/float types at
+// every conversion, and tests/test_oracle_ref.py holds this restatement to the
+// same BITS as oracle/_ref - those three reference files compiled unmodified
+// against stand-in cpl headers (oracle/build_ref.sh, oracle/ref_stubs/).
+// What stays unpinned: the reference (jthorborg/signalizer @ 8286702) ships no
+// tests, fixtures or golden vectors, and its numeric library `cpl`
+// (bitbucket.org/Mayae/cpl @ fa8e21e1, a git submodule, which itself bundles
+// pffft and DustFFT) is absent from the checkout.  The cpl primitives the path
+// calls are restated from their published/textbook definitions as constrained
+// by the call sites; each such decision is marked "cpl decision", and both this
+// file and oracle/_ref run on them.
 //
 // Paths cited as `TransformDSP.inl:N` are relative to
 // /root/reference/Source/Spectrum/.

@@ -2,7 +2,8 @@
 //
 // TEST INFRASTRUCTURE ONLY (see the header of sgz_oracle.hpp): used by tests/,
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
-// PARITY UNPINNED (no reference tests or golden vectors exist; cpl is absent).
+// The restatement is pinned bit for bit by the reference's own source (oracle/_ref, see below); the cpl primitives under
+// both are decisions (no reference tests or golden vectors exist; cpl is absent).
 //
 // The handle mirrors the product's batched C ABI (include/sgz.h) so one test
 // harness drives both: `n_streams` TransformPair objects sharing one
