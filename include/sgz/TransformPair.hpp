@@ -153,6 +153,25 @@ namespace sgz
 				static_cast<uint32_t>(numFrames), reinterpret_cast<float*>(results), resultsMem));
 		}
 
+		/// The same with a choice of what comes back: SGZ_OUT_LINE_MAIN = graph LineMain of every frame, what addAudioFrame keeps
+		/// in sfbuf ([pair][frame][axisPoints]); SGZ_OUT_LAST_FRAME = both graphs of the newest frame ([pair][graph][axisPoints]).
+		void processFrames(const float* audio, std::size_t numSamples, std::size_t pairStride, std::size_t hop, std::size_t numFrames,
+			UComplex* results, int output, int layout, int audioMem = SGZ_MEM_HOST, int resultsMem = SGZ_MEM_HOST)
+		{
+			check(sgz_spectrum_process_frames_select(handle, audio, audioMem, layout, numSamples, pairStride, static_cast<uint32_t>(hop),
+				static_cast<uint32_t>(numFrames), reinterpret_cast<float*>(results), resultsMem, output));
+		}
+		/// Sizes every lazily grown buffer once (a caller with a deadline reserves before its first callback).
+		void reserve(std::size_t numSamples, std::size_t pairStride, std::size_t numFrames)
+		{
+			check(sgz_spectrum_reserve(handle, numSamples, pairStride, static_cast<uint32_t>(numFrames)));
+		}
+		/// resonatingDispatch - TransformDSP.inl:1215-1295 (tensor cores for blocks of 2048 samples and more)
+		void resonatingDispatch(const float* audio, std::size_t numSamples, std::size_t pairStride, int layout = SGZ_LAYOUT_PLANAR, int mem = SGZ_MEM_HOST)
+		{
+			check(sgz_resonator_process(handle, audio, mem, layout, numSamples, pairStride));
+		}
+
 		/// Device-resident audio history (the cpl::AudioStream side of TransformDSP.inl:49,65-88): reserve once,
 		/// append each callback block, then run the frames that fell due (audioEntryPoint's scheduling, :1165-1211).
 		void historyReserve(std::size_t capacity) { check(sgz_spectrum_history_reserve(handle, capacity)); }

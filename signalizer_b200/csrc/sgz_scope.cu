@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -729,6 +730,25 @@ namespace sgz
 		return (num.x * denom.x + num.y * denom.y) / (denom.x * denom.x + denom.y * denom.y);
 	}
 
+	// W_8192^k = exp(-2 pi i k / 8192), k < 4096, for the fp64 FFT below: filled once per device by k_scope_period_twiddles
+	// (sincospi of the exact argument, so every stage's W_(2 half)^j = table[j (4096 / half)] has the bits a direct
+	// evaluation would give)
+	static __device__ double2 g_periodTwiddle[kLookahead / 2];
+
+	__global__ void k_scope_period_twiddles()
+	{
+		const int k = blockIdx.x * blockDim.x + threadIdx.x;
+		if (k >= kLookahead / 2) return;
+		double sn, cs;
+		sincospi(-double(k) / double(kLookahead / 2), &sn, &cs);
+		g_periodTwiddle[k] = make_double2(cs, sn);
+	}
+
+	// calculateFundamentalPeriod (OscilloscopeDSP.inl:61-223) up to the pick: fp64 8192-point FFT of one stream in shared
+	// memory (radix 2, twiddles from the table), |X| of the 4095 candidate bins in parallel, then the reference's scan
+	// (:128-184).  The scan carries `max` from bin to bin, but a bin only matters if it passes the entry test against the
+	// CURRENT max (`invHysteresis |X_i| > 2 max`); warp 0 tests 32 bins per step by ballot and lane 0 runs the reference's
+	// decision on the ones that pass, in order, re-testing each against the max as it stands.
 	__global__ void __launch_bounds__(512) k_scope_period_pick(PeriodPickArgs a)
 	{
 		extern __shared__ double2 tb[];
@@ -745,52 +765,70 @@ namespace sgz
 		__syncthreads();
 		for (int half = 1; half < N; half <<= 1)
 		{
+			const int step = (N >> 1) / half;
 			for (int b = threadIdx.x; b < (N >> 1); b += blockDim.x)
 			{
 				const int j = b & (half - 1);
 				const int i0 = ((b - j) << 1) + j;
-				double sn, cs;
-				sincospi(-double(j) / double(half), &sn, &cs); // W_(2 half)^j
+				const double2 w = g_periodTwiddle[j * step]; // W_(2 half)^j
 				const double2 u = tb[i0];
-				const double2 v = dmul(tb[i0 + half], make_double2(cs, sn));
+				const double2 v = dmul(tb[i0 + half], w);
 				tb[i0] = make_double2(u.x + v.x, u.y + v.y);
 				tb[i0 + half] = make_double2(u.x - v.x, u.y - v.y);
 			}
 			__syncthreads();
 		}
-		if (threadIdx.x != 0) return;
-		// OscilloscopeDSP.inl:128-184, one thread: the loop carries `max` from bin to bin
+		// |X_i| of the bins the scan looks at, into the upper half of the buffer (bins >= N / 2 are never read)
+		double* mag = reinterpret_cast<double*>(tb + (N >> 1));
+		for (int i = threadIdx.x; i < (N >> 1); i += blockDim.x) mag[i] = dabs(tb[i]);
+		__syncthreads();
+		if (threadIdx.x >= 32) return;
+		const int lane = threadIdx.x;
 		const double quarterSemitone = pow(2.0, 0.25 / 12.0) - 1;
 		const double invHysteresis = 1 - a.hysteresis;
-		uint64_t mIndex = 1; double mValue = fmax(a.threshold * N / 6.0, dabs(tb[1])), mOffset = quadDelta(tb, 1);
-		for (int i = 2; i < (N >> 1); ++i)
+		uint64_t mIndex = 1; double mValue = fmax(a.threshold * N / 6.0, mag[1]), mOffset = quadDelta(tb, 1);
+		for (int i0 = 2; i0 < (N >> 1); i0 += 32)
 		{
-			const double cValue = dabs(tb[i]);
-			if (invHysteresis * cValue > mValue * 2)
+			const int i = i0 + lane;
+			const double cMine = i < (N >> 1) ? mag[i] : 0.0;
+			// mValue only grows, so a bin that fails against the max at the start of the step fails against any later one
+			unsigned pending = __ballot_sync(0xffffffffu, invHysteresis * cMine > mValue * 2);
+			while (pending)
 			{
-				const double mOmega = double(mIndex) + mOffset;
-				if (mOmega > 0)
+				const int l = __ffs(pending) - 1;
+				pending &= pending - 1;
+				if (lane == 0)
 				{
-					const double cOffset = quadDelta(tb, i);
-					const double factor = (double(i) + cOffset) / mOmega;
-					const double sensivity = cValue / mValue;
-					bool take = false;
-					if (invHysteresis * sensivity > 20) take = true;
-					else if (fabs(1 - factor) < invHysteresis * quarterSemitone) take = true;
-					else
+					const int c = i0 + l;
+					const double cValue = mag[c];
+					if (invHysteresis * cValue > mValue * 2)
 					{
-						const double multipleDeviation = fabs(factor - floor(factor + 0.5));
-						if (invHysteresis * fabs(multipleDeviation) > quarterSemitone) take = true;
+						const double mOmega = double(mIndex) + mOffset;
+						if (mOmega > 0)
+						{
+							const double cOffset = quadDelta(tb, c);
+							const double factor = (double(c) + cOffset) / mOmega;
+							const double sensivity = cValue / mValue;
+							bool take = false;
+							if (invHysteresis * sensivity > 20) take = true;
+							else if (fabs(1 - factor) < invHysteresis * quarterSemitone) take = true;
+							else
+							{
+								const double multipleDeviation = fabs(factor - floor(factor + 0.5));
+								if (invHysteresis * fabs(multipleDeviation) > quarterSemitone) take = true;
+							}
+							if (take) { mIndex = c; mValue = cValue; mOffset = cOffset; }
+						}
+						else
+						{
+							mIndex = c; mValue = cValue; mOffset = quadDelta(tb, c);
+						}
 					}
-					if (take) { mIndex = i; mValue = cValue; mOffset = cOffset; }
-				}
-				else
-				{
-					mIndex = i; mValue = cValue; mOffset = quadDelta(tb, i);
 				}
 			}
+			mValue = __shfl_sync(0xffffffffu, mValue, 0); // the next step's entry test uses lane 0's max
 		}
-		a.picked[s].index = mIndex; a.picked[s].value = mValue; a.picked[s].offset = mOffset;
+		if (lane == 0) { a.picked[s].index = mIndex; a.picked[s].value = mValue; a.picked[s].offset = mOffset; }
 	}
 
 	struct GoertzelArgs
@@ -1131,7 +1169,19 @@ extern "C"
 		pa.firstSample = (long long)n_samples - (long long)offset1;
 		pa.threshold = prm->threshold; pa.hysteresis = prm->hysteresis; pa.picked = dPicked;
 		const size_t smem = TransformSize * sizeof(double2);
-		SGZS_CUDA(cudaFuncSetAttribute(k_scope_period_pick, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+		{
+			// once per device: the opt-in shared-memory size and the twiddle table (stream-ordered before the first use)
+			static std::atomic<uint64_t> ready{ 0 };
+			const uint64_t bit = uint64_t(1) << (c->device & 63);
+			if (!(ready.load(std::memory_order_acquire) & bit))
+			{
+				SGZS_CUDA(cudaFuncSetAttribute(k_scope_period_pick, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+				k_scope_period_twiddles<<<(kLookahead / 2 + 255) / 256, 256, 0, c->stream>>>();
+				SGZS_CUDA(cudaGetLastError());
+				SGZS_CUDA(cudaStreamSynchronize(c->stream));
+				ready.fetch_or(bit, std::memory_order_release);
+			}
+		}
 		k_scope_period_pick<<<n_streams, 512, smem, c->stream>>>(pa);
 		SGZS_CUDA(cudaGetLastError());
 		std::vector<sgz_scope_bin_record> picked(n_streams);
