@@ -16,14 +16,12 @@
 		//     LAST, from that state.  Same arithmetic in the same order as one CTA per stream.
 		//   chained = 0 (fewer streams than CTAs: a long recording): parts that do not begin a stream start from a zero
 		//     state and leave their final state in a slot (seam[c] if the part began mid-stream, seam[G + c] if it began
-		//     the stream); the peak hold is carried across afterwards (bit-identical, see seamFixup / k_seam_carry):
-		//       fixup = 1: by the CTAs themselves once their frames are done - the part that began the stream publishes its
-		//         (true) final state in seam[2 G + c] + flags[c]; a part that began mid-stream waits for its predecessor's,
-		//         raises its own results while they are still in L2, and publishes (or, at the stream's end, stores) its own;
-		//       fixup = 0 (Phase, whose second state is a filter): by k_seam_carry / k_seam_apply / k_phase_smooth.
-		uint32_t chained, epoch, fixup;
+		//     the stream); k_seam_carry / k_seam_apply carry the peak hold across afterwards, bit-identically (and
+		//     k_phase_smooth runs Phase's second state, which is a filter).  (Round 2 also had the CTAs do this themselves at
+		//     the end of the launch: measured no faster than the kernels at any shape, and removed.)
+		uint32_t chained, epoch;
 		float2* states;  // [S][2][P]
-		float2* seam;    // [3 G][2][P]
+		float2* seam;    // [2 G][2][P]
 		uint32_t* flags; // [G]
 		float2* results; // outMode 0: [S][F][2][P]; 1 (LineMain of every frame): [S][F][P]; 2 (last frame only): [S][2][P]
 		float2* lastResults; // [S][2][P] lineGraphs[k].results of the handle (see resultRow)
@@ -152,13 +150,6 @@
 		{
 			if (fEnd == F) out->dst = a.states + uint64_t(stream) * 2 * P;
 			else { out->dst = a.seam + uint64_t(cta) * 2 * P; out->publish = 1; }
-		}
-		else if (a.fixup && fBegin == 0)
-		{
-			// starts from the stream's real state, so its final state is the true one: to the handle if the stream ends here,
-			// otherwise published for the CTA that continues the stream
-			if (fEnd == F) out->dst = a.states + uint64_t(stream) * 2 * P;
-			else { out->dst = a.seam + uint64_t(2 * G + cta) * 2 * P; out->publish = 1; }
 		}
 		else out->dst = a.seam + uint64_t(fBegin ? cta : G + cta) * 2 * P;
 	}

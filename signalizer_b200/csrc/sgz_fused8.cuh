@@ -441,96 +441,20 @@
 		}
 	}
 
-	// Unchained launches, fixup = 1 (FusedArgs): what k_seam_carry + k_seam_apply do, done by the CTA for its own first part
-	// right after its frames, while its results are still in L2.  The part went through the frame loop from a zero state;
-	// with the true state `carry` its predecessor ended on, s_f = max(s_(f-1) pole, m_f) unrolls to
-	// max(carry pole^k, local_f), and multiplication by the pole and the dB scale are monotone, so
-	//     result_f = max(local result_f, scale(carry pole^k))        bit for bit what one CTA per stream computes.
-	// The chain along a stream is as long as the stream has parts (two or three); every CTA of the launch is resident
-	// (cooperative launch), so the wait is short and cannot deadlock.
-	template<int T, bool HOLD2>
-	__device__ __forceinline__ void seamFixup(const DeviceTables& t, const FusedArgs& a, int u)
+	__device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
+	// One stored result against the decayed carry: raised where the carry dominates (fmaxf, as the fix-up always did).
+	// Returns whether the carry can still matter at LATER frames of the part.  It cannot once scale(carry) is strictly
+	// below the stored scale(s): the scale is monotone, so carry < s, and s_(f+1) >= fl(s pole) >= fl(carry pole) keeps it
+	// so for good; nor once the scaled carry sits on the clip value, the least value the scale has.  (Equal scaled values
+	// do not count: two different states may share one, and part again a frame later.)
+	__device__ __forceinline__ bool seamRaise(float& res, float carried, float sm, const DeviceTables& t, bool& changed)
 	{
-		const int P = int(t.P);
-		const uint32_t F = a.nFrames, G = gridDim.x, cta = blockIdx.x;
-		const uint64_t items = uint64_t(a.numStreams) * F;
-		const uint64_t i0 = items * cta / G, i1 = items * (cta + 1) / G;
-		if (i1 == i0) return;
-		const uint32_t sA = uint32_t(i0 / F), fA = uint32_t(i0 - uint64_t(sA) * F);
-		if (fA == 0) return; // the range begins a stream: nothing is carried in
-		const uint32_t f1 = uint32_t(min(uint64_t(F), i1 - uint64_t(sA) * F));
-		if (u == 0)
-		{
-			uint32_t spins = 0;
-			while (ldAcquire(a.flags + (cta - 1)) != a.epoch) { __nanosleep(64); if (++spins > (1u << 24)) __trap(); }
-		}
-		__syncthreads(); // (also: this CTA's own state and result stores are visible to all its threads)
-		const float2* carryIn = a.seam + uint64_t(2 * G + cta - 1) * 2 * P; // true final state of the part before this one
-		const float2* local = a.seam + uint64_t(cta) * 2 * P;               // this part's final state from zero
-		const uint64_t stream = uint64_t(sA) + a.firstStream;
-		const bool ends = f1 == F;
-		float2* out = ends ? a.states + stream * 2 * P : a.seam + uint64_t(2 * G + cta) * 2 * P;
-		const float poles[2] = { t.pole0, t.pole1 };
-		// 1. this part's own true final state first - the next part of the stream is waiting for it: the carried state decayed
-		//    once per frame (the same chain of roundings as the frame loop), merged with the part's final state from zero
-		for (int x = u; x < P; x += T)
-		{
-#pragma unroll
-			for (int k = 0; k < 2; ++k)
-			{
-				float2 carry = __ldcg(carryIn + k * P + x);
-				for (uint32_t f = fA; f < f1; ++f) { carry.x *= poles[k]; if (HOLD2) carry.y *= poles[k]; }
-				const float2 own = __ldcg(local + k * P + x);
-				// (.y is only a peak hold in the two-channel forms; otherwise it stays what it was)
-				if (HOLD2) out[k * P + x] = make_float2(fmaxf(carry.x, own.x), fmaxf(carry.y, own.y));
-				else if (ends) out[k * P + x].x = fmaxf(carry.x, own.x);
-				else out[k * P + x] = make_float2(fmaxf(carry.x, own.x), own.y);
-			}
-		}
-		if (!ends)
-		{
-			__syncthreads();
-			if (u == 0) { __threadfence(); stRelease(a.flags + cta, a.epoch); }
-		}
-		// 2. raise the part's stored results where the decaying carry still dominates.  The walk is latency-bound (the rows
-		//    were written with streaming stores and come back from DRAM) and the loads do not depend on the carry, so both
-		//    graphs of four frames are requested per trip (eight loads in flight per thread; sixteen spilled and were no faster)
-#ifndef SGZ8_FIXUP_BATCH
-#define SGZ8_FIXUP_BATCH 4
-#endif
-		constexpr int kBatch = SGZ8_FIXUP_BATCH;
-		for (int x = u; x < P; x += T)
-		{
-			const float sm = t.slope[x] * t.minFracRecip;
-			float2 carry[2] = { __ldcg(carryIn + x), __ldcg(carryIn + P + x) };
-			for (uint32_t f = fA; f < f1; f += kBatch)
-			{
-				float2* row[kBatch][2]; float2 res[kBatch][2];
-#pragma unroll
-				for (int j = 0; j < kBatch; ++j)
-#pragma unroll
-					for (int k = 0; k < 2; ++k)
-					{
-						row[j][k] = f + j < f1 ? keptRow(a, stream, f + j, k, uint32_t(P)) : nullptr;
-						if (row[j][k]) res[j][k] = __ldcg(row[j][k] + x);
-					}
-#pragma unroll
-				for (int j = 0; j < kBatch; ++j)
-				{
-					if (f + j >= f1) break;
-#pragma unroll
-					for (int k = 0; k < 2; ++k)
-					{
-						carry[k].x *= poles[k];
-						if (HOLD2) carry[k].y *= poles[k];
-						if (!row[j][k]) continue;
-						res[j][k].x = fmaxf(res[j][k].x, fastLogScale(sm, carry[k].x, 1.f, t.deltaYLn2, t.lowerClip));
-						if (HOLD2) res[j][k].y = fmaxf(res[j][k].y, fastLogScale(sm, carry[k].y, 1.f, t.deltaYLn2, t.lowerClip));
-						row[j][k][x] = res[j][k];
-					}
-				}
-			}
-		}
+		const float c = fastLogScale(sm, carried, 1.f, t.deltaYLn2, t.lowerClip);
+		const float r = fmaxf(res, c);
+		const bool live = sm * carried > 0.f && !(c < res);
+		if (r != res) { res = r; changed = true; }
+		return live;
 	}
 
 	// ---- Phase configuration (MATRIX == 3): the display works on the complex split spectra themselves ----
@@ -1148,7 +1072,6 @@
 			}
 		}
 		} // parts
-		if (!a.chained && a.fixup) seamFixup<T, (STEREO && MATRIX != 3)>(t, a, u);
 	}
 
 	// Second half of the unchained launch mode (fewer streams than CTAs).  Every part of a stream went through k_fused8
@@ -1208,10 +1131,17 @@
 		}
 	}
 
-	__global__ void __launch_bounds__(128) k_seam_apply(DeviceTables t, FusedArgs a, uint32_t G, int stereo)
+	// (gridDim.z slices of a part's frames run side by side: a slice first decays the carry over the frames before it -
+	// multiplications only, the same chain of roundings - then walks its own frames four at a time.  One thread walking a
+	// whole part is a chain of DRAM round trips as long as the part: 77 us for 55 frames, whatever the GPU had left idle.
+	// The walk is bound by its instruction count, not by DRAM: V = 2 points per thread and 16-byte accesses when P is even.)
+	// FULL: every frame keeps both graphs, one after the other, so the rows of a slice are 2 P results apart and the walk
+	// steps a pointer; the other output modes ask keptRow frame by frame.
+	template<int V, bool FULL, bool STEREO>
+	__global__ void __launch_bounds__(128) k_seam_apply(DeviceTables t, FusedArgs a, uint32_t G)
 	{
 		const int P = int(t.P);
-		const int x = blockIdx.x * blockDim.x + threadIdx.x;
+		const int x = (blockIdx.x * blockDim.x + threadIdx.x) * V;
 		if (x >= P) return;
 		const uint32_t c = blockIdx.y, nFrames = a.nFrames;
 		const uint64_t items = uint64_t(a.numStreams) * nFrames, i0 = seamCut(items, G, c), i1 = seamCut(items, G, c + 1);
@@ -1219,25 +1149,96 @@
 		const uint32_t sLocal = uint32_t(i0 / nFrames), f0 = uint32_t(i0 - uint64_t(sLocal) * nFrames);
 		if (f0 == 0) return; // the range begins a stream: nothing is carried in
 		const uint32_t f1 = uint32_t(min(uint64_t(nFrames), i1 - uint64_t(sLocal) * nFrames));
-		const float sm = t.slope[x] * t.minFracRecip;
+		const uint32_t perSlice = ((f1 - f0 + gridDim.z - 1) / gridDim.z + 3) & ~3u;
+		const uint32_t fa = f0 + blockIdx.z * perSlice, fb = min(f1, fa + perSlice);
+		if (fa >= f1) return;
+		typedef typename std::conditional<V == 2, float4, float2>::type Word; // V points' (.x, .y) results
+		float sm[V];
+#pragma unroll
+		for (int v = 0; v < V; ++v) sm[v] = t.slope[x + v] * t.minFracRecip;
 		const float poles[2] = { t.pole0, t.pole1 };
 		const float2* mine = a.seam + uint64_t(c) * 2 * P + x;
-		float2 carry[2] = { mine[0], mine[P] };
-		const uint64_t stream = uint64_t(sLocal) + a.firstStream;
-		for (uint32_t f = f0; f < f1; ++f)
+		float2 carry[2][V];
+#pragma unroll
+		for (int k = 0; k < 2; ++k)
+#pragma unroll
+			for (int v = 0; v < V; ++v) carry[k][v] = mine[k * P + v];
+		for (uint32_t f = f0; f < fa; ++f)
 		{
 #pragma unroll
 			for (int k = 0; k < 2; ++k)
+#pragma unroll
+				for (int v = 0; v < V; ++v) { carry[k][v].x *= poles[k]; if (STEREO) carry[k][v].y *= poles[k]; }
+		}
+		const uint64_t stream = uint64_t(sLocal) + a.firstStream;
+		// one frame's two rows against the carry; returns whether the carry can still reach a later frame (seamRaise)
+		auto frame = [&](Word* const row[2], Word res[2]) -> bool
+		{
+			bool live = false;
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
 			{
-				carry[k].x *= poles[k];
-				if (stereo) carry[k].y *= poles[k];
-				float2* row = keptRow(a, stream, f, k, uint32_t(P));
-				if (!row) continue;
-				float2 res = row[x];
-				res.x = fmaxf(res.x, fastLogScale(sm, carry[k].x, 1.f, t.deltaYLn2, t.lowerClip));
-				if (stereo) res.y = fmaxf(res.y, fastLogScale(sm, carry[k].y, 1.f, t.deltaYLn2, t.lowerClip));
-				row[x] = res;
+				bool changed = false;
+				float* val = reinterpret_cast<float*>(&res[k]);
+#pragma unroll
+				for (int v = 0; v < V; ++v)
+				{
+					carry[k][v].x *= poles[k];
+					if (STEREO) carry[k][v].y *= poles[k];
+					if (!row[k]) { live = live || carry[k][v].x > 0.f || (STEREO && carry[k][v].y > 0.f); continue; }
+					live = seamRaise(val[2 * v], carry[k][v].x, sm[v], t, changed) || live;
+					if (STEREO) live = seamRaise(val[2 * v + 1], carry[k][v].y, sm[v], t, changed) || live;
+				}
+				if (changed) *row[k] = res[k];
 			}
+			return live;
+		};
+		if constexpr (FULL)
+		{
+			const size_t rowStep = size_t(P) / V; // Words between one graph and the next
+			Word* at = reinterpret_cast<Word*>(a.results + ((stream * nFrames + fa) * 2) * P + x);
+			uint32_t left = fb - fa;
+			for (; left >= 4; left -= 4, at += 8 * rowStep)
+			{
+				Word res[4][2];
+#pragma unroll
+				for (int j = 0; j < 4; ++j) { res[j][0] = __ldcg(at + (2 * j) * rowStep); res[j][1] = __ldcg(at + (2 * j + 1) * rowStep); }
+				bool live = false;
+#pragma unroll
+				for (int j = 0; j < 4; ++j)
+				{
+					Word* const row[2] = { at + (2 * j) * rowStep, at + (2 * j + 1) * rowStep };
+					live = frame(row, res[j]);
+				}
+				if (!live) return;
+			}
+			for (; left > 0; --left, at += 2 * rowStep)
+			{
+				Word* const row[2] = { at, at + rowStep };
+				Word res[2] = { __ldcg(row[0]), __ldcg(row[1]) };
+				if (!frame(row, res)) return;
+			}
+		}
+		else for (uint32_t f = fa; f < fb; f += 4)
+		{
+			Word* row[4][2]; Word res[4][2];
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+				{
+					float2* r = f + j < fb ? keptRow(a, stream, f + j, k, uint32_t(P)) : nullptr;
+					row[j][k] = r ? reinterpret_cast<Word*>(r + x) : nullptr;
+					if (r) res[j][k] = __ldcg(row[j][k]);
+				}
+			bool live = false;
+#pragma unroll
+			for (int j = 0; j < 4; ++j)
+			{
+				if (f + j >= fb) break;
+				live = frame(row[j], res[j]);
+			}
+			if (!live) break;
 		}
 	}
 

@@ -22,6 +22,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <atomic>
 #include <mutex>
 #include <complex>
@@ -695,7 +696,7 @@ struct sgz_spectrum
 	bool seamsOk{ false };        // the unchained launch mode is exact for this configuration (monotone hold and display scale)
 	uint32_t fusedCapacity{ 0 };  // CTAs of this handle's fused kernel the device holds at once (the launch size of k_fused8)
 	uint32_t fusedEpoch{ 0 };     // launch counter: the value a seam flag must show (no clearing between launches)
-	float2* dSeam{ nullptr };     // [3 capacity][2][P] peak-hold states at the seams between CTA ranges
+	float2* dSeam{ nullptr };     // [2 capacity][2][P] peak-hold states at the seams between CTA ranges
 	uint32_t* dSeamFlags{ nullptr }; // [capacity]
 	float2* dSpare{ nullptr };    // [P] sink for results an output mode does not keep (FusedArgs::spare)
 	void* dTrack{ nullptr }; // frequency tracker: [S] bounds in, [S] records out
@@ -1080,7 +1081,7 @@ extern "C"
 		{
 			FusedArgs none{};
 			SGZ_TRY(launchFused(h, none, nullptr)); // capacity query only
-			SGZ_TRY(allocZero(h, size_t(3) * h->fusedCapacity * 2 * t.P, &h->dSeam));
+			SGZ_TRY(allocZero(h, size_t(2) * h->fusedCapacity * 2 * t.P, &h->dSeam));
 			SGZ_TRY(allocZero(h, size_t(h->fusedCapacity), &h->dSeamFlags));
 			SGZ_TRY(allocZero(h, size_t(t.P), &h->dSpare));
 			// carrying the hold across zero-started parts relies on x -> x * pole and on the dB scale being monotone
@@ -1659,18 +1660,32 @@ extern "C"
 		{
 			plan.ctas = uint32_t(std::min<uint64_t>(capacity, items / kFrameParallelMinRun));
 			plan.chained = false;
-			// a stream in two to four parts: the CTAs carry the hold across the seams themselves (they wait on one another: a
-			// chain of that many short hops); longer chains - a few long recordings - and Phase go to the seam kernels
-			a.fixup = (!phase && uint64_t(plan.ctas) <= uint64_t(4) * nS) ? 1u : 0u;
-			plan.cooperative = a.fixup != 0;
 		}
 		a.lastResults = h->dResults; a.spare = h->dSpare;
 		int rc = launchFused(h, a, &plan);
 		if (rc != SGZ_OK) return rc;
-		if (plan.chained || a.fixup) return keepLastFrame(h, a);
+		if (plan.chained) return keepLastFrame(h, a);
+#if defined(SGZ_DIAG_SEAMS) && SGZ_DIAG_SEAMS == 2 // timing experiments: 2 = no carry at all (wrong results), 5 = k_seam_carry only (wrong results)
+		return keepLastFrame(h, a);
+#endif
 		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO form of the hold
 		k_seam_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSeam, h->dStates, F, nS, plan.ctas, stereoFlag, a.firstStream);
-		k_seam_apply<<<dim3((P + 127) / 128, plan.ctas), 128, 0, h->stream>>>(h->dev, a, plan.ctas, stereoFlag);
+#if !defined(SGZ_DIAG_SEAMS) || SGZ_DIAG_SEAMS != 5
+		{
+			// a part is at most ceil(items / ctas) frames; slices of eight or more frames, sixteen at most (k_seam_apply)
+			const uint32_t longest = uint32_t(std::min<uint64_t>(F, (items + plan.ctas - 1) / plan.ctas));
+			const uint32_t slices = std::max<uint32_t>(1, std::min<uint32_t>(16, longest / 8));
+			// (result rows are P float2 apart in every output mode: 16-byte accesses need an even P and a 16-byte aligned base)
+			const bool wide = P % 2 == 0 && (reinterpret_cast<uintptr_t>(a.results) & 15) == 0;
+			const bool full = a.outMode == SGZ_OUT_FULL;
+			const dim3 grid((P / (wide && full ? 2 : 1) + 127) / 128, plan.ctas, slices);
+			auto launch = [&](auto kern) { kern<<<grid, 128, 0, h->stream>>>(h->dev, a, plan.ctas); };
+			if (wide && full && stereoFlag) launch(k_seam_apply<2, true, true>);
+			else if (wide && full) launch(k_seam_apply<2, true, false>);
+			else if (stereoFlag) launch(k_seam_apply<1, false, true>);
+			else launch(k_seam_apply<1, false, false>);
+		}
+#endif
 		if (phase) k_phase_smooth<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, a.results, h->dStates, F, a.firstStream);
 		SGZ_CUDA(cudaGetLastError());
 		return keepLastFrame(h, a);
