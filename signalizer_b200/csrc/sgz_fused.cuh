@@ -19,7 +19,9 @@
 		//     the stream); k_seam_carry / k_seam_apply carry the peak hold across afterwards, bit-identically (and
 		//     k_phase_smooth runs Phase's second state, which is a filter).  (Round 2 also had the CTAs do this themselves at
 		//     the end of the launch: measured no faster than the kernels at any shape, and removed.)
-		uint32_t chained, epoch;
+		//     inlineCarry = 1 (a stream in a few parts): k_seam_apply walks the few parts before its own itself, no
+		//     k_seam_carry; a part that is a whole stream then stores its final state straight to `states`.
+		uint32_t chained, epoch, inlineCarry;
 		float2* states;  // [S][2][P]
 		float2* seam;    // [2 G][2][P]
 		uint32_t* flags; // [G]
@@ -151,6 +153,7 @@
 			if (fEnd == F) out->dst = a.states + uint64_t(stream) * 2 * P;
 			else { out->dst = a.seam + uint64_t(cta) * 2 * P; out->publish = 1; }
 		}
+		else if (a.inlineCarry && fBegin == 0 && fEnd == F) out->dst = a.states + uint64_t(stream) * 2 * P;
 		else out->dst = a.seam + uint64_t(fBegin ? cta : G + cta) * 2 * P;
 	}
 

@@ -33,6 +33,9 @@
 #define SGZ8_SPLIT_SMEM 1
 #endif
 // SGZ8_PAIR_BARRIER 1 = the barrier between passes 2 and 3 covers only the two warps that share a sub-transform
+#ifndef SGZ8_SCAN_ROTATE
+#define SGZ8_SCAN_ROTATE 0 // max-of-bins scan: lanes start their runs at different offsets so that even run lengths do not meet in one bank
+#endif
 #ifndef SGZ8_PAIR_BARRIER
 #define SGZ8_PAIR_BARRIER 0
 #endif
@@ -1016,11 +1019,28 @@
 					float bestL = 0.f, bestR = 0.f;
 					if (first >= linLimit)
 					{
+#if SGZ8_SCAN_ROTATE
+						// the lanes of a warp scan runs that lie `count` bins apart: with an even count, lanes 32 / g apart
+						// (g = the power of two count shares with the 32 banks) meet in one bank at every step.  A maximum does
+						// not care where the scan starts, so those lanes start o bins into their run and wrap around.
+						const int g = min(count & -count, 32), o = ((u & 31) * g) >> 5;
+						for (int c = o; c < count; ++c)
+						{
+							bestL = fmaxf(bestL, csfmag[first + c]);
+							if constexpr (STEREO) bestR = fmaxf(bestR, csfmag[N - first - c]);
+						}
+						for (int c = 0; c < o; ++c)
+						{
+							bestL = fmaxf(bestL, csfmag[first + c]);
+							if constexpr (STEREO) bestR = fmaxf(bestR, csfmag[N - first - c]);
+						}
+#else
 						for (int c = 0; c < count; ++c)
 						{
 							bestL = fmaxf(bestL, csfmag[first + c]);
 							if constexpr (STEREO) bestR = fmaxf(bestR, csfmag[N - first - c]);
 						}
+#endif
 					}
 					else
 					{
@@ -1159,18 +1179,77 @@
 		const float poles[2] = { t.pole0, t.pole1 };
 		const float2* mine = a.seam + uint64_t(c) * 2 * P + x;
 		float2 carry[2][V];
+		auto decay = [&](uint32_t frames)
+		{
+			for (uint32_t f = 0; f < frames; ++f)
+			{
 #pragma unroll
-		for (int k = 0; k < 2; ++k)
+				for (int k = 0; k < 2; ++k)
 #pragma unroll
-			for (int v = 0; v < V; ++v) carry[k][v] = mine[k * P + v];
-		for (uint32_t f = f0; f < fa; ++f)
+					for (int v = 0; v < V; ++v) { carry[k][v].x *= poles[k]; if (STEREO) carry[k][v].y *= poles[k]; }
+			}
+		};
+		auto merge = [&](const float2* own) // a part's final state from zero into the carried one: the true state there
 		{
 #pragma unroll
 			for (int k = 0; k < 2; ++k)
 #pragma unroll
-				for (int v = 0; v < V; ++v) { carry[k][v].x *= poles[k]; if (STEREO) carry[k][v].y *= poles[k]; }
-		}
+				for (int v = 0; v < V; ++v)
+				{
+					const float2 o = own[k * P + v];
+					carry[k][v].x = fmaxf(carry[k][v].x, o.x);
+					if (STEREO) carry[k][v].y = fmaxf(carry[k][v].y, o.y);
+				}
+		};
 		const uint64_t stream = uint64_t(sLocal) + a.firstStream;
+		if (a.inlineCarry)
+		{
+			// k_seam_carry's walk, done here when a stream has few parts: from the final state of the part that began the
+			// stream through the parts between it and this one
+			const uint64_t begin = uint64_t(sLocal) * nFrames;
+			uint32_t ch = uint32_t(begin * G / items);
+			while (ch + 1 < G && seamCut(items, G, ch + 1) <= begin) ++ch;
+			while (ch > 0 && seamCut(items, G, ch) > begin) --ch;
+			const float2* head = a.seam + uint64_t(G + ch) * 2 * P + x;
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+#pragma unroll
+				for (int v = 0; v < V; ++v) carry[k][v] = head[k * P + v];
+			for (uint32_t cc = ch + 1; cc < c; ++cc)
+			{
+				decay(uint32_t(seamCut(items, G, cc + 1) - seamCut(items, G, cc)));
+				merge(a.seam + uint64_t(cc) * 2 * P + x);
+			}
+			if (f1 == nFrames && blockIdx.z == 0)
+			{
+				// this part ends the stream: its true final state is the stream's (.y is only a peak hold in the stereo forms;
+				// otherwise it is left as it was - unused, or the Phase smoother's)
+				float2 keep[2][V];
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+#pragma unroll
+					for (int v = 0; v < V; ++v) keep[k][v] = carry[k][v];
+				decay(f1 - f0);
+				merge(mine);
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+#pragma unroll
+					for (int v = 0; v < V; ++v)
+					{
+						float2* st = a.states + (stream * 2 + k) * P + x + v;
+						if (STEREO) *st = carry[k][v]; else st->x = carry[k][v].x;
+						carry[k][v] = keep[k][v];
+					}
+			}
+		}
+		else
+		{
+#pragma unroll
+			for (int k = 0; k < 2; ++k)
+#pragma unroll
+				for (int v = 0; v < V; ++v) carry[k][v] = mine[k * P + v];
+		}
+		decay(fa - f0);
 		// one frame's two rows against the carry; returns whether the carry can still reach a later frame (seamRaise)
 		auto frame = [&](Word* const row[2], Word res[2]) -> bool
 		{

@@ -1660,6 +1660,13 @@ extern "C"
 		{
 			plan.ctas = uint32_t(std::min<uint64_t>(capacity, items / kFrameParallelMinRun));
 			plan.chained = false;
+			// a stream in at most a handful of parts, and not so long that decaying a state across it costs more than a launch
+			// (not Phase: a part that is a whole stream would store its state itself, and Phase's parts keep the smoother's
+			// input, not its state, in .y - k_seam_carry leaves .y alone)
+			a.inlineCarry = (!phase && uint64_t(plan.ctas) <= uint64_t(4) * nS && F <= 512) ? 1u : 0u;
+#if defined(SGZ_DIAG_SEAMS) && SGZ_DIAG_SEAMS == 1 // timing experiment: always k_seam_carry
+			a.inlineCarry = 0;
+#endif
 		}
 		a.lastResults = h->dResults; a.spare = h->dSpare;
 		int rc = launchFused(h, a, &plan);
@@ -1669,7 +1676,7 @@ extern "C"
 		return keepLastFrame(h, a);
 #endif
 		const int stereoFlag = (!phase && h->cfg.configuration != SGZ_CH_COMPLEX && h->tab.stateChannels == 2) ? 1 : 0; // the STEREO form of the hold
-		k_seam_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSeam, h->dStates, F, nS, plan.ctas, stereoFlag, a.firstStream);
+		if (!a.inlineCarry) k_seam_carry<<<dim3((P + 127) / 128, nS), 128, 0, h->stream>>>(h->dev, h->dSeam, h->dStates, F, nS, plan.ctas, stereoFlag, a.firstStream);
 #if !defined(SGZ_DIAG_SEAMS) || SGZ_DIAG_SEAMS != 5
 		{
 			// a part is at most ceil(items / ctas) frames; slices of eight or more frames, sixteen at most (k_seam_apply)

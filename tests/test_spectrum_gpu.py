@@ -285,6 +285,34 @@ def test_balanced_ranges_chain_the_seams(kw, S):
     compare_frames(whole.cpu().numpy()[sample][..., :last, :used], want[..., :last, :used], cfg, "chained seams vs oracle")
 
 
+@pytest.mark.parametrize("kw,S,F", [(dict(), 150, 14), (dict(axis_points=777), 130, 11), (dict(window_size=4096, configuration=_abi.CH_PHASE), 200, 9),
+                                    (dict(window_size=2048, configuration=_abi.CH_LEFT, bin_polation=_abi.BIN_LINEAR), 97, 23)])
+def test_a_stream_in_two_or_three_parts(kw, S, F):
+    """fewer streams than resident CTAs but not by much (the per-GPU shape of BASELINE config 3 on 4 or 8 GPUs): every
+    stream is cut into two or three parts, k_seam_apply walks the parts before its own itself and whole-stream parts store
+    their state directly.  Two calls in a row (the second starts from the first's states) against frame-by-frame calls,
+    bit for bit."""
+    import torch
+    cfg = _abi.default_config(**kw)
+    hop, W = cfg.window_size // 4, cfg.window_size
+    audio = frames_case(cfg, S, 2 * F, hop)
+    d = torch.from_numpy(np.ascontiguousarray(audio)).cuda()
+    first, second = d[:, :signals.frames_length(W, hop, F)].contiguous(), d[:, F * hop:].contiguous()
+    g = TransformPairBatch(cfg, S)
+    a, b = g.process_frames(first, hop, F), g.process_frames(second, hop, F)
+    g.synchronize()   # (the handle runs on its own stream: nothing may read the results before this)
+    whole = torch.cat([a, b], dim=1)
+    g2 = TransformPairBatch(cfg, S)
+    slices = [d[:, f * hop:f * hop + W].contiguous() for f in range(2 * F)]
+    torch.cuda.synchronize()
+    steps = [g2.process_frames(x, hop, 1) for x in slices]
+    g2.synchronize()
+    np.testing.assert_array_equal(whole.cpu().numpy(), torch.cat(steps, dim=1).cpu().numpy())
+    for k in (0, 1):
+        np.testing.assert_array_equal(g.get_states(k), g2.get_states(k))
+        np.testing.assert_array_equal(g.get_results(k), g2.get_results(k))
+
+
 VIEWS = [dict(view_scaling=_abi.VIEW_LINEAR), dict(view_left=0.2, view_right=0.4), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.0, view_right=0.03),
          dict(view_left=0.6, view_right=1.0, low_dbs=-60.0, high_dbs=6.0), dict(view_scaling=_abi.VIEW_LINEAR, view_left=0.9, view_right=1.0, slope_a=0.5, slope_b=0.02)]
 
