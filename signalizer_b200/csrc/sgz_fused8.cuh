@@ -451,13 +451,20 @@
 	// below the stored scale(s): the scale is monotone, so carry < s, and s_(f+1) >= fl(s pole) >= fl(carry pole) keeps it
 	// so for good; nor once the scaled carry sits on the clip value, the least value the scale has.  (Equal scaled values
 	// do not count: two different states may share one, and part again a frame later.)
-	__device__ __forceinline__ bool seamRaise(float& res, float carried, float sm, const DeviceTables& t, bool& changed)
+	template<bool ASK>
+	__device__ __forceinline__ bool seamRaise(float& res, float carried, float sm, const DeviceTables& t)
 	{
 		const float c = fastLogScale(sm, carried, 1.f, t.deltaYLn2, t.lowerClip);
-		const float r = fmaxf(res, c);
-		const bool live = sm * carried > 0.f && !(c < res);
-		if (r != res) { res = r; changed = true; }
+		const bool live = ASK && sm * carried > 0.f && !(c < res);
+		res = fmaxf(res, c);
 		return live;
+	}
+	// whether a raise changed any bit of a result word (a NaN that stays a NaN is no change)
+	__device__ __forceinline__ bool differs(float2 a, float2 b) { return ((__float_as_uint(a.x) ^ __float_as_uint(b.x)) | (__float_as_uint(a.y) ^ __float_as_uint(b.y))) != 0u; }
+	__device__ __forceinline__ bool differs(float4 a, float4 b)
+	{
+		return ((__float_as_uint(a.x) ^ __float_as_uint(b.x)) | (__float_as_uint(a.y) ^ __float_as_uint(b.y)) | (__float_as_uint(a.z) ^ __float_as_uint(b.z)) |
+			(__float_as_uint(a.w) ^ __float_as_uint(b.w))) != 0u;
 	}
 
 	// ---- Phase configuration (MATRIX == 3): the display works on the complex split spectra themselves ----
@@ -1123,23 +1130,42 @@
 		const float poles[2] = { t.pole0, t.pole1 };
 		const float2* firstSlot = seam + uint64_t(G + c) * 2 * P + x;
 		float2 carry[2] = { firstSlot[0], firstSlot[P] }; // final state of the stream's first part = the true state there
-		for (++c; c < G && seamCut(items, G, c) < end; ++c)
+		// (a long recording is a chain of hundreds of parts: their final states are fetched eight parts at a time, ahead of
+		// the walk, which otherwise is one L2 round trip per part - 200 us for one stream in 296 parts)
+		constexpr int kAheadParts = 8;
+		for (++c; c < G && seamCut(items, G, c) < end; c += kAheadParts)
 		{
-			float2* mine = seam + uint64_t(c) * 2 * P + x;
-			const float2 own[2] = { mine[0], mine[P] };
-			mine[0] = carry[0]; mine[P] = carry[1]; // what this part starts from
-			const uint64_t stop = seamCut(items, G, c + 1);
-			const uint32_t len = uint32_t((stop < end ? stop : end) - seamCut(items, G, c));
-			for (uint32_t f = 0; f < len; ++f)
-			{
+			float2 own[kAheadParts][2];
+			uint64_t cut[kAheadParts + 1]; // (64-bit divisions: once per part)
+			cut[0] = seamCut(items, G, c);
 #pragma unroll
-				for (int k = 0; k < 2; ++k) { carry[k].x *= poles[k]; if (stereo) carry[k].y *= poles[k]; }
+			for (int j = 0; j < kAheadParts; ++j)
+			{
+				cut[j + 1] = c + j < G ? seamCut(items, G, c + j + 1) : end;
+				if (c + j < G && cut[j] < end)
+				{
+					const float2* theirs = seam + uint64_t(c + j) * 2 * P + x;
+					own[j][0] = theirs[0]; own[j][1] = theirs[P];
+				}
 			}
 #pragma unroll
-			for (int k = 0; k < 2; ++k)
+			for (int j = 0; j < kAheadParts; ++j)
 			{
-				carry[k].x = fmaxf(carry[k].x, own[k].x);
-				if (stereo) carry[k].y = fmaxf(carry[k].y, own[k].y);
+				if (!(c + j < G && cut[j] < end)) break;
+				float2* mine = seam + uint64_t(c + j) * 2 * P + x;
+				mine[0] = carry[0]; mine[P] = carry[1]; // what this part starts from
+				const uint32_t len = uint32_t((cut[j + 1] < end ? cut[j + 1] : end) - cut[j]);
+				for (uint32_t f = 0; f < len; ++f)
+				{
+#pragma unroll
+					for (int k = 0; k < 2; ++k) { carry[k].x *= poles[k]; if (stereo) carry[k].y *= poles[k]; }
+				}
+#pragma unroll
+				for (int k = 0; k < 2; ++k)
+				{
+					carry[k].x = fmaxf(carry[k].x, own[j][k].x);
+					if (stereo) carry[k].y = fmaxf(carry[k].y, own[j][k].y);
+				}
 			}
 		}
 		// (.y is only a peak hold in the stereo forms; otherwise it is left as it was - unused, or the Phase smoother's)
@@ -1250,28 +1276,31 @@
 				for (int v = 0; v < V; ++v) carry[k][v] = mine[k * P + v];
 		}
 		decay(fa - f0);
-		// one frame's two rows against the carry; returns whether the carry can still reach a later frame (seamRaise)
-		auto frame = [&](Word* const row[2], Word res[2]) -> bool
+		// one frame's two rows against the carry; with `ask`, returns whether the carry can still reach a later frame
+		// (seamRaise) - only the last frame of a trip asks
+		auto frame = [&](Word* const row[2], Word res[2], auto ask) -> bool
 		{
+			constexpr bool kAsk = decltype(ask)::value;
 			bool live = false;
 #pragma unroll
 			for (int k = 0; k < 2; ++k)
 			{
-				bool changed = false;
+				Word was = res[k];
 				float* val = reinterpret_cast<float*>(&res[k]);
 #pragma unroll
 				for (int v = 0; v < V; ++v)
 				{
 					carry[k][v].x *= poles[k];
 					if (STEREO) carry[k][v].y *= poles[k];
-					if (!row[k]) { live = live || carry[k][v].x > 0.f || (STEREO && carry[k][v].y > 0.f); continue; }
-					live = seamRaise(val[2 * v], carry[k][v].x, sm[v], t, changed) || live;
-					if (STEREO) live = seamRaise(val[2 * v + 1], carry[k][v].y, sm[v], t, changed) || live;
+					if (!row[k]) { if (kAsk) live = live || carry[k][v].x > 0.f || (STEREO && carry[k][v].y > 0.f); continue; }
+					live = seamRaise<kAsk>(val[2 * v], carry[k][v].x, sm[v], t) || live;
+					if (STEREO) live = seamRaise<kAsk>(val[2 * v + 1], carry[k][v].y, sm[v], t) || live;
 				}
-				if (changed) *row[k] = res[k];
+				if (row[k] && differs(was, res[k])) *row[k] = res[k];
 			}
 			return live;
 		};
+		const std::true_type asking; const std::false_type quiet;
 		if constexpr (FULL)
 		{
 			const size_t rowStep = size_t(P) / V; // Words between one graph and the next
@@ -1287,7 +1316,7 @@
 				for (int j = 0; j < 4; ++j)
 				{
 					Word* const row[2] = { at + (2 * j) * rowStep, at + (2 * j + 1) * rowStep };
-					live = frame(row, res[j]);
+					if (j < 3) frame(row, res[j], quiet); else live = frame(row, res[j], asking);
 				}
 				if (!live) return;
 			}
@@ -1295,7 +1324,7 @@
 			{
 				Word* const row[2] = { at, at + rowStep };
 				Word res[2] = { __ldcg(row[0]), __ldcg(row[1]) };
-				if (!frame(row, res)) return;
+				if (!frame(row, res, asking)) return;
 			}
 		}
 		else for (uint32_t f = fa; f < fb; f += 4)
@@ -1315,7 +1344,7 @@
 			for (int j = 0; j < 4; ++j)
 			{
 				if (f + j >= fb) break;
-				live = frame(row[j], res[j]);
+				live = frame(row[j], res[j], asking);
 			}
 			if (!live) break;
 		}
