@@ -87,6 +87,32 @@
 	__device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 	__device__ __forceinline__ void cpAsyncWaitAll() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
+	// mbarrier + bulk copy (SGZ8_BULK_STAGE): one thread asks the copy engine for a contiguous run of this GPU's global
+	// memory into this CTA's shared memory; the bytes complete a transaction on the mbarrier the consumers wait on
+	__device__ __forceinline__ void mbarInit(void* bar, unsigned count)
+	{
+		const unsigned b = static_cast<unsigned>(__cvta_generic_to_shared(bar));
+		asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(b), "r"(count) : "memory");
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__device__ __forceinline__ void bulkStage(void* smemDst, const void* gmemSrc, unsigned bytes, void* bar)
+	{
+		const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smemDst)), b = static_cast<unsigned>(__cvta_generic_to_shared(bar));
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+		asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(b), "r"(bytes) : "memory");
+		asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" :: "r"(d), "l"(gmemSrc), "r"(bytes), "r"(b) : "memory");
+	}
+	__device__ __forceinline__ void mbarWaitParity(void* bar, unsigned parity)
+	{
+		const unsigned b = static_cast<unsigned>(__cvta_generic_to_shared(bar));
+		unsigned done = 0, spins = 0;
+		do
+		{
+			asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(b), "r"(parity) : "memory");
+		} while (!done && ++spins < (1u << 22));
+		if (!done) __trap(); // a copy that never lands must not hang the GPU
+	}
+
 	// seam flags of the chained launch mode (gpu-scope release / acquire)
 	__device__ __forceinline__ uint32_t ldAcquire(const uint32_t* p)
 	{

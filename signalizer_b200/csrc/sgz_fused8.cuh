@@ -33,6 +33,9 @@
 #define SGZ8_SPLIT_SMEM 1
 #endif
 // SGZ8_PAIR_BARRIER 1 = the barrier between passes 2 and 3 covers only the two warps that share a sub-transform
+#ifndef SGZ8_BULK_STAGE
+#define SGZ8_BULK_STAGE 1 // next frame's newest half of the audio: 1 = one cp.async.bulk by thread 0 onto an mbarrier instead of four cp.async per thread
+#endif
 #ifndef SGZ8_SCAN_ROTATE
 #define SGZ8_SCAN_ROTATE 0 // max-of-bins scan: lanes start their runs at different offsets so that even run lengths do not meet in one bank
 #endif
@@ -536,6 +539,11 @@
 		// registers across the frame loop, which has none to spare)
 		FusedPart* part = reinterpret_cast<FusedPart*>(smemRaw + Gm::partOffset(t.P));
 		const int W = int(t.W);
+#if SGZ8_BULK_STAGE
+		uint32_t stagePhase = 0; // parity of the staging mbarrier's current phase (every copy asked for is waited for, so it carries over the parts)
+		if (u == 0) mbarInit(smemRaw + Gm::partOffset(t.P) + 48, 1);
+		// (the barrier at the top of the part loop publishes it)
+#endif
 
 		for (uint32_t q = 0;; ++q)
 		{
@@ -586,7 +594,12 @@
 					for (int n1 = 0; n1 < 4; ++n1) rv[n1] = ldg_stream_f4(src + n1 * T);
 					if (staged)
 					{
+#if SGZ8_BULK_STAGE
+						mbarWaitParity(smemRaw + Gm::partOffset(t.P) + 48, stagePhase);
+						stagePhase ^= 1u;
+#else
 						cpAsyncWaitAll();
+#endif
 #pragma unroll
 						for (int n1 = 4; n1 < 8; ++n1) rv[n1] = stage[(n1 - 4) * T + u];
 					}
@@ -662,10 +675,16 @@
 			staged = false;
 			if (MATRIX != 3 && vec4 && f + 1 < plan->fEnd)
 			{
+#if SGZ8_BULK_STAGE
+				// (the barrier above ordered every generic-proxy access of the lower half before this thread; the fence orders them
+				// before the async-proxy write.  Source and destination are this GPU's / this CTA's own memory, no multicast.)
+				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 48);
+#else
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
 				for (int n1 = 4; n1 < 8; ++n1) cpAsync16(stage + (n1 - 4) * T + u, src + n1 * T);
 				cpAsyncCommit();
+#endif
 				staged = true;
 			}
 #endif
@@ -821,10 +840,16 @@
 			staged = false;
 			if (MATRIX != 3 && vec4 && f + 1 < plan->fEnd)
 			{
+#if SGZ8_BULK_STAGE
+				// (the barrier above ordered every generic-proxy access of the lower half before this thread; the fence orders them
+				// before the async-proxy write.  Source and destination are this GPU's / this CTA's own memory, no multicast.)
+				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 48);
+#else
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
 				for (int n1 = 4; n1 < 8; ++n1) cpAsync16(stage + (n1 - 4) * T + u, src + n1 * T);
 				cpAsyncCommit();
+#endif
 				staged = true;
 			}
 #endif
