@@ -677,7 +677,7 @@
 			{
 #if SGZ8_BULK_STAGE
 				// (the barrier above ordered every generic-proxy access of the lower half before this thread; the fence orders them
-				// before the async-proxy write.  Source and destination are this GPU's / this CTA's own memory, no multicast.)
+				// before the async-proxy write)
 				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 48);
 #else
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
@@ -842,7 +842,7 @@
 			{
 #if SGZ8_BULK_STAGE
 				// (the barrier above ordered every generic-proxy access of the lower half before this thread; the fence orders them
-				// before the async-proxy write.  Source and destination are this GPU's / this CTA's own memory, no multicast.)
+				// before the async-proxy write)
 				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 48);
 #else
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;

@@ -1685,10 +1685,10 @@ extern "C"
 			// (result rows are P float2 apart in every output mode: 16-byte accesses need an even P and a 16-byte aligned base)
 			const bool wide = P % 2 == 0 && (reinterpret_cast<uintptr_t>(a.results) & 15) == 0;
 			const bool full = a.outMode == SGZ_OUT_FULL;
-			const dim3 grid((P / (wide && full ? 2 : 1) + 127) / 128, plan.ctas, slices);
+			const dim3 grid((P / (wide ? 2 : 1) + 127) / 128, plan.ctas, slices);
 			auto launch = [&](auto kern) { kern<<<grid, 128, 0, h->stream>>>(h->dev, a, plan.ctas); };
-			if (wide && full && stereoFlag) launch(k_seam_apply<2, true, true>);
-			else if (wide && full) launch(k_seam_apply<2, true, false>);
+			if (wide && full) { if (stereoFlag) launch(k_seam_apply<2, true, true>); else launch(k_seam_apply<2, true, false>); }
+			else if (wide) { if (stereoFlag) launch(k_seam_apply<2, false, true>); else launch(k_seam_apply<2, false, false>); }
 			else if (stereoFlag) launch(k_seam_apply<1, false, true>);
 			else launch(k_seam_apply<1, false, false>);
 		}
