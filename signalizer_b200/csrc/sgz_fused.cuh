@@ -131,7 +131,9 @@
 		uint32_t nParts, fBegin, fEnd, publish;
 		int stream;
 		uint32_t vec4;        // the frame loop may fetch the stream's audio as 16-byte words
+		float2* row[2];       // where the current frame's two graphs go (resultRow), renewed by thread 0 every frame
 	};
+	static_assert(sizeof(FusedPart) == 64, "the fused kernel's shared-memory layout reserves 64 bytes for the part plan");
 
 	// Part q of CTA blockIdx.x (FusedArgs explains the two launch modes).  Also waits for the neighbour's flag when the
 	// part continues a stream the previous CTA began.  One thread runs it once per part; everything it computes is dead afterwards.

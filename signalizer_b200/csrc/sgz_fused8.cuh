@@ -69,7 +69,7 @@
 		static constexpr size_t stateOffset = twOffset + twBytes;
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
 		__host__ __device__ static size_t partOffset(uint32_t P) { return (mapOffset(P) + size_t(P) * 12 + 15) & ~size_t(15); }
-		static size_t smemBytes(uint32_t P) { return partOffset(P) + 64; } // ... + the part plan (FusedPart)
+		static size_t smemBytes(uint32_t P) { return partOffset(P) + 80; } // ... + the part plan (FusedPart, 64 bytes) + the staging mbarrier
 	};
 	typedef Fused8GeomT<8> Fused8Geom;
 
@@ -541,7 +541,7 @@
 		const int W = int(t.W);
 #if SGZ8_BULK_STAGE
 		uint32_t stagePhase = 0; // parity of the staging mbarrier's current phase (every copy asked for is waited for, so it carries over the parts)
-		if (u == 0) mbarInit(smemRaw + Gm::partOffset(t.P) + 48, 1);
+		if (u == 0) mbarInit(smemRaw + Gm::partOffset(t.P) + 64, 1);
 		// (the barrier at the top of the part loop publishes it)
 #endif
 
@@ -595,7 +595,7 @@
 					if (staged)
 					{
 #if SGZ8_BULK_STAGE
-						mbarWaitParity(smemRaw + Gm::partOffset(t.P) + 48, stagePhase);
+						mbarWaitParity(smemRaw + Gm::partOffset(t.P) + 64, stagePhase);
 						stagePhase ^= 1u;
 #else
 						cpAsyncWaitAll();
@@ -678,7 +678,7 @@
 #if SGZ8_BULK_STAGE
 				// (the barrier above ordered every generic-proxy access of the lower half before this thread; the fence orders them
 				// before the async-proxy write)
-				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 48);
+				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 64);
 #else
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -832,6 +832,10 @@
 					csfmag[j] = (j < linLimit) ? approxSqrt(m2) : m2;
 				}
 			}
+			// where this frame's two graphs go (resultRow: always somewhere, so the stores below are unconditional): sixty
+			// instructions of 64-bit index arithmetic, done by one thread and read by all after the barrier (the previous frame's
+			// readers passed several barriers ago)
+			if (u == 0) { part->row[0] = resultRow(a, uint64_t(plan->stream), f, 0, uint32_t(P)); part->row[1] = resultRow(a, uint64_t(plan->stream), f, 1, uint32_t(P)); }
 			__syncthreads();
 
 #if SGZ8_STAGE_LATE || SGZ8_SPLIT_SMEM
@@ -843,7 +847,7 @@
 #if SGZ8_BULK_STAGE
 				// (the barrier above ordered every generic-proxy access of the lower half before this thread; the fence orders them
 				// before the async-proxy write)
-				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 48);
+				if (u == 0) bulkStage(stage, reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + 4 * T, 4 * T * 16, smemRaw + Gm::partOffset(t.P) + 64);
 #else
 				const float4* src = reinterpret_cast<const float4*>(sbase + 2 * (start + a.hop)) + u;
 #pragma unroll
@@ -854,8 +858,7 @@
 			}
 #endif
 			// ---- display points: one per thread per step ----
-			// where this frame's two graphs go (resultRow: always somewhere, so the stores below are unconditional)
-			float2* const resRow[2] = { resultRow(a, uint64_t(plan->stream), f, 0, uint32_t(P)), resultRow(a, uint64_t(plan->stream), f, 1, uint32_t(P)) };
+			float2* const resRow[2] = { plan->row[0], plan->row[1] };
 			const float poles[2] = { t.pole0, t.pole1 };
 			const int safeFrom = int(t.safeFrom);
 			const float magScale = STEREO ? 0.5f * t.invSize : t.invSize; // the stereo split stores 2 |.|
