@@ -155,16 +155,29 @@
 					const long long tile0 = (long long)hi - kTcSpan; // block-relative; below lo (even negative) for the block's last, short tile
 					const bool whole = tile0 >= (long long)lo;
 					float2 raw[4][4];
+					// (a whole tile of an interleaved, 16-byte aligned stream: a thread's four consecutive samples are two 16-byte words)
+					const bool wide = whole && a.layout == SGZ_LAYOUT_INTERLEAVED && (reinterpret_cast<uintptr_t>(base) & 15) == 0 &&
+						((a.first + uint64_t(tile0)) & 1) == 0;
 #pragma unroll
 					for (int i = 0; i < 4; ++i)
 					{
 						const uint32_t task = fw + kTcFillWarps * i, rg = task & 7, kg = (task >> 3) * 4 + kq;
 						const long long n0 = tile0 + (long long)((rg * 8 + r) * kTcL + kg * 4);
-#pragma unroll
-						for (int e = 0; e < 4; ++e)
+						if (wide)
 						{
-							raw[i][e] = make_float2(0.f, 0.f);
-							if (whole || n0 + e >= (long long)lo) fetchLR(base, a.layout, a.nSamples, a.first + uint64_t(n0 + e), raw[i][e].x, raw[i][e].y);
+							const float4* p = reinterpret_cast<const float4*>(base + 2 * (a.first + uint64_t(n0)));
+							const float4 v0 = __ldg(p), v1 = __ldg(p + 1);
+							raw[i][0] = make_float2(v0.x, v0.y); raw[i][1] = make_float2(v0.z, v0.w);
+							raw[i][2] = make_float2(v1.x, v1.y); raw[i][3] = make_float2(v1.z, v1.w);
+						}
+						else
+						{
+#pragma unroll
+							for (int e = 0; e < 4; ++e)
+							{
+								raw[i][e] = make_float2(0.f, 0.f);
+								if (whole || n0 + e >= (long long)lo) fetchLR(base, a.layout, a.nSamples, a.first + uint64_t(n0 + e), raw[i][e].x, raw[i][e].y);
+							}
 						}
 					}
 					mbarWait(bEmpty + st, ((m >> 1) & 1u) ^ 1u); // the MMAs that read this stage two tiles ago are done
