@@ -86,6 +86,16 @@
 		r.rt = uint32_t(it / (uint64_t(tiles) * ch * nStreams));
 		return r;
 	}
+	// the item after q (the 64-bit divisions of tcItem once per segment, not once per tile)
+	__device__ __forceinline__ void tcNext(TcItem& q, uint32_t tiles, uint32_t ch, uint32_t nStreams)
+	{
+		if (++q.tt < tiles) return;
+		q.tt = 0;
+		if (++q.c < ch) return;
+		q.c = 0;
+		if (++q.s < nStreams) return;
+		q.s = 0; ++q.rt;
+	}
 
 	// Warp roles (13 warps): 0-3 chain (they own the four TMEM lane quarters), 4-11 fill, 12 issues the MMAs.  Two stages of
 	// the B operand and of the accumulators are in flight, handed over through mbarriers:
@@ -146,9 +156,9 @@
 				// samples are requested before the first is used ----
 				const uint32_t fw = warp - kTcChainWarps, r = lane & 7, kq = lane >> 3;
 				uint32_t m = n;
-				for (uint64_t it = seg0; it < seg1; ++it, ++m)
+				TcItem q = tcItem(seg0, a.tiles, ch, a.nStreams);
+				for (uint64_t it = seg0; it < seg1; ++it, ++m, tcNext(q, a.tiles, ch, a.nStreams))
 				{
-					const TcItem q = tcItem(it, a.tiles, ch, a.nStreams);
 					const uint32_t st = m & 1u;
 					const float* base = a.audio + uint64_t(q.s) * a.streamStride;
 					const uint64_t lo = uint64_t(q.tt) * kTcSpan, hi = min(lo + uint64_t(kTcSpan), uint64_t(a.count));
@@ -250,9 +260,9 @@
 				const float2 pL = a.powL[g];
 				const uint32_t laneBase = tmem + ((warp * 32u) << 16);
 				uint32_t m = n;
-				for (uint64_t it = seg0; it < seg1; ++it, ++m)
+				TcItem q = tcItem(seg0, a.tiles, ch, a.nStreams);
+				for (uint64_t it = seg0; it < seg1; ++it, ++m, tcNext(q, a.tiles, ch, a.nStreams))
 				{
-					const TcItem q = tcItem(it, a.tiles, ch, a.nStreams);
 					const uint32_t st = m & 1u;
 					mbarWait(tFull + st, (m >> 1) & 1u);
 					asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
