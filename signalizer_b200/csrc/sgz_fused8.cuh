@@ -33,6 +33,9 @@
 #define SGZ8_SPLIT_SMEM 1
 #endif
 // SGZ8_PAIR_BARRIER 1 = the barrier between passes 2 and 3 covers only the two warps that share a sub-transform
+#ifndef SGZ8_TW_BROADCAST
+#define SGZ8_TW_BROADCAST 0 // twiddle powers derived as broadcast pairs with packed arithmetic (no scalar products, no pairing moves)
+#endif
 #ifndef SGZ8_BULK_STAGE
 #define SGZ8_BULK_STAGE 1 // next frame's newest half of the audio: 1 = one cp.async.bulk by thread 0 onto an mbarrier instead of four cp.async per thread
 #endif
@@ -110,6 +113,51 @@
 	// shared-memory pipe, not by FP issue, and this trades 7 LDS.64 for 6 complex products.
 	__device__ __forceinline__ void applyTwiddlePowers(float2 w1, float2 (&re)[8], float2 (&im)[8])
 	{
+#if SGZ8_TW_BROADCAST
+		// the powers are derived as (x, x), (y, y) pairs, the form the packed multiply wants: five packed operations per
+		// product instead of four scalar ones and the moves that pair their results up
+		const float2 X1 = bc2(w1.x), Y1 = bc2(w1.y);
+		auto product = [](float2 Xa, float2 Ya, float2 Xb, float2 Yb, float2& X, float2& Y)
+		{
+			X = sub2(mul2(Xa, Xb), mul2(Ya, Yb));
+			Y = fma2(Xa, Yb, mul2(Ya, Xb));
+		};
+		auto apply = [&](int k, float2 X, float2 Y)
+		{
+			float2& r = re[perm8(k)]; float2& i = im[perm8(k)];
+			const float2 nr = sub2(mul2(r, X), mul2(i, Y));
+			const float2 ni = fma2(r, Y, mul2(i, X));
+			r = nr; i = ni;
+		};
+#if SGZ8_TW_BROADCAST == 2
+		// one running power (w_k = w_(k-1) w1): four registers fewer than the tree below, three products deeper
+		float2 Xk = X1, Yk = Y1;
+		apply(1, X1, Y1);
+#pragma unroll
+		for (int k = 2; k < 8; ++k)
+		{
+			float2 Xn, Yn;
+			product(Xk, Yk, X1, Y1, Xn, Yn);
+			Xk = Xn; Yk = Yn;
+			apply(k, Xk, Yk);
+		}
+		return;
+#endif
+		float2 X2, Y2, X3, Y3, X4, Y4, Xn, Yn;
+		product(X1, Y1, X1, Y1, X2, Y2);
+		apply(1, X1, Y1);
+		apply(2, X2, Y2);
+		product(X2, Y2, X1, Y1, X3, Y3);
+		apply(3, X3, Y3);
+		product(X2, Y2, X2, Y2, X4, Y4);
+		apply(4, X4, Y4);
+		product(X4, Y4, X1, Y1, Xn, Yn);
+		apply(5, Xn, Yn);
+		product(X3, Y3, X3, Y3, Xn, Yn);
+		apply(6, Xn, Yn);
+		product(X4, Y4, X3, Y3, Xn, Yn);
+		apply(7, Xn, Yn);
+#else
 		const float2 w2 = cmul(w1, w1);
 		mulTwiddleP(re[perm8(1)], im[perm8(1)], make_float4(w1.x, w1.x, w1.y, w1.y));
 		mulTwiddleP(re[perm8(2)], im[perm8(2)], make_float4(w2.x, w2.x, w2.y, w2.y));
@@ -123,6 +171,7 @@
 		mulTwiddleP(re[perm8(6)], im[perm8(6)], make_float4(w6.x, w6.x, w6.y, w6.y));
 		const float2 w7 = cmul(w4, w3);
 		mulTwiddleP(re[perm8(7)], im[perm8(7)], make_float4(w7.x, w7.x, w7.y, w7.y));
+#endif
 	}
 
 	// Which bins a thread owns after the last pass: t + T k4.  The two-for-one split pairs bin j with bin N - j, i.e. thread
