@@ -23,6 +23,11 @@
 	// its tiles; it is built on the host in double precision, already in the shared-memory order of the UMMA
 	// "K-major, no swizzle" canonical layout: 8-row x 16-byte core matrices, [k / 4][row / 8][row % 8][k % 4].
 	// ------------------------------------------------------------------------------------------
+#ifndef SGZ_TC_A_TMEM
+#define SGZ_TC_A_TMEM 0 // 1 = the pole-power operand lives in tensor memory (columns 256..511) instead of shared memory, so that an MMA reads 2 KB of
+                        // shared memory, not 6.  Measured (B200): same results, same time (0.120 vs 0.117 ms on BASELINE config 2) - the 125 cycles a
+                        // 128x64x8 TF32 MMA takes here are not operand fetch
+#endif
 	constexpr int kTcL = 64;                          // samples per slice = GEMM K
 	constexpr int kTcSlices = 64;                     // slices per tile   = GEMM N
 	constexpr int kTcRows = 128;                      // filter rows per CTA = GEMM M = TMEM lanes
@@ -33,6 +38,7 @@
 	constexpr uint32_t kTcSbo = 128;                  // bytes between core matrices along M / N
 	constexpr uint32_t kTcLboA = (kTcRows / 8) * 128; // bytes between core matrices along K, A operand
 	constexpr uint32_t kTcLboB = (kTcSlices / 8) * 128; // ... B operand
+	constexpr uint32_t kTcTmemColumns = SGZ_TC_A_TMEM ? 512 : 256; // accumulators: 2 stages x (re, im) x 64; then A: (re, im) x (head, tail) x 64
 	constexpr int kTcChainWarps = 4, kTcFillWarps = 8;
 	constexpr int kTcThreads = 32 * (kTcChainWarps + kTcFillWarps + 1);
 	constexpr size_t kTcSmemBytes = size_t(4) * kTcAFloats * 4 + size_t(kTcStages) * 2 * kTcBFloats * 4 + 128; // A: re/im x head/tail; B: stages x head/tail; barriers, TMEM address
@@ -118,7 +124,7 @@
 
 		if (warp == 0)
 		{
-			asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(smemAddr(tmemSlot)) : "memory");
+			asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smemAddr(tmemSlot)), "r"(kTcTmemColumns) : "memory");
 			asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 		}
 		if (tid == 0)
@@ -143,6 +149,34 @@
 			// ---- a segment: the CTA's items of one row tile; its A operand is loaded by everybody, then the roles part ----
 			const uint32_t rt = uint32_t(seg0 / perRowTile);
 			const uint64_t seg1 = min(i1, uint64_t(rt + 1) * perRowTile);
+#if SGZ_TC_A_TMEM
+			if (warp < kTcChainWarps)
+			{
+				// thread = TMEM lane = filter row: its 64 pole powers of each of the four matrices go to columns 256 + 64 mi + k.
+				// The host tiles are in the shared-memory operand order [k / 4][row / 8][row % 8][k % 4]: for a given k / 4 the
+				// rows are consecutive 16-byte words, so a warp's loads are contiguous.
+				const float4* src = reinterpret_cast<const float4*>(a.aTiles + size_t(rt) * 4 * kTcAFloats);
+				const uint32_t laneBase = tmem + ((warp * 32u) << 16);
+				for (int mi = 0; mi < 4; ++mi)
+#pragma unroll 1
+					for (int kc = 0; kc < 4; ++kc)
+					{
+						float4 v[4];
+#pragma unroll
+						for (int j = 0; j < 4; ++j) v[j] = __ldg(src + size_t(mi) * (kTcAFloats / 4) + size_t(kc * 4 + j) * kTcRows + tid);
+						asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+							:: "r"(laneBase + 256u + uint32_t(mi) * 64u + uint32_t(kc) * 16u),
+							   "r"(__float_as_uint(v[0].x)), "r"(__float_as_uint(v[0].y)), "r"(__float_as_uint(v[0].z)), "r"(__float_as_uint(v[0].w)),
+							   "r"(__float_as_uint(v[1].x)), "r"(__float_as_uint(v[1].y)), "r"(__float_as_uint(v[1].z)), "r"(__float_as_uint(v[1].w)),
+							   "r"(__float_as_uint(v[2].x)), "r"(__float_as_uint(v[2].y)), "r"(__float_as_uint(v[2].z)), "r"(__float_as_uint(v[2].w)),
+							   "r"(__float_as_uint(v[3].x)), "r"(__float_as_uint(v[3].y)), "r"(__float_as_uint(v[3].z)), "r"(__float_as_uint(v[3].w)) : "memory");
+					}
+				asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+				asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+			}
+			__syncthreads();
+			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#else
 			{
 				const float4* src = reinterpret_cast<const float4*>(a.aTiles + size_t(rt) * 4 * kTcAFloats);
 				float4* dst = reinterpret_cast<float4*>(aMat);
@@ -150,6 +184,7 @@
 				asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 			}
 			__syncthreads();
+#endif
 			if (warp >= kTcChainWarps && warp < kTcChainWarps + kTcFillWarps)
 			{
 				// ---- fill: operand row = slice n = 8 rg + r, k = 4 kg + e; a warp task is one rg x four kg; a thread's 16
@@ -227,23 +262,37 @@
 					asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 					if (lane == 0)
 					{
-						const uint32_t aBase = smemAddr(aMat), bH = smemAddr(bMat + size_t(st) * 2 * kTcBFloats), bT = bH + kTcBFloats * 4;
+						[[maybe_unused]] const uint32_t aBase = smemAddr(aMat);
+						const uint32_t bH = smemAddr(bMat + size_t(st) * 2 * kTcBFloats), bT = bH + kTcBFloats * 4;
 #pragma unroll
 						for (int comp = 0; comp < 2; ++comp)
 						{
 							const uint32_t d = tmem + st * (2 * kTcSlices) + uint32_t(comp) * kTcSlices;
+#if !SGZ_TC_A_TMEM
 							const uint32_t aH = aBase + uint32_t(2 * comp) * kTcAFloats * 4, aT = aH + kTcAFloats * 4;
+#endif
 #pragma unroll
 							for (int term = 0; term < 3; ++term)
 							{
-								const uint32_t aAddr = term == 2 ? aT : aH, bAddr = term == 1 ? bT : bH;
+								const uint32_t bAddr = term == 1 ? bT : bH;
+#if !SGZ_TC_A_TMEM
+								const uint32_t aAddr = term == 2 ? aT : aH;
+#endif
 #pragma unroll
 								for (int ks = 0; ks < kTcL / 8; ++ks)
 								{
-									const uint64_t da = tcDesc(aAddr + uint32_t(ks) * 2 * kTcLboA, kTcLboA), db = tcDesc(bAddr + uint32_t(ks) * 2 * kTcLboB, kTcLboB);
+									const uint64_t db = tcDesc(bAddr + uint32_t(ks) * 2 * kTcLboB, kTcLboB);
 									const uint32_t accumulate = (term | ks) ? 1u : 0u;
+#if SGZ_TC_A_TMEM
+									// A from tensor memory: matrix 2 comp (+ 1 for the tail), eight columns per K step
+									const uint32_t ta = tmem + 256u + uint32_t(2 * comp + (term == 2 ? 1 : 0)) * 64u + uint32_t(ks) * 8u;
+									asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+										:: "r"(d), "r"(ta), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+#else
+									const uint64_t da = tcDesc(aAddr + uint32_t(ks) * 2 * kTcLboA, kTcLboA);
 									asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
 										:: "r"(d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+#endif
 								}
 							}
 						}
@@ -304,5 +353,5 @@
 		}
 		asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 		__syncthreads();
-		if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem) : "memory");
+		if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(kTcTmemColumns) : "memory");
 	}
