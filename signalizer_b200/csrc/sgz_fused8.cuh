@@ -36,6 +36,13 @@
 #ifndef SGZ8_TW_BROADCAST
 #define SGZ8_TW_BROADCAST 0 // twiddle powers derived as broadcast pairs with packed arithmetic (no scalar products, no pairing moves)
 #endif
+// SGZ8_PHASE_CLOCK (diagnostic build only): thread 0 of CTA 0 adds up the SM clock between the phase boundaries of its
+// frames and prints the sums when the kernel ends - where a CTA's frame time goes (tools/ab_libs.sh build pc "-DSGZ8_PHASE_CLOCK")
+#ifdef SGZ8_PHASE_CLOCK
+#define SGZ8_TICK(i) phaseTick(i)
+#else
+#define SGZ8_TICK(i)
+#endif
 #ifndef SGZ8_BULK_STAGE
 #define SGZ8_BULK_STAGE 1 // next frame's newest half of the audio: 1 = one cp.async.bulk by thread 0 onto an mbarrier instead of four cp.async per thread
 #endif
@@ -98,6 +105,20 @@
 		}
 	}
 
+#ifdef SGZ8_CTA_CLOCK
+	__device__ __forceinline__ unsigned long long& ctaClock0() { __shared__ unsigned long long b; return b; }
+#endif
+#ifdef SGZ8_PHASE_CLOCK
+	__device__ __forceinline__ long long* phaseClockBuffer() { __shared__ long long b[18]; return b; } // [0..15] sums, [16] last clock, [17] frames
+	__device__ __forceinline__ void phaseTick(int i)
+	{
+		if (threadIdx.x != 0 || blockIdx.x != 0) return;
+		long long* b = phaseClockBuffer();
+		const long long c = clock64();
+		if (i >= 0) b[i] += c - b[16];
+		b[16] = c;
+	}
+#endif
 	// exchange element (k1, d2, d3, d4) of the 512-point sub-transform k1.  The XOR keeps every pass free of bank
 	// conflicts on 128-bit words: the lanes of a quarter warp differ in d4 (passes 1-3) or, in pass 4, in k1 and - when
 	// k1 has fewer than three bits (K1 = 4, 2) - in the low bit(s) of d2 as well
@@ -337,6 +358,7 @@
 			__syncthreads();
 		}
 
+		SGZ8_TICK(1); // pass 1 written, barrier passed
 		// ---- pass 2 (in place): thread (k1 n3 n4), DFT8 over n2, twiddle W_512^(v k2) ----
 		{
 			const int k1 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7, v = u & 63;
@@ -377,6 +399,7 @@
 		__syncthreads();
 #endif
 
+		SGZ8_TICK(2); // pass 2 + barrier
 		// ---- pass 3 (in place): thread (k1 k2 n4), DFT8 over n3, twiddle W_64^(n4 k3) ----
 		{
 			const int k1 = u >> 6, k2 = (u >> 3) & 7, n4 = u & 7;
@@ -411,6 +434,7 @@
 		}
 		__syncthreads();
 
+		SGZ8_TICK(3); // pass 3 + barrier
 		// ---- pass 4: thread t = k1 + K1 k2 + 8 K1 k3, DFT8 over n4; owns bins k = t + T k4 ----
 #if SGZ8_SPLIT_SMEM
 		const float2 wt = wu;
@@ -608,6 +632,24 @@
 		if (u == 0) planFusedPart(a, q, t.P, W == N, part);
 #endif
 		__syncthreads();
+#ifdef SGZ8_CTA_CLOCK // diagnostic build only: when each CTA of the launch began and ended (globaltimer, ns) and on which SM
+		if (q == 0 && u == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ctaClock0() = g; }
+		if (q >= part->nParts && u == 0)
+		{
+			unsigned long long g; unsigned smid;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+			asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+			printf("cta %u sm %u begin %llu end %llu\n", blockIdx.x, smid, ctaClock0(), g);
+		}
+#endif
+#ifdef SGZ8_PHASE_CLOCK
+		if (q >= part->nParts && u == 0 && blockIdx.x == 0)
+		{
+			const long long* b = phaseClockBuffer();
+			printf("phase clocks over %lld frames (cycles per frame): load+window %lld | pass1+exchange %lld | pass2 %lld | pass3 %lld | pass4+radix2 %lld | split+magnitudes %lld | rows+barrier+stage %lld | display %lld\n",
+				b[17], b[0] / b[17], b[1] / b[17], b[2] / b[17], b[3] / b[17], b[4] / b[17], b[5] / b[17], b[6] / b[17], b[7] / b[17]);
+		}
+#endif
 		if (q >= part->nParts) break;
 		// (the frame loop reads the plan from shared memory where it needs it, like the kernel arguments from constant memory:
 		// its registers are all spoken for)
@@ -621,6 +663,10 @@
 
 		bool staged = false;
 
+#ifdef SGZ8_PHASE_CLOCK
+		if (u == 0 && blockIdx.x == 0 && q == 0) { for (int i = 0; i < 18; ++i) phaseClockBuffer()[i] = 0; }
+		SGZ8_TICK(-1);
+#endif
 		for (uint32_t f = plan->fBegin; f < plan->fEnd; ++f)
 		{
 			float2 re[8], im[8];
@@ -715,8 +761,10 @@
 					}
 				}
 			}
+			SGZ8_TICK(0); // audio + window loaded, multiplied
 			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u, tb, t.tw3);
 			__syncthreads(); // every pass-4 read of xbuf is done before csfmag and the staged audio overwrite it
+			SGZ8_TICK(4); // pass 4, last radix-2, barrier
 
 #if !SGZ8_STAGE_LATE && !SGZ8_SPLIT_SMEM
 			// newest half of the next frame -> lower half of the exchange buffer, in flight behind the split and the display
@@ -884,6 +932,7 @@
 			// where this frame's two graphs go (resultRow: always somewhere, so the stores below are unconditional): sixty
 			// instructions of 64-bit index arithmetic, done by one thread and read by all after the barrier (the previous frame's
 			// readers passed several barriers ago)
+			SGZ8_TICK(5); // split exchange + magnitudes written
 			if (u == 0) { part->row[0] = resultRow(a, uint64_t(plan->stream), f, 0, uint32_t(P)); part->row[1] = resultRow(a, uint64_t(plan->stream), f, 1, uint32_t(P)); }
 			__syncthreads();
 
@@ -907,6 +956,7 @@
 			}
 #endif
 			// ---- display points: one per thread per step ----
+			SGZ8_TICK(6); // barrier before the display, staging issued
 			float2* const resRow[2] = { plan->row[0], plan->row[1] };
 			const float poles[2] = { t.pole0, t.pole1 };
 			const int safeFrom = int(t.safeFrom);
@@ -1164,6 +1214,10 @@
 					stg_stream_f2(resRow[k] + x, res);
 				}
 			}
+			SGZ8_TICK(7); // this thread's display points
+#ifdef SGZ8_PHASE_CLOCK
+			if (u == 0 && blockIdx.x == 0) phaseClockBuffer()[17] += 1;
+#endif
 		}
 		__syncthreads(); // every display point of the part's last frame has updated its state
 		{

@@ -800,6 +800,9 @@ namespace
 			SGZ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, threads, smem));
 			SGZ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
 			h->fusedCapacity = uint32_t(std::max(1, perSm) * std::max(1, sms));
+#ifdef SGZ_DIAG_CAPACITY_DIV // timing experiments: fewer CTAs than the GPU holds (2: one per SM for the 8192-point kernel)
+			h->fusedCapacity = std::max<uint32_t>(1, h->fusedCapacity / SGZ_DIAG_CAPACITY_DIV);
+#endif
 			return SGZ_OK;
 		}
 		a.chained = plan->chained ? 1u : 0u;
