@@ -554,7 +554,10 @@
 	__device__ __forceinline__ float mag2(float2 v) { return sqrtf(v.x * v.x + v.y * v.y); }
 
 	template<int K1, bool STEREO, int BINPOL, int MATRIX>
-	__global__ void __launch_bounds__(64 * K1, K1 == 16 ? 1 : K1 == 8 ? 2 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
+#ifndef SGZ8_MINB8
+#define SGZ8_MINB8 2 // resident CTAs per SM the 8192-point kernel is compiled for (1: twice the registers per thread, experiment)
+#endif
+	__global__ void __launch_bounds__(64 * K1, K1 == 16 ? 1 : K1 == 8 ? SGZ8_MINB8 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
 	k_fused8(DeviceTables t, FusedArgs a)
 	{
 		typedef Fused8GeomT<K1> Gm;
