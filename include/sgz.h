@@ -142,7 +142,7 @@ int  sgz_spectrum_get_info(const sgz_spectrum* h, sgz_spectrum_info* out);
 const char* sgz_last_error(void);
 
 /* The fused kernel sgz_spectrum_process_frames launches for this handle, as a
- * profiler prints it ("sgz::k_fused8<8, 1, 2, 0>"; "" when the configuration
+ * profiler prints it ("sgz::k_fused8<8, 1, 2, 0, 0>"; "" when the configuration
  * runs the staged kernels).  No reference counterpart: measurement only. */
 const char* sgz_spectrum_kernel_name(const sgz_spectrum* h);
 /* All work of a handle is enqueued on one CUDA stream (default: a stream the

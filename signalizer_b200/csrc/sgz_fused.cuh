@@ -137,9 +137,9 @@
 
 	// Part q of CTA blockIdx.x (FusedArgs explains the two launch modes).  Also waits for the neighbour's flag when the
 	// part continues a stream the previous CTA began.  One thread runs it once per part; everything it computes is dead afterwards.
-	__device__ __forceinline__ void planFusedPart(const FusedArgs& a, uint32_t q, uint32_t P, bool wholeWindow, FusedPart* out)
+	__device__ __forceinline__ void planFusedPart(const FusedArgs& a, uint32_t q, uint32_t P, bool wholeWindow, FusedPart* out, uint32_t cta, uint32_t G)
 	{
-		const uint32_t F = a.nFrames, G = gridDim.x, cta = blockIdx.x;
+		const uint32_t F = a.nFrames;
 		const uint64_t items = uint64_t(a.numStreams) * F;
 		const uint64_t i0 = items * cta / G, i1 = items * (cta + 1) / G;
 		if (i1 == i0) { out->nParts = 0; return; } // (the host never launches more CTAs than items)

@@ -43,6 +43,12 @@
 #else
 #define SGZ8_TICK(i)
 #endif
+#ifndef SGZ8_DUAL
+#define SGZ8_DUAL 0 // the headline shape runs two ranges per 1024-thread CTA (k_fused8<..., DUAL = true>)
+#endif
+#ifndef SGZ8_DUAL_TURNS
+#define SGZ8_DUAL_TURNS 0 // ... and the two halves take turns at the exchange-heavy part of a frame
+#endif
 #ifndef SGZ8_BULK_STAGE
 #define SGZ8_BULK_STAGE 1 // next frame's newest half of the audio: 1 = one cp.async.bulk by thread 0 onto an mbarrier instead of four cp.async per thread
 #endif
@@ -79,7 +85,7 @@
 		static constexpr size_t stateOffset = twOffset + twBytes;
 		__host__ __device__ static size_t mapOffset(uint32_t P) { return stateOffset + size_t(P) * 16; }
 		__host__ __device__ static size_t partOffset(uint32_t P) { return (mapOffset(P) + size_t(P) * 12 + 15) & ~size_t(15); }
-		static size_t smemBytes(uint32_t P) { return partOffset(P) + 80; } // ... + the part plan (FusedPart, 64 bytes) + the staging mbarrier
+		__host__ __device__ static size_t smemBytes(uint32_t P) { return partOffset(P) + 80; } // ... + the part plan (FusedPart, 64 bytes) + the staging mbarrier
 	};
 	typedef Fused8GeomT<8> Fused8Geom;
 
@@ -210,6 +216,13 @@
 		return (u & 16) ? (i == 0 ? T / 2 : T - i) : i;
 	}
 
+	// block-wide barrier, or (bar > 0) the named barrier of one 512-thread half of a DUAL CTA
+	__device__ __forceinline__ void ctaSync(int bar)
+	{
+		if (bar == 0) __syncthreads();
+		else asm volatile("bar.sync %0, 512;" :: "r"(bar) : "memory");
+	}
+
 	// The FFT of one frame once its 8 windowed (E, O) pairs per thread sit in registers: first pass in registers,
 	// three in-place radix-8 passes through the exchange buffer, the last radix-2 that joins the even and odd halves.
 	// On return re[perm8(k4)] = (Z[k].re, Z[k + M].re), im[...] likewise, for the bins k = t + T k4 (t = pairedBin(u); `wt`
@@ -217,7 +230,7 @@
 	// block-wide barriers of the exchanges; the first one also orders whatever the caller still had in xbuf before it.
 	template<int K1>
 	__device__ __forceinline__ void fusedFftCore(float2 (&re)[8], float2 (&im)[8], float4* xbuf, const float2* twA, const float2* twB, const float2* twC,
-		float2 wu, int u, int t, const float2* __restrict__ twN)
+		float2 wu, int u, int t, const float2* __restrict__ twN, int bar = 0, int turn = 0)
 	{
 		constexpr int T = Fused8GeomT<K1>::T;
 
@@ -272,7 +285,9 @@
 					}
 				}
 			}
-			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+			// (DUAL with turns: the other half of the CTA is through the exchange-heavy part of its frame)
+			if (turn) asm volatile("bar.sync %0, 1024;" :: "r"(turn) : "memory");
+			ctaSync(bar); // previous frame's csfmag and the staged audio are no longer needed
 			if constexpr (K1 == 8)
 			{
 				const int n2 = u >> 6, n3 = (u >> 3) & 7, n4 = u & 7;
@@ -298,7 +313,7 @@
 					}
 				}
 			}
-			__syncthreads();
+			ctaSync(bar);
 		}
 		else
 		{
@@ -317,14 +332,14 @@
 					mulTwiddleP(re[perm8(k)], im[perm8(k)], make_float4(w.x, w.x, w.y, w.y));
 				}
 			}
-			__syncthreads(); // previous frame's csfmag and the staged audio are no longer needed
+			ctaSync(bar); // previous frame's csfmag and the staged audio are no longer needed
 #pragma unroll
 			for (int k = 0; k < 8; ++k)
 			{
 				const float2 r = re[perm8(k)], i = im[perm8(k)];
 				xbuf[k * T + u] = make_float4(r.x, r.y, i.x, i.y);
 			}
-			__syncthreads();
+			ctaSync(bar);
 #pragma unroll
 			for (int k = 0; k < 8; ++k)
 			{
@@ -345,7 +360,7 @@
 				for (int k = 0; k < 8; ++k) mulTwiddleP(re[k], im[k], make_float4(w8.x, w8.x, w8.y, w8.y));
 			}
 			applyTwiddlePowers(w1, re, im);
-			__syncthreads(); // every partner read is done before the buffer is rewritten
+			ctaSync(bar); // every partner read is done before the buffer is rewritten
 			{
 				const int n2 = v >> 6, n3 = (v >> 3) & 7, n4 = v & 7;
 #pragma unroll
@@ -355,7 +370,7 @@
 					xbuf[phys8<K1>(8 * h + k, n2, n3, n4)] = make_float4(r.x, r.y, i.x, i.y);
 				}
 			}
-			__syncthreads();
+			ctaSync(bar);
 		}
 
 		SGZ8_TICK(1); // pass 1 written, barrier passed
@@ -394,9 +409,9 @@
 #if SGZ8_PAIR_BARRIER
 		// passes 2 and 3 stay inside the 512-point sub-transform k1 = u >> 6, i.e. inside one pair of warps: only they wait
 		if constexpr (K1 <= 8) asm volatile("bar.sync %0, 64;" :: "r"(1 + (u >> 6)) : "memory");
-		else __syncthreads();
+		else ctaSync(bar);
 #else
-		__syncthreads();
+		ctaSync(bar);
 #endif
 
 		SGZ8_TICK(2); // pass 2 + barrier
@@ -432,7 +447,7 @@
 			}
 #endif
 		}
-		__syncthreads();
+		ctaSync(bar);
 
 		SGZ8_TICK(3); // pass 3 + barrier
 		// ---- pass 4: thread t = k1 + K1 k2 + 8 K1 k3, DFT8 over n4; owns bins k = t + T k4 ----
@@ -553,16 +568,22 @@
 	__device__ __forceinline__ float2 phaseEntry(const float2* csf, int i, int N) { return (i >= 0 && i <= N) ? csf[i] : make_float2(0.f, 0.f); }
 	__device__ __forceinline__ float mag2(float2 v) { return sqrtf(v.x * v.x + v.y * v.y); }
 
-	template<int K1, bool STEREO, int BINPOL, int MATRIX>
+	template<int K1, bool STEREO, int BINPOL, int MATRIX, bool DUAL = false>
 #ifndef SGZ8_MINB8
 #define SGZ8_MINB8 2 // resident CTAs per SM the 8192-point kernel is compiled for (1: twice the registers per thread, experiment)
 #endif
-	__global__ void __launch_bounds__(64 * K1, K1 == 16 ? 1 : K1 == 8 ? SGZ8_MINB8 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
+	__global__ void __launch_bounds__(DUAL ? 128 * K1 : 64 * K1, DUAL ? 1 : K1 == 16 ? 1 : K1 == 8 ? SGZ8_MINB8 : K1 == 4 ? 3 : K1 == 2 ? 4 : 5)
 	k_fused8(DeviceTables t, FusedArgs a)
 	{
 		typedef Fused8GeomT<K1> Gm;
 		constexpr int T = Gm::T, M = Gm::M, N = Gm::N;
-		extern __shared__ __align__(16) unsigned char smemRaw[];
+		extern __shared__ __align__(16) unsigned char smemAll[];
+		// DUAL: one CTA of 2 T threads runs two frames side by side, each half with its own copy of the whole shared-memory
+		// layout, its own range of the launch and its own named barrier - two CTAs in one, which can take turns (below)
+		const int half = DUAL ? int(threadIdx.x) / T : 0;
+		const int bar = DUAL ? 1 + half : 0;
+		unsigned char* const smemRaw = smemAll + (DUAL ? size_t(half) * ((Gm::smemBytes(t.P) + 127) & ~size_t(127)) : 0);
+		const uint32_t cta = DUAL ? 2 * blockIdx.x + half : blockIdx.x, nCtas = DUAL ? 2 * gridDim.x : gridDim.x; // this half's range of the launch
 		float4* xbuf = reinterpret_cast<float4*>(smemRaw);
 		float4* stage = reinterpret_cast<float4*>(smemRaw);               // [4][T] next frame's newest half
 		float* csfmag = reinterpret_cast<float*>(smemRaw + size_t(M) * 8); // [N+1], upper half of xbuf (+4 B)
@@ -578,7 +599,7 @@
 #endif
 		float2* st = reinterpret_cast<float2*>(smemRaw + Gm::stateOffset); // [2][P]
 
-		const int u = threadIdx.x;
+		const int u = DUAL ? int(threadIdx.x) - half * T : int(threadIdx.x);
 		const int tb = pairedBin<T>(u); // this thread owns bins tb + T k4 after the FFT
 		const int P = int(t.P);
 		const int conf = t.conf;
@@ -600,7 +621,18 @@
 		for (int i = u; i < Gm::twEntries; i += T) twA[i] = t.tw8[i];
 #endif
 		const float2 wu = t.tw3[u]; // W_N^u: pass 1 uses its square W_M^u
-		__syncthreads();
+		// DUAL with turns: [0] frames this half did in its earlier parts, [1] frames both halves have (the shorter range): for that many
+		// frames the halves alternate - half 1 starts the exchange-heavy part of frame i (passes, split, magnitudes) when
+		// half 0 is through it, half 0 that of frame i + 1 when half 1 is through frame i - so that one half's shared-
+		// memory traffic runs against the other's display points instead of against its exchanges
+		volatile uint32_t* const turns = reinterpret_cast<volatile uint32_t*>(smemRaw + Gm::partOffset(t.P) + 72);
+		if (DUAL && SGZ8_DUAL_TURNS && u == 0)
+		{
+			const uint64_t items = uint64_t(a.numStreams) * a.nFrames;
+			const uint64_t mine = items * (cta + 1) / nCtas - items * cta / nCtas, other = items * ((cta ^ 1u) + 1) / nCtas - items * (cta ^ 1u) / nCtas;
+			turns[0] = 0; turns[1] = uint32_t(min(mine, other));
+		}
+		ctaSync(bar);
 
 #ifdef SGZ8_STAGGER
 		// A/B switch: the two CTAs of an SM start half a frame apart instead of in lock step
@@ -623,18 +655,22 @@
 
 		for (uint32_t q = 0;; ++q)
 		{
-		__syncthreads(); // the previous part's plan is no longer read (and its state has been written out)
+		ctaSync(bar); // the previous part's plan is no longer read (and its state has been written out)
 #ifdef SGZ8_NO_PARTS // A/B: one CTA per stream, nothing planned
 		if (u == 0)
 		{
-			part->nParts = 1; part->fBegin = 0; part->fEnd = a.nFrames; part->stream = int(blockIdx.x + a.firstStream); part->publish = 0;
+			part->nParts = 1; part->fBegin = 0; part->fEnd = a.nFrames; part->stream = int(cta + a.firstStream); part->publish = 0;
 			part->src = a.states + uint64_t(part->stream) * 2 * P; part->dst = a.states + uint64_t(part->stream) * 2 * P;
 			part->audio = a.audio + uint64_t(part->stream) * a.streamStride; part->vec4 = 1;
 		}
 #else
-		if (u == 0) planFusedPart(a, q, t.P, W == N, part);
+		if (u == 0)
+		{
+			if (DUAL && SGZ8_DUAL_TURNS && q > 0) turns[0] += part->fEnd - part->fBegin; // (the part just finished; nobody reads between the two barriers)
+			planFusedPart(a, q, t.P, W == N, part, cta, nCtas);
+		}
 #endif
-		__syncthreads();
+		ctaSync(bar);
 #ifdef SGZ8_CTA_CLOCK // diagnostic build only: when each CTA of the launch began and ended (globaltimer, ns) and on which SM
 		if (q == 0 && u == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ctaClock0() = g; }
 		if (q >= part->nParts && u == 0)
@@ -642,7 +678,7 @@
 			unsigned long long g; unsigned smid;
 			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
 			asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-			printf("cta %u sm %u begin %llu end %llu\n", blockIdx.x, smid, ctaClock0(), g);
+			printf("cta %u sm %u begin %llu end %llu\n", cta, smid, ctaClock0(), g);
 		}
 #endif
 #ifdef SGZ8_PHASE_CLOCK
@@ -765,8 +801,14 @@
 				}
 			}
 			SGZ8_TICK(0); // audio + window loaded, multiplied
-			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u, tb, t.tw3);
-			__syncthreads(); // every pass-4 read of xbuf is done before csfmag and the staged audio overwrite it
+			int turn = 0;
+			if (DUAL && SGZ8_DUAL_TURNS)
+			{
+				const uint32_t fi = turns[0] + (f - plan->fBegin), both = turns[1];
+				if (half == 0 ? (fi > 0 && fi < both) : (fi < both)) turn = half == 0 ? 4 : 3;
+			}
+			fusedFftCore<K1>(re, im, xbuf, twA, twB, twC, wu, u, tb, t.tw3, bar, turn);
+			ctaSync(bar); // every pass-4 read of xbuf is done before csfmag and the staged audio overwrite it
 			SGZ8_TICK(4); // pass 4, last radix-2, barrier
 
 #if !SGZ8_STAGE_LATE && !SGZ8_SPLIT_SMEM
@@ -797,7 +839,7 @@
 				// read and rewritten by one thread only, and the lower half (the A's) holds nothing that is still needed.
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4) csfC[M + tb + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
-				__syncthreads();
+				ctaSync(bar);
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
@@ -826,7 +868,7 @@
 				float2* zm = reinterpret_cast<float2*>(smemRaw);
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4) zm[u + T * k4] = make_float2(re[perm8(k4)].y, im[perm8(k4)].y);
-				__syncthreads();
+				ctaSync(bar);
 #pragma unroll
 				for (int k4 = 0; k4 < 8; ++k4)
 				{
@@ -936,8 +978,14 @@
 			// instructions of 64-bit index arithmetic, done by one thread and read by all after the barrier (the previous frame's
 			// readers passed several barriers ago)
 			SGZ8_TICK(5); // split exchange + magnitudes written
+			if (DUAL && SGZ8_DUAL_TURNS)
+			{
+				// through the exchange-heavy part: the other half may start its own (non-blocking)
+				const uint32_t fi = turns[0] + (f - plan->fBegin), both = turns[1];
+				if (half == 0 ? (fi < both) : (fi + 1 < both)) asm volatile("bar.arrive %0, 1024;" :: "r"(half == 0 ? 3 : 4) : "memory");
+			}
 			if (u == 0) { part->row[0] = resultRow(a, uint64_t(plan->stream), f, 0, uint32_t(P)); part->row[1] = resultRow(a, uint64_t(plan->stream), f, 1, uint32_t(P)); }
-			__syncthreads();
+			ctaSync(bar);
 
 #if SGZ8_STAGE_LATE || SGZ8_SPLIT_SMEM
 			// newest half of the next frame -> lower half of the exchange buffer, in flight behind the split and the display
@@ -1222,14 +1270,14 @@
 			if (u == 0 && blockIdx.x == 0) phaseClockBuffer()[17] += 1;
 #endif
 		}
-		__syncthreads(); // every display point of the part's last frame has updated its state
+		ctaSync(bar); // every display point of the part's last frame has updated its state
 		{
 			float2* stateDst = part->dst;
 			for (int i = u; i < 2 * P; i += T) stateDst[i] = st[i];
 			if (part->publish)
 			{
-				__syncthreads();
-				if (u == 0) { __threadfence(); stRelease(a.flags + blockIdx.x, a.epoch); }
+				ctaSync(bar);
+				if (u == 0) { __threadfence(); stRelease(a.flags + cta, a.epoch); }
 			}
 		}
 		} // parts

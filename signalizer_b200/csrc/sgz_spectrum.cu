@@ -770,7 +770,7 @@ namespace
 
 	// FusedLaunch: what one k_fused8 launch of `a` should look like.  query = true only fills h->fusedCapacity (the
 	// number of CTAs of this handle's kernel the device holds at once), launching nothing.
-	struct FusedPlan { uint32_t ctas; bool chained; bool cooperative; };
+	struct FusedPlan { uint32_t ctas; bool chained; bool cooperative; bool dual = false; }; // dual: pairs of ranges run as the two halves of one 1024-thread CTA
 
 	template<void (*kern)(DeviceTables, FusedArgs)>
 	int launchFusedKernel(sgz_spectrum* h, int threads, size_t smem, FusedArgs& a, const FusedPlan* plan)
@@ -830,7 +830,15 @@ namespace
 		case SGZ_BIN_NONE: return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_NONE, MATRIX>>(h, T, smem, a, plan);
 		case SGZ_BIN_LINEAR: return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_LINEAR, MATRIX>>(h, T, smem, a, plan);
 #endif
-		default: return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_LANCZOS, MATRIX>>(h, T, smem, a, plan);
+		default:
+			if constexpr (K1 == 8 && STEREO && MATRIX == 0)
+				if (plan && plan->dual)
+				{
+					FusedPlan halves = *plan;
+					halves.ctas = plan->ctas / 2;
+					return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_LANCZOS, MATRIX, true>>(h, 2 * T, 2 * ((smem + 127) & ~size_t(127)), a, &halves);
+				}
+			return launchFusedKernel<k_fused8<K1, STEREO, SGZ_BIN_LANCZOS, MATRIX>>(h, T, smem, a, plan);
 		}
 	}
 
@@ -1120,7 +1128,7 @@ extern "C"
 		const int conf = h->cfg.configuration;
 		const bool stereo = conf == SGZ_CH_SEPARATE || conf == SGZ_CH_PHASE || (conf != SGZ_CH_COMPLEX && h->tab.stateChannels == 2);
 		const int matrix = conf == SGZ_CH_SEPARATE ? 0 : conf == SGZ_CH_COMPLEX ? 2 : conf == SGZ_CH_PHASE ? 3 : 1;
-		std::snprintf(name, sizeof(name), "sgz::k_fused8<%d, %d, %d, %d>", h->fusedK1, stereo ? 1 : 0, int(h->cfg.bin_polation), matrix);
+		std::snprintf(name, sizeof(name), "sgz::k_fused8<%d, %d, %d, %d, 0>", h->fusedK1, stereo ? 1 : 0, int(h->cfg.bin_polation), matrix);
 		return name;
 	}
 
@@ -1658,6 +1666,11 @@ extern "C"
 		{
 			plan.ctas = capacity;                 // balanced ranges of >= one stream's worth of frames each
 			plan.cooperative = nS > capacity;     // some range ends mid-stream: CTAs wait on their neighbour's flag
+#if SGZ8_DUAL
+			// the headline shape (8192 points, Separate, Lanczos): two ranges per 1024-thread CTA
+			plan.dual = h->fusedK1 == 8 && h->cfg.configuration == SGZ_CH_SEPARATE && h->cfg.bin_polation == SGZ_BIN_LANCZOS && capacity % 2 == 0 &&
+				2 * ((Fused8GeomT<8>::smemBytes(P) + 127) & ~size_t(127)) <= size_t(227) * 1024;
+#endif
 		}
 		else if (h->seamsOk && items / kFrameParallelMinRun > nS && !(phase && a.outMode != SGZ_OUT_FULL))
 		{
